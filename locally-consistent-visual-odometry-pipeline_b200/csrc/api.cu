@@ -1,0 +1,224 @@
+// C-ABI entry points of libvo_b200.so: context, frame cache, unit-level KLT.
+// (Pipeline-level entry points live in pipeline.cu.)
+#include <stdarg.h>
+#include "ctx.cuh"
+
+namespace vo {
+
+thread_local std::string g_create_error;
+
+int set_error(Ctx* c, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    else g_create_error = buf;
+    return code;
+}
+
+static FrameSlot* find_slot(Ctx* c, int64_t key)
+{
+    for (auto& s : c->slots)
+        if (s.valid && s.key == key) { s.stamp = ++c->clock; return &s; }
+    return nullptr;
+}
+
+FrameSlot* get_frame(Ctx* c, int64_t key) { return find_slot(c, key); }
+
+}  // namespace vo
+
+using namespace vo;
+
+extern "C" {
+
+void vo_klt_params_default(vo_klt_params* p)
+{
+    p->win = 21; p->max_level = 3; p->max_iters = 30; p->epsilon = 0.01; p->min_eig_thr = 1e-4;
+    p->fb_check = 0; p->fb_thresh = 1.0;
+}
+
+void vo_pnp_params_default(vo_pnp_params* p)
+{
+    p->max_iters = 100; p->confidence = 0.99999; p->reproj_thresh = 2.0; p->refine_iters = 20;
+    p->min_inliers = 4;
+}
+
+int vo_abi_version(void) { return VO_B200_ABI_VERSION; }
+
+int vo_device_count(void)
+{
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) { cudaGetLastError(); return -(int)e; }
+    return n;
+}
+
+int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity, int hyp_capacity,
+              void* stream_handle)
+{
+    if (!out) return VO_ERR_INVALID;
+    *out = nullptr;
+    if (max_w <= 0 || max_h <= 0) return set_error(nullptr, VO_ERR_INVALID, "bad frame size %dx%d", max_w, max_h);
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess)
+        return set_error(nullptr, VO_ERR_CUDA, "cudaSetDevice(%d) failed: %s - libvo_b200 has no CPU fallback", device, cudaGetErrorString(e));
+    vo_ctx* c = new (std::nothrow) vo_ctx();
+    if (!c) return set_error(nullptr, VO_ERR_NOMEM, "out of host memory");
+    c->device = device; c->max_w = max_w; c->max_h = max_h;
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) { delete c; return set_error(nullptr, VO_ERR_CUDA, "cudaGetDeviceProperties failed: %s", cudaGetErrorString(e)); }
+    c->sm_count = prop.multiProcessorCount;
+    if (stream_handle) { c->stream = (cudaStream_t)stream_handle; c->own_stream = false; }
+    else {
+        e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) { delete c; return set_error(nullptr, VO_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e)); }
+        c->own_stream = true;
+    }
+    c->pinned_stage_bytes = (size_t)max_w * max_h;
+    e = cudaMallocHost((void**)&c->pinned_stage, c->pinned_stage_bytes);
+    if (e != cudaSuccess) { delete c; return set_error(nullptr, VO_ERR_NOMEM, "cudaMallocHost failed: %s", cudaGetErrorString(e)); }
+    int r = pipeline_init(c, track_capacity, hyp_capacity);
+    if (r != VO_OK) { g_create_error = c->err; vo_destroy(c); return r; }
+    *out = c;
+    return VO_OK;
+}
+
+int vo_destroy(vo_ctx* c)
+{
+    if (!c) return VO_OK;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    pipeline_free(c);
+    for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); }
+    cudaFree(c->u_pts.p); cudaFree(c->u_out.p); cudaFree(c->u_err.p); cudaFree(c->u_status.p);
+    cudaFree(c->u_iters.p); cudaFree(c->u_n.p);
+    cudaFreeHost(c->pinned_stage);
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+    return VO_OK;
+}
+
+const char* vo_last_error(vo_ctx* c) { return c ? c->err.c_str() : g_create_error.c_str(); }
+
+int vo_synchronize(vo_ctx* c)
+{
+    if (!c) return VO_ERR_INVALID;
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+int64_t vo_launch_count(vo_ctx* c) { return c ? c->launches : 0; }
+
+int vo_alloc_pinned(void** out, uint64_t bytes)
+{
+    if (!out) return VO_ERR_INVALID;
+    cudaError_t e = cudaMallocHost(out, bytes);
+    if (e != cudaSuccess) { *out = nullptr; return set_error(nullptr, VO_ERR_NOMEM, "cudaMallocHost(%llu) failed: %s", (unsigned long long)bytes, cudaGetErrorString(e)); }
+    return VO_OK;
+}
+
+int vo_free_pinned(void* p)
+{
+    if (p) cudaFreeHost(p);
+    return VO_OK;
+}
+
+int vo_has_frame(vo_ctx* c, int64_t key)
+{
+    if (!c) return 0;
+    for (auto& s : c->slots) if (s.valid && s.key == key) return 1;
+    return 0;
+}
+
+int vo_drop_frames(vo_ctx* c)
+{
+    if (!c) return VO_ERR_INVALID;
+    for (auto& s : c->slots) s.valid = false;
+    return VO_OK;
+}
+
+int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
+{
+    if (!c || !img) return VO_ERR_INVALID;
+    if (w <= 0 || h <= 0 || w > c->max_w || h > c->max_h || pitch < w)
+        return set_error(c, VO_ERR_INVALID, "frame %dx%d (pitch %d) outside ctx limits %dx%d", w, h, pitch, c->max_w, c->max_h);
+    if (find_slot(c, key)) return VO_OK;
+    FrameSlot* s = nullptr;
+    for (auto& t : c->slots) if (!t.valid) { s = &t; break; }
+    if (!s) { s = &c->slots[0]; for (auto& t : c->slots) if (t.stamp < s->stamp) s = &t; }
+    s->valid = false;
+    const size_t bytes = (size_t)w * h;
+    if (bytes > s->raw_bytes) {
+        if (s->raw) { cudaStreamSynchronize(c->stream); cudaFree(s->raw); s->raw = nullptr; s->raw_bytes = 0; }
+        VO_CUDA(c, cudaMalloc((void**)&s->raw, bytes));
+        s->raw_bytes = bytes;
+    }
+    // Pageable host memory is staged through the ctx's pinned buffer so the copy is a true
+    // async DMA; pinned host and device sources are copied directly.
+    cudaPointerAttributes at;
+    cudaError_t e = cudaPointerGetAttributes(&at, img);
+    bool pageable = (e != cudaSuccess) || at.type == cudaMemoryTypeUnregistered;
+    if (e != cudaSuccess) cudaGetLastError();
+    if (pageable) {
+        // the previous async copy out of the staging buffer must have completed
+        VO_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int y = 0; y < h; y++) memcpy(c->pinned_stage + (size_t)y * w, img + (size_t)y * pitch, w);
+        VO_CUDA(c, cudaMemcpyAsync(s->raw, c->pinned_stage, bytes, cudaMemcpyHostToDevice, c->stream));
+    } else {
+        VO_CUDA(c, cudaMemcpy2DAsync(s->raw, w, img, pitch, w, h, cudaMemcpyDefault, c->stream));
+    }
+    s->w = w; s->h = h;
+    VO_TRY(build_pyramid(c, *s, 3));
+    s->key = key; s->valid = true; s->stamp = ++c->clock;
+    return VO_OK;
+}
+
+int vo_get_pyramid_level(vo_ctx* c, int64_t key, int level, uint8_t* img, int16_t* deriv, int* w, int* h)
+{
+    if (!c) return VO_ERR_INVALID;
+    FrameSlot* s = find_slot(c, key);
+    if (!s) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)key);
+    if (level < 0 || level >= s->pyr.nlevels) return set_error(c, VO_ERR_INVALID, "level %d of %d", level, s->pyr.nlevels);
+    const LevelDesc& d = s->pyr.lv[level];
+    if (w) *w = d.w;
+    if (h) *h = d.h;
+    if (img)
+        VO_CUDA(c, cudaMemcpy2DAsync(img, d.w, d.img + (size_t)kPad * d.stride + kPad, d.stride, d.w, d.h, cudaMemcpyDeviceToHost, c->stream));
+    if (deriv)
+        VO_CUDA(c, cudaMemcpy2DAsync(deriv, (size_t)d.w * 4, d.deriv + (size_t)kPad * d.stride + kPad, (size_t)d.stride * 4, (size_t)d.w * 4, d.h, cudaMemcpyDeviceToHost, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+int vo_calc_optical_flow_pyr_lk(vo_ctx* c, int64_t prev_key, int64_t next_key, const float* pts, int n,
+                                float* next_pts, uint8_t* status, float* err, int32_t* iters,
+                                const vo_klt_params* params)
+{
+    if (!c || n < 0 || (n > 0 && (!pts || !next_pts || !status))) return VO_ERR_INVALID;
+    vo_klt_params prm;
+    if (params) prm = *params; else vo_klt_params_default(&prm);
+    FrameSlot* a = find_slot(c, prev_key);
+    FrameSlot* b = find_slot(c, next_key);
+    if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    if (n == 0) return VO_OK;
+    VO_TRY(ensure(c, c->u_pts, (size_t)n * 2));
+    VO_TRY(ensure(c, c->u_out, (size_t)n * 2));
+    VO_TRY(ensure(c, c->u_err, (size_t)n));
+    VO_TRY(ensure(c, c->u_status, (size_t)n));
+    VO_TRY(ensure(c, c->u_iters, (size_t)n));
+    VO_CUDA(c, cudaMemcpyAsync(c->u_pts.p, pts, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
+    VO_TRY(launch_klt(c, a->pyr, b->pyr, c->u_pts.p, nullptr, n, c->u_out.p, c->u_status.p, c->u_err.p, c->u_iters.p, prm));
+    if (prm.fb_check) VO_TRY(klt_fb_check(c, a->pyr, b->pyr, c->u_pts.p, nullptr, n, c->u_out.p, c->u_status.p, prm));
+    VO_CUDA(c, cudaMemcpyAsync(next_pts, c->u_out.p, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(status, c->u_status.p, n, cudaMemcpyDefault, c->stream));
+    if (err) VO_CUDA(c, cudaMemcpyAsync(err, c->u_err.p, sizeof(float) * n, cudaMemcpyDefault, c->stream));
+    if (iters) VO_CUDA(c, cudaMemcpyAsync(iters, c->u_iters.p, sizeof(int32_t) * n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+}  // extern "C"

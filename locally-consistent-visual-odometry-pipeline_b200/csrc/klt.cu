@@ -1,0 +1,247 @@
+// K2: pyramidal Lucas-Kanade tracking, one warp per track, all levels in one launch.
+//
+// Replaces cv2.calcOpticalFlowPyrLK(old, new, pts, None) at
+//   /root/reference/src/vo_pipeline.py:215 (landmark tracks P) and :501 (candidate tracks C),
+// following the behaviour recorded in SURVEY.md App. A.1 (OpenCV LKTrackerInvoker): 14-bit fixed
+// point bilinear weights, int16 window with 5 fractional bits, Scharr derivatives that are zero
+// outside the image, float32 2x2 solve, both break rules, level-0-only status writes and the
+// post-loop error pass that can still clear status.
+//
+// Mapping: the 21x21 window (441 px) is spread flat over the 32 lanes (14 px per lane, 98 %
+// lane use).  The template window I and its derivatives stay in registers for the whole level;
+// only the moving window of the next image is gathered each Gauss-Newton step (4 u8 taps per
+// px, L1/L2 resident).  The per-step sums are exact: products fit int32 per lane and the
+// cross-lane sum is two REDUX.SUM instructions (16-bit split), so results do not depend on the
+// lane mapping or summation order.
+#include "ctx.cuh"
+
+namespace vo {
+
+namespace {
+
+constexpr int kWarpsPerBlock = 4;
+
+__device__ __forceinline__ long long warp_sum_i64(int v)
+{
+    const unsigned lo = __reduce_add_sync(0xffffffffu, (unsigned)(v & 0xFFFF));
+    const int hi = __reduce_add_sync(0xffffffffu, v >> 16);
+    return ((long long)hi << 16) + (long long)lo;
+}
+
+struct Weights { int w00, w01, w10, w11; };
+
+// iw00=round((1-a)(1-b)2^14) ... with float32 products evaluated in the reference's order
+__device__ __forceinline__ Weights make_weights(float a, float b)
+{
+    const float na = __fsub_rn(1.f, a), nb = __fsub_rn(1.f, b);
+    Weights w;
+    w.w00 = __float2int_rn(__fmul_rn(__fmul_rn(na, nb), 16384.f));
+    w.w01 = __float2int_rn(__fmul_rn(__fmul_rn(a, nb), 16384.f));
+    w.w10 = __float2int_rn(__fmul_rn(__fmul_rn(na, b), 16384.f));
+    w.w11 = 16384 - w.w00 - w.w01 - w.w10;
+    return w;
+}
+
+__device__ __forceinline__ int bilerp_u8(const uint8_t* __restrict__ p, int stride, const Weights& w)
+{
+    return p[0] * w.w00 + p[1] * w.w01 + p[stride] * w.w10 + p[stride + 1] * w.w11;
+}
+
+template <int WIN>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const float2* __restrict__ pts,
+                 const int32_t* __restrict__ n_dev, const int n_upper, float2* __restrict__ out,
+                 uint8_t* __restrict__ status_out, float* __restrict__ err_out,
+                 int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
+                 const double min_eig_thr)
+{
+    constexpr int NPX = WIN * WIN;
+    constexpr int K = (NPX + 31) / 32;
+    const int lane = threadIdx.x & 31;
+    const int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    const int n = n_dev ? min(*n_dev, n_upper) : n_upper;
+    if (track >= n) return;
+
+    const float2 pt = pts[track];
+    const float half = (WIN - 1) * 0.5f;
+    float cx = 0.f, cy = 0.f;  // stored nextPts (window centre)
+    int st = 1, iters = 0;
+    float err = 0.f;
+
+    // window-relative coordinates of this lane's pixels (the last slot may be past the window)
+    int wy[K], wx[K];
+#pragma unroll
+    for (int k = 0; k < K; k++) {
+        const int idx = lane + 32 * k;
+        const int c = idx < NPX ? idx : 0;
+        wy[k] = c / WIN;
+        wx[k] = c - wy[k] * WIN;
+    }
+    const bool last_valid = (lane + 32 * (K - 1)) < NPX;
+
+    int Iw[K];       // template window, 5 fractional bits
+    short2 dIw[K];   // its derivatives
+
+    for (int level = top; level >= 0; level--) {
+        const LevelDesc LI = I.lv[level];
+        const LevelDesc LJ = J.lv[level];
+        const float scale = 1.f / (float)(1 << level);
+        float px = __fmul_rn(pt.x, scale), py = __fmul_rn(pt.y, scale);
+        if (level == top) { cx = px; cy = py; }
+        else { cx = __fmul_rn(cx, 2.f); cy = __fmul_rn(cy, 2.f); }
+
+        px = __fsub_rn(px, half); py = __fsub_rn(py, half);
+        const int ix = __float2int_rd(px), iy = __float2int_rd(py);
+        if (ix < -WIN || ix >= LI.w || iy < -WIN || iy >= LI.h) {
+            if (level == 0) { st = 0; err = 0.f; }
+            continue;
+        }
+        Weights w = make_weights(__fsub_rn(px, (float)ix), __fsub_rn(py, (float)iy));
+        const int stride = LI.stride;
+        const size_t base = (size_t)(iy + kPad) * stride + (ix + kPad);
+        int a11 = 0, a12 = 0, a22 = 0;
+#pragma unroll
+        for (int k = 0; k < K; k++) {
+            const int off = wy[k] * stride + wx[k];
+            const uint8_t* s = LI.img + base + off;
+            const short2* d = LI.deriv + base + off;
+            const int ival = (bilerp_u8(s, stride, w) + (1 << 8)) >> 9;
+            const short2 d00 = d[0], d01 = d[1], d10 = d[stride], d11 = d[stride + 1];
+            int ixv = (d00.x * w.w00 + d01.x * w.w01 + d10.x * w.w10 + d11.x * w.w11 + (1 << 13)) >> 14;
+            int iyv = (d00.y * w.w00 + d01.y * w.w01 + d10.y * w.w10 + d11.y * w.w11 + (1 << 13)) >> 14;
+            if (k == K - 1 && !last_valid) { ixv = 0; iyv = 0; }
+            Iw[k] = ival;
+            dIw[k] = make_short2((short)ixv, (short)iyv);
+            a11 += ixv * ixv; a12 += ixv * iyv; a22 += iyv * iyv;
+        }
+        const float FLT_SCALE = 1.f / (1 << 20);
+        const float A11 = __fmul_rn(__ll2float_rn(warp_sum_i64(a11)), FLT_SCALE);
+        const float A12 = __fmul_rn(__ll2float_rn(warp_sum_i64(a12)), FLT_SCALE);
+        const float A22 = __fmul_rn(__ll2float_rn(warp_sum_i64(a22)), FLT_SCALE);
+        float D = __fsub_rn(__fmul_rn(A11, A22), __fmul_rn(A12, A12));
+        const float dd = __fsub_rn(A11, A22);
+        const float disc = __fadd_rn(__fmul_rn(dd, dd), __fmul_rn(__fmul_rn(4.f, A12), A12));
+        const float min_eig = __fdiv_rn(__fsub_rn(__fadd_rn(A22, A11), __fsqrt_rn(disc)), (float)(2 * WIN * WIN));
+        if ((double)min_eig < min_eig_thr || D < 1.1920928955078125e-07f) {
+            if (level == 0) st = 0;
+            continue;
+        }
+        D = __fdiv_rn(1.f, D);
+
+        float qx = __fsub_rn(cx, half), qy = __fsub_rn(cy, half);  // nextPt (window top-left)
+        float pdx = 0.f, pdy = 0.f;
+        const int jstride = LJ.stride;
+        for (int j = 0; j < max_iters; j++) {
+            const int jx = __float2int_rd(qx), jy = __float2int_rd(qy);
+            if (jx < -WIN || jx >= LJ.w || jy < -WIN || jy >= LJ.h) {
+                if (level == 0) st = 0;
+                break;
+            }
+            iters++;
+            w = make_weights(__fsub_rn(qx, (float)jx), __fsub_rn(qy, (float)jy));
+            const uint8_t* jb = LJ.img + (size_t)(jy + kPad) * jstride + (jx + kPad);
+            int b1 = 0, b2 = 0;
+#pragma unroll
+            for (int k = 0; k < K; k++) {
+                const int diff = ((bilerp_u8(jb + wy[k] * jstride + wx[k], jstride, w) + (1 << 8)) >> 9) - Iw[k];
+                b1 += diff * dIw[k].x;
+                b2 += diff * dIw[k].y;
+            }
+            const float fb1 = __fmul_rn(__ll2float_rn(warp_sum_i64(b1)), FLT_SCALE);
+            const float fb2 = __fmul_rn(__ll2float_rn(warp_sum_i64(b2)), FLT_SCALE);
+            const float dx = __fmul_rn(__fsub_rn(__fmul_rn(A12, fb2), __fmul_rn(A22, fb1)), D);
+            const float dy = __fmul_rn(__fsub_rn(__fmul_rn(A12, fb1), __fmul_rn(A11, fb2)), D);
+            qx = __fadd_rn(qx, dx); qy = __fadd_rn(qy, dy);
+            cx = __fadd_rn(qx, half); cy = __fadd_rn(qy, half);
+            if ((double)dx * dx + (double)dy * dy <= eps2) break;
+            if (j > 0 && fabsf(__fadd_rn(dx, pdx)) < 0.01 && fabsf(__fadd_rn(dy, pdy)) < 0.01) {
+                cx = __fsub_rn(cx, __fmul_rn(dx, 0.5f));
+                cy = __fsub_rn(cy, __fmul_rn(dy, 0.5f));
+                break;
+            }
+            pdx = dx; pdy = dy;
+        }
+
+        if (level == 0 && st) {
+            const float ex = __fsub_rn(cx, half), ey = __fsub_rn(cy, half);
+            const int jx = __float2int_rd(ex), jy = __float2int_rd(ey);
+            if (jx < -WIN || jx >= LJ.w || jy < -WIN || jy >= LJ.h) {
+                st = 0;
+            } else {
+                w = make_weights(__fsub_rn(ex, (float)jx), __fsub_rn(ey, (float)jy));
+                const uint8_t* jb = LJ.img + (size_t)(jy + kPad) * jstride + (jx + kPad);
+                int e = 0;
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    const int diff = ((bilerp_u8(jb + wy[k] * jstride + wx[k], jstride, w) + (1 << 8)) >> 9) - Iw[k];
+                    if (k < K - 1 || last_valid) e += abs(diff);
+                }
+                e = __reduce_add_sync(0xffffffffu, e);
+                err = __fmul_rn((float)e, 1.f / (32 * WIN * WIN));
+            }
+        }
+    }
+    if (lane == 0) {
+        out[track] = make_float2(cx, cy);
+        status_out[track] = (uint8_t)st;
+        if (err_out) err_out[track] = err;
+        if (iters_out) iters_out[track] = iters;
+    }
+}
+
+__global__ void fb_compare_kernel(const float2* __restrict__ pts, const float2* __restrict__ back,
+                                  const uint8_t* __restrict__ back_status, const int32_t* __restrict__ n_dev,
+                                  int n_upper, float thr2, uint8_t* __restrict__ status)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = n_dev ? min(*n_dev, n_upper) : n_upper;
+    if (i >= n) return;
+    const float dx = back[i].x - pts[i].x, dy = back[i].y - pts[i].y;
+    if (!back_status[i] || dx * dx + dy * dy > thr2) status[i] = 0;
+}
+
+}  // namespace
+
+int klt_fb_check(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
+                 const int32_t* d_n, int n_upper, const float* d_out, uint8_t* d_status,
+                 const vo_klt_params& prm)
+{
+    if (n_upper <= 0) return VO_OK;
+    VO_TRY(ensure(c, c->fb_pts, (size_t)n_upper * 2));
+    VO_TRY(ensure(c, c->fb_status, (size_t)n_upper));
+    VO_TRY(launch_klt(c, next, prev, d_out, d_n, n_upper, c->fb_pts.p, c->fb_status.p, nullptr, nullptr, prm));
+    fb_compare_kernel<<<(n_upper + 255) / 256, 256, 0, c->stream>>>(
+        (const float2*)d_pts, (const float2*)c->fb_pts.p, c->fb_status.p, d_n, n_upper,
+        (float)(prm.fb_thresh * prm.fb_thresh), d_status);
+    c->launches++;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
+               const int32_t* d_n, int n_upper, float* d_out, uint8_t* d_status, float* d_err,
+               int32_t* d_iters, const vo_klt_params& prm)
+{
+    if (n_upper <= 0) return VO_OK;
+    if (prm.win != 21) return set_error(c, VO_ERR_INVALID, "KLT window %d not built (only 21)", prm.win);
+    if (prev.nlevels != next.nlevels || prev.lv[0].w != next.lv[0].w || prev.lv[0].h != next.lv[0].h)
+        return set_error(c, VO_ERR_INVALID, "KLT frames differ in size");
+    // effective top level, as buildOpticalFlowPyramid: stop before a level that is <= winSize
+    int top = 0;
+    for (int l = 1; l <= prm.max_level && l < prev.nlevels; l++) {
+        if (prev.lv[l].w <= prm.win || prev.lv[l].h <= prm.win) break;
+        top = l;
+    }
+    int max_iters = prm.max_iters < 0 ? 0 : (prm.max_iters > 100 ? 100 : prm.max_iters);
+    const double eps = prm.epsilon < 0. ? 0. : (prm.epsilon > 10. ? 10. : prm.epsilon);
+    const double eps2 = eps * eps;
+    const int blocks = (n_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, c->stream>>>(
+        prev, next, top, (const float2*)d_pts, d_n, n_upper, (float2*)d_out, d_status, d_err, d_iters,
+        max_iters, eps2, prm.min_eig_thr);
+    c->launches++;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+}  // namespace vo
