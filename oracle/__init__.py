@@ -83,3 +83,118 @@ def scharr(img):
     out = np.empty((h, w, 2), np.int16)
     lib().vo_oracle_scharr(_p(img), w, h, _p(out))
     return out
+
+
+# ---- PnP-RANSAC (oracle/pnp.c) -------------------------------------------------------------------
+def _f(name, restype, argtypes):
+    fn = getattr(lib(), name)
+    fn.restype = restype
+    fn.argtypes = argtypes
+    return fn
+
+
+_VP, _I, _D = ctypes.c_void_p, ctypes.c_int, ctypes.c_double
+
+
+def ransac_sets(n, m, H):
+    """The H x m minimal-set table cv2's RANSAC draws for n points (cv::RNG(2^64-1))."""
+    out = np.empty((H, m), np.int32)
+    _f("vo_oracle_ransac_sets", None, [_I, _I, _I, _VP])(n, m, H, _p(out))
+    return out
+
+
+def update_num_iters(p, ep, m, max_iters):
+    return _f("vo_oracle_update_num_iters", _I, [_D, _D, _I, _I])(p, ep, m, max_iters)
+
+
+def p3p_all(X3, p3, K):
+    X3 = np.ascontiguousarray(X3, np.float64).reshape(3, 3)
+    p3 = np.ascontiguousarray(p3, np.float64).reshape(3, 2)
+    K = np.ascontiguousarray(K, np.float64)
+    Rs = np.zeros((4, 3, 3)); ts = np.zeros((4, 3))
+    ns = _f("vo_oracle_p3p_all", _I, [_VP] * 5)(_p(X3), _p(p3), _p(K), _p(Rs), _p(ts))
+    return Rs[:ns], ts[:ns]
+
+
+def p3p4(X4, p4, K):
+    """cv2.solvePnP(flags=SOLVEPNP_P3P) on 4 correspondences -> (ok, R, t)."""
+    X4 = np.ascontiguousarray(X4, np.float64).reshape(4, 3)
+    p4 = np.ascontiguousarray(p4, np.float64).reshape(4, 2)
+    K = np.ascontiguousarray(K, np.float64)
+    R = np.zeros((3, 3)); t = np.zeros(3)
+    ok = _f("vo_oracle_p3p4", _I, [_VP] * 5)(_p(X4), _p(p4), _p(K), _p(R), _p(t))
+    return bool(ok), R, t
+
+
+def score(X, P, K, R, t, thr=2.0):
+    X = np.ascontiguousarray(np.asarray(X, np.float32), np.float64)
+    P = np.ascontiguousarray(P, np.float32)
+    n = len(X)
+    mask = np.zeros(n, np.uint8)
+    _f("vo_oracle_score", _I, [_VP, _VP, _I, _VP, _VP, _VP, _D, _VP])(
+        _p(X), _p(P), n, _p(np.ascontiguousarray(K, np.float64)), _p(np.ascontiguousarray(R, np.float64)),
+        _p(np.ascontiguousarray(t, np.float64)), thr, _p(mask))
+    return mask
+
+
+def refine_lm(X, P, mask, K, R, t, max_iters=50):
+    X = np.ascontiguousarray(np.asarray(X, np.float32), np.float64)
+    P = np.ascontiguousarray(P, np.float32)
+    R = np.array(R, np.float64).reshape(3, 3).copy(); t = np.array(t, np.float64).reshape(3).copy()
+    m = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+    it = _f("vo_oracle_refine_lm", _I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _I])(
+        _p(X), _p(P), _p(m), len(X), _p(np.ascontiguousarray(K, np.float64)), _p(R), _p(t), max_iters)
+    return R, t, it
+
+
+def rotation_to_rvec(R):
+    R = np.ascontiguousarray(R, np.float64)
+    r = np.zeros(3)
+    _f("vo_oracle_rotation_to_rvec", None, [_VP, _VP])(_p(R), _p(r))
+    return r
+
+
+def solve_pnp_ransac(X, P, K, max_iters=100, confidence=0.99999, thr=2.0, refine_iters=50, sets=None):
+    """cv2.solvePnPRansac(X, P, K, 0, flags=SOLVEPNP_P3P-hypotheses, ...) + ITERATIVE refit restated.
+    Returns dict(ok, R, t, Rh, th, mask, iters, best_iter, n_inliers, lm_iters)."""
+    X = np.ascontiguousarray(X, np.float64).reshape(-1, 3)
+    P = np.ascontiguousarray(P, np.float32).reshape(-1, 2)
+    K = np.ascontiguousarray(K, np.float64)
+    n = len(X)
+    R = np.zeros((3, 3)); t = np.zeros(3); Rh = np.zeros((3, 3)); th = np.zeros(3)
+    mask = np.zeros(n, np.uint8); info = np.zeros(4, np.int32)
+    s = None if sets is None else np.ascontiguousarray(sets, np.int32)
+    if s is not None:
+        assert s.shape[0] >= max_iters and s.shape[1] == 4
+    ok = _f("vo_oracle_solve_pnp_ransac", _I, [_VP, _VP, _I, _VP, _I, _D, _D, _I] + [_VP] * 7)(
+        _p(X), _p(P), n, _p(K), max_iters, confidence, thr, refine_iters, _p(s), _p(R), _p(t), _p(Rh),
+        _p(th), _p(mask), _p(info))
+    return dict(ok=bool(ok), R=R, t=t, Rh=Rh, th=th, mask=mask, iters=int(info[0]), best_iter=int(info[1]),
+                n_inliers=int(info[2]), lm_iters=int(info[3]))
+
+
+# ---- DLT triangulation + bearing test (oracle/dlt.c) ---------------------------------------------
+def triangulate_points(M1, M2, p1, p2):
+    """cv2.triangulatePoints(M1, M2, p1.T, p2.T).T restated -> n x 4 homogeneous (unit norm)."""
+    M1 = np.ascontiguousarray(M1, np.float64); M2 = np.ascontiguousarray(M2, np.float64)
+    p1 = np.ascontiguousarray(p1, np.float64).reshape(-1, 2); p2 = np.ascontiguousarray(p2, np.float64).reshape(-1, 2)
+    out = np.zeros((len(p1), 4))
+    _f("vo_oracle_triangulate_points", None, [_VP] * 4 + [_I, _VP])(_p(M1), _p(M2), _p(p1), _p(p2), len(p1), _p(out))
+    return out
+
+
+def bearing_angle_deg(c, f):
+    c = np.ascontiguousarray(c, np.float64); f = np.ascontiguousarray(f, np.float64)
+    return _f("vo_oracle_bearing_angle_deg", _D, [_VP, _VP])(_p(c), _p(f))
+
+
+def bearing_triangulate(C, F, T, Tnew, K, alpha_deg):
+    """Promotion step of LandmarkTriangulator.triangulate_landmark -> (promote mask, X n x 3, alpha)."""
+    C = np.ascontiguousarray(C, np.float64).reshape(-1, 2); F = np.ascontiguousarray(F, np.float64).reshape(-1, 2)
+    n = len(C)
+    T = np.ascontiguousarray(T, np.float64).reshape(n, 16)
+    promote = np.zeros(n, np.uint8); X = np.zeros((n, 3)); alpha = np.zeros(n)
+    _f("vo_oracle_bearing_triangulate", _I, [_VP, _VP, _VP, _I, _VP, _VP, _D, _VP, _VP, _VP])(
+        _p(C), _p(F), _p(T), n, _p(np.ascontiguousarray(Tnew, np.float64)), _p(np.ascontiguousarray(K, np.float64)),
+        alpha_deg, _p(promote), _p(X), _p(alpha))
+    return promote, X, alpha

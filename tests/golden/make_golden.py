@@ -35,8 +35,80 @@ def klt():
     np.savez_compressed(os.path.join(HERE, "pyrdown.npz"), cv2_version=cv2.__version__, **out)
 
 
+PNP_CASES = {  # name: (n, outlier_frac, H, seed) - SURVEY.md 8 d1
+    "n500_o20_h100": (500, 0.2, 100, 1),
+    "n2000_o20_h100": (2000, 0.2, 100, 2),
+    "n2000_o20_h2000": (2000, 0.2, 2000, 3),
+    "n2000_o50_h2000": (2000, 0.5, 2000, 4),
+    "n10000_o50_h4096": (10000, 0.5, 4096, 5),
+    "n300_o60_h2000": (300, 0.6, 2000, 6),
+    "n50_o30_h100": (50, 0.3, 100, 7),
+}
+
+
+def pnp():
+    """Primary PnP gate: masks of cv2.solvePnPRansac(flags=SOLVEPNP_P3P, iterationsCount=H)
+    - its RANSAC loop with cv::RNG(2^64-1) minimal sets - and the pose of cv2.solvePnP(ITERATIVE)
+    on that inlier set (= the refit the reference's literal call performs, vo_pipeline.py:258-264).
+    Report-only: the literal reference call (EPnP-5 hypotheses, <=100 iterations)."""
+    out = {"cv2_version": cv2.__version__}
+    for name, (n, of, H, seed) in PNP_CASES.items():
+        X, P, R, t, _ = synth.pnp_scene(n, of, seed)
+        ok, rv, tv, inl = cv2.solvePnPRansac(X, P, synth.K_KITTI, np.zeros(4), flags=cv2.SOLVEPNP_P3P,
+                                             confidence=0.99999, reprojectionError=2, iterationsCount=H)
+        assert ok
+        mask = np.zeros(n, np.uint8)
+        mask[inl.ravel()] = 1
+        Xi = X[mask == 1].astype(np.float32).astype(np.float64)
+        ok2, rv2, tv2 = cv2.solvePnP(Xi, P[mask == 1].astype(np.float64), synth.K_KITTI, np.zeros(4),
+                                     flags=cv2.SOLVEPNP_ITERATIVE)
+        assert ok2
+        okl, rvl, tvl, inll = cv2.solvePnPRansac(X, P, synth.K_KITTI, np.zeros(4), flags=cv2.SOLVEPNP_ITERATIVE,
+                                                 confidence=0.99999, reprojectionError=2)
+        ml = np.zeros(n, np.uint8)
+        ml[inll.ravel()] = 1
+        out[name + "_mask"] = np.packbits(mask)
+        out[name + "_rvec"] = rv2.ravel()
+        out[name + "_tvec"] = tv2.ravel()
+        out[name + "_xsum"] = X.sum()
+        out[name + "_literal_mask"] = np.packbits(ml)
+        out[name + "_literal_rvec"] = rvl.ravel()
+        out[name + "_literal_tvec"] = tvl.ravel()
+    np.savez_compressed(os.path.join(HERE, "pnp.npz"), **out)
+
+
+TRI_CASES = {"n500": (500, 1), "n2000": (2000, 2), "n3000": (3000, 3)}
+
+
+def tri():
+    """cv2.triangulatePoints on two-view scenes (dehomogenised: the sign of the homogeneous vector is
+    arbitrary), called batched as at vo_pipeline.py:172 and one point per call as at :666; plus the
+    reference's bearing-angle loop (vo_pipeline.py:621-642) evaluated with numpy exactly as written."""
+    out = {"cv2_version": cv2.__version__}
+    K = synth.K_KITTI
+    for name, (n, seed) in TRI_CASES.items():
+        X, T1, T2, p1, p2 = synth.two_view_scene(n, seed)
+        Xh = cv2.triangulatePoints(K @ T1[:3], K @ T2[:3], p1.T.copy(), p2.T.copy()).T
+        out[name + "_X"] = Xh[:, :3] / Xh[:, 3:]
+        one = np.stack([cv2.triangulatePoints(K @ T1[0:3, :], K @ T2[0:3, :], p1[i].T, p2[i].T) for i in range(16)])
+        assert np.allclose(one[:, :3, 0] / one[:, 3:, 0], out[name + "_X"][:16], rtol=1e-9)
+    C, F = synth.bearing_pairs(4000, 9)
+    al = []
+    for idx in range(len(C)):
+        uc, vc = C[idx]
+        wc = np.sqrt(uc**2 + vc**2 + 1)
+        vector_a = np.array([uc / wc, vc / wc, 1 / wc])
+        uf, vf = F[idx]
+        wf = np.sqrt(uf**2 + vf**2 + 1)
+        vector_b = np.array([uf / wf, vf / wf, 1 / wf])
+        cos = np.dot(vector_a, vector_b) / (np.linalg.norm(vector_a) * np.linalg.norm(vector_b))
+        al.append(np.degrees(np.arccos(np.clip(cos, -1.0, 1.0))))
+    out["bearing_alpha"] = np.array(al)
+    np.savez_compressed(os.path.join(HERE, "tri.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["klt"]
+    which = sys.argv[1:] or ["klt", "pnp", "tri"]
     for w in which:
         globals()[w]()
     print("golden vectors written with cv2", cv2.__version__)

@@ -124,3 +124,12 @@ def two_view_scene(n, seed, K=K_KITTI, noise=0.3, baseline=1.0):
     p1 = proj(T1) + rng.normal(0, noise, (n, 2))
     p2 = proj(T2) + rng.normal(0, noise, (n, 2))
     return X, T1, T2, p1, p2
+
+
+def bearing_pairs(n, seed, w=1241, h=376, sigma=15.0):
+    """Candidate current/first observations (float32-representable, as KLT output / detector
+    output are) whose bearing angle straddles the reference's 1-1.5 degree thresholds."""
+    rng = np.random.default_rng(seed)
+    C = np.stack([rng.uniform(0, w, n), rng.uniform(0, h, n)], 1).astype(np.float32).astype(np.float64)
+    F = (C + rng.normal(0, sigma, C.shape)).astype(np.float32).astype(np.float64)
+    return C, F
