@@ -68,7 +68,7 @@ struct Ctx {
     DevBuf<float> fb_pts;
     DevBuf<uint8_t> fb_status;
 
-    struct Pipeline* pipe = nullptr;  // device-resident Markov state + PnP scratch (pipeline.cu)
+    struct Pipeline* pipe = nullptr;  // device-resident Markov state + PnP scratch
 };
 
 extern thread_local std::string g_create_error;
@@ -112,11 +112,83 @@ int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
     return VO_OK;
 }
 
+// ---- device-resident Markov state (reference: BestVision.state / .extended_state,
+// /root/reference/src/vo_pipeline.py:36-37) and PnP / promotion scratch ------------------------
+constexpr int kMinimal = 4;          // P3P on 3 points + 1 disambiguation point
+constexpr int kPnpChunks = 3;        // hypotheses are evaluated in <=3 chunks (adaptive stop between)
+
+// small block of scalars living in device memory; mirrored to pinned host memory on demand
+struct DevScalars {
+    int32_t n_land;        // |P| = |X|
+    int32_t n_cand;        // |C| = |F| = |T|
+    int32_t n_lost;        // landmarks lost by the last KLT
+    int32_t n_tracked;     // landmarks kept by the last KLT (input size of the last PnP)
+    int32_t n_promoted;    // candidates promoted by the last promotion step
+    int32_t n_cand_lost;   // candidates lost by the last KLT
+    int32_t cf_alias;      // reference quirk App. B-5: C and F are the same ndarray
+    int32_t cand_was_empty;// C was empty after the tracking/removal step (decides cf_alias on add)
+    // RANSAC
+    uint64_t rng;          // cv::RNG state
+    int32_t niters;        // current (shrinking) iteration budget
+    int32_t best_count;
+    int32_t best_hyp;      // -1: none
+    int32_t iters_run;     // number of loop iterations the sequential reference would have run
+    int32_t done;          // scan passed niters
+    int32_t sets_ready;    // rows of the minimal-set table generated so far
+    int32_t n_inliers;
+    int32_t ok;
+    int32_t lm_iters;
+    int32_t klt_iters;     // sum of LK iterations (roofline accounting)
+    double T[16];          // refined pose, row-major 4x4 world->camera
+    double Th[12];         // winning unrefined hypothesis [R|t]
+    double cost;           // final sum of squared reprojection errors over the inliers
+};
+
+struct Pipeline {
+    int track_capacity = 0, hyp_capacity = 0;
+    // landmarks, ping-pong (cur = index of the live buffers)
+    int cur = 0;
+    DevBuf<float> P[2];     // n x 2
+    DevBuf<double> X[2];    // n x 3
+    int n_land_upper = 0;   // host-known upper bound of n_land
+    // candidates, ping-pong
+    int ccur = 0;
+    DevBuf<float> C[2];     // n x 2 (current observation; float32-exact)
+    DevBuf<double> F[2];    // n x 2 (first observation)
+    DevBuf<int32_t> Ti[2];  // n (index into the pose table)
+    int n_cand_upper = 0;
+    DevBuf<double> poses;   // pose table, 16 doubles per entry (4x4 row-major)
+    int n_poses = 0;
+    // KLT outputs for landmarks + candidates (one fused launch)
+    DevBuf<float> klt_in, klt_out, klt_err;
+    DevBuf<uint8_t> klt_status;
+    DevBuf<int32_t> klt_iters;
+    DevBuf<float> lost;     // positions of lost landmark tracks (debug output of a1)
+    int64_t cand_tracked_prev = -1, cand_tracked_next = -1;  // frames of the cached candidate KLT
+    bool cand_tracked_valid = false;
+    // PnP scratch
+    DevBuf<float> q4;       // n x 4: float32(X) and u
+    DevBuf<float> qv;       // n: v
+    DevBuf<int32_t> sets;   // H x 4
+    DevBuf<double> hyp;     // H x 12 [R|t]
+    DevBuf<int32_t> counts; // H (-1 = no model)
+    DevBuf<uint8_t> mask;   // n
+    DevBuf<uint8_t> promote;// n_cand
+    DevScalars* d_sc = nullptr;
+    DevScalars* h_sc = nullptr;  // pinned mirror
+};
+
 // ---- stage launchers implemented in the .cu files -------------------------------------------
 int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap);
 int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
                const int32_t* d_n, int n_upper, float* d_out, uint8_t* d_status, float* d_err,
                int32_t* d_iters, const vo_klt_params& prm);
+// two track lists in one launch (landmarks + candidates): list B starts at element offset
+// `b_off` of out/status/err/iters
+int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_ptsA,
+                const int32_t* d_nA, int nA_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
+                int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
+                const vo_klt_params& prm);
 
 // optional extra (off in parity mode): track `out` back into `prev` and clear status where the
 // round trip misses the start point by more than prm.fb_thresh
@@ -126,6 +198,27 @@ int klt_fb_check(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const
 FrameSlot* get_frame(Ctx* c, int64_t key);
 int pipeline_init(Ctx* c, int track_capacity, int hyp_capacity);
 void pipeline_free(Ctx* c);
+
+// pnp.cu: RANSAC over the packed points (q4,qv; n on device at sc->n_tracked or given),
+// then mask + LM refit + (optionally) compaction of the landmark buffers by the inlier mask.
+struct PnpLaunch {
+    const float* q4; const float* qv;   // packed float32 points
+    const int32_t* d_n; int n_upper;    // point count (device) and its host upper bound
+    const int32_t* d_sets_in;           // explicit H x 4 table or nullptr (cv::RNG emulation)
+    double K[9];
+    vo_pnp_params prm;
+    bool compact;                       // prune landmark buffers to the inliers (estimatePose)
+};
+int launch_pnp(Ctx* c, const PnpLaunch& L);
+// tri.cu
+int launch_landmark_compact(Ctx* c, int n_upper);   // after KLT: keep status==1, pack q4/qv
+// Tnew == nullptr: take the pose the last PnP left on the device (fused per-frame call)
+int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper,
+                   bool use_klt, int b_off);
+// d_pts: n_new x 2 doubles on the device; d_Thost: 16 doubles on the device or nullptr (= device pose)
+int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost);
+int launch_triangulate(Ctx* c, const double* d_M1, const double* d_M2, int per_point, const double* d_p1,
+                       const double* d_p2, int n, double* d_X4);
 
 }  // namespace vo
 

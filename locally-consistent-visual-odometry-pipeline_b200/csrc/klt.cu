@@ -49,20 +49,31 @@ __device__ __forceinline__ int bilerp_u8(const uint8_t* __restrict__ p, int stri
 
 template <int WIN>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32)
-klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const float2* __restrict__ pts,
-                 const int32_t* __restrict__ n_dev, const int n_upper, float2* __restrict__ out,
-                 uint8_t* __restrict__ status_out, float* __restrict__ err_out,
+klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const float2* __restrict__ ptsA,
+                 const int32_t* __restrict__ nA_dev, const int nA_upper, const float2* __restrict__ ptsB,
+                 const int32_t* __restrict__ nB_dev, const int nB_upper, const int b_off,
+                 float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
                  int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
                  const double min_eig_thr)
 {
     constexpr int NPX = WIN * WIN;
     constexpr int K = (NPX + 31) / 32;
     const int lane = threadIdx.x & 31;
-    const int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-    const int n = n_dev ? min(*n_dev, n_upper) : n_upper;
-    if (track >= n) return;
+    int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
+    // two track lists share one launch: landmarks (A) then candidates (B, written at b_off)
+    float2 pt;
+    if (track < nA_upper) {
+        const int n = nA_dev ? min(*nA_dev, nA_upper) : nA_upper;
+        if (track >= n) return;
+        pt = ptsA[track];
+    } else {
+        track -= nA_upper;
+        const int n = nB_dev ? min(*nB_dev, nB_upper) : nB_upper;
+        if (track >= n) return;
+        pt = ptsB[track];
+        track += b_off;
+    }
 
-    const float2 pt = pts[track];
     const float half = (WIN - 1) * 0.5f;
     float cx = 0.f, cy = 0.f;  // stored nextPts (window centre)
     int st = 1, iters = 0;
@@ -222,7 +233,18 @@ int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const f
                const int32_t* d_n, int n_upper, float* d_out, uint8_t* d_status, float* d_err,
                int32_t* d_iters, const vo_klt_params& prm)
 {
-    if (n_upper <= 0) return VO_OK;
+    return launch_klt2(c, prev, next, d_pts, d_n, n_upper, nullptr, nullptr, 0, 0, d_out, d_status, d_err,
+                       d_iters, prm);
+}
+
+int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
+                const int32_t* d_n, int n_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
+                int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
+                const vo_klt_params& prm)
+{
+    if (n_upper < 0) n_upper = 0;
+    if (nB_upper < 0) nB_upper = 0;
+    if (n_upper + nB_upper <= 0) return VO_OK;
     if (prm.win != 21) return set_error(c, VO_ERR_INVALID, "KLT window %d not built (only 21)", prm.win);
     if (prev.nlevels != next.nlevels || prev.lv[0].w != next.lv[0].w || prev.lv[0].h != next.lv[0].h)
         return set_error(c, VO_ERR_INVALID, "KLT frames differ in size");
@@ -235,10 +257,10 @@ int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const f
     int max_iters = prm.max_iters < 0 ? 0 : (prm.max_iters > 100 ? 100 : prm.max_iters);
     const double eps = prm.epsilon < 0. ? 0. : (prm.epsilon > 10. ? 10. : prm.epsilon);
     const double eps2 = eps * eps;
-    const int blocks = (n_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const int blocks = (n_upper + nB_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
     klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, c->stream>>>(
-        prev, next, top, (const float2*)d_pts, d_n, n_upper, (float2*)d_out, d_status, d_err, d_iters,
-        max_iters, eps2, prm.min_eig_thr);
+        prev, next, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
+        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;

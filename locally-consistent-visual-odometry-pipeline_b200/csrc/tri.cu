@@ -1,0 +1,353 @@
+// K7/K8: state compaction after tracking, the bearing-angle baseline test fused with batched DLT
+// triangulation and the C -> P/X promotion, candidate append.
+//
+// Replaces, in /root/reference/src/vo_pipeline.py:
+//   :217-225  boolean-mask selection of tracked landmarks (associateKeypointsToLandmarks)
+//   :503-545  update of tracked candidates, removal of lost rows of C/F/T
+//   :564-591  append of new candidates (F := C, T := new pose)
+//   :608-642  bearing-angle test (Python loop over all candidates, raw pixel bearing vectors)
+//   :658-674  cv2.triangulatePoints per validated candidate + np.concatenate onto P and X
+//   :718-721  np.delete of the validated rows
+// cv2.triangulatePoints behaviour per SURVEY.md App. A.3: unnormalised 4x4 DLT, right singular
+// vector of the smallest singular value; here one-sided Jacobi in FP64 (FP32 misses the 1e-4 gate).
+// All compactions are order-preserving (prefix sums), so row order equals the reference's.
+#include "ctx.cuh"
+
+namespace vo {
+
+namespace {
+
+constexpr int kScanThreads = 1024;
+
+// block-wide exclusive rank of `flag` among the CTA's threads for the current tile; `base` is the
+// running total (shared), advanced by the tile's total.  All threads must call.
+__device__ __forceinline__ int tile_rank(bool flag, int* sWarp, int* sBase)
+{
+    const int tid = threadIdx.x;
+    const unsigned bal = __ballot_sync(0xffffffffu, flag);
+    const int wpre = __popc(bal & ((1u << (tid & 31)) - 1));
+    if ((tid & 31) == 0) sWarp[tid >> 5] = __popc(bal);
+    __syncthreads();
+    int off = *sBase;
+    for (int w = 0; w < (tid >> 5); w++) off += sWarp[w];
+    __syncthreads();
+    if (tid == 0) {
+        int s = 0;
+        for (int w = 0; w < kScanThreads / 32; w++) s += sWarp[w];
+        *sBase += s;
+    }
+    __syncthreads();
+    return off + wpre;
+}
+
+// after KLT on the landmarks: keep status==1 rows (new position, X), pack the float32 PnP inputs
+__global__ void __launch_bounds__(kScanThreads)
+landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ klt_out,
+                        const uint8_t* __restrict__ status, const int32_t* __restrict__ iters,
+                        const double* __restrict__ X_in, float2* __restrict__ P_out, double* __restrict__ X_out,
+                        float4* __restrict__ q4, float* __restrict__ qv, float2* __restrict__ lost)
+{
+    __shared__ int sWarp[kScanThreads / 32];
+    __shared__ int sKeep, sLost, sIter;
+    const int tid = threadIdx.x;
+    const int n = min(sc->n_land, n_upper);
+    if (tid == 0) { sKeep = 0; sLost = 0; sIter = 0; }
+    __syncthreads();
+    int it = 0;
+    for (int i0 = 0; i0 < n; i0 += kScanThreads) {
+        const int i = i0 + tid;
+        const bool in = i < n;
+        const bool keep = in && status[i] != 0;
+        if (in && iters) it += iters[i];
+        const int o = tile_rank(keep, sWarp, &sKeep);
+        const int ol = tile_rank(in && !keep, sWarp, &sLost);
+        if (keep) {
+            const float2 p = klt_out[i];
+            const double x = X_in[3 * (size_t)i], y = X_in[3 * (size_t)i + 1], z = X_in[3 * (size_t)i + 2];
+            P_out[o] = p;
+            X_out[3 * (size_t)o] = x; X_out[3 * (size_t)o + 1] = y; X_out[3 * (size_t)o + 2] = z;
+            q4[o] = make_float4((float)x, (float)y, (float)z, p.x);   // cv2 converts X to float32
+            qv[o] = p.y;
+        } else if (in) {
+            lost[ol] = klt_out[i];
+        }
+    }
+    it = __reduce_add_sync(0xffffffffu, it);
+    if ((tid & 31) == 0) atomicAdd(&sIter, it);
+    __syncthreads();
+    if (tid == 0) { sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
+}
+
+// ---- DLT ---------------------------------------------------------------------------------------
+// right singular vector of the smallest singular value of the 4x4 A (rows x*M[2]-M[0], ...),
+// one-sided Jacobi (Hestenes).  M1, M2: 3x4 row-major.
+__device__ void dlt_point(const double* M1, const double* M2, double x1, double y1, double x2, double y2, double* Xh)
+{
+    double A[4][4], V[4][4];
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        A[0][c] = x1 * M1[8 + c] - M1[c];
+        A[1][c] = y1 * M1[8 + c] - M1[4 + c];
+        A[2][c] = x2 * M2[8 + c] - M2[c];
+        A[3][c] = y2 * M2[8 + c] - M2[4 + c];
+#pragma unroll
+        for (int r = 0; r < 4; r++) V[r][c] = r == c ? 1. : 0.;
+    }
+    for (int sweep = 0; sweep < 30; sweep++) {
+        bool rotated = false;
+#pragma unroll
+        for (int p = 0; p < 3; p++)
+#pragma unroll
+            for (int q = p + 1; q < 4; q++) {
+                double app = 0., aqq = 0., apq = 0.;
+#pragma unroll
+                for (int r = 0; r < 4; r++) { app += A[r][p] * A[r][p]; aqq += A[r][q] * A[r][q]; apq += A[r][p] * A[r][q]; }
+                if (fabs(apq) <= 1e-17 * sqrt(app * aqq) || apq == 0.) continue;
+                rotated = true;
+                const double zeta = (aqq - app) / (2. * apq);
+                const double t = (zeta >= 0. ? 1. : -1.) / (fabs(zeta) + sqrt(1. + zeta * zeta));
+                const double cs = 1. / sqrt(1. + t * t), sn = cs * t;
+#pragma unroll
+                for (int r = 0; r < 4; r++) {
+                    const double ap = A[r][p], aq = A[r][q];
+                    A[r][p] = cs * ap - sn * aq; A[r][q] = sn * ap + cs * aq;
+                    const double vp = V[r][p], vq = V[r][q];
+                    V[r][p] = cs * vp - sn * vq; V[r][q] = sn * vp + cs * vq;
+                }
+            }
+        if (!rotated) break;
+    }
+    double bn = 0.;
+    int best = 0;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        double nn = 0.;
+#pragma unroll
+        for (int r = 0; r < 4; r++) nn += A[r][c] * A[r][c];
+        if (c == 0 || nn < bn) { bn = nn; best = c; }
+    }
+#pragma unroll
+    for (int r = 0; r < 4; r++) Xh[r] = best == 0 ? V[r][0] : (best == 1 ? V[r][1] : (best == 2 ? V[r][2] : V[r][3]));
+}
+
+// M = K(3x3) @ T[0:3,:] (T 4x4 row-major)
+__device__ __forceinline__ void k_times_pose(const double* K, const double* T, double* M)
+{
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+#pragma unroll
+        for (int c = 0; c < 4; c++) M[4 * r + c] = K[3 * r] * T[c] + K[3 * r + 1] * T[4 + c] + K[3 * r + 2] * T[8 + c];
+}
+
+// vo_pipeline.py:621-642 evaluated as written (float64): raw-pixel bearing vectors, normalised,
+// cos clipped, arccos, degrees
+__device__ __forceinline__ double bearing_angle_deg(double uc, double vc, double uf, double vf)
+{
+    const double wc = sqrt(uc * uc + vc * vc + 1.), wf = sqrt(uf * uf + vf * vf + 1.);
+    const double a0 = uc / wc, a1 = vc / wc, a2 = 1. / wc, b0 = uf / wf, b1 = vf / wf, b2 = 1. / wf;
+    const double na = sqrt(a0 * a0 + a1 * a1 + a2 * a2), nb = sqrt(b0 * b0 + b1 * b1 + b2 * b2);
+    double cs = (a0 * b0 + a1 * b1 + a2 * b2) / (na * nb);
+    cs = fmin(fmax(cs, -1.), 1.);
+    return acos(cs) * (180. / 3.14159265358979323846);
+}
+
+struct PromoteArgs {
+    double K[9];
+    double Tnew[16];
+    double alpha_deg;
+    int use_dev_T;     // take the new pose from sc->T (fused per-frame call) instead of Tnew
+    int use_klt;       // candidates were tracked: positions/status at klt_out/klt_status + b_off
+    int b_off;
+    int ncand_upper;
+};
+
+// Single CTA.  Tracked candidates: C := new position (F too while C/F alias, App. B-5); lost rows
+// dropped; alpha(C,F) > threshold => triangulate with (T_first, T_new), append to P/X, drop from
+// C/F/T; the rest is compacted into the other candidate buffers.
+__global__ void __launch_bounds__(kScanThreads)
+promote_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out, const uint8_t* __restrict__ status,
+               const float2* __restrict__ C_in, const double2* __restrict__ F_in, const int32_t* __restrict__ Ti_in,
+               float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
+               const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap)
+{
+    __shared__ int sWarp[kScanThreads / 32];
+    __shared__ int sStay, sProm, sKept;
+    __shared__ double sM2[12];
+    const int tid = threadIdx.x;
+    const int n = min(sc->n_cand, a.ncand_upper);
+    const int n_land = sc->n_land;
+    const bool alias = sc->cf_alias != 0;
+    const bool have_pose = a.use_dev_T ? sc->ok != 0 : true;
+    if (tid == 0) {
+        sStay = 0; sProm = 0; sKept = 0;
+        k_times_pose(a.K, a.use_dev_T ? sc->T : a.Tnew, sM2);
+    }
+    __syncthreads();
+    for (int i0 = 0; i0 < n; i0 += kScanThreads) {
+        const int i = i0 + tid;
+        const bool in = i < n;
+        bool keep = in;
+        float2 cpos = make_float2(0.f, 0.f);
+        double2 f = make_double2(0., 0.);
+        if (in) {
+            if (a.use_klt) { keep = status[a.b_off + i] != 0; cpos = klt_out[a.b_off + i]; }
+            else cpos = C_in[i];
+            f = (alias && a.use_klt) ? make_double2((double)cpos.x, (double)cpos.y) : F_in[i];
+        }
+        bool prom = false;
+        if (keep && have_pose) prom = bearing_angle_deg((double)cpos.x, (double)cpos.y, f.x, f.y) > a.alpha_deg;
+        const int op = tile_rank(prom, sWarp, &sProm);
+        const int os = tile_rank(keep && !prom, sWarp, &sStay);
+        if (keep && !prom) { C_out[os] = cpos; F_out[os] = f; Ti_out[os] = Ti_in[i]; }
+        if (prom && n_land + op < land_cap) {
+            double M1[12], Xh[4];
+            k_times_pose(a.K, poses + 16 * (size_t)Ti_in[i], M1);
+            dlt_point(M1, sM2, f.x, f.y, (double)cpos.x, (double)cpos.y, Xh);
+            const int o = n_land + op;
+            P[o] = cpos;
+            X[3 * (size_t)o] = Xh[0] / Xh[3]; X[3 * (size_t)o + 1] = Xh[1] / Xh[3]; X[3 * (size_t)o + 2] = Xh[2] / Xh[3];
+        }
+        const unsigned kb = __ballot_sync(0xffffffffu, keep);
+        if ((tid & 31) == 0 && kb) atomicAdd(&sKept, __popc(kb));
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const int n_lost = n - sKept;
+        sc->n_cand = sStay;
+        sc->n_promoted = sProm;
+        sc->n_cand_lost = n_lost;
+        sc->n_land = min(n_land + sProm, land_cap);
+        sc->cand_was_empty = sKept == 0;                      // C empty after tracking/removal (vo:579)
+        sc->cf_alias = alias && n_lost == 0 && sProm == 0;    // np.delete re-allocates: aliasing ends
+    }
+}
+
+// append n_new candidates: C := F := pts, T := pose (vo_pipeline.py:574-591)
+__global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts, int n_new, int use_dev_T,
+                                const double* __restrict__ Thost, float2* __restrict__ C, double2* __restrict__ F,
+                                int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n0 = sc->n_cand;
+    if (use_dev_T && !sc->ok) return;   // no pose this frame: nothing is added
+    if (i < 16) poses[16 * (size_t)pose_idx + i] = use_dev_T ? sc->T[i] : Thost[i];
+    if (i < n_new && n0 + i < cand_cap) {
+        const double2 p = pts[i];
+        C[n0 + i] = make_float2((float)p.x, (float)p.y);
+        F[n0 + i] = p;
+        Ti[n0 + i] = pose_idx;
+    }
+}
+
+__global__ void cand_add_commit_kernel(DevScalars* sc, int n_new, int use_dev_T, int cand_cap)
+{
+    if (use_dev_T && !sc->ok) return;
+    if (n_new <= 0) return;
+    // C empty when the batch arrives: the reference binds C and F to one ndarray (App. B-5);
+    // otherwise np.concatenate allocates fresh arrays and any aliasing ends
+    sc->cf_alias = sc->cand_was_empty ? 1 : 0;
+    sc->n_cand = min(sc->n_cand + n_new, cand_cap);
+    sc->cand_was_empty = 0;
+}
+
+__global__ void triangulate_kernel(const double* __restrict__ M1, const double* __restrict__ M2, int per_point,
+                                   const double2* __restrict__ p1, const double2* __restrict__ p2, int n,
+                                   double* __restrict__ X4)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double m1[12], m2[12], Xh[4];
+    const double* a = M1 + (per_point ? 12 * (size_t)i : 0);
+#pragma unroll
+    for (int k = 0; k < 12; k++) { m1[k] = a[k]; m2[k] = M2[k]; }
+    dlt_point(m1, m2, p1[i].x, p1[i].y, p2[i].x, p2[i].y, Xh);
+#pragma unroll
+    for (int k = 0; k < 4; k++) X4[4 * (size_t)i + k] = Xh[k];
+}
+
+}  // namespace
+
+int launch_landmark_compact(Ctx* c, int n_upper)
+{
+    Pipeline* p = c->pipe;
+    const size_t n = n_upper > 0 ? n_upper : 1;
+    VO_TRY(ensure(c, p->P[p->cur ^ 1], n * 2));
+    VO_TRY(ensure(c, p->X[p->cur ^ 1], n * 3));
+    VO_TRY(ensure(c, p->q4, n * 4));
+    VO_TRY(ensure(c, p->qv, n));
+    VO_TRY(ensure(c, p->lost, n * 2));
+    landmark_compact_kernel<<<1, kScanThreads, 0, c->stream>>>(
+        p->d_sc, n_upper, (const float2*)p->klt_out.p, p->klt_status.p, p->klt_iters.p, p->X[p->cur].p,
+        (float2*)p->P[p->cur ^ 1].p, p->X[p->cur ^ 1].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p);
+    c->launches++;
+    p->cur ^= 1;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper, bool use_klt,
+                   int b_off)
+{
+    Pipeline* p = c->pipe;
+    PromoteArgs a;
+    memcpy(a.K, K, sizeof(a.K));
+    if (Tnew) memcpy(a.Tnew, Tnew, sizeof(a.Tnew)); else memset(a.Tnew, 0, sizeof(a.Tnew));
+    a.alpha_deg = alpha_deg;
+    a.use_dev_T = Tnew == nullptr;
+    a.use_klt = use_klt;
+    a.b_off = b_off;
+    a.ncand_upper = ncand_upper;
+    const size_t nc = ncand_upper > 0 ? ncand_upper : 1;
+    VO_TRY(ensure(c, p->C[p->ccur ^ 1], nc * 2));
+    VO_TRY(ensure(c, p->F[p->ccur ^ 1], nc * 2));
+    VO_TRY(ensure(c, p->Ti[p->ccur ^ 1], nc));
+    // promoted rows are appended in place behind the live landmarks
+    const size_t need = (size_t)p->n_land_upper + nc;
+    VO_TRY(ensure(c, p->P[p->cur], need * 2, true));
+    VO_TRY(ensure(c, p->X[p->cur], need * 3, true));
+    const int land_cap = (int)(p->P[p->cur].cap / 2);
+    promote_kernel<<<1, kScanThreads, 0, c->stream>>>(
+        p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
+        (const double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, (float2*)p->C[p->ccur ^ 1].p,
+        (double2*)p->F[p->ccur ^ 1].p, p->Ti[p->ccur ^ 1].p, p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p,
+        land_cap);
+    c->launches++;
+    p->ccur ^= 1;
+    p->n_land_upper += ncand_upper;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost)
+{
+    Pipeline* p = c->pipe;
+    const size_t need = (size_t)p->n_cand_upper + (n_new > 0 ? n_new : 0) + 1;
+    VO_TRY(ensure(c, p->C[p->ccur], need * 2, true));
+    VO_TRY(ensure(c, p->F[p->ccur], need * 2, true));
+    VO_TRY(ensure(c, p->Ti[p->ccur], need, true));
+    VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));
+    const int cap = (int)(p->C[p->ccur].cap / 2);
+    const int threads = 256, blocks = ((n_new > 16 ? n_new : 16) + threads - 1) / threads;
+    cand_add_kernel<<<blocks, threads, 0, c->stream>>>(p->d_sc, (const double2*)d_pts, n_new, d_Thost == nullptr,
+                                                       d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
+                                                       p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap);
+    cand_add_commit_kernel<<<1, 1, 0, c->stream>>>(p->d_sc, n_new, d_Thost == nullptr, cap);
+    c->launches += 2;
+    p->n_poses++;
+    p->n_cand_upper += n_new > 0 ? n_new : 0;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+int launch_triangulate(Ctx* c, const double* d_M1, const double* d_M2, int per_point, const double* d_p1,
+                       const double* d_p2, int n, double* d_X4)
+{
+    if (n <= 0) return VO_OK;
+    triangulate_kernel<<<(n + 127) / 128, 128, 0, c->stream>>>(d_M1, d_M2, per_point, (const double2*)d_p1,
+                                                              (const double2*)d_p2, n, d_X4);
+    c->launches++;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+}  // namespace vo
