@@ -107,6 +107,75 @@ int vo_calc_optical_flow_pyr_lk(vo_ctx* ctx, int64_t prev_key, int64_t next_key,
                                 int n, float* next_pts, uint8_t* status, float* err, int32_t* iters,
                                 const vo_klt_params* params);
 
+/* ---- device-resident Markov state: BestVision.state {'P','X'} and .extended_state {'C','F','T'}
+ * (vo_pipeline.py:36-37).  P: n x 2 float32, X: n x 3 float64, C: n x 2 float32 (candidate positions
+ * are float32-exact in the reference: KLT outputs / detector outputs), F: n x 2 float64,
+ * T: n x 16 float64 (4x4 row-major world->camera pose of the first observation). -------------- */
+typedef struct vo_counters {
+    int32_t n_landmarks, n_candidates;   /* current |P|, |C| */
+    int32_t n_tracked, n_lost;           /* last landmark KLT: kept / lost */
+    int32_t n_inliers, pnp_ok;           /* last PnP */
+    int32_t ransac_iters, best_hypothesis, lm_iters;
+    int32_t n_promoted, n_candidates_lost, cf_alias;
+    int32_t klt_iters;                   /* sum of LK iterations over the last landmark KLT */
+    double reproj_cost;                  /* sum of squared reprojection errors of the refit */
+} vo_counters;
+
+/* Upload landmarks after bootstrap (main.py:198-200 vision.state = state).  Synchronises. */
+int vo_set_state(vo_ctx* ctx, const float* P, const double* X, int n);
+/* Host mirror of state['P'], state['X'] (main.py:248 reads state['X'] every frame).  P/X may be
+ * NULL to query n only.  Synchronises. */
+int vo_get_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
+/* Load / read the candidate set (tests, checkpoint/resume).  cf_alias: reference quirk App. B-5. */
+int vo_set_candidates(vo_ctx* ctx, const float* C, const double* F, const double* T, int n, int cf_alias);
+int vo_get_candidates(vo_ctx* ctx, float* C, double* F, double* T, int cap, int* n);
+/* points_tracking_lost of associateKeypointsToLandmarks (vo_pipeline.py:220-221). */
+int vo_get_lost(vo_ctx* ctx, float* lost, int cap, int* n);
+int vo_get_counters(vo_ctx* ctx, vo_counters* out);   /* synchronises */
+
+/* a1  KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227):
+ * KLT of P from prev to next frame, keep status==1 rows of P and X.  The candidates C are tracked
+ * in the same launch (the reference does it later, at vo_pipeline.py:501, on the same frame pair).
+ * n_kept may be NULL: then nothing synchronises. */
+int vo_klt_track_landmarks(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
+                           int* n_kept);
+/* a3  PoseEstimator.estimatePose (vo_pipeline.py:245-335): PnP-RANSAC + LM refit, prunes P/X to
+ * the inliers (vo_pipeline.py:327-331), T44 = 4x4 row-major world->camera (vo_pipeline.py:333).
+ * ok=0 (no model / n<4) leaves the state untouched: the caller takes the re-bootstrap branch of
+ * vo_pipeline.py:274-324.  Synchronises. */
+int vo_pnp_ransac(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, double T44[16], int* n_inliers,
+                  int* ok);
+/* a6  LandmarkTriangulator.triangulate_landmark, steps 1 and 3 (vo_pipeline.py:489-545, 608-721):
+ * track C, drop lost rows of C/F/T, alpha(C,F) > alpha_deg => DLT with (T_first, T44) and append to
+ * P/X, remove from C/F/T.  prev_key = next_key = -1 runs the promotion step without tracking.
+ * n_promoted may be NULL (no sync). */
+int vo_track_triangulate_promote(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const double K[9],
+                                 const double T44[16], double alpha_deg, const vo_klt_params* params,
+                                 int* n_promoted);
+/* a6 step 2 (vo_pipeline.py:564-591): append candidates C := F := pts (n x 2 float64), T := T44.
+ * Call after vo_track_triangulate_promote (new rows have alpha = 0 and are never promoted in the
+ * frame they arrive, so the order does not change results). */
+int vo_add_candidates(vo_ctx* ctx, const double* pts, int n, const double T44[16]);
+
+/* One frame of main.py:216-284 with a single host synchronisation: upload (img may be NULL if
+ * next_key is resident), KLT of P and C, PnP-RANSAC + LM + pruning, promotion, append of
+ * new_candidates (n_new x 2 float64; the reference's detectors stay on the CPU). */
+int vo_process_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
+                     const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
+                     const double* new_candidates, int n_new, double T44[16], vo_counters* counters);
+
+/* ---- unit-level entry point mirroring cv2.solvePnPRansac (vo_pipeline.py:258-264) with P3P
+ * hypotheses.  minimal_sets: max_iters x 4 int32 or NULL (cv::RNG(2^64-1) emulation = what cv2
+ * draws).  All outputs optional.  info = {iterations run, winning iteration, inliers, LM iters}.
+ * Does not touch the Markov state.  Synchronises. */
+int vo_solve_pnp_ransac(vo_ctx* ctx, const double* X, const float* P, int n, const double K[9],
+                        const vo_pnp_params* params, const int32_t* minimal_sets, double T44[16], double Th12[12],
+                        double rvec[3], double tvec[3], uint8_t* inlier_mask, int32_t info[4], int* ok);
+/* ---- unit-level entry point mirroring cv2.triangulatePoints (vo_pipeline.py:666, :172).
+ * M1: 3x4 (per_point_m1=0) or n x 12; X4: n x 4 homogeneous, unit norm.  Synchronises. */
+int vo_triangulate_points(vo_ctx* ctx, const double* M1, const double* M2, int per_point_m1, const double* p1,
+                          const double* p2, int n, double* X4);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

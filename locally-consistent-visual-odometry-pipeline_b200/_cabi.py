@@ -33,6 +33,20 @@ class PnpParams(ctypes.Structure):
                 ("refine_iters", c_int), ("min_inliers", c_int)]
 
 
+class Counters(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_int32) for n in (
+        "n_landmarks", "n_candidates", "n_tracked", "n_lost", "n_inliers", "pnp_ok", "ransac_iters",
+        "best_hypothesis", "lm_iters", "n_promoted", "n_candidates_lost", "cf_alias", "klt_iters")] + [
+        ("reproj_cost", c_double)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+_PK = ctypes.POINTER(KltParams)
+_PP = ctypes.POINTER(PnpParams)
+_PI = ctypes.POINTER(c_int)
+
 # name -> (restype, argtypes); every symbol include/vo_b200.h declares must be listed here
 # (tests/test_abi.py cross-checks this table against the header).
 SIGNATURES = {
@@ -54,6 +68,21 @@ SIGNATURES = {
                                      ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "vo_calc_optical_flow_pyr_lk": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_int, c_void_p, c_void_p,
                                             c_void_p, c_void_p, ctypes.POINTER(KltParams)]),
+    "vo_set_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
+    "vo_get_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
+    "vo_set_candidates": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "vo_get_candidates": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
+    "vo_get_lost": (c_int, [c_void_p, c_void_p, c_int, _PI]),
+    "vo_get_counters": (c_int, [c_void_p, ctypes.POINTER(Counters)]),
+    "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
+    "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
+    "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
+    "vo_add_candidates": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vo_process_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64, c_i64, c_void_p, _PK, _PP,
+                                 c_double, c_void_p, c_int, c_void_p, ctypes.POINTER(Counters)]),
+    "vo_solve_pnp_ransac": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _PI]),
+    "vo_triangulate_points": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
 }
 
 _lib = None
@@ -197,3 +226,135 @@ class Context:
         if want_iters:
             return out, status, err, iters
         return out, status, err
+
+    # ---- Markov state ------------------------------------------------------------------------------
+    def set_state(self, P, X):
+        P = np.ascontiguousarray(P, np.float32).reshape(-1, 2)
+        X = np.ascontiguousarray(X, np.float64).reshape(-1, 3)
+        if len(P) != len(X):
+            raise ValueError("P and X differ in length")
+        self._check(self.lib.vo_set_state(self.h, _ptr(P), _ptr(X), len(P)))
+
+    def n_state(self):
+        n = c_int()
+        self._check(self.lib.vo_get_state(self.h, None, None, 0, ctypes.byref(n)))
+        return n.value
+
+    def get_state(self):
+        n = self.n_state()
+        P = np.empty((n, 2), np.float32)
+        X = np.empty((n, 3), np.float64)
+        m = c_int()
+        self._check(self.lib.vo_get_state(self.h, _ptr(P), _ptr(X), n, ctypes.byref(m)))
+        return P, X
+
+    def set_candidates(self, C, F, T, cf_alias=False):
+        C = np.ascontiguousarray(C, np.float32).reshape(-1, 2)
+        F = np.ascontiguousarray(F, np.float64).reshape(-1, 2)
+        T = np.ascontiguousarray(T, np.float64).reshape(-1, 16)
+        if not (len(C) == len(F) == len(T)):
+            raise ValueError("C, F, T differ in length")
+        self._check(self.lib.vo_set_candidates(self.h, _ptr(C), _ptr(F), _ptr(T), len(C), int(cf_alias)))
+
+    def get_candidates(self):
+        n = c_int()
+        self._check(self.lib.vo_get_candidates(self.h, None, None, None, 0, ctypes.byref(n)))
+        C = np.empty((n.value, 2), np.float32)
+        F = np.empty((n.value, 2), np.float64)
+        T = np.empty((n.value, 4, 4), np.float64)
+        self._check(self.lib.vo_get_candidates(self.h, _ptr(C), _ptr(F), _ptr(T), n.value, ctypes.byref(n)))
+        return C, F, T
+
+    def get_lost(self):
+        n = c_int()
+        self._check(self.lib.vo_get_lost(self.h, None, 0, ctypes.byref(n)))
+        lost = np.empty((n.value, 2), np.float32)
+        self._check(self.lib.vo_get_lost(self.h, _ptr(lost), n.value, ctypes.byref(n)))
+        return lost
+
+    def counters(self):
+        cnt = Counters()
+        self._check(self.lib.vo_get_counters(self.h, ctypes.byref(cnt)))
+        return cnt.as_dict()
+
+    # ---- per-frame stages ------------------------------------------------------------------------
+    def klt_track_landmarks(self, prev_key, next_key, params=None, sync=False):
+        n = c_int()
+        self._check(self.lib.vo_klt_track_landmarks(
+            self.h, prev_key, next_key, ctypes.byref(params) if params is not None else None,
+            ctypes.byref(n) if sync else None))
+        return n.value if sync else None
+
+    def pnp_ransac(self, K, params=None):
+        K = np.ascontiguousarray(K, np.float64)
+        T = np.empty((4, 4), np.float64)
+        ninl, ok = c_int(), c_int()
+        self._check(self.lib.vo_pnp_ransac(self.h, _ptr(K), ctypes.byref(params) if params is not None else None,
+                                           _ptr(T), ctypes.byref(ninl), ctypes.byref(ok)))
+        return bool(ok.value), T, ninl.value
+
+    def track_triangulate_promote(self, prev_key, next_key, K, T44, alpha_deg, params=None, sync=False):
+        K = np.ascontiguousarray(K, np.float64)
+        T44 = np.ascontiguousarray(T44, np.float64)
+        n = c_int()
+        self._check(self.lib.vo_track_triangulate_promote(
+            self.h, prev_key, next_key, _ptr(K), _ptr(T44), float(alpha_deg),
+            ctypes.byref(params) if params is not None else None, ctypes.byref(n) if sync else None))
+        return n.value if sync else None
+
+    def add_candidates(self, pts, T44):
+        pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)
+        T44 = np.ascontiguousarray(T44, np.float64)
+        self._check(self.lib.vo_add_candidates(self.h, _ptr(pts), len(pts), _ptr(T44)))
+
+    def process_frame(self, img, prev_key, next_key, K, alpha_deg, new_candidates=None, klt=None, pnp=None,
+                      want_counters=True):
+        K = np.ascontiguousarray(K, np.float64)
+        T = np.empty((4, 4), np.float64)
+        cnt = Counters() if want_counters else None
+        if new_candidates is not None:
+            new_candidates = np.ascontiguousarray(new_candidates, np.float64).reshape(-1, 2)
+        nn = 0 if new_candidates is None else len(new_candidates)
+        if img is not None:
+            h, w = img.shape
+            ip, pitch = c_void_p(img.ctypes.data), img.strides[0]
+        else:
+            h = w = pitch = 0
+            ip = None
+        self._check(self.lib.vo_process_frame(
+            self.h, ip, w, h, pitch, prev_key, next_key, _ptr(K), ctypes.byref(klt) if klt is not None else None,
+            ctypes.byref(pnp) if pnp is not None else None, float(alpha_deg),
+            _ptr(new_candidates) if nn else None, nn, _ptr(T), ctypes.byref(cnt) if cnt is not None else None))
+        return T, (cnt.as_dict() if cnt is not None else None)
+
+    # ---- unit-level: cv2.solvePnPRansac / cv2.triangulatePoints ------------------------------------
+    def solve_pnp_ransac(self, X, P, K, params=None, sets=None):
+        X = np.ascontiguousarray(X, np.float64).reshape(-1, 3)
+        P = np.ascontiguousarray(P, np.float32).reshape(-1, 2)
+        K = np.ascontiguousarray(K, np.float64)
+        n = len(X)
+        if params is None:
+            params = pnp_defaults()
+        if sets is not None:
+            sets = np.ascontiguousarray(sets, np.int32)
+            if sets.shape[0] < params.max_iters or sets.shape[1] != 4:
+                raise ValueError("minimal-set table must be max_iters x 4")
+        T = np.zeros((4, 4)); Th = np.zeros(12); rvec = np.zeros(3); tvec = np.zeros(3)
+        mask = np.zeros(n, np.uint8); info = np.zeros(4, np.int32); ok = c_int()
+        self._check(self.lib.vo_solve_pnp_ransac(self.h, _ptr(X), _ptr(P), n, _ptr(K), ctypes.byref(params), _ptr(sets),
+                                                 _ptr(T), _ptr(Th), _ptr(rvec), _ptr(tvec), _ptr(mask), _ptr(info),
+                                                 ctypes.byref(ok)))
+        return dict(ok=bool(ok.value), T=T, R=T[:3, :3].copy(), t=T[:3, 3].copy(), Rh=Th[:9].reshape(3, 3),
+                    th=Th[9:], rvec=rvec, tvec=tvec, mask=mask, iters=int(info[0]), best_iter=int(info[1]),
+                    n_inliers=int(info[2]), lm_iters=int(info[3]))
+
+    def triangulate_points(self, M1, M2, p1, p2):
+        M1 = np.ascontiguousarray(M1, np.float64)
+        M2 = np.ascontiguousarray(M2, np.float64).reshape(3, 4)
+        p1 = np.ascontiguousarray(p1, np.float64).reshape(-1, 2)
+        p2 = np.ascontiguousarray(p2, np.float64).reshape(-1, 2)
+        n = len(p1)
+        per_point = int(M1.size == 12 * n and n > 1 or M1.ndim == 3)
+        out = np.zeros((n, 4))
+        self._check(self.lib.vo_triangulate_points(self.h, _ptr(M1), _ptr(M2), per_point, _ptr(p1), _ptr(p2), n, _ptr(out)))
+        return out

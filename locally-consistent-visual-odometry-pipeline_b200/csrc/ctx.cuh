@@ -174,6 +174,11 @@ struct Pipeline {
     DevBuf<int32_t> counts; // H (-1 = no model)
     DevBuf<uint8_t> mask;   // n
     DevBuf<uint8_t> promote;// n_cand
+    DevBuf<double> stage_d; // host->device staging (unit-level calls, candidate feed)
+    DevBuf<float> stage_f;
+    DevBuf<int32_t> stage_i;
+    int klt_b_off = 0;      // offset of the candidate results inside the klt_* buffers
+    bool packed_valid = false;  // q4/qv hold the current landmarks (set by the post-KLT compaction)
     DevScalars* d_sc = nullptr;
     DevScalars* h_sc = nullptr;  // pinned mirror
 };

@@ -1,25 +1,454 @@
-// Pipeline-level state and entry points (filled in below).
+// Pipeline-level C-ABI: the device-resident Markov state (P, X | C, F, T) and the three per-frame
+// stages of /root/reference/src/main.py:229-284 (associate -> estimatePose -> triangulate_landmark),
+// plus unit-level entry points that mirror the cv2 signatures for differential tests.
+#include <math.h>
 #include "ctx.cuh"
 
 namespace vo {
 
-struct Pipeline {
-    int track_capacity = 0, hyp_capacity = 0;
-};
-
 int pipeline_init(Ctx* c, int track_capacity, int hyp_capacity)
 {
-    c->pipe = new (std::nothrow) Pipeline();
-    if (!c->pipe) return set_error(c, VO_ERR_NOMEM, "out of host memory");
-    c->pipe->track_capacity = track_capacity;
-    c->pipe->hyp_capacity = hyp_capacity;
+    Pipeline* p = new (std::nothrow) Pipeline();
+    if (!p) return set_error(c, VO_ERR_NOMEM, "out of host memory");
+    c->pipe = p;
+    p->track_capacity = track_capacity > 0 ? track_capacity : 4096;
+    p->hyp_capacity = hyp_capacity > 0 ? hyp_capacity : 2048;
+    VO_CUDA(c, cudaMalloc((void**)&p->d_sc, sizeof(DevScalars)));
+    VO_CUDA(c, cudaMemsetAsync(p->d_sc, 0, sizeof(DevScalars), c->stream));
+    VO_CUDA(c, cudaMallocHost((void**)&p->h_sc, sizeof(DevScalars)));
+    memset(p->h_sc, 0, sizeof(DevScalars));
+    const size_t n = p->track_capacity;
+    for (int k = 0; k < 2; k++) {
+        VO_TRY(ensure(c, p->P[k], n * 2)); VO_TRY(ensure(c, p->X[k], n * 3));
+        VO_TRY(ensure(c, p->C[k], n * 2)); VO_TRY(ensure(c, p->F[k], n * 2)); VO_TRY(ensure(c, p->Ti[k], n));
+    }
+    VO_TRY(ensure(c, p->klt_out, n * 4)); VO_TRY(ensure(c, p->klt_err, n * 2));
+    VO_TRY(ensure(c, p->klt_status, n * 2)); VO_TRY(ensure(c, p->klt_iters, n * 2));
+    VO_TRY(ensure(c, p->q4, n * 4)); VO_TRY(ensure(c, p->qv, n)); VO_TRY(ensure(c, p->lost, n * 2));
+    VO_TRY(ensure(c, p->mask, n)); VO_TRY(ensure(c, p->poses, 16 * 1024));
+    VO_TRY(ensure(c, p->sets, (size_t)p->hyp_capacity * kMinimal));
+    VO_TRY(ensure(c, p->hyp, (size_t)p->hyp_capacity * 12));
+    VO_TRY(ensure(c, p->counts, (size_t)p->hyp_capacity));
     return VO_OK;
 }
 
 void pipeline_free(Ctx* c)
 {
-    delete c->pipe;
+    Pipeline* p = c->pipe;
+    if (!p) return;
+    for (int k = 0; k < 2; k++) {
+        cudaFree(p->P[k].p); cudaFree(p->X[k].p); cudaFree(p->C[k].p); cudaFree(p->F[k].p); cudaFree(p->Ti[k].p);
+    }
+    cudaFree(p->poses.p); cudaFree(p->klt_in.p); cudaFree(p->klt_out.p); cudaFree(p->klt_err.p);
+    cudaFree(p->klt_status.p); cudaFree(p->klt_iters.p); cudaFree(p->lost.p); cudaFree(p->q4.p); cudaFree(p->qv.p);
+    cudaFree(p->sets.p); cudaFree(p->hyp.p); cudaFree(p->counts.p); cudaFree(p->mask.p); cudaFree(p->promote.p);
+    cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
+    cudaFree(p->d_sc);
+    cudaFreeHost(p->h_sc);
+    delete p;
     c->pipe = nullptr;
 }
 
+// D2H of the scalar block + stream sync; tightens the host-side upper bounds
+static int read_scalars(Ctx* c)
+{
+    Pipeline* p = c->pipe;
+    VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    p->n_land_upper = p->h_sc->n_land;
+    p->n_cand_upper = p->h_sc->n_cand;
+    return VO_OK;
+}
+
+__global__ void set_counts_kernel(DevScalars* sc, int n_land, int n_cand, int alias)
+{
+    if (n_land >= 0) sc->n_land = n_land;
+    if (n_cand >= 0) { sc->n_cand = n_cand; sc->cf_alias = alias; sc->cand_was_empty = n_cand == 0; }
+}
+
+// KLT of landmarks (list A) and candidates (list B, stored behind A at offset n_land_upper)
+static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& prm, bool with_candidates)
+{
+    Pipeline* p = c->pipe;
+    const int nA = p->n_land_upper, nB = with_candidates ? p->n_cand_upper : 0;
+    const size_t tot = (size_t)nA + nB > 0 ? (size_t)nA + nB : 1;
+    VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
+    VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
+    VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, p->C[p->ccur].p, &p->d_sc->n_cand, nB,
+                       nA, p->klt_out.p, p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm));
+    p->klt_b_off = nA;
+    return VO_OK;
+}
+
 }  // namespace vo
+
+using namespace vo;
+
+__global__ void expand_poses_kernel(const int32_t* __restrict__ Ti, const double* __restrict__ poses, int n,
+                                    double* __restrict__ T)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * 16) return;
+    T[i] = poses[16 * (size_t)Ti[i >> 4] + (i & 15)];
+}
+
+__global__ void pack_points_kernel(DevScalars* sc, const double* __restrict__ X, const float2* __restrict__ P, int n,
+                                   int from_state, float4* __restrict__ q4, float* __restrict__ qv)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int m = from_state ? min(sc->n_land, n) : n;
+    if (i == 0) sc->n_tracked = m;
+    if (i >= m) return;
+    const float2 p = P[i];
+    q4[i] = make_float4((float)X[3 * (size_t)i], (float)X[3 * (size_t)i + 1], (float)X[3 * (size_t)i + 2], p.x);
+    qv[i] = p.y;
+}
+
+#define VO_NEED(c) do { if (!(c) || !(c)->pipe) return VO_ERR_INVALID; } while (0)
+
+extern "C" {
+
+// ---- state I/O --------------------------------------------------------------------------------
+int vo_set_state(vo_ctx* c, const float* P, const double* X, int n)
+{
+    VO_NEED(c);
+    if (n < 0 || (n > 0 && (!P || !X))) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    const size_t m = n > 0 ? n : 1;
+    VO_TRY(ensure(c, p->P[p->cur], m * 2)); VO_TRY(ensure(c, p->X[p->cur], m * 3));
+    if (n > 0) {
+        VO_CUDA(c, cudaMemcpyAsync(p->P[p->cur].p, P, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->X[p->cur].p, X, sizeof(double) * 3 * n, cudaMemcpyDefault, c->stream));
+    }
+    set_counts_kernel<<<1, 1, 0, c->stream>>>(p->d_sc, n, -1, 0);
+    c->launches++;
+    p->n_land_upper = n;
+    p->cand_tracked_valid = false;
+    p->packed_valid = false;
+    // the caller's buffers may be pageable and go away: finish the copies before returning
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    VO_TRY(read_scalars(c));
+    const int m = p->h_sc->n_land;
+    if (n) *n = m;
+    if (m > cap) return (P || X) ? set_error(c, VO_ERR_CAPACITY, "state has %d rows, buffer %d", m, cap) : VO_OK;
+    if (m > 0 && P) VO_CUDA(c, cudaMemcpyAsync(P, p->P[p->cur].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && X) VO_CUDA(c, cudaMemcpyAsync(X, p->X[p->cur].p, sizeof(double) * 3 * m, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+
+// test / bootstrap hook: load a candidate set; T is n x 16 (4x4 row-major per candidate)
+int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* T, int n, int cf_alias)
+{
+    VO_NEED(c);
+    if (n < 0 || (n > 0 && (!C || !F || !T))) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    const size_t m = n > 0 ? n : 1;
+    VO_TRY(ensure(c, p->C[p->ccur], m * 2)); VO_TRY(ensure(c, p->F[p->ccur], m * 2)); VO_TRY(ensure(c, p->Ti[p->ccur], m));
+    VO_TRY(ensure(c, p->poses, m * 16));
+    if (n > 0) {
+        std::vector<int32_t> idx(n);
+        for (int i = 0; i < n; i++) idx[i] = i;
+        VO_CUDA(c, cudaMemcpyAsync(p->C[p->ccur].p, C, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->F[p->ccur].p, F, sizeof(double) * 2 * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->poses.p, T, sizeof(double) * 16 * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->Ti[p->ccur].p, idx.data(), sizeof(int32_t) * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    p->n_poses = n;
+    set_counts_kernel<<<1, 1, 0, c->stream>>>(p->d_sc, -1, n, cf_alias ? 1 : 0);
+    c->launches++;
+    p->n_cand_upper = n;
+    p->cand_tracked_valid = false;
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+int vo_get_candidates(vo_ctx* c, float* C, double* F, double* T, int cap, int* n)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    VO_TRY(read_scalars(c));
+    const int m = p->h_sc->n_cand;
+    if (n) *n = m;
+    if (m > cap) return (C || F || T) ? set_error(c, VO_ERR_CAPACITY, "%d candidates, buffer %d", m, cap) : VO_OK;
+    if (m > 0 && C) VO_CUDA(c, cudaMemcpyAsync(C, p->C[p->ccur].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && F) VO_CUDA(c, cudaMemcpyAsync(F, p->F[p->ccur].p, sizeof(double) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && T) {
+        VO_TRY(ensure(c, p->stage_d, (size_t)m * 16));
+        expand_poses_kernel<<<(m * 16 + 255) / 256, 256, 0, c->stream>>>(p->Ti[p->ccur].p, p->poses.p, m, p->stage_d.p);
+        c->launches++;
+        VO_CUDA(c, cudaMemcpyAsync(T, p->stage_d.p, sizeof(double) * 16 * m, cudaMemcpyDefault, c->stream));
+    }
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+int vo_get_lost(vo_ctx* c, float* lost, int cap, int* n)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    VO_TRY(read_scalars(c));
+    const int m = p->h_sc->n_lost;
+    if (n) *n = m;
+    if (m > cap) return lost ? set_error(c, VO_ERR_CAPACITY, "%d lost tracks, buffer %d", m, cap) : VO_OK;
+    if (m > 0 && lost) VO_CUDA(c, cudaMemcpyAsync(lost, p->lost.p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+int vo_get_counters(vo_ctx* c, vo_counters* out)
+{
+    VO_NEED(c);
+    if (!out) return VO_ERR_INVALID;
+    VO_TRY(read_scalars(c));
+    const DevScalars* s = c->pipe->h_sc;
+    out->n_landmarks = s->n_land; out->n_candidates = s->n_cand; out->n_tracked = s->n_tracked; out->n_lost = s->n_lost;
+    out->n_inliers = s->n_inliers; out->pnp_ok = s->ok; out->ransac_iters = s->iters_run; out->best_hypothesis = s->best_hyp;
+    out->lm_iters = s->lm_iters; out->n_promoted = s->n_promoted; out->n_candidates_lost = s->n_cand_lost;
+    out->cf_alias = s->cf_alias; out->klt_iters = s->klt_iters; out->reproj_cost = s->cost;
+    return VO_OK;
+}
+
+// ---- a1: KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227)
+int vo_klt_track_landmarks(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params, int* n_kept)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    vo_klt_params prm;
+    if (params) prm = *params; else vo_klt_params_default(&prm);
+    FrameSlot* a = get_frame(c, prev_key);
+    FrameSlot* b = get_frame(c, next_key);
+    if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    // candidates ride along in the same launch: triangulate_landmark (vo:501) tracks them over the
+    // same frame pair, and their tracking does not depend on the pose
+    VO_TRY(track_both(c, a, b, prm, true));
+    p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
+    VO_TRY(launch_landmark_compact(c, p->n_land_upper));
+    p->packed_valid = true;
+    if (n_kept) { VO_TRY(read_scalars(c)); *n_kept = p->h_sc->n_land; }
+    return VO_OK;
+}
+
+// ---- a3: PoseEstimator.estimatePose (vo_pipeline.py:245-335); synchronises
+int vo_pnp_ransac(vo_ctx* c, const double K[9], const vo_pnp_params* params, double T44[16], int* n_inliers, int* ok)
+{
+    VO_NEED(c);
+    if (!K) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    PnpLaunch L{};
+    if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
+    if (!p->packed_valid) {   // no tracking step preceded (state set directly): pack P/X now
+        const size_t m = p->n_land_upper > 0 ? p->n_land_upper : 1;
+        VO_TRY(ensure(c, p->q4, m * 4)); VO_TRY(ensure(c, p->qv, m));
+        pack_points_kernel<<<(int)((m + 255) / 256), 256, 0, c->stream>>>(p->d_sc, p->X[p->cur].p, (const float2*)p->P[p->cur].p,
+                                                                          p->n_land_upper, 1, (float4*)p->q4.p, p->qv.p);
+        c->launches++;
+    }
+    L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
+    L.d_sets_in = nullptr; L.compact = true;
+    memcpy(L.K, K, sizeof(L.K));
+    VO_TRY(launch_pnp(c, L));
+    p->packed_valid = false;
+    VO_TRY(read_scalars(c));
+    if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
+    if (n_inliers) *n_inliers = p->h_sc->n_inliers;
+    if (ok) *ok = p->h_sc->ok;
+    return VO_OK;
+}
+
+// ---- a6 (second half): append new candidates, F := C, T := pose (vo_pipeline.py:574-591)
+int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
+{
+    VO_NEED(c);
+    if (n < 0 || (n > 0 && !pts) || !T44) return VO_ERR_INVALID;
+    if (n == 0) return VO_OK;   // the reference appends nothing (vo:574)
+    Pipeline* p = c->pipe;
+    VO_TRY(ensure(c, p->stage_d, (size_t)n * 2 + 16));
+    VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, pts, sizeof(double) * 2 * n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p, T44, sizeof(double) * 16, cudaMemcpyDefault, c->stream));
+    VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n, p->stage_d.p));
+    return VO_OK;
+}
+
+// ---- a6 (first half): track C, drop lost, bearing test, DLT, promote (vo_pipeline.py:489-545, 608-721)
+int vo_track_triangulate_promote(vo_ctx* c, int64_t prev_key, int64_t next_key, const double K[9], const double T44[16],
+                                 double alpha_deg, const vo_klt_params* params, int* n_promoted)
+{
+    VO_NEED(c);
+    if (!K || !T44) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    bool use_klt = true;
+    if (prev_key == next_key && prev_key < 0) use_klt = false;   // promotion step only (tests)
+    if (use_klt && !(p->cand_tracked_valid && p->cand_tracked_prev == prev_key && p->cand_tracked_next == next_key)) {
+        vo_klt_params prm;
+        if (params) prm = *params; else vo_klt_params_default(&prm);
+        FrameSlot* a = get_frame(c, prev_key);
+        FrameSlot* b = get_frame(c, next_key);
+        if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+        const int nB = p->n_cand_upper;
+        const size_t tot = nB > 0 ? nB : 1;
+        VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
+        VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
+        VO_TRY(launch_klt(c, a->pyr, b->pyr, p->C[p->ccur].p, &p->d_sc->n_cand, nB, p->klt_out.p, p->klt_status.p,
+                          p->klt_err.p, p->klt_iters.p, prm));
+        p->klt_b_off = 0;
+    }
+    p->cand_tracked_valid = false;
+    VO_TRY(launch_promote(c, K, T44, alpha_deg, p->n_cand_upper, use_klt, p->klt_b_off));
+    if (n_promoted) { VO_TRY(read_scalars(c)); *n_promoted = p->h_sc->n_promoted; }
+    return VO_OK;
+}
+
+// ---- fused per-frame call: main.py:216-284 for one frame with ONE host sync ----------------------
+// upload + pyramid of the new frame, KLT of P and C (one launch), landmark compaction, PnP-RANSAC +
+// LM + pruning, candidate update + bearing test + DLT + promotion, append of the new candidates
+// (pose taken from the device), D2H of the pose and counters.
+int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
+                     const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
+                     const double* new_candidates, int n_new, double T44[16], vo_counters* counters)
+{
+    VO_NEED(c);
+    if (!K || n_new < 0 || (n_new > 0 && !new_candidates)) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    vo_klt_params kp;
+    if (kparams) kp = *kparams; else vo_klt_params_default(&kp);
+    if (img) VO_TRY(vo_upload_frame(c, img, w, h, pitch, next_key));
+    FrameSlot* a = get_frame(c, prev_key);
+    FrameSlot* b = get_frame(c, next_key);
+    if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    if (n_new > 0) {   // stage the candidate feed early so the copy overlaps the tracking
+        VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
+    }
+    VO_TRY(track_both(c, a, b, kp, true));
+    VO_TRY(launch_landmark_compact(c, p->n_land_upper));
+    p->packed_valid = true;
+    PnpLaunch L{};
+    if (pparams) L.prm = *pparams; else vo_pnp_params_default(&L.prm);
+    L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
+    L.d_sets_in = nullptr; L.compact = true;
+    memcpy(L.K, K, sizeof(L.K));
+    VO_TRY(launch_pnp(c, L));
+    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+    if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
+    p->cand_tracked_valid = false;
+    p->packed_valid = false;
+    VO_TRY(read_scalars(c));
+    if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
+    if (counters) {
+        const DevScalars* s = p->h_sc;
+        counters->n_landmarks = s->n_land; counters->n_candidates = s->n_cand; counters->n_tracked = s->n_tracked;
+        counters->n_lost = s->n_lost; counters->n_inliers = s->n_inliers; counters->pnp_ok = s->ok;
+        counters->ransac_iters = s->iters_run; counters->best_hypothesis = s->best_hyp; counters->lm_iters = s->lm_iters;
+        counters->n_promoted = s->n_promoted; counters->n_candidates_lost = s->n_cand_lost; counters->cf_alias = s->cf_alias;
+        counters->klt_iters = s->klt_iters; counters->reproj_cost = s->cost;
+    }
+    return VO_OK;
+}
+
+// ---- unit level: cv2.solvePnPRansac (vo_pipeline.py:258-264) ------------------------------------
+
+static void rotation_to_rvec(const double* T, double* rvec)
+{
+    const double R[9] = { T[0], T[1], T[2], T[4], T[5], T[6], T[8], T[9], T[10] };
+    double rx = R[7] - R[5], ry = R[2] - R[6], rz = R[3] - R[1];
+    const double s = sqrt((rx * rx + ry * ry + rz * rz) * 0.25);
+    double cs = (R[0] + R[4] + R[8] - 1.) * 0.5;
+    cs = cs > 1. ? 1. : (cs < -1. ? -1. : cs);
+    const double theta = acos(cs);
+    if (s < 1e-5) {
+        if (cs > 0.) { rvec[0] = rvec[1] = rvec[2] = 0.; return; }
+        double t;
+        t = (R[0] + 1.) * 0.5; rx = sqrt(t > 0. ? t : 0.);
+        t = (R[4] + 1.) * 0.5; ry = sqrt(t > 0. ? t : 0.) * (R[1] < 0. ? -1. : 1.);
+        t = (R[8] + 1.) * 0.5; rz = sqrt(t > 0. ? t : 0.) * (R[2] < 0. ? -1. : 1.);
+        if (fabs(rx) < fabs(ry) && fabs(rx) < fabs(rz) && (R[5] > 0.) != (ry * rz > 0.)) rz = -rz;
+        const double nn = theta / sqrt(rx * rx + ry * ry + rz * rz);
+        rvec[0] = rx * nn; rvec[1] = ry * nn; rvec[2] = rz * nn;
+    } else {
+        const double vth = 0.5 / s * theta;
+        rvec[0] = rx * vth; rvec[1] = ry * vth; rvec[2] = rz * vth;
+    }
+}
+
+// X: n x 3 float64, P: n x 2 float32 (host or device).  minimal_sets: H x 4 int32 (H >= max_iters)
+// or NULL = cv::RNG(2^64-1) emulation.  Outputs (all optional): T44 refined pose, Th12 the winning
+// unrefined hypothesis [R|t], rvec/tvec as cv2 returns them, inlier_mask n bytes, info[4] =
+// {iterations run, winning iteration, inlier count, LM iterations}.  Does not touch the state.
+int vo_solve_pnp_ransac(vo_ctx* c, const double* X, const float* P, int n, const double K[9],
+                        const vo_pnp_params* params, const int32_t* minimal_sets, double T44[16], double Th12[12],
+                        double rvec[3], double tvec[3], uint8_t* inlier_mask, int32_t info[4], int* ok)
+{
+    VO_NEED(c);
+    if (n < 0 || !K || (n > 0 && (!X || !P))) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    PnpLaunch L{};
+    if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
+    const size_t m = n > 0 ? n : 1;
+    VO_TRY(ensure(c, p->stage_d, m * 3)); VO_TRY(ensure(c, p->stage_f, m * 2));
+    VO_TRY(ensure(c, p->q4, m * 4)); VO_TRY(ensure(c, p->qv, m));
+    if (n > 0) {
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p, X, sizeof(double) * 3 * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_f.p, P, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
+    }
+    pack_points_kernel<<<(int)((m + 255) / 256), 256, 0, c->stream>>>(p->d_sc, p->stage_d.p, (const float2*)p->stage_f.p, n, 0,
+                                                                      (float4*)p->q4.p, p->qv.p);
+    c->launches++;
+    if (minimal_sets) {
+        const size_t H = L.prm.max_iters > 0 ? L.prm.max_iters : 1;
+        VO_TRY(ensure(c, p->stage_i, H * kMinimal));
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_i.p, minimal_sets, sizeof(int32_t) * kMinimal * H, cudaMemcpyDefault, c->stream));
+        L.d_sets_in = p->stage_i.p;
+    }
+    L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = nullptr; L.n_upper = n; L.compact = false;
+    memcpy(L.K, K, sizeof(L.K));
+    p->packed_valid = false;
+    VO_TRY(launch_pnp(c, L));
+    if (inlier_mask && n > 0) VO_CUDA(c, cudaMemcpyAsync(inlier_mask, p->mask.p, n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    const DevScalars* s = p->h_sc;
+    if (ok) *ok = s->ok;
+    if (T44) memcpy(T44, s->T, sizeof(double) * 16);
+    if (Th12) memcpy(Th12, s->Th, sizeof(double) * 12);
+    if (rvec) { if (s->ok) rotation_to_rvec(s->T, rvec); else rvec[0] = rvec[1] = rvec[2] = 0.; }
+    if (tvec) { tvec[0] = s->T[3]; tvec[1] = s->T[7]; tvec[2] = s->T[11]; }
+    if (info) { info[0] = s->iters_run; info[1] = s->best_hyp; info[2] = s->n_inliers; info[3] = s->lm_iters; }
+    return VO_OK;
+}
+
+// ---- unit level: cv2.triangulatePoints (vo_pipeline.py:666, :172) --------------------------------
+// M1: 3x4 row-major (per_point_m1 = 0) or n x 12 (one first-view matrix per point, as the
+// reference's loop uses K @ T[idx]); M2: 3x4; p1, p2: n x 2 float64; X4: n x 4 homogeneous, unit
+// norm, sign arbitrary (as OpenCV).  Host or device pointers.  Synchronises.
+int vo_triangulate_points(vo_ctx* c, const double* M1, const double* M2, int per_point_m1, const double* p1,
+                          const double* p2, int n, double* X4)
+{
+    VO_NEED(c);
+    if (n < 0 || (n > 0 && (!M1 || !M2 || !p1 || !p2 || !X4))) return VO_ERR_INVALID;
+    if (n == 0) return VO_OK;
+    Pipeline* p = c->pipe;
+    const size_t nm1 = per_point_m1 ? (size_t)n * 12 : 12;
+    VO_TRY(ensure(c, p->stage_d, nm1 + 12 + (size_t)n * 8));
+    double* dM1 = p->stage_d.p; double* dM2 = dM1 + nm1; double* dp1 = dM2 + 12; double* dp2 = dp1 + 2 * (size_t)n;
+    double* dX = dp2 + 2 * (size_t)n;
+    VO_CUDA(c, cudaMemcpyAsync(dM1, M1, sizeof(double) * nm1, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(dM2, M2, sizeof(double) * 12, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(dp1, p1, sizeof(double) * 2 * n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(dp2, p2, sizeof(double) * 2 * n, cudaMemcpyDefault, c->stream));
+    VO_TRY(launch_triangulate(c, dM1, dM2, per_point_m1, dp1, dp2, n, dX));
+    VO_CUDA(c, cudaMemcpyAsync(X4, dX, sizeof(double) * 4 * n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
+}  // extern "C"

@@ -406,7 +406,9 @@ __global__ void pnp_select_kernel(DevScalars* sc, int32_t* sets, const int32_t* 
     if (h >= niters || last) done = 1;
     if (lane == 0) {
         sc->niters = niters; sc->best_count = best; sc->best_hyp = best_hyp; sc->done = done;
-        sc->iters_run = min(min(h, h1), niters);
+        // iterations the sequential loop executes: it leaves at the first iter >= niters, and the
+        // budget may have dropped below the iteration that lowered it
+        sc->iters_run = h >= niters ? max(niters, best_hyp + 1) : h1;
         if (!done && !a.explicit_sets && next_end > sc->sets_ready) gen_sets(sc, sets, n, next_end);
     }
 }

@@ -18,9 +18,11 @@ namespace vo {
 namespace {
 
 constexpr int kScanThreads = 1024;
+constexpr int kPromoteThreads = 512;   // FP64 DLT needs > 64 registers per thread
 
 // block-wide exclusive rank of `flag` among the CTA's threads for the current tile; `base` is the
 // running total (shared), advanced by the tile's total.  All threads must call.
+template <int NT>
 __device__ __forceinline__ int tile_rank(bool flag, int* sWarp, int* sBase)
 {
     const int tid = threadIdx.x;
@@ -33,7 +35,7 @@ __device__ __forceinline__ int tile_rank(bool flag, int* sWarp, int* sBase)
     __syncthreads();
     if (tid == 0) {
         int s = 0;
-        for (int w = 0; w < kScanThreads / 32; w++) s += sWarp[w];
+        for (int w = 0; w < NT / 32; w++) s += sWarp[w];
         *sBase += s;
     }
     __syncthreads();
@@ -59,8 +61,8 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
         const bool in = i < n;
         const bool keep = in && status[i] != 0;
         if (in && iters) it += iters[i];
-        const int o = tile_rank(keep, sWarp, &sKeep);
-        const int ol = tile_rank(in && !keep, sWarp, &sLost);
+        const int o = tile_rank<kScanThreads>(keep, sWarp, &sKeep);
+        const int ol = tile_rank<kScanThreads>(in && !keep, sWarp, &sLost);
         if (keep) {
             const float2 p = klt_out[i];
             const double x = X_in[3 * (size_t)i], y = X_in[3 * (size_t)i + 1], z = X_in[3 * (size_t)i + 2];
@@ -164,13 +166,13 @@ struct PromoteArgs {
 // Single CTA.  Tracked candidates: C := new position (F too while C/F alias, App. B-5); lost rows
 // dropped; alpha(C,F) > threshold => triangulate with (T_first, T_new), append to P/X, drop from
 // C/F/T; the rest is compacted into the other candidate buffers.
-__global__ void __launch_bounds__(kScanThreads)
+__global__ void __launch_bounds__(kPromoteThreads)
 promote_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out, const uint8_t* __restrict__ status,
                const float2* __restrict__ C_in, const double2* __restrict__ F_in, const int32_t* __restrict__ Ti_in,
                float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
                const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap)
 {
-    __shared__ int sWarp[kScanThreads / 32];
+    __shared__ int sWarp[kPromoteThreads / 32];
     __shared__ int sStay, sProm, sKept;
     __shared__ double sM2[12];
     const int tid = threadIdx.x;
@@ -183,7 +185,7 @@ promote_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out
         k_times_pose(a.K, a.use_dev_T ? sc->T : a.Tnew, sM2);
     }
     __syncthreads();
-    for (int i0 = 0; i0 < n; i0 += kScanThreads) {
+    for (int i0 = 0; i0 < n; i0 += kPromoteThreads) {
         const int i = i0 + tid;
         const bool in = i < n;
         bool keep = in;
@@ -196,8 +198,8 @@ promote_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out
         }
         bool prom = false;
         if (keep && have_pose) prom = bearing_angle_deg((double)cpos.x, (double)cpos.y, f.x, f.y) > a.alpha_deg;
-        const int op = tile_rank(prom, sWarp, &sProm);
-        const int os = tile_rank(keep && !prom, sWarp, &sStay);
+        const int op = tile_rank<kPromoteThreads>(prom, sWarp, &sProm);
+        const int os = tile_rank<kPromoteThreads>(keep && !prom, sWarp, &sStay);
         if (keep && !prom) { C_out[os] = cpos; F_out[os] = f; Ti_out[os] = Ti_in[i]; }
         if (prom && n_land + op < land_cap) {
             double M1[12], Xh[4];
@@ -306,7 +308,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     VO_TRY(ensure(c, p->P[p->cur], need * 2, true));
     VO_TRY(ensure(c, p->X[p->cur], need * 3, true));
     const int land_cap = (int)(p->P[p->cur].cap / 2);
-    promote_kernel<<<1, kScanThreads, 0, c->stream>>>(
+    promote_kernel<<<1, kPromoteThreads, 0, c->stream>>>(
         p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
         (const double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, (float2*)p->C[p->ccur ^ 1].p,
         (double2*)p->F[p->ccur ^ 1].p, p->Ti[p->ccur ^ 1].p, p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p,
