@@ -126,6 +126,11 @@ int vo_set_state(vo_ctx* ctx, const float* P, const double* X, int n);
 /* Host mirror of state['P'], state['X'] (main.py:248 reads state['X'] every frame).  P/X may be
  * NULL to query n only.  Synchronises. */
 int vo_get_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
+/* Asynchronous pinned-host snapshot of P/X as they are now, readable after later calls have
+ * replaced them on the device (main.py:248 reads the previous frame's state['X'] after the next
+ * frame's associate/estimatePose).  vo_get_snapshot synchronises. */
+int vo_snapshot_state(vo_ctx* ctx);
+int vo_get_snapshot(vo_ctx* ctx, float* P, double* X, int cap, int* n);
 /* Load / read the candidate set (tests, checkpoint/resume).  cf_alias: reference quirk App. B-5. */
 int vo_set_candidates(vo_ctx* ctx, const float* C, const double* F, const double* T, int n, int cf_alias);
 int vo_get_candidates(vo_ctx* ctx, float* C, double* F, double* T, int cap, int* n);
@@ -152,6 +157,12 @@ int vo_pnp_ransac(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, d
 int vo_track_triangulate_promote(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const double K[9],
                                  const double T44[16], double alpha_deg, const vo_klt_params* params,
                                  int* n_promoted);
+/* Track C over (prev, next) now (vo_pipeline.py:501) - a no-op if vo_klt_track_landmarks already
+ * did for this frame pair - and read the pending result: previous / tracked positions and status
+ * (vo_pipeline.py:503-508; the 'shi-mask' detector masks the well-tracked previous positions,
+ * vo_pipeline.py:376-379, :568).  vo_get_candidate_tracks synchronises. */
+int vo_track_candidates(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params);
+int vo_get_candidate_tracks(vo_ctx* ctx, float* prev_pts, float* next_pts, uint8_t* status, int cap, int* n);
 /* a6 step 2 (vo_pipeline.py:564-591): append candidates C := F := pts (n x 2 float64), T := T44.
  * Call after vo_track_triangulate_promote (new rows have alpha = 0 and are never promoted in the
  * frame they arrive, so the order does not change results). */

@@ -70,6 +70,8 @@ SIGNATURES = {
                                             c_void_p, c_void_p, ctypes.POINTER(KltParams)]),
     "vo_set_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int]),
     "vo_get_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
+    "vo_snapshot_state": (c_int, [c_void_p]),
+    "vo_get_snapshot": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_set_candidates": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "vo_get_candidates": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_get_lost": (c_int, [c_void_p, c_void_p, c_int, _PI]),
@@ -78,6 +80,8 @@ SIGNATURES = {
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
     "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
     "vo_add_candidates": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vo_track_candidates": (c_int, [c_void_p, c_i64, c_i64, _PK]),
+    "vo_get_candidate_tracks": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_process_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64, c_i64, c_void_p, _PK, _PP,
                                  c_double, c_void_p, c_int, c_void_p, ctypes.POINTER(Counters)]),
     "vo_solve_pnp_ransac": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
@@ -248,6 +252,17 @@ class Context:
         self._check(self.lib.vo_get_state(self.h, _ptr(P), _ptr(X), n, ctypes.byref(m)))
         return P, X
 
+    def snapshot_state(self):
+        self._check(self.lib.vo_snapshot_state(self.h))
+
+    def get_snapshot(self):
+        n = c_int()
+        self._check(self.lib.vo_get_snapshot(self.h, None, None, 0, ctypes.byref(n)))
+        P = np.empty((n.value, 2), np.float32)
+        X = np.empty((n.value, 3), np.float64)
+        self._check(self.lib.vo_get_snapshot(self.h, _ptr(P), _ptr(X), n.value, ctypes.byref(n)))
+        return P, X
+
     def set_candidates(self, C, F, T, cf_alias=False):
         C = np.ascontiguousarray(C, np.float32).reshape(-1, 2)
         F = np.ascontiguousarray(F, np.float64).reshape(-1, 2)
@@ -301,6 +316,19 @@ class Context:
             self.h, prev_key, next_key, _ptr(K), _ptr(T44), float(alpha_deg),
             ctypes.byref(params) if params is not None else None, ctypes.byref(n) if sync else None))
         return n.value if sync else None
+
+    def track_candidates(self, prev_key, next_key, params=None):
+        self._check(self.lib.vo_track_candidates(self.h, prev_key, next_key,
+                                                 ctypes.byref(params) if params is not None else None))
+
+    def candidate_tracks(self):
+        n = c_int()
+        self._check(self.lib.vo_get_candidate_tracks(self.h, None, None, None, 0, ctypes.byref(n)))
+        a = np.empty((n.value, 2), np.float32)
+        b = np.empty((n.value, 2), np.float32)
+        st = np.empty(n.value, np.uint8)
+        self._check(self.lib.vo_get_candidate_tracks(self.h, _ptr(a), _ptr(b), _ptr(st), n.value, ctypes.byref(n)))
+        return a, b, st
 
     def add_candidates(self, pts, T44):
         pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)

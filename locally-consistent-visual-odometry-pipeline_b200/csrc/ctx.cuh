@@ -181,6 +181,9 @@ struct Pipeline {
     bool packed_valid = false;  // q4/qv hold the current landmarks (set by the post-KLT compaction)
     DevScalars* d_sc = nullptr;
     DevScalars* h_sc = nullptr;  // pinned mirror
+    // pinned snapshot of the landmarks before a tracking step (serves main.py:248)
+    float* h_snapP = nullptr; double* h_snapX = nullptr; DevScalars* h_snap_sc = nullptr;
+    size_t snap_cap = 0; int snap_rows = 0;
 };
 
 // ---- stage launchers implemented in the .cu files -------------------------------------------

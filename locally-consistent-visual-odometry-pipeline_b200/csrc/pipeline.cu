@@ -45,6 +45,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
     cudaFree(p->d_sc);
     cudaFreeHost(p->h_sc);
+    cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
     delete p;
     c->pipe = nullptr;
 }
@@ -144,6 +145,49 @@ int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
     return VO_OK;
 }
 
+
+// main.py:248 reads the PREVIOUS frame's state['X'] after the next frame's associate/estimatePose
+// have already replaced it on the device: keep an asynchronous pinned-host snapshot (64 KB at 2k
+// landmarks; the copy engine is idle at that point) that the stale dict can still be served from.
+int vo_snapshot_state(vo_ctx* c)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    const size_t n = p->n_land_upper > 0 ? p->n_land_upper : 1;
+    if (n > p->snap_cap) {
+        VO_CUDA(c, cudaStreamSynchronize(c->stream));
+        cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX);
+        p->h_snapP = nullptr; p->h_snapX = nullptr; p->snap_cap = 0;
+        size_t cap = 4096;
+        while (cap < n) cap *= 2;
+        VO_CUDA(c, cudaMallocHost((void**)&p->h_snapP, cap * 2 * sizeof(float)));
+        VO_CUDA(c, cudaMallocHost((void**)&p->h_snapX, cap * 3 * sizeof(double)));
+        p->snap_cap = cap;
+    }
+    if (!p->h_snap_sc) VO_CUDA(c, cudaMallocHost((void**)&p->h_snap_sc, sizeof(DevScalars)));
+    VO_CUDA(c, cudaMemcpyAsync(p->h_snap_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+    if (p->n_land_upper > 0) {
+        VO_CUDA(c, cudaMemcpyAsync(p->h_snapP, p->P[p->cur].p, sizeof(float) * 2 * p->n_land_upper, cudaMemcpyDeviceToHost, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->h_snapX, p->X[p->cur].p, sizeof(double) * 3 * p->n_land_upper, cudaMemcpyDeviceToHost, c->stream));
+    }
+    p->snap_rows = p->n_land_upper;
+    return VO_OK;
+}
+
+int vo_get_snapshot(vo_ctx* c, float* P, double* X, int cap, int* n)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    if (!p->h_snap_sc) return set_error(c, VO_ERR_STATE, "no snapshot taken");
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    int m = p->h_snap_sc->n_land;
+    if (m > p->snap_rows) m = p->snap_rows;
+    if (n) *n = m;
+    if (m > cap) return (P || X) ? set_error(c, VO_ERR_CAPACITY, "snapshot has %d rows, buffer %d", m, cap) : VO_OK;
+    if (P && m > 0) memcpy(P, p->h_snapP, sizeof(float) * 2 * m);
+    if (X && m > 0) memcpy(X, p->h_snapX, sizeof(double) * 3 * m);
+    return VO_OK;
+}
 
 // test / bootstrap hook: load a candidate set; T is n x 16 (4x4 row-major per candidate)
 int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* T, int n, int cf_alias)
@@ -279,6 +323,49 @@ int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
     return VO_OK;
 }
 
+// Tracks the candidates C over (prev, next) unless vo_klt_track_landmarks already did for this
+// frame pair; the result is consumed by vo_track_triangulate_promote.  (vo_pipeline.py:501)
+int vo_track_candidates(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    if (p->cand_tracked_valid && p->cand_tracked_prev == prev_key && p->cand_tracked_next == next_key) return VO_OK;
+    vo_klt_params prm;
+    if (params) prm = *params; else vo_klt_params_default(&prm);
+    FrameSlot* a = get_frame(c, prev_key);
+    FrameSlot* b = get_frame(c, next_key);
+    if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    const int nB = p->n_cand_upper;
+    const size_t tot = nB > 0 ? nB : 1;
+    VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
+    VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
+    VO_TRY(launch_klt(c, a->pyr, b->pyr, p->C[p->ccur].p, &p->d_sc->n_cand, nB, p->klt_out.p, p->klt_status.p,
+                      p->klt_err.p, p->klt_iters.p, prm));
+    p->klt_b_off = 0;
+    p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
+    return VO_OK;
+}
+
+// Host view of the pending candidate tracking (before vo_track_triangulate_promote consumes it):
+// previous positions, tracked positions, status - what vo_pipeline.py:503-508 computes; the
+// 'shi-mask' detector needs the well-tracked previous positions (vo_pipeline.py:568).  Synchronises.
+int vo_get_candidate_tracks(vo_ctx* c, float* prev_pts, float* next_pts, uint8_t* status, int cap, int* n)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    if (!p->cand_tracked_valid) return set_error(c, VO_ERR_STATE, "no pending candidate tracking");
+    const int off = p->klt_b_off;
+    VO_TRY(read_scalars(c));
+    const int m = p->h_sc->n_cand;
+    if (n) *n = m;
+    if (m > cap) return (prev_pts || next_pts || status) ? set_error(c, VO_ERR_CAPACITY, "%d candidates, buffer %d", m, cap) : VO_OK;
+    if (m > 0 && prev_pts) VO_CUDA(c, cudaMemcpyAsync(prev_pts, p->C[p->ccur].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && next_pts) VO_CUDA(c, cudaMemcpyAsync(next_pts, p->klt_out.p + 2 * (size_t)off, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && status) VO_CUDA(c, cudaMemcpyAsync(status, p->klt_status.p + off, m, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
+
 // ---- a6 (first half): track C, drop lost, bearing test, DLT, promote (vo_pipeline.py:489-545, 608-721)
 int vo_track_triangulate_promote(vo_ctx* c, int64_t prev_key, int64_t next_key, const double K[9], const double T44[16],
                                  double alpha_deg, const vo_klt_params* params, int* n_promoted)
@@ -288,20 +375,7 @@ int vo_track_triangulate_promote(vo_ctx* c, int64_t prev_key, int64_t next_key, 
     Pipeline* p = c->pipe;
     bool use_klt = true;
     if (prev_key == next_key && prev_key < 0) use_klt = false;   // promotion step only (tests)
-    if (use_klt && !(p->cand_tracked_valid && p->cand_tracked_prev == prev_key && p->cand_tracked_next == next_key)) {
-        vo_klt_params prm;
-        if (params) prm = *params; else vo_klt_params_default(&prm);
-        FrameSlot* a = get_frame(c, prev_key);
-        FrameSlot* b = get_frame(c, next_key);
-        if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
-        const int nB = p->n_cand_upper;
-        const size_t tot = nB > 0 ? nB : 1;
-        VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
-        VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
-        VO_TRY(launch_klt(c, a->pyr, b->pyr, p->C[p->ccur].p, &p->d_sc->n_cand, nB, p->klt_out.p, p->klt_status.p,
-                          p->klt_err.p, p->klt_iters.p, prm));
-        p->klt_b_off = 0;
-    }
+    if (use_klt) VO_TRY(vo_track_candidates(c, prev_key, next_key, params));
     p->cand_tracked_valid = false;
     VO_TRY(launch_promote(c, K, T44, alpha_deg, p->n_cand_upper, use_klt, p->klt_b_off));
     if (n_promoted) { VO_TRY(read_scalars(c)); *n_promoted = p->h_sc->n_promoted; }

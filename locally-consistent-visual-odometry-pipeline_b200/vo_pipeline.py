@@ -1,0 +1,571 @@
+"""Drop-in replacement for the reference's src/vo_pipeline.py (same module name, same class surface).
+
+Put this directory ahead of /root/reference/src on sys.path and the reference's src/main.py runs
+unchanged (`from vo_pipeline import *`, main.py:7): the three per-frame stages
+
+    KeypointsToLandmarksAssociator.associateKeypointsToLandmarks   (reference vo_pipeline.py:188-227)
+    PoseEstimator.estimatePose                                     (reference vo_pipeline.py:245-335)
+    LandmarkTriangulator.triangulate_landmark                      (reference vo_pipeline.py:470-750)
+
+run as hand-written sm_100a CUDA kernels behind the C-ABI of libvo_b200.so (include/vo_b200.h),
+with the Markov state P/X/C/F/T resident on the GPU.  The dicts handed back to main.py are lazy
+host mirrors: `state['X']` is copied from the device the first time it is read in a frame
+(main.py:248 reads it every frame).  Bootstrap (VOInitializer) and the candidate detectors
+(SIFT / Shi-Tomasi) are out of the hot path and stay on the CPU through cv2, as in the reference.
+
+There is no CPU fallback for the three stages: without a CUDA device the first call raises.
+
+Differences a caller can observe (DESIGN.md lists them with reasons):
+  - hypotheses of the PnP-RANSAC come from P3P (BASELINE.json north_star), not EPnP-5;
+  - row matching is by tracking status, not by the reference's element-wise np.isin (App. B-4);
+  - the per-frame debug prints of the reference are omitted unless config['debug'] is set.
+"""
+import os
+import sys
+import time
+from typing import Dict
+
+import numpy as np
+import yaml
+
+try:   # cv2 is needed only for bootstrap, detectors and the re-bootstrap fallback
+    import cv2
+except Exception:   # pragma: no cover - the hot path does not need it
+    cv2 = None
+try:   # the reference leaks `plt` through its star import; main.py imports its own
+    import matplotlib.pyplot as plt
+except Exception:   # pragma: no cover
+    plt = None
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+if __package__:
+    from . import _cabi
+else:   # imported as top-level `vo_pipeline` (the drop-in case): load the sibling binding by path
+    import importlib.util as _ilu
+    _pkg_name = "_vo_b200_pkg"
+    if _pkg_name not in sys.modules:
+        _spec = _ilu.spec_from_file_location(_pkg_name, os.path.join(_HERE, "__init__.py"),
+                                             submodule_search_locations=[_HERE])
+        _mod = _ilu.module_from_spec(_spec)
+        sys.modules[_pkg_name] = _mod
+        _spec.loader.exec_module(_mod)
+    _cabi = sys.modules[_pkg_name]._cabi
+
+# ---- configuration: same file, same keys, loaded at import from the CWD (reference vo_pipeline.py:11-17)
+config_path = 'config.yaml'
+
+
+def load_config(config_path):
+    with open(config_path, 'r') as file:
+        return yaml.safe_load(file)
+
+
+config = load_config('config.yaml')
+
+# optional keys of this implementation; an unmodified config.yaml reproduces the reference's settings
+_DEFAULTS = {
+    'pnp_max_iters': 100,        # cv2.solvePnPRansac default iterationsCount (never passed, vo:258-264)
+    'pnp_refine_iters': 20,
+    'klt_fb_check': False,       # the reference has no forward-backward check
+    'klt_fb_thresh': 1.0,
+    'emulate_cf_alias': True,    # reference quirk App. B-5 (first candidate batch: F follows C)
+    'device': 0,
+}
+
+
+def _cfg(key):
+    return config.get(key, _DEFAULTS[key]) if isinstance(config, dict) else _DEFAULTS[key]
+
+
+# ---- runtime: one vo_ctx per process ---------------------------------------------------------------
+class _Runtime:
+    def __init__(self, w, h):
+        self.ctx = _cabi.Context(device=int(_cfg('device')), max_w=max(w, 2048), max_h=max(h, 1024))
+        self.klt = _cabi.klt_defaults()
+        self.klt.fb_check = int(bool(_cfg('klt_fb_check')))
+        self.klt.fb_thresh = float(_cfg('klt_fb_thresh'))
+        self.frames = {}          # id(array) -> (key, strong ref, fingerprint)
+        self.next_key = 1
+        self.state_version = 0    # bumped whenever the device landmarks change
+        self.ext_version = 0      # bumped whenever the device candidates change
+        self.timers = {}
+        self.snap_id = 0
+
+    # frames arrive as host uint8 arrays; the same object is passed to several stages and then
+    # becomes the "old" frame of the next iteration (main.py:293), so upload + pyramid happen once
+    def frame_key(self, img):
+        if img.dtype != np.uint8 or img.ndim != 2:
+            raise ValueError("frames must be 2-D uint8 (cv2.IMREAD_GRAYSCALE) arrays")
+        if img.strides[1] != 1:
+            img = np.ascontiguousarray(img)
+        fp = (img.shape, img.ctypes.data, int(img[::max(1, img.shape[0] // 8), ::max(1, img.shape[1] // 16)].sum()))
+        ent = self.frames.get(id(img))
+        if ent is not None and ent[2] == fp and self.ctx.has_frame(ent[0]):
+            return ent[0]
+        key = self.next_key
+        self.next_key += 1
+        self.ctx.upload_frame(img, key)
+        self.frames[id(img)] = (key, img, fp)
+        if len(self.frames) > 3:   # the ctx keeps 4 pyramids; drop the oldest host references
+            for k in sorted(self.frames, key=lambda i: self.frames[i][0])[:-3]:
+                del self.frames[k]
+        return key
+
+
+_rt = None
+
+
+def _runtime(img=None):
+    global _rt
+    if _rt is None:
+        h, w = (img.shape if img is not None else (1024, 2048))
+        _rt = _Runtime(w, h)
+    return _rt
+
+
+def _reset_runtime():
+    """Drop the process-wide context (tests)."""
+    global _rt
+    if _rt is not None:
+        _rt.ctx.close()
+    _rt = None
+
+
+class DeviceState(dict):
+    """state {'P','X'} whose arrays live on the GPU; reading an item mirrors both to the host once."""
+
+    def __init__(self, rt, version):
+        super().__init__()
+        self._rt, self._version, self._dirty = rt, version, False
+
+    def _current(self):
+        return not self._dirty and self._rt is _rt and self._version == self._rt.state_version
+
+    def _load(self):
+        if not dict.__contains__(self, 'P'):
+            if self._current():
+                P, X = self._rt.ctx.get_state()
+            elif self._rt is _rt and getattr(self, '_snap', None) == self._rt.snap_id:
+                P, X = self._rt.ctx.get_snapshot()   # previous frame's state (main.py:248)
+            else:
+                raise RuntimeError("stale DeviceState: the device landmarks have moved on to a later frame")
+            dict.__setitem__(self, 'P', P)
+            dict.__setitem__(self, 'X', X)
+
+    def __getitem__(self, k):
+        if k in ('P', 'X'):
+            self._load()
+        return dict.__getitem__(self, k)
+
+    def __setitem__(self, k, v):
+        if k in ('P', 'X'):
+            self._load()
+            self._dirty = True     # the host copy is now the authority; the next stage re-uploads
+        dict.__setitem__(self, k, v)
+
+    def __contains__(self, k):
+        return k in ('P', 'X') or dict.__contains__(self, k)
+
+    def __len__(self):
+        return max(2, dict.__len__(self))
+
+    def __iter__(self):
+        self._load()
+        return dict.__iter__(self)
+
+    def keys(self):
+        self._load()
+        return dict.keys(self)
+
+    def items(self):
+        self._load()
+        return dict.items(self)
+
+    def values(self):
+        self._load()
+        return dict.values(self)
+
+    def get(self, k, d=None):
+        return self[k] if k in self else d
+
+    def _rebind(self, version):
+        dict.clear(self)
+        self._version, self._dirty = version, False
+
+
+class DeviceExtendedState(dict):
+    """extended_state {'C','F','T'} resident on the GPU, mirrored lazily like DeviceState."""
+
+    def __init__(self, rt, version):
+        super().__init__()
+        self._rt, self._version, self._dirty = rt, version, False
+
+    def _current(self):
+        return not self._dirty and self._rt is _rt and self._version == self._rt.ext_version
+
+    def _load(self):
+        if not dict.__contains__(self, 'C'):
+            if not self._current():
+                raise RuntimeError("stale DeviceExtendedState: the device candidates have moved on")
+            C, F, T = self._rt.ctx.get_candidates()
+            dict.__setitem__(self, 'C', C.astype(np.float64))
+            dict.__setitem__(self, 'F', F)
+            dict.__setitem__(self, 'T', T)
+
+    def __getitem__(self, k):
+        if k in ('C', 'F', 'T'):
+            self._load()
+        return dict.__getitem__(self, k)
+
+    def __setitem__(self, k, v):
+        if k in ('C', 'F', 'T'):
+            self._load()
+            self._dirty = True
+        dict.__setitem__(self, k, v)
+
+    def __contains__(self, k):
+        return k in ('C', 'F', 'T') or dict.__contains__(self, k)
+
+    def __len__(self):
+        return max(3, dict.__len__(self))
+
+    def __iter__(self):
+        self._load()
+        return dict.__iter__(self)
+
+    def keys(self):
+        self._load()
+        return dict.keys(self)
+
+    def items(self):
+        self._load()
+        return dict.items(self)
+
+    def _rebind(self, version):
+        dict.clear(self)
+        self._version, self._dirty = version, False
+
+
+def _sync_state_to_device(rt, state):
+    """Make the device landmarks equal to `state` (upload unless it already mirrors the device)."""
+    if isinstance(state, DeviceState) and state._current():
+        return
+    P = np.asarray(state['P'], np.float32).reshape(-1, 2)      # reference vo_pipeline.py:214
+    X = np.asarray(state['X'], np.float64).reshape(-1, 3)
+    rt.ctx.set_state(P, X)
+    rt.state_version += 1
+    if isinstance(state, DeviceState):
+        state._version, state._dirty = rt.state_version, False
+
+
+def _sync_ext_to_device(rt, ext):
+    if isinstance(ext, DeviceExtendedState) and ext._current():
+        return
+    C = np.asarray(ext['C'], np.float64).reshape(-1, 2)
+    F = np.asarray(ext['F'], np.float64).reshape(-1, 2)
+    T = np.asarray(ext['T'], np.float64).reshape(-1, 4, 4)
+    alias = bool(_cfg('emulate_cf_alias')) and len(C) > 0 and (ext['C'] is ext['F'])
+    rt.ctx.set_candidates(C.astype(np.float32), F, T, cf_alias=alias)
+    rt.ext_version += 1
+    if isinstance(ext, DeviceExtendedState):
+        ext._version, ext._dirty = rt.ext_version, False
+
+
+# ---- the reference's class surface --------------------------------------------------------------------
+class BestVision():
+    """State holder (reference vo_pipeline.py:20-38): K, previous_image, state{P,X}, extended_state{C,F,T}."""
+
+    def __init__(self, K: np.ndarray):
+        self.K = K
+        self.previous_image = np.ndarray
+        self.state = {'P': np.ndarray, 'X': np.ndarray}
+        self.extended_state = {'C': np.ndarray, 'F': np.ndarray, 'T': np.ndarray}
+
+
+class VOInitializer():
+    """Bootstrap from two frames (reference vo_pipeline.py:41-177).  Runs once per sequence (and in
+    the rare re-bootstrap of estimatePose), so it stays on the CPU through cv2 like the reference."""
+
+    def __init__(self, K):
+        self.K = K
+
+    @staticmethod
+    def _need_cv2():
+        if cv2 is None:
+            raise ImportError("VOInitializer / the candidate detectors need cv2 (CPU, out of the hot path)")
+
+    def getKeypointMatches(self, frame1: np.ndarray, frame2: np.ndarray):
+        """Detector from config['init_detector'] ('sift' | 'shi'), SIFT descriptors, brute-force 2-NN,
+        0.8 ratio test.  Returns matched pixel positions in frame1 and frame2."""
+        self._need_cv2()
+        sift = cv2.SIFT.create()
+        detector = config['init_detector']
+        if detector == 'shi':
+            shi = dict(maxCorners=600, qualityLevel=0.03, minDistance=10, mask=None, blockSize=3,
+                       gradientSize=3, useHarrisDetector=False, k=0.04)
+            kps = [[cv2.KeyPoint(x=float(c[0][0]), y=float(c[0][1]), size=20)
+                    for c in cv2.goodFeaturesToTrack(f, **shi)] for f in (frame1, frame2)]
+        elif detector == 'sift':
+            kps = [sift.detect(f, None) for f in (frame1, frame2)]
+        else:
+            raise ValueError("init_detector must be 'sift' or 'shi'")
+        if config['init_descriptor'] != 'sift':
+            raise ValueError("init_descriptor must be 'sift'")
+        (kps1, des1), (kps2, des2) = (sift.compute(f, k) for f, k in zip((frame1, frame2), kps))
+        pairs = cv2.BFMatcher.create(cv2.NORM_L2, crossCheck=False).knnMatch(des1, des2, k=2)
+        good = [m for m, n in pairs if m.distance < 0.8 * n.distance]
+        return (np.array([kps1[m.queryIdx].pt for m in good]), np.array([kps2[m.trainIdx].pt for m in good]))
+
+    def getPoseEstimate(self, kps_f1, kps_f2):
+        """5-point essential-matrix RANSAC + cheirality: 3x4 [R|t] of frame2 w.r.t. frame1, inlier mask."""
+        self._need_cv2()
+        E, mask = cv2.findEssentialMat(kps_f1, kps_f2, self.K, cv2.RANSAC, 0.999, 1.0, None)
+        _, R, t, _ = cv2.recoverPose(E, kps_f1, kps_f2, self.K, mask=mask)
+        return np.hstack((R, t)), mask
+
+    def get_2D_3D_landmarks_association(self, kps_1: np.ndarray, kps_2: np.ndarray, T_img1_img2: np.ndarray) -> Dict:
+        """Triangulate the matches; state['P'] is taken from frame 1 as in the reference (App. B-1).
+        The batched DLT runs on the GPU (same kernel as the per-frame promotion) when a device is there."""
+        m1 = self.K @ np.eye(3, 4)
+        m2 = self.K @ T_img1_img2
+        try:
+            XH = _runtime().ctx.triangulate_points(m1, m2, kps_1, kps_2)
+        except _cabi.VoError:
+            self._need_cv2()
+            XH = cv2.triangulatePoints(m1, m2, kps_1.T, kps_2.T).T
+        return {'X': XH[:, 0:3] / XH[:, 3:4], 'P': kps_1}
+
+
+class KeypointsToLandmarksAssociator():
+    def __init__(self, K, current_pose):
+        self.K = K
+        self.current_pose = current_pose     # stored and never used, as in the reference (App. B-11)
+
+    def associateKeypointsToLandmarks(self, old_frame: np.ndarray, new_frame: np.ndarray, state: dict):
+        """KLT of state['P'] from old_frame to new_frame; returns (new_state, points_tracking_lost)
+        with new_state = rows of P (new positions, float32) and X whose status is 1."""
+        rt = _runtime(new_frame)
+        k_old, k_new = rt.frame_key(old_frame), rt.frame_key(new_frame)
+        _sync_state_to_device(rt, state)
+        if not isinstance(state, DeviceState):
+            state['P'] = np.asarray(state['P']).astype(np.float32)   # reference side effect (vo:214)
+        elif not dict.__contains__(state, 'P'):
+            # the caller may still read this (now previous) state after the device has moved on
+            rt.ctx.snapshot_state()
+            rt.snap_id += 1
+            state._snap = rt.snap_id
+        rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt)
+        rt.state_version += 1
+        return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
+
+
+class _LazyLost:
+    """points_tracking_lost (only printed by main.py in debug mode): fetched on first use."""
+
+    def __init__(self, rt, version):
+        self._rt, self._version, self._a = rt, version, None
+
+    def _arr(self):
+        if self._a is None:
+            if self._rt.state_version != self._version:
+                raise RuntimeError("lost-track positions of an earlier frame are gone")
+            self._a = self._rt.ctx.get_lost()
+        return self._a
+
+    def __array__(self, dtype=None, copy=None):
+        return self._arr() if dtype is None else self._arr().astype(dtype)
+
+    def __len__(self):
+        return len(self._arr())
+
+    def __getitem__(self, i):
+        return self._arr()[i]
+
+    def __repr__(self):
+        return repr(self._arr())
+
+
+Associator = KeypointsToLandmarksAssociator
+KeypointsToLandmarksAssociation = KeypointsToLandmarksAssociator   # name used by the README / north_star
+
+
+class PoseEstimator():
+    def __init__(self, K):
+        self.K = K
+        self.REPOJ_THRESH = 2
+        self.CONFIDENCE = 0.99999
+        if config['find_new_candidates_method'] == 'sift-sift':
+            self.CONFIDENCE = config['sift_ransac_confidence']
+        if config['find_new_candidates_method'] == 'shi-mask':
+            self.CONFIDENCE = config['shi_ransac_confidence']
+        self.last = {}
+
+    def _params(self):
+        p = _cabi.pnp_defaults()
+        p.max_iters = int(_cfg('pnp_max_iters'))
+        p.confidence = float(self.CONFIDENCE)
+        p.reproj_thresh = float(self.REPOJ_THRESH)
+        p.refine_iters = int(_cfg('pnp_refine_iters'))
+        return p
+
+    def estimatePose(self, associations, img_idx) -> np.ndarray:
+        """PnP-RANSAC + LM refit over associations{'P','X'}; prunes associations to the inliers in
+        place and returns the 4x4 world->camera pose (host ndarray: main.py:239 inverts it)."""
+        rt = _runtime()
+        _sync_state_to_device(rt, associations)
+        ok, T, n_inl = rt.ctx.pnp_ransac(self.K, self._params())
+        self.last = {'ok': ok, 'n_inliers': n_inl}
+        if config.get('debug'):
+            print('len inliers', n_inl)
+        if not ok or n_inl < 4:
+            return self._rebootstrap(associations, img_idx)
+        rt.state_version += 1
+        if isinstance(associations, DeviceState):
+            associations._rebind(rt.state_version)
+        else:   # a plain dict was passed: prune it on the host too
+            P, X = rt.ctx.get_state()
+            associations['P'], associations['X'] = P, X
+        return T
+
+    def _rebootstrap(self, associations, img_idx):
+        """Fewer than 4 inliers: bootstrap again from frames img_idx and img_idx+4 read from disk,
+        append the new landmarks and retry (reference vo_pipeline.py:274-324).  CPU, rare."""
+        VOInitializer._need_cv2()
+        print('less than 4 inliers (or None)! re-bootstrapping at frame', img_idx)
+        init = VOInitializer(self.K)
+        ds = config['dataset']
+        if ds == 'kitti':
+            names = ['kitti-dataset/05/image_0/%06d.png' % i for i in (img_idx, img_idx + 4)]
+        elif ds == 'malaga':
+            d = 'malaga-urban-dataset-extract-07/malaga-urban-dataset-extract-07_rectified_800x600_Images'
+            left = sorted(f for f in os.listdir(d) if f.endswith('left.jpg'))
+            names = [os.path.join(d, left[i]) for i in (img_idx, img_idx + 4)]
+        elif ds == 'parking':
+            names = ['parking/images/img_%05d.png' % i for i in (img_idx, img_idx + 4)]
+        else:
+            raise ValueError("Invalid dataset selection")
+        cur, nxt = (cv2.imread(n, cv2.IMREAD_GRAYSCALE) for n in names)
+        k1, k2 = init.getKeypointMatches(cur, nxt)
+        T12, mask = init.getPoseEstimate(k1, k2)
+        mask = np.hstack(mask).astype(np.bool_)
+        fresh = init.get_2D_3D_landmarks_association(k1[mask, :], k2[mask, :], T12)
+        P = np.vstack((np.asarray(associations['P'], np.float64).reshape(-1, 2), fresh['P']))
+        X = np.vstack((np.asarray(associations['X'], np.float64).reshape(-1, 3), fresh['X']))
+        associations['P'], associations['X'] = P, X
+        return self.estimatePose(associations, img_idx)
+
+
+class LandmarkTriangulator():
+    """Detects new candidate keypoints, tracks the candidates from frame to frame and promotes them
+    to landmarks once the bearing angle between first and current observation exceeds a threshold
+    (reference vo_pipeline.py:337-750).  Constructed every frame by main.py:280: O(1), no allocation."""
+
+    def __init__(self, K, old_des):
+        self.K = K
+        self.old_des = old_des
+
+    # ---- candidate detectors: CPU / cv2, outside the timed hot path ----------
+    @staticmethod
+    def _pixel_mask(frame, keypoints_well_tracked):
+        mask = np.full(frame.shape[:2], 255, np.uint8)
+        pts = np.asarray(keypoints_well_tracked, np.float64).reshape(-1, 2)
+        if len(pts):
+            x = pts[:, 0].astype(np.int64)      # int() truncation toward zero, as the reference
+            y = pts[:, 1].astype(np.int64)
+            ok = (y >= 0) & (y < mask.shape[0]) & (x >= 0) & (x < mask.shape[1])
+            mask[y[ok], x[ok]] = 0
+        return mask
+
+    def find_new_candidates_shi(self, new_frame: np.ndarray, state: dict, keypoints_well_tracked):
+        """Shi-Tomasi corners (500, quality 0.03, min distance 10, block 4) outside the single pixels
+        of the well-tracked candidates (reference vo_pipeline.py:357-390)."""
+        VOInitializer._need_cv2()
+        mask = self._pixel_mask(new_frame, keypoints_well_tracked)
+        corners = cv2.goodFeaturesToTrack(new_frame, maxCorners=500, qualityLevel=0.03, minDistance=10, mask=mask,
+                                          blockSize=4, gradientSize=3, useHarrisDetector=False, k=0.04)
+        if corners is None:
+            return np.zeros((0, 2))
+        return corners.reshape(-1, 2).astype(np.float64)
+
+    def find_new_candidates_sift_mask(self, new_frame: np.ndarray, state: dict, keypoints_well_tracked):
+        """SIFT keypoints outside the masked pixels (reference vo_pipeline.py:392-425)."""
+        VOInitializer._need_cv2()
+        mask = self._pixel_mask(new_frame, keypoints_well_tracked)
+        kps = cv2.SIFT.create().detect(new_frame, mask=mask)
+        return np.array([kp.pt for kp in kps]).reshape(-1, 2)
+
+    def find_new_candidates_sift_sift(self, new_frame: np.ndarray, state: dict, extended_state: dict):
+        """SIFT keypoints of the new frame minus those whose descriptor matches self.old_des (ratio
+        0.8); returns (new_keypoints, descriptors) (reference vo_pipeline.py:427-467)."""
+        VOInitializer._need_cv2()
+        keypoints, cur_des = cv2.SIFT.create().detectAndCompute(new_frame, None)
+        pairs = cv2.BFMatcher.create(cv2.NORM_L2, crossCheck=False).knnMatch(self.old_des, cur_des, k=2)
+        good = [m for m, n in pairs if m.distance < 0.8 * n.distance]
+        old_keypoints = np.array([keypoints[m.trainIdx].pt for m in good])
+        keypoints = np.array([kp.pt for kp in keypoints])
+        keep = np.isin(keypoints, old_keypoints, invert=True).all(axis=1)   # element-wise, as the reference
+        return (keypoints[keep], cur_des)
+
+    # ---- the per-frame stage ---------------------------------------------------------------------------
+    def triangulate_landmark(self, old_frame: np.ndarray, new_frame: np.ndarray, state: dict, extended_state: dict,
+                             new_pose):
+        """Track C old->new, drop lost rows of C/F/T, add the new candidates (F := C, T := new_pose),
+        promote every candidate whose bearing angle alpha(C, F) exceeds the threshold: triangulate it
+        with (T, new_pose), append it to state P/X and remove it from C/F/T.
+        Returns (state, extended_state, cur_des)."""
+        rt = _runtime(new_frame)
+        k_old, k_new = rt.frame_key(old_frame), rt.frame_key(new_frame)
+        _sync_state_to_device(rt, state)
+        if not isinstance(extended_state, DeviceExtendedState) and len(np.asarray(extended_state['C'])) == 0:
+            extended_state = {'C': np.zeros((0, 2)), 'F': np.zeros((0, 2)), 'T': np.zeros((0, 4, 4))}   # main.py:185-188
+        _sync_ext_to_device(rt, extended_state)
+        method = config['find_new_candidates_method']
+        threshold = 1
+        if method == 'sift-sift':
+            threshold = config['sift_alpha']
+        if method == 'shi-mask':
+            threshold = config['shi_alpha']
+        new_pose = np.ascontiguousarray(new_pose, np.float64)
+
+        # 1) + 3) on the device: candidate KLT (already done with the landmarks' launch when the same
+        # frame pair went through associateKeypointsToLandmarks), removal, bearing test, DLT, promotion
+        rt.ctx.track_candidates(k_old, k_new, rt.klt)
+        well_tracked_prev = []
+        if method in ('shi-mask', 'sift-mask'):
+            prev, _, st = rt.ctx.candidate_tracks()          # the detectors mask these pixels
+            well_tracked_prev = prev[st == 1]
+        rt.ctx.track_triangulate_promote(k_old, k_new, self.K, new_pose, float(threshold), rt.klt)
+
+        # 2) new candidates: CPU detectors run while the GPU works on the promotion
+        new_candidates_list, cur_des = [], []
+        if method == 'shi-mask':
+            new_candidates_list = self.find_new_candidates_shi(new_frame, state, well_tracked_prev)
+        elif method == 'sift-mask':
+            new_candidates_list = self.find_new_candidates_sift_mask(new_frame, state, well_tracked_prev)
+        elif method == 'sift-sift':
+            new_candidates_list, cur_des = self.find_new_candidates_sift_sift(new_frame, state, extended_state)
+        elif method == 'feed':   # pre-generated candidate feed (benchmarks / tests)
+            new_candidates_list = _candidate_feed.pop(0) if _candidate_feed else []
+        if len(new_candidates_list) > 0:
+            rt.ctx.add_candidates(np.asarray(new_candidates_list, np.float64), np.eye(4) @ new_pose)
+
+        rt.state_version += 1
+        rt.ext_version += 1
+        if isinstance(state, DeviceState):
+            state._rebind(rt.state_version)
+        else:
+            state = DeviceState(rt, rt.state_version)
+        if isinstance(extended_state, DeviceExtendedState):
+            extended_state._rebind(rt.ext_version)
+        else:
+            extended_state = DeviceExtendedState(rt, rt.ext_version)
+        return (state, extended_state, cur_des)
+
+
+# candidate feed for find_new_candidates_method == 'feed': a list of (n x 2) arrays, one per frame
+_candidate_feed = []
+
+
+def set_candidate_feed(feed):
+    """Per-frame candidate positions used when config['find_new_candidates_method'] == 'feed'."""
+    _candidate_feed[:] = list(feed)

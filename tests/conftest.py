@@ -33,3 +33,36 @@ def ctx(pkg):
     c = pkg.Context(device=0, max_w=2048, max_h=1024)
     yield c
     c.close()
+
+
+CONFIG_YAML = """dataset: 'kitti'
+find_new_candidates_method: '%s'
+init_detector: 'sift'
+init_descriptor: 'sift'
+debug: False
+visualization: False
+animation: False
+sift_alpha: 1
+sift_ransac_confidence: 0.99999
+shi_alpha: 1.5
+shi_ransac_confidence: 0.999993
+"""
+
+
+@pytest.fixture(scope="session")
+def scene_mod():
+    return importlib.import_module(PKG_NAME + ".scene")
+
+
+@pytest.fixture()
+def dropin(tmp_path, monkeypatch):
+    """The drop-in module imported the way main.py does it: as top-level `vo_pipeline`, with the
+    package directory ahead on sys.path and config.yaml in the CWD (method 'feed' = candidate feed)."""
+    (tmp_path / "config.yaml").write_text(CONFIG_YAML % "feed")
+    monkeypatch.chdir(tmp_path)
+    monkeypatch.syspath_prepend(os.path.join(ROOT, PKG_NAME))
+    sys.modules.pop("vo_pipeline", None)
+    mod = importlib.import_module("vo_pipeline")
+    yield mod
+    mod._reset_runtime()
+    sys.modules.pop("vo_pipeline", None)

@@ -14,6 +14,7 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(HERE))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 import cv2  # noqa: E402
 import synth  # noqa: E402
 
@@ -107,8 +108,101 @@ def tri():
     np.savez_compressed(os.path.join(HERE, "tri.npz"), **out)
 
 
+SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, n_feed, seed)
+    "kitti_half": ("kitti", 0.5, 36, 600, 80, 3),
+    "parking_half": ("parking", 0.5, 24, 300, 60, 4),
+}
+
+
+def _import_reference(workdir, method="sift-sift"):
+    """Import the reference's own src/vo_pipeline.py (config.yaml in CWD, matplotlib stubbed)."""
+    import importlib
+    for name in ("matplotlib", "matplotlib.pyplot"):
+        if name not in sys.modules:
+            m = types.ModuleType(name)
+            m.__getattr__ = lambda k: (lambda *a, **kw: None)
+            sys.modules[name] = m
+    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    os.makedirs(workdir, exist_ok=True)
+    with open(os.path.join(workdir, "config.yaml"), "w") as f:
+        f.write("dataset: 'kitti'\nfind_new_candidates_method: '%s'\ninit_detector: 'sift'\n"
+                "init_descriptor: 'sift'\ndebug: False\nvisualization: False\nanimation: False\n"
+                "sift_alpha: 1\nsift_ransac_confidence: 0.99999\nshi_alpha: 1.5\nshi_ransac_confidence: 0.999993\n" % method)
+    cwd = os.getcwd()
+    os.chdir(workdir)
+    sys.path.insert(0, "/root/reference/src")
+    try:
+        sys.modules.pop("vo_pipeline", None)
+        ref = importlib.import_module("vo_pipeline")
+    finally:
+        sys.path.remove("/root/reference/src")
+        os.chdir(cwd)
+    sys.modules.pop("vo_pipeline", None)
+    return ref
+
+
+def seq():
+    """The reference's OWN classes (imported from /root/reference/src) driven in main.py's order
+    (main.py:229-284) over synthetic sequences; the SIFT detector is replaced by the pre-generated
+    candidate feed (detectors are outside the hot path).  Two PnP variants are recorded:
+      literal - the reference as is (EPnP-5 hypotheses, <=100 iterations): the trajectory/ATE gate;
+      p3p     - cv2.solvePnPRansac patched to flags=SOLVEPNP_P3P + ITERATIVE refit on the inliers:
+                the primary parity oracle of SURVEY.md 8c (frame-by-frame state sizes and poses)."""
+    import contextlib
+    import importlib
+    import io
+    scene_mod = importlib.import_module("locally-consistent-visual-odometry-pipeline_b200.scene")
+    ref = _import_reference("/tmp/ref_golden_cwd")
+    real_ransac = cv2.solvePnPRansac
+
+    def p3p_ransac(X, P, K, dist, flags=None, confidence=0.99, reprojectionError=8.0, **kw):
+        ok, rv, tv, inl = real_ransac(X, P, K, dist, flags=cv2.SOLVEPNP_P3P, confidence=confidence,
+                                      reprojectionError=reprojectionError, iterationsCount=100)
+        if inl is not None and len(inl) >= 4:
+            idx = np.hstack(inl)
+            Xi = np.asarray(X, np.float64)[idx].astype(np.float32).astype(np.float64)
+            _, rv, tv = cv2.solvePnP(Xi, np.asarray(P, np.float64)[idx], K, dist, flags=cv2.SOLVEPNP_ITERATIVE)
+        return ok, rv, tv, inl
+
+    out = {"cv2_version": cv2.__version__}
+    for name, (shape, scale, nf, nt, nfeed, seed) in SEQ_CASES.items():
+        sq = scene_mod.Sequence(shape, n_frames=nf, n_tracks=nt, n_feed=nfeed, seed=seed, scale=scale)
+        out[name + "_checksum"] = sq.checksum()
+        for variant in ("literal", "p3p"):
+            ref.cv2.solvePnPRansac = p3p_ransac if variant == "p3p" else real_ransac
+            feeds = [f.copy() for f in sq.feeds]
+            ref.LandmarkTriangulator.find_new_candidates_sift_sift = lambda self, fr, st, ex: (feeds.pop(0), [])
+            state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+            ext = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+            assoc = ref.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+            pe = ref.PoseEstimator(sq.K)
+            feeds.pop(0)
+            Ts, nP, nC, nInl = [], [], [], []
+            with contextlib.redirect_stdout(io.StringIO()):
+                for k in range(1, nf):
+                    new_state, _ = assoc.associateKeypointsToLandmarks(sq.frames[k - 1], sq.frames[k], state)
+                    T = pe.estimatePose(new_state, k)
+                    nInl.append(len(new_state["P"]))
+                    tri = ref.LandmarkTriangulator(sq.K, None)
+                    state, ext, _ = tri.triangulate_landmark(sq.frames[k - 1], sq.frames[k], new_state, ext, T)
+                    Ts.append(T); nP.append(len(state["P"])); nC.append(len(ext["C"]))
+            out["%s_%s_T" % (name, variant)] = np.array(Ts)
+            out["%s_%s_nP" % (name, variant)] = np.array(nP)
+            out["%s_%s_nC" % (name, variant)] = np.array(nC)
+            out["%s_%s_nInl" % (name, variant)] = np.array(nInl)
+            if variant == "p3p":
+                out[name + "_p3p_P_last"] = np.asarray(state["P"], np.float64)
+                out[name + "_p3p_X_last"] = np.asarray(state["X"], np.float64)
+                out[name + "_p3p_C_last"] = np.asarray(ext["C"], np.float64)
+            gt = sq.poses[1:]
+            print(name, variant, "ATE %.4f m over %.1f m" % (scene_mod.ate(Ts, gt), sq.scene.step * (nf - 1)),
+                  "nP", nP[0], nP[-1], "nC", nC[0], nC[-1])
+        ref.cv2.solvePnPRansac = real_ransac
+    np.savez_compressed(os.path.join(HERE, "seq.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["klt", "pnp", "tri"]
+    which = sys.argv[1:] or ["klt", "pnp", "tri", "seq"]
     for w in which:
         globals()[w]()
     print("golden vectors written with cv2", cv2.__version__)
