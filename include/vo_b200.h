@@ -137,6 +137,7 @@ int vo_get_candidates(vo_ctx* ctx, float* C, double* F, double* T, int cap, int*
 /* points_tracking_lost of associateKeypointsToLandmarks (vo_pipeline.py:220-221). */
 int vo_get_lost(vo_ctx* ctx, float* lost, int cap, int* n);
 int vo_get_counters(vo_ctx* ctx, vo_counters* out);   /* synchronises */
+int vo_peek_counters(vo_ctx* ctx, vo_counters* out);  /* as of the last synchronising call; no sync */
 
 /* a1  KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227):
  * KLT of P from prev to next frame, keep status==1 rows of P and X.  The candidates C are tracked
@@ -174,6 +175,12 @@ int vo_add_candidates(vo_ctx* ctx, const double* pts, int n, const double T44[16
 int vo_process_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
                      const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
                      const double* new_candidates, int n_new, double T44[16], vo_counters* counters);
+
+/* Stage timers of vo_process_frame (CUDA events on the ctx stream; bench.py's roofline leg).
+ * ms[5] = {upload+pyramid, KLT, landmark compaction, PnP-RANSAC+LM, promotion+append} summed over
+ * `frames` frames since vo_set_profiling(ctx, 1). */
+int vo_set_profiling(vo_ctx* ctx, int enable);
+int vo_get_stage_times(vo_ctx* ctx, double ms[5], int* frames);
 
 /* ---- unit-level entry point mirroring cv2.solvePnPRansac (vo_pipeline.py:258-264) with P3P
  * hypotheses.  minimal_sets: max_iters x 4 int32 or NULL (cv::RNG(2^64-1) emulation = what cv2

@@ -76,6 +76,7 @@ SIGNATURES = {
     "vo_get_candidates": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_get_lost": (c_int, [c_void_p, c_void_p, c_int, _PI]),
     "vo_get_counters": (c_int, [c_void_p, ctypes.POINTER(Counters)]),
+    "vo_peek_counters": (c_int, [c_void_p, ctypes.POINTER(Counters)]),
     "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
     "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
@@ -84,6 +85,8 @@ SIGNATURES = {
     "vo_get_candidate_tracks": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_process_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64, c_i64, c_void_p, _PK, _PP,
                                  c_double, c_void_p, c_int, c_void_p, ctypes.POINTER(Counters)]),
+    "vo_set_profiling": (c_int, [c_void_p, c_int]),
+    "vo_get_stage_times": (c_int, [c_void_p, c_void_p, _PI]),
     "vo_solve_pnp_ransac": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _PI]),
     "vo_triangulate_points": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
@@ -287,9 +290,10 @@ class Context:
         self._check(self.lib.vo_get_lost(self.h, _ptr(lost), n.value, ctypes.byref(n)))
         return lost
 
-    def counters(self):
+    def counters(self, sync=True):
         cnt = Counters()
-        self._check(self.lib.vo_get_counters(self.h, ctypes.byref(cnt)))
+        fn = self.lib.vo_get_counters if sync else self.lib.vo_peek_counters
+        self._check(fn(self.h, ctypes.byref(cnt)))
         return cnt.as_dict()
 
     # ---- per-frame stages ------------------------------------------------------------------------
@@ -354,6 +358,16 @@ class Context:
             ctypes.byref(pnp) if pnp is not None else None, float(alpha_deg),
             _ptr(new_candidates) if nn else None, nn, _ptr(T), ctypes.byref(cnt) if cnt is not None else None))
         return T, (cnt.as_dict() if cnt is not None else None)
+
+    def set_profiling(self, enable):
+        self._check(self.lib.vo_set_profiling(self.h, int(enable)))
+
+    def stage_times(self):
+        ms = np.zeros(5)
+        n = c_int()
+        self._check(self.lib.vo_get_stage_times(self.h, _ptr(ms), ctypes.byref(n)))
+        names = ("upload_pyramid", "klt", "compact", "pnp", "promote")
+        return {k: float(v) / max(n.value, 1) for k, v in zip(names, ms)}, n.value
 
     # ---- unit-level: cv2.solvePnPRansac / cv2.triangulatePoints ------------------------------------
     def solve_pnp_ransac(self, X, P, K, params=None, sets=None):

@@ -184,6 +184,8 @@ struct Pipeline {
     // pinned snapshot of the landmarks before a tracking step (serves main.py:248)
     float* h_snapP = nullptr; double* h_snapX = nullptr; DevScalars* h_snap_sc = nullptr;
     size_t snap_cap = 0; int snap_rows = 0;
+    // optional stage timers (vo_set_profiling)
+    bool profiling = false; cudaEvent_t ev[6] = {}; double stage_ms[5] = {}; int stage_frames = 0;
 };
 
 // ---- stage launchers implemented in the .cu files -------------------------------------------

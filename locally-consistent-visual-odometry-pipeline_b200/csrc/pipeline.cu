@@ -45,6 +45,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
     cudaFree(p->d_sc);
     cudaFreeHost(p->h_sc);
+    for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
     delete p;
     c->pipe = nullptr;
@@ -156,7 +157,8 @@ int vo_snapshot_state(vo_ctx* c)
     const size_t n = p->n_land_upper > 0 ? p->n_land_upper : 1;
     if (n > p->snap_cap) {
         VO_CUDA(c, cudaStreamSynchronize(c->stream));
-        cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX);
+        for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
+    cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX);
         p->h_snapP = nullptr; p->h_snapX = nullptr; p->snap_cap = 0;
         size_t cap = 4096;
         while (cap < n) cap *= 2;
@@ -249,11 +251,11 @@ int vo_get_lost(vo_ctx* c, float* lost, int cap, int* n)
     return VO_OK;
 }
 
-int vo_get_counters(vo_ctx* c, vo_counters* out)
+static int fill_counters(vo_ctx* c, vo_counters* out, bool sync)
 {
     VO_NEED(c);
     if (!out) return VO_ERR_INVALID;
-    VO_TRY(read_scalars(c));
+    if (sync) VO_TRY(read_scalars(c));
     const DevScalars* s = c->pipe->h_sc;
     out->n_landmarks = s->n_land; out->n_candidates = s->n_cand; out->n_tracked = s->n_tracked; out->n_lost = s->n_lost;
     out->n_inliers = s->n_inliers; out->pnp_ok = s->ok; out->ransac_iters = s->iters_run; out->best_hypothesis = s->best_hyp;
@@ -261,6 +263,10 @@ int vo_get_counters(vo_ctx* c, vo_counters* out)
     out->cf_alias = s->cf_alias; out->klt_iters = s->klt_iters; out->reproj_cost = s->cost;
     return VO_OK;
 }
+
+int vo_get_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, true); }
+// values as of the last synchronising call (no device access)
+int vo_peek_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, false); }
 
 // ---- a1: KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227)
 int vo_klt_track_landmarks(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params, int* n_kept)
@@ -395,6 +401,7 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
     Pipeline* p = c->pipe;
     vo_klt_params kp;
     if (kparams) kp = *kparams; else vo_klt_params_default(&kp);
+    if (p->profiling) cudaEventRecord(p->ev[0], c->stream);
     if (img) VO_TRY(vo_upload_frame(c, img, w, h, pitch, next_key));
     FrameSlot* a = get_frame(c, prev_key);
     FrameSlot* b = get_frame(c, next_key);
@@ -403,7 +410,10 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
         VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
         VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
     }
+    const bool prof = p->profiling;
+    if (prof) cudaEventRecord(p->ev[1], c->stream);
     VO_TRY(track_both(c, a, b, kp, true));
+    if (prof) cudaEventRecord(p->ev[2], c->stream);
     VO_TRY(launch_landmark_compact(c, p->n_land_upper));
     p->packed_valid = true;
     PnpLaunch L{};
@@ -411,12 +421,22 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
     L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
     L.d_sets_in = nullptr; L.compact = true;
     memcpy(L.K, K, sizeof(L.K));
+    if (prof) cudaEventRecord(p->ev[3], c->stream);
     VO_TRY(launch_pnp(c, L));
+    if (prof) cudaEventRecord(p->ev[4], c->stream);
     VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
     if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
+    if (prof) cudaEventRecord(p->ev[5], c->stream);
     p->cand_tracked_valid = false;
     p->packed_valid = false;
     VO_TRY(read_scalars(c));
+    if (prof) {   // accumulate stage times (ms): upload+pyramid, KLT, compaction, PnP, promotion
+        for (int k = 0; k < 5; k++) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, p->ev[k], p->ev[k + 1]) == cudaSuccess) p->stage_ms[k] += ms;
+        }
+        p->stage_frames++;
+    }
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
     if (counters) {
         const DevScalars* s = p->h_sc;
@@ -426,6 +446,29 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
         counters->n_promoted = s->n_promoted; counters->n_candidates_lost = s->n_cand_lost; counters->cf_alias = s->cf_alias;
         counters->klt_iters = s->klt_iters; counters->reproj_cost = s->cost;
     }
+    return VO_OK;
+}
+
+// Stage timers of vo_process_frame (CUDA events on the ctx stream).  enable: 1 = on (resets the
+// accumulators), 0 = off.  vo_get_stage_times: ms summed over `frames` frames for the 5 stages
+// {upload+pyramid, KLT, landmark compaction, PnP-RANSAC+LM, promotion+append}.
+int vo_set_profiling(vo_ctx* c, int enable)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    if (enable && !p->ev[0]) for (int k = 0; k < 6; k++) VO_CUDA(c, cudaEventCreate(&p->ev[k]));
+    p->profiling = enable != 0;
+    for (int k = 0; k < 5; k++) p->stage_ms[k] = 0.;
+    p->stage_frames = 0;
+    return VO_OK;
+}
+
+int vo_get_stage_times(vo_ctx* c, double ms[5], int* frames)
+{
+    VO_NEED(c);
+    if (!ms) return VO_ERR_INVALID;
+    for (int k = 0; k < 5; k++) ms[k] = c->pipe->stage_ms[k];
+    if (frames) *frames = c->pipe->stage_frames;
     return VO_OK;
 }
 
