@@ -128,7 +128,7 @@ struct DevScalars {
     int32_t cf_alias;      // reference quirk App. B-5: C and F are the same ndarray
     int32_t cand_was_empty;// C was empty after the tracking/removal step (decides cf_alias on add)
     // RANSAC
-    uint64_t rng;          // cv::RNG state
+    uint64_t rng;          // position in the precomputed cv::RNG(2^64-1) output stream
     int32_t niters;        // current (shrinking) iteration budget
     int32_t best_count;
     int32_t best_hyp;      // -1: none
@@ -139,6 +139,8 @@ struct DevScalars {
     int32_t ok;
     int32_t lm_iters;
     int32_t klt_iters;     // sum of LK iterations (roofline accounting)
+    int32_t rng_exhausted; // the RNG draw table ran out (host reports VO_ERR_CAPACITY)
+    int32_t ticket;        // multi-CTA kernels: last-block-done counter (always 0 between kernels)
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -170,6 +172,10 @@ struct Pipeline {
     DevBuf<float> q4;       // n x 4: float32(X) and u
     DevBuf<float> qv;       // n: v
     DevBuf<int32_t> sets;   // H x 4
+    DevBuf<uint32_t> rng_tab; // raw 32-bit outputs of cv::RNG(2^64-1), in draw order
+    int rng_tab_len = 0;
+    DevBuf<int32_t> blk_counts; // per-CTA counts of the multi-CTA compactions (3 per CTA)
+    DevBuf<uint8_t> cand_flag;  // per candidate: 0 lost, 1 stays, 2 promoted
     DevBuf<double> hyp;     // H x 12 [R|t]
     DevBuf<int32_t> counts; // H (-1 = no model)
     DevBuf<uint8_t> mask;   // n

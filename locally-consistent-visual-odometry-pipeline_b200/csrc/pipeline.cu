@@ -43,6 +43,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->klt_status.p); cudaFree(p->klt_iters.p); cudaFree(p->lost.p); cudaFree(p->q4.p); cudaFree(p->qv.p);
     cudaFree(p->sets.p); cudaFree(p->hyp.p); cudaFree(p->counts.p); cudaFree(p->mask.p); cudaFree(p->promote.p);
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
+    cudaFree(p->rng_tab.p); cudaFree(p->blk_counts.p); cudaFree(p->cand_flag.p);
     cudaFree(p->d_sc);
     cudaFreeHost(p->h_sc);
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
@@ -59,6 +60,14 @@ static int read_scalars(Ctx* c)
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     p->n_land_upper = p->h_sc->n_land;
     p->n_cand_upper = p->h_sc->n_cand;
+    return VO_OK;
+}
+
+// the RNG draw table ran out during the last RANSAC (needs > 16 draws per iteration on average)
+static int check_rng(Ctx* c)
+{
+    if (c->pipe->h_sc->rng_exhausted)
+        return set_error(c, VO_ERR_CAPACITY, "cv::RNG draw table exhausted during RANSAC");
     return VO_OK;
 }
 
@@ -309,6 +318,7 @@ int vo_pnp_ransac(vo_ctx* c, const double K[9], const vo_pnp_params* params, dou
     VO_TRY(launch_pnp(c, L));
     p->packed_valid = false;
     VO_TRY(read_scalars(c));
+    VO_TRY(check_rng(c));
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
     if (n_inliers) *n_inliers = p->h_sc->n_inliers;
     if (ok) *ok = p->h_sc->ok;
@@ -430,6 +440,7 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
     p->cand_tracked_valid = false;
     p->packed_valid = false;
     VO_TRY(read_scalars(c));
+    VO_TRY(check_rng(c));
     if (prof) {   // accumulate stage times (ms): upload+pyramid, KLT, compaction, PnP, promotion
         for (int k = 0; k < 5; k++) {
             float ms = 0.f;
@@ -533,6 +544,7 @@ int vo_solve_pnp_ransac(vo_ctx* c, const double* X, const float* P, int n, const
     if (inlier_mask && n > 0) VO_CUDA(c, cudaMemcpyAsync(inlier_mask, p->mask.p, n, cudaMemcpyDefault, c->stream));
     VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    VO_TRY(check_rng(c));
     const DevScalars* s = p->h_sc;
     if (ok) *ok = s->ok;
     if (T44) memcpy(T44, s->T, sizeof(double) * 16);

@@ -38,32 +38,68 @@ struct PnpArgs {
 };
 
 // ---- cv::RNG -----------------------------------------------------------------------------------
-__device__ __forceinline__ unsigned rng_next(uint64_t& s)
-{
-    s = (uint64_t)(unsigned)s * 4164903690ULL + (unsigned)(s >> 32);
-    return (unsigned)s;
-}
+// cv::RNG is a multiply-with-carry generator: strictly sequential, but its raw 32-bit output
+// stream does not depend on the data (the seed is fixed at 2^64-1 inside RANSAC's run()).  The
+// host tabulates the stream once (rng_table_host); the device turns it into minimal sets with
+// `% n` and the duplicate re-draws of getSubset, 32 sets per step.
+struct RngTab { const uint32_t* tab; int len; };
 
-// rows [sc->sets_ready, to) of the minimal-set table, exactly as getSubset draws them
-__device__ void gen_sets(DevScalars* sc, int32_t* sets, int n, int to)
+// rows [sc->sets_ready, to) of the minimal-set table, exactly as getSubset draws them.
+// Called by one full warp.  Optimistic step: lane l assumes sets h..h+l-1 needed no re-draw and
+// reads draws pos+4l..pos+4l+3; the prefix of lanes for which that held is committed, the first
+// set with a duplicate is drawn serially by lane 0.
+__device__ void gen_sets_warp(DevScalars* sc, int32_t* sets, RngTab rt, int n, int to)
 {
-    uint64_t s = sc->rng;
-    for (int h = sc->sets_ready; h < to; h++) {
-        int idx[kMinimal];
-#pragma unroll
-        for (int i = 0; i < kMinimal; i++) {
-            for (;;) {
-                const int v = (int)(rng_next(s) % (unsigned)n);
-                bool dup = false;
-#pragma unroll
-                for (int j = 0; j < kMinimal; j++) dup |= (j < i) && idx[j] == v;
-                if (!dup) { idx[i] = v; break; }
-            }
+    const int lane = threadIdx.x & 31;
+    int h = sc->sets_ready;
+    long long pos = (long long)sc->rng;
+    int exhausted = 0;
+    while (h < to && !exhausted) {
+        const int cnt = min(32, to - h);
+        bool ok = false;
+        int4 v = make_int4(0, 0, 0, 0);
+        const long long p0 = pos + 4 * lane;
+        if (lane < cnt && p0 + 3 < rt.len) {
+            v.x = (int)(rt.tab[p0] % (unsigned)n);
+            v.y = (int)(rt.tab[p0 + 1] % (unsigned)n);
+            v.z = (int)(rt.tab[p0 + 2] % (unsigned)n);
+            v.w = (int)(rt.tab[p0 + 3] % (unsigned)n);
+            ok = v.y != v.x && v.z != v.x && v.z != v.y && v.w != v.x && v.w != v.y && v.w != v.z;
         }
-        reinterpret_cast<int4*>(sets)[h] = make_int4(idx[0], idx[1], idx[2], idx[3]);
+        const unsigned bad = __ballot_sync(0xffffffffu, lane < cnt && !ok);
+        const int good = bad ? __ffs(bad) - 1 : cnt;
+        if (lane < good) reinterpret_cast<int4*>(sets)[h + lane] = v;
+        h += good; pos += 4 * good;
+        if (good < cnt) {   // set h: serial draw with re-draws (or the table ran out)
+            long long np = pos;
+            int fail = 0;
+            if (lane == 0) {
+                int idx[kMinimal];
+#pragma unroll
+                for (int i = 0; i < kMinimal; i++) {
+                    for (;;) {
+                        if (np >= rt.len) { fail = 1; break; }
+                        const int x = (int)(rt.tab[np++] % (unsigned)n);
+                        bool dup = false;
+#pragma unroll
+                        for (int j = 0; j < kMinimal; j++) dup |= (j < i) && idx[j] == x;
+                        if (!dup) { idx[i] = x; break; }
+                    }
+                    if (fail) break;
+                }
+                if (!fail) reinterpret_cast<int4*>(sets)[h] = make_int4(idx[0], idx[1], idx[2], idx[3]);
+            }
+            exhausted = __shfl_sync(0xffffffffu, fail, 0);
+            pos = __shfl_sync(0xffffffffu, np, 0);
+            if (!exhausted) h++;
+        }
     }
-    sc->rng = s;
-    sc->sets_ready = to;
+    __syncwarp();
+    if (lane == 0) {
+        sc->rng = (uint64_t)pos;
+        sc->sets_ready = exhausted ? to : h;   // rows past h stay unset; rng_exhausted aborts the run
+        if (exhausted) sc->rng_exhausted = 1;
+    }
 }
 
 // RANSACUpdateNumIters
@@ -174,12 +210,121 @@ __device__ __forceinline__ float reproj_err2(const double* R, const double* t, c
     return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
 }
 
+// ---- 4-lane cooperative root isolation -----------------------------------------------------------
+// The serial chain of real_roots/p3p4 is what bounds a RANSAC chunk (every hypothesis CTA waits
+// for its pose), so one hypothesis is solved by a quad of lanes: the <=4 bracketing intervals of a
+// derivative level, and later the <=4 quartic roots, are independent and run one per lane.  The
+// arithmetic per interval / per root is the same as in the serial code (same expressions, same
+// order), so both give identical bits.
+template <int DEG>
+__device__ __forceinline__ double peval_t(const double* c, double x)
+{
+    double v = c[DEG];
+#pragma unroll
+    for (int i = DEG - 1; i >= 0; i--) v = v * x + c[i];
+    return v;
+}
+
+// d = coefficients of the derivative of c (degree DEG-1)
+template <int DEG>
+__device__ __forceinline__ double bracket_root_t(const double* c, const double* d, double lo, double hi, double flo)
+{
+    double x = 0.5 * (lo + hi);
+    for (int it = 0; it < 200; it++) {
+        const double f = peval_t<DEG>(c, x);
+        if (f == 0.) return x;
+        if ((f < 0.) == (flo < 0.)) lo = x; else hi = x;
+        const double df = peval_t<DEG - 1>(d, x);
+        double xn = df != 0. ? x - f / df : 0.5 * (lo + hi);
+        if (!(xn > lo && xn < hi)) xn = 0.5 * (lo + hi);
+        if (fabs(xn - x) <= 4e-16 * fabs(x) || hi - lo <= 4e-16 * fabs(x)) return xn;
+        x = xn;
+    }
+    return x;
+}
+
+__device__ __forceinline__ double sel4(int i, double a0, double a1, double a2, double a3)
+{
+    return i == 0 ? a0 : (i == 1 ? a1 : (i == 2 ? a2 : a3));
+}
+
+// one derivative level: lane q of the quad takes interval q of (lo, prev..., hi]; the roots found
+// are gathered back, ascending, into prev[0..return)
+template <int DEG>
+__device__ __forceinline__ int quad_level(const double* p, const double* dp, double lo, double hi, double* prev,
+                                          int nprev, int q, unsigned qmask)
+{
+    bool has = false;
+    double root = 0.;
+    if (q <= nprev) {
+        const double a = q == 0 ? lo : sel4(q - 1, prev[0], prev[1], prev[2], prev[3]);
+        const double b = q < nprev ? sel4(q, prev[0], prev[1], prev[2], prev[3]) : hi;
+        const double fa = peval_t<DEG>(p, a), fb = peval_t<DEG>(p, b);
+        if (b > a) {
+            if (fb == 0.) { has = true; root = b; }
+            else if (fa != 0. && (fa < 0.) != (fb < 0.)) { has = true; root = bracket_root_t<DEG>(p, dp, a, b, fa); }
+        }
+    }
+    int n = 0;
+#pragma unroll
+    for (int s = 0; s < 4; s++) {
+        const int hs = __shfl_sync(qmask, (int)has, s, 4);
+        const double rs = __shfl_sync(qmask, root, s, 4);
+        if (hs) {
+            if (n == 0) prev[0] = rs; else if (n == 1) prev[1] = rs; else if (n == 2) prev[2] = rs; else prev[3] = rs;
+            n++;
+        }
+    }
+    return n;
+}
+
+// real roots of the quartic c[0..4] in (lo, hi], ascending, by a quad of lanes (all 4 lanes get
+// the full result).  Same result as real_roots(c, 4, lo, hi, roots).
+__device__ int real_roots4_quad(const double* cin, double lo, double hi, double* roots, int q, unsigned qmask)
+{
+    double big = 0.;
+#pragma unroll
+    for (int i = 0; i <= 4; i++) big = fmax(big, fabs(cin[i]));
+    if (fabs(cin[4]) <= 1e-14 * big) {   // degenerate leading coefficient: rare, serial path on lane 0
+        int nv = 0;
+        double r[4] = { 0., 0., 0., 0. };
+        if (q == 0) nv = real_roots(cin, 4, lo, hi, r);
+        nv = __shfl_sync(qmask, nv, 0, 4);
+#pragma unroll
+        for (int i = 0; i < 4; i++) roots[i] = __shfl_sync(qmask, r[i], 0, 4);
+        return nv;
+    }
+    double d1[4], d2[3], d3[2];
+#pragma unroll
+    for (int i = 1; i <= 4; i++) d1[i - 1] = cin[i] * i;
+#pragma unroll
+    for (int i = 1; i <= 3; i++) d2[i - 1] = d1[i] * i;
+#pragma unroll
+    for (int i = 1; i <= 2; i++) d3[i - 1] = d2[i] * i;
+    double prev[4] = { 0., 0., 0., 0. };
+    int nprev = 0;
+    {
+        const double x = -d3[0] / d3[1];
+        if (x > lo && x <= hi) prev[nprev++] = x;
+    }
+    nprev = quad_level<2>(d2, d3, lo, hi, prev, nprev, q, qmask);
+    nprev = quad_level<3>(d1, d2, lo, hi, prev, nprev, q, qmask);
+    nprev = quad_level<4>(cin, d1, lo, hi, prev, nprev, q, qmask);
+#pragma unroll
+    for (int i = 0; i < 4; i++) roots[i] = prev[i];
+    return nprev;
+}
+
 // P3P (Grunert quartic; roots isolated by bracketing; distances polished by Gauss-Newton; exact
 // 3-point alignment).  X: 4 world points (rows), p: 4 pixel points.  Roots come from the first
-// three correspondences, the fourth picks the root with the smallest pixel error.  Rt = [R|t]
-// as 12 doubles (R row-major then t).
-__device__ bool p3p4(const double* X, const double* p, const double* K, double* Rt)
+// three correspondences, the fourth picks the root with the smallest pixel error.  Called by the
+// 4 lanes of a quad (q = lane in quad) with identical inputs; returns true on the ONE lane that
+// holds the selected solution in Rt = [R|t] (12 doubles: R row-major then t); *found is set on all
+// four lanes.
+__device__ bool p3p4_quad(const double* X, const double* p, const double* K, double* Rt, int q, unsigned qmask,
+                          bool* found_any)
 {
+    *found_any = false;
     double j[9];
 #pragma unroll
     for (int i = 0; i < 3; i++) {
@@ -207,8 +352,8 @@ __device__ bool p3p4(const double* X, const double* p, const double* K, double* 
         for (int i = 0; i < 3; i++) { XmInv[i] = bc[i] * id; XmInv[3 + i] = cA[i] * id; XmInv[6 + i] = ab[i] * id; }
     }
     // u = N(v)/D(v); quartic  N^2 - 2 cg N D + (1 - k W) D^2 = 0  in v = s3/s1
-    const double q = (a2 - c2) / b2, k = c2 / b2;
-    const double N[3] = { 1. + q, -2. * q * cb, q - 1. };
+    const double qq = (a2 - c2) / b2, k = c2 / b2;
+    const double N[3] = { 1. + qq, -2. * qq * cb, qq - 1. };
     const double D[2] = { 2. * cg, -2. * ca };
     const double W[3] = { 1., -2. * cb, 1. };
     double NN[5] = { 0, 0, 0, 0, 0 }, ND[4] = { 0, 0, 0, 0 }, DD[3] = { 0, 0, 0 }, G[3], GDD[5] = { 0, 0, 0, 0, 0 }, Q[5];
@@ -235,27 +380,29 @@ __device__ bool p3p4(const double* X, const double* p, const double* K, double* 
     for (int a = 0; a < 5; a++) { Q[a] = NN[a] + GDD[a] - (a < 4 ? 2. * cg * ND[a] : 0.); big = fmax(big, fabs(Q[a])); }
     if (!(big > 0.) || !isfinite(big)) return false;
     double vr[4];
-    const int nv = real_roots(Q, 4, 0., 1e6, vr);
+    const int nv = real_roots4_quad(Q, 0., 1e6, vr, q, qmask);
 
-    bool found = false;
-    double beste = 0.;
-    for (int r = 0; r < nv; r++) {
-        const double v = vr[r];
+    // lane q evaluates root q
+    bool mine = false;
+    double e = 0.;
+    do {
+        if (q >= nv) break;
+        const double v = sel4(q, vr[0], vr[1], vr[2], vr[3]);
         const double Wv = 1. + v * (v - 2. * cb);
-        if (!(Wv > 0.)) continue;
+        if (!(Wv > 0.)) break;
         const double Dv = D[0] + D[1] * v;
         double u;
         if (fabs(Dv) > 1e-9) {
             u = (N[0] + v * (N[1] + v * N[2])) / Dv;
         } else {
             const double cc = 1. - k * Wv, disc = cg * cg - cc;
-            if (!(disc >= 0.)) continue;
+            if (!(disc >= 0.)) break;
             const double sq = sqrt(disc), u0 = cg + sq, u1 = cg - sq;
             const double e0 = fabs(u0 * u0 + v * v - 2. * u0 * v * ca - (a2 / b2) * Wv);
             const double e1 = fabs(u1 * u1 + v * v - 2. * u1 * v * ca - (a2 / b2) * Wv);
             u = e0 <= e1 ? u0 : u1;
         }
-        if (!(u > 0.)) continue;
+        if (!(u > 0.)) break;
         double s1 = sqrt(b2 / Wv), s2 = u * s1, s3 = v * s1;
         for (int it = 0; it < 5; it++) {
             const double r12 = s1 * s1 + s2 * s2 - 2. * s1 * s2 * cg - c2;
@@ -272,7 +419,7 @@ __device__ bool p3p4(const double* X, const double* p, const double* K, double* 
             s1 -= ds1; s2 -= ds2; s3 -= ds3;
             if (fabs(ds1) + fabs(ds2) + fabs(ds3) <= 1e-15 * (s1 + s2 + s3)) break;
         }
-        if (!(s1 > 0. && s2 > 0. && s3 > 0.)) continue;
+        if (!(s1 > 0. && s2 > 0. && s3 > 0.)) break;
         double e12[3], e13[3], nY[3], Y1[3];
 #pragma unroll
         for (int i = 0; i < 3; i++) {
@@ -281,53 +428,61 @@ __device__ bool p3p4(const double* X, const double* p, const double* K, double* 
             e13[i] = Y1[i] - s3 * j[6 + i];
         }
         cross3(e12, e13, nY);
-        double Rc[12];
         bool fin = true;
 #pragma unroll
         for (int i = 0; i < 3; i++) {
 #pragma unroll
             for (int c = 0; c < 3; c++) {
-                Rc[3 * i + c] = e12[i] * XmInv[c] + e13[i] * XmInv[3 + c] + nY[i] * XmInv[6 + c];
-                fin &= isfinite(Rc[3 * i + c]);
+                Rt[3 * i + c] = e12[i] * XmInv[c] + e13[i] * XmInv[3 + c] + nY[i] * XmInv[6 + c];
+                fin &= isfinite(Rt[3 * i + c]);
             }
-            Rc[9 + i] = Y1[i] - (Rc[3 * i] * X1[0] + Rc[3 * i + 1] * X1[1] + Rc[3 * i + 2] * X1[2]);
+            Rt[9 + i] = Y1[i] - (Rt[3 * i] * X1[0] + Rt[3 * i + 1] * X1[1] + Rt[3 * i + 2] * X1[2]);
         }
-        if (!fin) continue;
+        if (!fin) break;
         // 4th point: pixel reprojection error (float64)
         const double* X4 = X + 9;
-        double x = Rc[0] * X4[0] + Rc[1] * X4[1] + Rc[2] * X4[2] + Rc[9];
-        double y = Rc[3] * X4[0] + Rc[4] * X4[1] + Rc[5] * X4[2] + Rc[10];
-        double z = Rc[6] * X4[0] + Rc[7] * X4[1] + Rc[8] * X4[2] + Rc[11];
+        double x = Rt[0] * X4[0] + Rt[1] * X4[1] + Rt[2] * X4[2] + Rt[9];
+        double y = Rt[3] * X4[0] + Rt[4] * X4[1] + Rt[5] * X4[2] + Rt[10];
+        double z = Rt[6] * X4[0] + Rt[7] * X4[1] + Rt[8] * X4[2] + Rt[11];
         z = z != 0. ? 1. / z : 1.;
         const double du = x * z * K[0] + K[2] - p[6], dv = y * z * K[4] + K[5] - p[7];
-        const double e = du * du + dv * dv;
-        if (!found || e < beste) {
-            found = true; beste = e;
+        e = du * du + dv * dv;
+        mine = true;
+    } while (false);
+    // the serial loop keeps the first root (ascending) with the strictly smallest error
+    int win = -1;
+    double beste = 0.;
 #pragma unroll
-            for (int i = 0; i < 12; i++) Rt[i] = Rc[i];
-        }
+    for (int s = 0; s < 4; s++) {
+        const int ms = __shfl_sync(qmask, (int)mine, s, 4);
+        const double es = __shfl_sync(qmask, e, s, 4);
+        if (ms && (win < 0 || es < beste)) { win = s; beste = es; }
     }
-    return found;
+    *found_any = win >= 0;
+    return win == q;
 }
 
 // ---- kernels -----------------------------------------------------------------------------------
-__global__ void pnp_init_kernel(DevScalars* sc, int32_t* sets, const int32_t* d_n, PnpArgs a, int chunk0_end)
+__global__ void pnp_init_kernel(DevScalars* sc, int32_t* sets, const int32_t* d_n, PnpArgs a, RngTab rt, int chunk0_end)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    // one warp
     const int n = d_n ? min(*d_n, a.n_upper) : a.n_upper;
-    sc->n_tracked = n;
-    sc->niters = a.max_iters; sc->best_count = 0; sc->best_hyp = -1; sc->iters_run = 0; sc->done = 0;
-    sc->sets_ready = 0; sc->rng = 0xFFFFFFFFFFFFFFFFULL; sc->ok = 0; sc->n_inliers = 0; sc->lm_iters = 0;
-    if (n < kMinimal || a.max_iters <= 0) { sc->niters = 0; sc->done = 1; return; }
-    if (n == kMinimal) {   // cv2: count == modelPoints -> one direct solve on all points
-        reinterpret_cast<int4*>(sets)[0] = make_int4(0, 1, 2, 3);
-        sc->niters = 1; sc->sets_ready = a.max_iters;
-        return;
+    __syncwarp();
+    if (threadIdx.x == 0) {
+        sc->n_tracked = n;
+        sc->niters = a.max_iters; sc->best_count = 0; sc->best_hyp = -1; sc->iters_run = 0; sc->done = 0;
+        sc->sets_ready = 0; sc->rng = 0; sc->ok = 0; sc->n_inliers = 0; sc->lm_iters = 0; sc->rng_exhausted = 0;
+        if (n < kMinimal || a.max_iters <= 0) { sc->niters = 0; sc->done = 1; }
+        else if (n == kMinimal) {   // cv2: count == modelPoints -> one direct solve on all points
+            reinterpret_cast<int4*>(sets)[0] = make_int4(0, 1, 2, 3);
+            sc->niters = 1; sc->sets_ready = a.max_iters;
+        }
     }
-    if (!a.explicit_sets) gen_sets(sc, sets, n, chunk0_end);
+    __syncwarp();
+    if (n > kMinimal && a.max_iters > 0 && !a.explicit_sets) gen_sets_warp(sc, sets, rt, n, chunk0_end);
 }
 
-// one CTA per hypothesis: thread 0 solves P3P, the CTA scores all points
+// one CTA per hypothesis: lanes 0-3 solve P3P, the CTA scores all points
 __global__ void __launch_bounds__(kHypThreads)
 pnp_hyp_kernel(const DevScalars* __restrict__ sc, const int32_t* __restrict__ sets, const float4* __restrict__ q4,
                const float* __restrict__ qv, double* __restrict__ hyp, int32_t* __restrict__ counts, PnpArgs a, int h0)
@@ -338,7 +493,7 @@ pnp_hyp_kernel(const DevScalars* __restrict__ sc, const int32_t* __restrict__ se
     __shared__ double sRt[12];
     __shared__ int sValid;
     __shared__ int sCount[kHypThreads / 32];
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 4) {   // a quad of lanes solves the minimal problem
         const int4 s = reinterpret_cast<const int4*>(sets)[h];
         const int idx[4] = { s.x, s.y, s.z, s.w };
         double X[12], p[8];
@@ -352,9 +507,10 @@ pnp_hyp_kernel(const DevScalars* __restrict__ sc, const int32_t* __restrict__ se
             p[2 * k] = q.w; p[2 * k + 1] = qv[i];
         }
         double Rt[12];
-        ok = ok && p3p4(X, p, a.K, Rt);
-        sValid = ok;
-        if (ok) {
+        bool found = false;
+        const bool winner = ok && p3p4_quad(X, p, a.K, Rt, threadIdx.x, 0xFu, &found);
+        if (threadIdx.x == 0) sValid = ok && found;
+        if (winner) {
 #pragma unroll
             for (int i = 0; i < 12; i++) { sRt[i] = Rt[i]; hyp[(size_t)h * 12 + i] = Rt[i]; }
         }
@@ -384,7 +540,7 @@ pnp_hyp_kernel(const DevScalars* __restrict__ sc, const int32_t* __restrict__ se
 
 // one warp: sequential RANSAC bookkeeping over the counts of hypotheses [h0, h1)
 __global__ void pnp_select_kernel(DevScalars* sc, int32_t* sets, const int32_t* __restrict__ counts, PnpArgs a,
-                                  int h0, int h1, int next_end, int last)
+                                  RngTab rt, int h0, int h1, int next_end, int last)
 {
     if (sc->done) return;
     const int lane = threadIdx.x;
@@ -409,8 +565,9 @@ __global__ void pnp_select_kernel(DevScalars* sc, int32_t* sets, const int32_t* 
         // iterations the sequential loop executes: it leaves at the first iter >= niters, and the
         // budget may have dropped below the iteration that lowered it
         sc->iters_run = h >= niters ? max(niters, best_hyp + 1) : h1;
-        if (!done && !a.explicit_sets && next_end > sc->sets_ready) gen_sets(sc, sets, n, next_end);
     }
+    __syncwarp();
+    if (!done && !a.explicit_sets && next_end > sc->sets_ready && n > kMinimal) gen_sets_warp(sc, sets, rt, n, next_end);
 }
 
 // Single CTA: inlier mask of the winner, LM refit on SE(3), pose output, optional pruning of the
@@ -646,6 +803,29 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
 
 }  // namespace
 
+// raw outputs of cv::RNG(2^64-1) in draw order; 16 draws per iteration + slack covers the re-draws
+// of getSubset with overwhelming margin (4 + O(1/n) are used); if it ever runs out the device sets
+// rng_exhausted and the host reports VO_ERR_CAPACITY
+static int ensure_rng_table(Ctx* c, int H)
+{
+    Pipeline* p = c->pipe;
+    const size_t need = (size_t)(H > 0 ? H : 1) * 16 + 1024;
+    if ((size_t)p->rng_tab_len >= need) return VO_OK;
+    size_t len = 1 << 16;
+    while (len < need) len *= 2;
+    std::vector<uint32_t> tab(len);
+    uint64_t s = 0xFFFFFFFFFFFFFFFFULL;
+    for (size_t i = 0; i < len; i++) {
+        s = (uint64_t)(unsigned)s * 4164903690ULL + (unsigned)(s >> 32);
+        tab[i] = (uint32_t)s;
+    }
+    VO_TRY(ensure(c, p->rng_tab, len));
+    VO_CUDA(c, cudaMemcpyAsync(p->rng_tab.p, tab.data(), len * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));   // `tab` is a local
+    p->rng_tab_len = (int)len;
+    return VO_OK;
+}
+
 int launch_pnp(Ctx* c, const PnpLaunch& L)
 {
     Pipeline* p = c->pipe;
@@ -667,9 +847,14 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         VO_TRY(ensure(c, p->sets, (size_t)(H > 0 ? H : 1) * kMinimal));
         sets = p->sets.p;
     }
+    RngTab rt{ nullptr, 0 };
+    if (!L.d_sets_in) {
+        VO_TRY(ensure_rng_table(c, H));
+        rt.tab = p->rng_tab.p; rt.len = p->rng_tab_len;
+    }
     // chunk boundaries: small first chunk (the adaptive stop usually ends inside it)
     int bounds[kPnpChunks + 1] = { 0, H < 128 ? H : 128, H < 512 ? H : 512, H };
-    pnp_init_kernel<<<1, 32, 0, c->stream>>>(p->d_sc, sets, L.d_n, a, bounds[1]);
+    pnp_init_kernel<<<1, 32, 0, c->stream>>>(p->d_sc, sets, L.d_n, a, rt, bounds[1]);
     c->launches++;
     for (int k = 0; k < kPnpChunks; k++) {
         const int h0 = bounds[k], h1 = bounds[k + 1];
@@ -677,7 +862,7 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         const bool last = (h1 == H);
         pnp_hyp_kernel<<<h1 - h0, kHypThreads, 0, c->stream>>>(p->d_sc, sets, (const float4*)L.q4, L.qv, p->hyp.p,
                                                                p->counts.p, a, h0);
-        pnp_select_kernel<<<1, 32, 0, c->stream>>>(p->d_sc, sets, p->counts.p, a, h0, h1,
+        pnp_select_kernel<<<1, 32, 0, c->stream>>>(p->d_sc, sets, p->counts.p, a, rt, h0, h1,
                                                    k + 2 <= kPnpChunks ? bounds[k + 2] : H, last ? 1 : 0);
         c->launches += 2;
     }

@@ -18,7 +18,6 @@ namespace vo {
 namespace {
 
 constexpr int kScanThreads = 1024;
-constexpr int kPromoteThreads = 512;   // FP64 DLT needs > 64 registers per thread
 
 // block-wide exclusive rank of `flag` among the CTA's threads for the current tile; `base` is the
 // running total (shared), advanced by the tile's total.  All threads must call.
@@ -163,64 +162,122 @@ struct PromoteArgs {
     int ncand_upper;
 };
 
-// Single CTA.  Tracked candidates: C := new position (F too while C/F alias, App. B-5); lost rows
-// dropped; alpha(C,F) > threshold => triangulate with (T_first, T_new), append to P/X, drop from
-// C/F/T; the rest is compacted into the other candidate buffers.
-__global__ void __launch_bounds__(kPromoteThreads)
-promote_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out, const uint8_t* __restrict__ status,
-               const float2* __restrict__ C_in, const double2* __restrict__ F_in, const int32_t* __restrict__ Ti_in,
-               float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
-               const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap)
+// Promotion step, two launches of ceil(n/256) CTAs (a single CTA was the longest serial piece of
+// the frame after RANSAC):
+//   cand_classify_kernel  per candidate: lost / stays / promoted (bearing test) + per-CTA counts
+//   cand_apply_kernel     per-CTA offsets from the counts (order-preserving), C := new position
+//                         (F too while C/F alias, App. B-5), DLT with (T_first, T_new) for the
+//                         promoted rows appended to P/X, the rest compacted into the other
+//                         candidate buffers; the last CTA to finish publishes the new sizes.
+constexpr int kCandThreads = 256;
+enum : uint8_t { kCandLost = 0, kCandStay = 1, kCandPromote = 2, kCandNone = 255 };
+
+struct CandRow { float2 c; double2 f; bool keep; };
+
+__device__ __forceinline__ CandRow load_cand(const PromoteArgs& a, bool alias, int i, const float2* __restrict__ klt_out,
+                                             const uint8_t* __restrict__ status, const float2* __restrict__ C_in,
+                                             const double2* __restrict__ F_in)
 {
-    __shared__ int sWarp[kPromoteThreads / 32];
-    __shared__ int sStay, sProm, sKept;
+    CandRow r;
+    r.keep = true;
+    if (a.use_klt) { r.keep = status[a.b_off + i] != 0; r.c = klt_out[a.b_off + i]; }
+    else r.c = C_in[i];
+    r.f = (alias && a.use_klt) ? make_double2((double)r.c.x, (double)r.c.y) : F_in[i];
+    return r;
+}
+
+__global__ void __launch_bounds__(kCandThreads)
+cand_classify_kernel(const DevScalars* __restrict__ sc, PromoteArgs a, const float2* __restrict__ klt_out,
+                     const uint8_t* __restrict__ status, const float2* __restrict__ C_in,
+                     const double2* __restrict__ F_in, uint8_t* __restrict__ flag, int32_t* __restrict__ blk_counts)
+{
+    const int n = min(sc->n_cand, a.ncand_upper);
+    const bool alias = sc->cf_alias != 0;
+    const bool have_pose = a.use_dev_T ? sc->ok != 0 : true;
+    const int i = blockIdx.x * kCandThreads + threadIdx.x;
+    uint8_t f = kCandNone;
+    if (i < n) {
+        const CandRow r = load_cand(a, alias, i, klt_out, status, C_in, F_in);
+        f = kCandLost;
+        if (r.keep) {
+            f = kCandStay;
+            if (have_pose && bearing_angle_deg((double)r.c.x, (double)r.c.y, r.f.x, r.f.y) > a.alpha_deg) f = kCandPromote;
+        }
+        flag[i] = f;
+    }
+    const int n_stay = __syncthreads_count(f == kCandStay);
+    const int n_prom = __syncthreads_count(f == kCandPromote);
+    if (threadIdx.x == 0) { blk_counts[2 * blockIdx.x] = n_stay; blk_counts[2 * blockIdx.x + 1] = n_prom; }
+}
+
+__global__ void __launch_bounds__(kCandThreads)
+cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out, const uint8_t* __restrict__ status,
+                  const float2* __restrict__ C_in, const double2* __restrict__ F_in, const int32_t* __restrict__ Ti_in,
+                  const uint8_t* __restrict__ flag, const int32_t* __restrict__ blk_counts,
+                  float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
+                  const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap)
+{
+    __shared__ int sWarpStay[kCandThreads / 32], sWarpProm[kCandThreads / 32];
+    __shared__ int sBaseStay, sBaseProm, sLast;
     __shared__ double sM2[12];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(sc->n_cand, a.ncand_upper);
     const int n_land = sc->n_land;
     const bool alias = sc->cf_alias != 0;
-    const bool have_pose = a.use_dev_T ? sc->ok != 0 : true;
-    if (tid == 0) {
-        sStay = 0; sProm = 0; sKept = 0;
+    if (warp == 0) {   // offsets of this CTA = counts of the CTAs before it
+        int st = 0, pr = 0;
+        for (int b = lane; b < (int)blockIdx.x; b += 32) { st += blk_counts[2 * b]; pr += blk_counts[2 * b + 1]; }
+        st = __reduce_add_sync(0xffffffffu, st);
+        pr = __reduce_add_sync(0xffffffffu, pr);
+        if (lane == 0) { sBaseStay = st; sBaseProm = pr; }
+    } else if (warp == 1 && lane == 0) {
         k_times_pose(a.K, a.use_dev_T ? sc->T : a.Tnew, sM2);
     }
+    const int i = blockIdx.x * kCandThreads + tid;
+    const uint8_t f = i < n ? flag[i] : (uint8_t)kCandNone;
+    const unsigned bs = __ballot_sync(0xffffffffu, f == kCandStay);
+    const unsigned bp = __ballot_sync(0xffffffffu, f == kCandPromote);
+    if (lane == 0) { sWarpStay[warp] = __popc(bs); sWarpProm[warp] = __popc(bp); }
     __syncthreads();
-    for (int i0 = 0; i0 < n; i0 += kPromoteThreads) {
-        const int i = i0 + tid;
-        const bool in = i < n;
-        bool keep = in;
-        float2 cpos = make_float2(0.f, 0.f);
-        double2 f = make_double2(0., 0.);
-        if (in) {
-            if (a.use_klt) { keep = status[a.b_off + i] != 0; cpos = klt_out[a.b_off + i]; }
-            else cpos = C_in[i];
-            f = (alias && a.use_klt) ? make_double2((double)cpos.x, (double)cpos.y) : F_in[i];
-        }
-        bool prom = false;
-        if (keep && have_pose) prom = bearing_angle_deg((double)cpos.x, (double)cpos.y, f.x, f.y) > a.alpha_deg;
-        const int op = tile_rank<kPromoteThreads>(prom, sWarp, &sProm);
-        const int os = tile_rank<kPromoteThreads>(keep && !prom, sWarp, &sStay);
-        if (keep && !prom) { C_out[os] = cpos; F_out[os] = f; Ti_out[os] = Ti_in[i]; }
-        if (prom && n_land + op < land_cap) {
+    int os = sBaseStay, op = sBaseProm;
+    for (int w = 0; w < warp; w++) { os += sWarpStay[w]; op += sWarpProm[w]; }
+    const unsigned below = (1u << lane) - 1;
+    os += __popc(bs & below); op += __popc(bp & below);
+    if (f == kCandStay || f == kCandPromote) {
+        const CandRow r = load_cand(a, alias, i, klt_out, status, C_in, F_in);
+        if (f == kCandStay) { C_out[os] = r.c; F_out[os] = r.f; Ti_out[os] = Ti_in[i]; }
+        else if (n_land + op < land_cap) {
             double M1[12], Xh[4];
             k_times_pose(a.K, poses + 16 * (size_t)Ti_in[i], M1);
-            dlt_point(M1, sM2, f.x, f.y, (double)cpos.x, (double)cpos.y, Xh);
+            dlt_point(M1, sM2, r.f.x, r.f.y, (double)r.c.x, (double)r.c.y, Xh);
             const int o = n_land + op;
-            P[o] = cpos;
+            P[o] = r.c;
             X[3 * (size_t)o] = Xh[0] / Xh[3]; X[3 * (size_t)o + 1] = Xh[1] / Xh[3]; X[3 * (size_t)o + 2] = Xh[2] / Xh[3];
         }
-        const unsigned kb = __ballot_sync(0xffffffffu, keep);
-        if ((tid & 31) == 0 && kb) atomicAdd(&sKept, __popc(kb));
     }
+    // the last CTA to get here publishes the sizes: every CTA has read the old ones by then
     __syncthreads();
     if (tid == 0) {
-        const int n_lost = n - sKept;
-        sc->n_cand = sStay;
-        sc->n_promoted = sProm;
-        sc->n_cand_lost = n_lost;
-        sc->n_land = min(n_land + sProm, land_cap);
-        sc->cand_was_empty = sKept == 0;                      // C empty after tracking/removal (vo:579)
-        sc->cf_alias = alias && n_lost == 0 && sProm == 0;    // np.delete re-allocates: aliasing ends
+        __threadfence();
+        sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!sLast) return;
+    if (warp == 0) {
+        int st = 0, pr = 0;
+        for (int b = lane; b < (int)gridDim.x; b += 32) { st += blk_counts[2 * b]; pr += blk_counts[2 * b + 1]; }
+        st = __reduce_add_sync(0xffffffffu, st);
+        pr = __reduce_add_sync(0xffffffffu, pr);
+        if (lane == 0) {
+            const int kept = st + pr, n_lost = n - kept;
+            sc->n_cand = st;
+            sc->n_promoted = pr;
+            sc->n_cand_lost = n_lost;
+            sc->n_land = min(n_land + pr, land_cap);
+            sc->cand_was_empty = kept == 0;                    // C empty after tracking/removal (vo:579)
+            sc->cf_alias = alias && n_lost == 0 && pr == 0;    // np.delete re-allocates: aliasing ends
+            sc->ticket = 0;
+        }
     }
 }
 
@@ -308,11 +365,18 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     VO_TRY(ensure(c, p->P[p->cur], need * 2, true));
     VO_TRY(ensure(c, p->X[p->cur], need * 3, true));
     const int land_cap = (int)(p->P[p->cur].cap / 2);
-    promote_kernel<<<1, kPromoteThreads, 0, c->stream>>>(
+    const int nb = ncand_upper > 0 ? (ncand_upper + kCandThreads - 1) / kCandThreads : 1;
+    VO_TRY(ensure(c, p->cand_flag, nc));
+    VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
+    cand_classify_kernel<<<nb, kCandThreads, 0, c->stream>>>(
         p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, (float2*)p->C[p->ccur ^ 1].p,
-        (double2*)p->F[p->ccur ^ 1].p, p->Ti[p->ccur ^ 1].p, p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p,
-        land_cap);
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p);
+    cand_apply_kernel<<<nb, kCandThreads, 0, c->stream>>>(
+        p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
+        (const double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, p->cand_flag.p, p->blk_counts.p,
+        (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p, p->Ti[p->ccur ^ 1].p, p->poses.p,
+        (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap);
+    c->launches++;
     c->launches++;
     p->ccur ^= 1;
     p->n_land_upper += ncand_upper;
