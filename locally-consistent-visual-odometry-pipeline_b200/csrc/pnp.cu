@@ -294,6 +294,15 @@ __device__ int real_roots4_quad(const double* cin, double lo, double hi, double*
         for (int i = 0; i < 4; i++) roots[i] = __shfl_sync(qmask, r[i], 0, 4);
         return nv;
     }
+    // Cauchy bound: every (complex) root, hence by Gauss-Lucas every critical point of every
+    // derivative, has modulus < 1 + max|c_i/c_4|.  Shrinking the search interval from 1e6 to the
+    // bound keeps the root set and saves the ~40 Newton steps a start at 5e5 spends coming down.
+    {
+        double m = 0.;
+#pragma unroll
+        for (int i = 0; i < 4; i++) m = fmax(m, fabs(cin[i]));
+        hi = fmin(hi, 1. + m / fabs(cin[4]));
+    }
     double d1[4], d2[3], d3[2];
 #pragma unroll
     for (int i = 1; i <= 4; i++) d1[i - 1] = cin[i] * i;
@@ -588,17 +597,40 @@ __device__ __forceinline__ void so3_exp(const double* w, double* R)
     R[6] = B * wx * wz - A * wy;        R[7] = B * wy * wz + A * wx;        R[8] = 1. - B * (wx * wx + wy * wy);
 }
 
-__device__ bool chol6_solve(double* A, double* b)
+// solves (L L^T) x = b for the SPD 6x6 A (lower triangle used), x returned in b.  Fully unrolled
+// (registers only); one rsqrt per column is the only special op on the dependent chain.
+__device__ __forceinline__ bool chol6_solve(double* A, double* b)
 {
-    for (int i = 0; i < 6; i++)
-        for (int j = 0; j <= i; j++) {
-            double s = A[6 * i + j];
-            for (int k = 0; k < j; k++) s -= A[6 * i + k] * A[6 * j + k];
-            if (i == j) { if (!(s > 0.)) return false; A[6 * i + i] = sqrt(s); }
-            else A[6 * i + j] = s / A[6 * j + j];
+    double inv[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) {
+        double s = A[6 * j + j];
+#pragma unroll
+        for (int k = 0; k < j; k++) s -= A[6 * j + k] * A[6 * j + k];
+        if (!(s > 0.)) return false;
+        inv[j] = rsqrt(s);
+#pragma unroll
+        for (int i = j + 1; i < 6; i++) {
+            double t = A[6 * i + j];
+#pragma unroll
+            for (int k = 0; k < j; k++) t -= A[6 * i + k] * A[6 * j + k];
+            A[6 * i + j] = t * inv[j];
         }
-    for (int i = 0; i < 6; i++) { double s = b[i]; for (int k = 0; k < i; k++) s -= A[6 * i + k] * b[k]; b[i] = s / A[6 * i + i]; }
-    for (int i = 5; i >= 0; i--) { double s = b[i]; for (int k = i + 1; k < 6; k++) s -= A[6 * k + i] * b[k]; b[i] = s / A[6 * i + i]; }
+    }
+#pragma unroll
+    for (int i = 0; i < 6; i++) {
+        double s = b[i];
+#pragma unroll
+        for (int k = 0; k < i; k++) s -= A[6 * i + k] * b[k];
+        b[i] = s * inv[i];
+    }
+#pragma unroll
+    for (int i = 5; i >= 0; i--) {
+        double s = b[i];
+#pragma unroll
+        for (int k = i + 1; k < 6; k++) s -= A[6 * k + i] * b[k];
+        b[i] = s * inv[i];
+    }
     return true;
 }
 
@@ -610,9 +642,9 @@ __device__ void lm_accumulate(const double* Rt, const double* K, const float4* _
                               const float* __restrict__ qv, const uint8_t* __restrict__ mask, int n,
                               double (*sPart)[kAcc], double* sAcc)
 {
-    double acc[kAcc];
+    double acc[32];   // kAcc used, padded to the warp width for the halving reduction
 #pragma unroll
-    for (int i = 0; i < kAcc; i++) acc[i] = 0.;
+    for (int i = 0; i < 32; i++) acc[i] = 0.;
     for (int i = threadIdx.x; i < n; i += kFinThreads) {
         if (!mask[i]) continue;
         const float4 q = q4[i];
@@ -638,18 +670,21 @@ __device__ void lm_accumulate(const double* Rt, const double* K, const float4* _
         for (int a = 0; a < 6; a++) acc[21 + a] += Ju[a] * ru + Jv[a] * rv;
         acc[27] += ru * ru + rv * rv;
     }
+    // warp reduction by recursive halving: after the 5 exchange steps lane L holds the warp total
+    // of element L (31 shuffles instead of 28 x 5)
+    const int lane = threadIdx.x & 31;
 #pragma unroll
-    for (int i = 0; i < kAcc; i++) {
-        double v = acc[i];
+    for (int off = 16; off >= 1; off >>= 1) {
+        const bool upper = (lane & off) != 0;
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        acc[i] = v;
+        for (int k = 0; k < off; k++) {
+            const double send = upper ? acc[k] : acc[k + off];
+            const double keep = upper ? acc[k + off] : acc[k];
+            acc[k] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+        }
     }
     __syncthreads();   // previous readers of sPart/sAcc are done
-    if ((threadIdx.x & 31) == 0) {
-#pragma unroll
-        for (int i = 0; i < kAcc; i++) sPart[threadIdx.x >> 5][i] = acc[i];
-    }
+    if (lane < kAcc) sPart[threadIdx.x >> 5][lane] = acc[0];
     __syncthreads();
     if (threadIdx.x < kAcc) {
         double s = 0.;
@@ -724,7 +759,9 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
                     double step = 0.;
                     for (int r = 0; r < 6; r++) step += d[r] * d[r];
                     sStep = step;
-                    sState = 0;
+                    // a step below 1e-11 (rad / scene units) cannot move the pose at the 1e-9 level:
+                    // converged, no trial evaluation needed
+                    sState = step < 1e-22 ? 1 : 0;
                 }
             }
             __syncthreads();
@@ -739,7 +776,7 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
                     for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
                     sCost = cn; sLambda = fmax(sLambda * 0.1, 1e-12);
                     sFails = 0; sIters++;
-                    sState = (sStep < 1e-24 || dec <= 1e-15 * cn) ? 1 : 0;   // 1 = converged
+                    sState = (sStep < 1e-22 || dec <= 1e-13 * cn) ? 1 : 0;   // 1 = converged
                 } else {
                     sLambda *= 10.;
                     if (++sFails >= 12) sState = 1;

@@ -94,30 +94,38 @@ __device__ void dlt_point(const double* M1, const double* M2, double x1, double 
 #pragma unroll
         for (int r = 0; r < 4; r++) V[r][c] = r == c ? 1. : 0.;
     }
+    // One rotation of columns (p,q).  The rotation angle costs one sqrt, one division and one rsqrt
+    // on the dependent chain; the two rotations of a step touch disjoint columns, so their chains
+    // overlap (round-robin ordering (0,1)(2,3) / (0,2)(1,3) / (0,3)(1,2)).  Converged when every
+    // pair is orthogonal to 1e-15 relative (a tighter bound sits below the rounding noise of the
+    // dot products and would spin until the sweep limit).
+#define VO_JACOBI_ROT(p, q)                                                                         \
+    {                                                                                               \
+        double app = 0., aqq = 0., apq = 0.;                                                        \
+        _Pragma("unroll") for (int r = 0; r < 4; r++) {                                             \
+            app += A[r][p] * A[r][p]; aqq += A[r][q] * A[r][q]; apq += A[r][p] * A[r][q];           \
+        }                                                                                           \
+        if (apq * apq > 1e-30 * (app * aqq)) {                                                      \
+            rotated = true;                                                                         \
+            const double d = aqq - app;                                                             \
+            const double t = (d >= 0. ? 2. : -2.) * apq / (fabs(d) + sqrt(d * d + 4. * apq * apq)); \
+            const double cs = rsqrt(1. + t * t), sn = cs * t;                                       \
+            _Pragma("unroll") for (int r = 0; r < 4; r++) {                                         \
+                const double ap = A[r][p], aq = A[r][q];                                            \
+                A[r][p] = cs * ap - sn * aq; A[r][q] = sn * ap + cs * aq;                           \
+                const double vp = V[r][p], vq = V[r][q];                                            \
+                V[r][p] = cs * vp - sn * vq; V[r][q] = sn * vp + cs * vq;                           \
+            }                                                                                       \
+        }                                                                                           \
+    }
     for (int sweep = 0; sweep < 30; sweep++) {
         bool rotated = false;
-#pragma unroll
-        for (int p = 0; p < 3; p++)
-#pragma unroll
-            for (int q = p + 1; q < 4; q++) {
-                double app = 0., aqq = 0., apq = 0.;
-#pragma unroll
-                for (int r = 0; r < 4; r++) { app += A[r][p] * A[r][p]; aqq += A[r][q] * A[r][q]; apq += A[r][p] * A[r][q]; }
-                if (fabs(apq) <= 1e-17 * sqrt(app * aqq) || apq == 0.) continue;
-                rotated = true;
-                const double zeta = (aqq - app) / (2. * apq);
-                const double t = (zeta >= 0. ? 1. : -1.) / (fabs(zeta) + sqrt(1. + zeta * zeta));
-                const double cs = 1. / sqrt(1. + t * t), sn = cs * t;
-#pragma unroll
-                for (int r = 0; r < 4; r++) {
-                    const double ap = A[r][p], aq = A[r][q];
-                    A[r][p] = cs * ap - sn * aq; A[r][q] = sn * ap + cs * aq;
-                    const double vp = V[r][p], vq = V[r][q];
-                    V[r][p] = cs * vp - sn * vq; V[r][q] = sn * vp + cs * vq;
-                }
-            }
+        VO_JACOBI_ROT(0, 1) VO_JACOBI_ROT(2, 3)
+        VO_JACOBI_ROT(0, 2) VO_JACOBI_ROT(1, 3)
+        VO_JACOBI_ROT(0, 3) VO_JACOBI_ROT(1, 2)
         if (!rotated) break;
     }
+#undef VO_JACOBI_ROT
     double bn = 0.;
     int best = 0;
 #pragma unroll
