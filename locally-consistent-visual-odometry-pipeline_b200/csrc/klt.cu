@@ -7,12 +7,14 @@
 // outside the image, float32 2x2 solve, both break rules, level-0-only status writes and the
 // post-loop error pass that can still clear status.
 //
-// Mapping: the 21x21 window (441 px) is spread flat over the 32 lanes (14 px per lane, 98 %
-// lane use).  The template window I and its derivatives stay in registers for the whole level;
-// only the moving window of the next image is gathered each Gauss-Newton step (4 u8 taps per
-// px, L1/L2 resident).  The per-step sums are exact: products fit int32 per lane and the
-// cross-lane sum is two REDUX.SUM instructions (16-bit split), so results do not depend on the
-// lane mapping or summation order.
+// Mapping: the 21x21 window is cut into 63 horizontal runs of 7 px (3 per row); lane l owns runs
+// l and l+32 (98 % lane use).  A run needs 8+8 bytes of the image (two rows), fetched as 3+3
+// aligned 32-bit words and re-aligned with funnel shifts, and its 7 bilinear values cost 14
+// DP2A (two 14-bit weights x two u8 taps per instruction) instead of 28 byte loads + 28 IMAD.
+// The template window I and its derivatives stay in registers for the whole level; only the
+// moving window of the next image is gathered each Gauss-Newton step (L1/L2 resident).  The
+// per-step sums are exact: products fit int32 per lane and the cross-lane sum is two REDUX.SUM
+// instructions (16-bit split), so results do not depend on the lane mapping or summation order.
 #include "ctx.cuh"
 
 namespace vo {
@@ -38,17 +40,68 @@ __device__ __forceinline__ Weights make_weights(float a, float b)
     w.w00 = __float2int_rn(__fmul_rn(__fmul_rn(na, nb), 16384.f));
     w.w01 = __float2int_rn(__fmul_rn(__fmul_rn(a, nb), 16384.f));
     w.w10 = __float2int_rn(__fmul_rn(__fmul_rn(na, b), 16384.f));
-    w.w11 = 16384 - w.w00 - w.w01 - w.w10;
+    w.w11 = 16384 - w.w00 - w.w01 - w.w10;   // may round to -1: weights are signed 16-bit halves
     return w;
 }
 
-__device__ __forceinline__ int bilerp_u8(const uint8_t* __restrict__ p, int stride, const Weights& w)
+// d = c + a.s16[0]*b.u8[0] + a.s16[1]*b.u8[1]   (lo)   /   ... b.u8[2], b.u8[3]   (hi)
+__device__ __forceinline__ int dp2a_lo(int a, unsigned b, int c)
 {
-    return p[0] * w.w00 + p[1] * w.w01 + p[stride] * w.w10 + p[stride + 1] * w.w11;
+    int d;
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi(int a, unsigned b, int c)
+{
+    int d;
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ int pack_w(int lo, int hi) { return (lo & 0xFFFF) | (hi << 16); }
+
+constexpr int kRun = 7;   // px per run
+
+// 8 consecutive bytes at an arbitrary address as two words (the third aligned word is read even
+// when p is aligned: every level row has >= 32 px of border + stride slack behind it)
+__device__ __forceinline__ void load8(const uint8_t* __restrict__ p, unsigned& W0, unsigned& W1)
+{
+    const unsigned* a = reinterpret_cast<const unsigned*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)3);
+    const unsigned sh = ((unsigned)reinterpret_cast<uintptr_t>(p) & 3u) * 8u;
+    const unsigned a0 = __ldg(a), a1 = __ldg(a + 1), a2 = __ldg(a + 2);
+    W0 = __funnelshift_r(a0, a1, sh);
+    W1 = __funnelshift_r(a1, a2, sh);
+}
+
+// acc[x] += wl * byte[x] + wr * byte[x+1] for the 7 px of a run (bytes 0..7 in W0:W1)
+__device__ __forceinline__ void row7(unsigned W0, unsigned W1, int wpair, int* acc)
+{
+    const unsigned S1 = __funnelshift_r(W0, W1, 8);   // bytes 1..4
+    const unsigned S5 = W1 >> 8;                      // bytes 5..7
+    acc[0] = dp2a_lo(wpair, W0, acc[0]);
+    acc[1] = dp2a_lo(wpair, S1, acc[1]);
+    acc[2] = dp2a_hi(wpair, W0, acc[2]);
+    acc[3] = dp2a_hi(wpair, S1, acc[3]);
+    acc[4] = dp2a_lo(wpair, W1, acc[4]);
+    acc[5] = dp2a_lo(wpair, S5, acc[5]);
+    acc[6] = dp2a_hi(wpair, W1, acc[6]);
+}
+
+// the 7 bilinear samples ((sum + 2^8) >> 9, 5 fractional bits) of the run starting at p
+__device__ __forceinline__ void sample_run(const uint8_t* __restrict__ p, int stride, int wtop, int wbot, int* v)
+{
+    unsigned T0, T1, B0, B1;
+    load8(p, T0, T1);
+    load8(p + stride, B0, B1);
+#pragma unroll
+    for (int x = 0; x < kRun; x++) v[x] = 1 << 8;
+    row7(T0, T1, wtop, v);
+    row7(B0, B1, wbot, v);
+#pragma unroll
+    for (int x = 0; x < kRun; x++) v[x] >>= 9;
 }
 
 template <int WIN>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32)
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
 klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const float2* __restrict__ ptsA,
                  const int32_t* __restrict__ nA_dev, const int nA_upper, const float2* __restrict__ ptsB,
                  const int32_t* __restrict__ nB_dev, const int nB_upper, const int b_off,
@@ -56,8 +109,10 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
                  int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
                  const double min_eig_thr)
 {
-    constexpr int NPX = WIN * WIN;
-    constexpr int K = (NPX + 31) / 32;
+    static_assert(WIN % kRun == 0, "window side must be a multiple of the run length");
+    constexpr int RPR = WIN / kRun;            // runs per row
+    constexpr int NRUNS = WIN * RPR;           // 63
+    constexpr int NR = (NRUNS + 31) / 32;      // runs per lane
     const int lane = threadIdx.x & 31;
     int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     // two track lists share one launch: landmarks (A) then candidates (B, written at b_off)
@@ -79,19 +134,21 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
     int st = 1, iters = 0;
     float err = 0.f;
 
-    // window-relative coordinates of this lane's pixels (the last slot may be past the window)
-    int wy[K], wx[K];
+    // window-relative origin of this lane's runs (a slot past the window recomputes the last run
+    // and is masked out of every sum)
+    int rrow[NR], rcol[NR];
+    bool rvalid[NR];
 #pragma unroll
-    for (int k = 0; k < K; k++) {
-        const int idx = lane + 32 * k;
-        const int c = idx < NPX ? idx : 0;
-        wy[k] = c / WIN;
-        wx[k] = c - wy[k] * WIN;
+    for (int r = 0; r < NR; r++) {
+        const int j = lane + 32 * r;
+        rvalid[r] = j < NRUNS;
+        const int jj = rvalid[r] ? j : NRUNS - 1;
+        rrow[r] = jj / RPR;
+        rcol[r] = (jj - rrow[r] * RPR) * kRun;
     }
-    const bool last_valid = (lane + 32 * (K - 1)) < NPX;
 
-    int Iw[K];       // template window, 5 fractional bits
-    short2 dIw[K];   // its derivatives
+    int Iw[NR][kRun];              // template window, 5 fractional bits
+    int dIx[NR][kRun], dIy[NR][kRun];   // its derivatives
 
     for (int level = top; level >= 0; level--) {
         const LevelDesc LI = I.lv[level];
@@ -112,18 +169,21 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
         const size_t base = (size_t)(iy + kPad) * stride + (ix + kPad);
         int a11 = 0, a12 = 0, a22 = 0;
 #pragma unroll
-        for (int k = 0; k < K; k++) {
-            const int off = wy[k] * stride + wx[k];
-            const uint8_t* s = LI.img + base + off;
+        for (int r = 0; r < NR; r++) {
+            const int off = rrow[r] * stride + rcol[r];
+            sample_run(LI.img + base + off, stride, pack_w(w.w00, w.w01), pack_w(w.w10, w.w11), Iw[r]);
             const short2* d = LI.deriv + base + off;
-            const int ival = (bilerp_u8(s, stride, w) + (1 << 8)) >> 9;
-            const short2 d00 = d[0], d01 = d[1], d10 = d[stride], d11 = d[stride + 1];
-            int ixv = (d00.x * w.w00 + d01.x * w.w01 + d10.x * w.w10 + d11.x * w.w11 + (1 << 13)) >> 14;
-            int iyv = (d00.y * w.w00 + d01.y * w.w01 + d10.y * w.w10 + d11.y * w.w11 + (1 << 13)) >> 14;
-            if (k == K - 1 && !last_valid) { ixv = 0; iyv = 0; }
-            Iw[k] = ival;
-            dIw[k] = make_short2((short)ixv, (short)iyv);
-            a11 += ixv * ixv; a12 += ixv * iyv; a22 += iyv * iyv;
+            short2 t = d[0], b = d[stride];
+#pragma unroll
+            for (int x = 0; x < kRun; x++) {
+                const short2 tn = d[x + 1], bn = d[stride + x + 1];
+                int ixv = (t.x * w.w00 + tn.x * w.w01 + b.x * w.w10 + bn.x * w.w11 + (1 << 13)) >> 14;
+                int iyv = (t.y * w.w00 + tn.y * w.w01 + b.y * w.w10 + bn.y * w.w11 + (1 << 13)) >> 14;
+                if (!rvalid[r]) { ixv = 0; iyv = 0; }
+                dIx[r][x] = ixv; dIy[r][x] = iyv;
+                a11 += ixv * ixv; a12 += ixv * iyv; a22 += iyv * iyv;
+                t = tn; b = bn;
+            }
         }
         const float FLT_SCALE = 1.f / (1 << 20);
         const float A11 = __fmul_rn(__ll2float_rn(warp_sum_i64(a11)), FLT_SCALE);
@@ -142,6 +202,9 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
         float qx = __fsub_rn(cx, half), qy = __fsub_rn(cy, half);  // nextPt (window top-left)
         float pdx = 0.f, pdy = 0.f;
         const int jstride = LJ.stride;
+        int joff[NR];
+#pragma unroll
+        for (int r = 0; r < NR; r++) joff[r] = rrow[r] * jstride + rcol[r];
         for (int j = 0; j < max_iters; j++) {
             const int jx = __float2int_rd(qx), jy = __float2int_rd(qy);
             if (jx < -WIN || jx >= LJ.w || jy < -WIN || jy >= LJ.h) {
@@ -150,13 +213,19 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
             }
             iters++;
             w = make_weights(__fsub_rn(qx, (float)jx), __fsub_rn(qy, (float)jy));
+            const int wtop = pack_w(w.w00, w.w01), wbot = pack_w(w.w10, w.w11);
             const uint8_t* jb = LJ.img + (size_t)(jy + kPad) * jstride + (jx + kPad);
             int b1 = 0, b2 = 0;
 #pragma unroll
-            for (int k = 0; k < K; k++) {
-                const int diff = ((bilerp_u8(jb + wy[k] * jstride + wx[k], jstride, w) + (1 << 8)) >> 9) - Iw[k];
-                b1 += diff * dIw[k].x;
-                b2 += diff * dIw[k].y;
+            for (int r = 0; r < NR; r++) {
+                int v[kRun];
+                sample_run(jb + joff[r], jstride, wtop, wbot, v);
+#pragma unroll
+                for (int x = 0; x < kRun; x++) {
+                    const int diff = v[x] - Iw[r][x];
+                    b1 += diff * dIx[r][x];
+                    b2 += diff * dIy[r][x];
+                }
             }
             const float fb1 = __fmul_rn(__ll2float_rn(warp_sum_i64(b1)), FLT_SCALE);
             const float fb2 = __fmul_rn(__ll2float_rn(warp_sum_i64(b2)), FLT_SCALE);
@@ -183,9 +252,13 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
                 const uint8_t* jb = LJ.img + (size_t)(jy + kPad) * jstride + (jx + kPad);
                 int e = 0;
 #pragma unroll
-                for (int k = 0; k < K; k++) {
-                    const int diff = ((bilerp_u8(jb + wy[k] * jstride + wx[k], jstride, w) + (1 << 8)) >> 9) - Iw[k];
-                    if (k < K - 1 || last_valid) e += abs(diff);
+                for (int r = 0; r < NR; r++) {
+                    int v[kRun];
+                    sample_run(jb + joff[r], jstride, pack_w(w.w00, w.w01), pack_w(w.w10, w.w11), v);
+                    if (rvalid[r]) {
+#pragma unroll
+                        for (int x = 0; x < kRun; x++) e += abs(v[x] - Iw[r][x]);
+                    }
                 }
                 e = __reduce_add_sync(0xffffffffu, e);
                 err = __fmul_rn((float)e, 1.f / (32 * WIN * WIN));
