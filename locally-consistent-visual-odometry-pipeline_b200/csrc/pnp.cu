@@ -115,76 +115,6 @@ __device__ int update_num_iters(double p, double ep, int model_points, int max_i
     return denom >= 0 || -num >= max_iters * (-denom) ? max_iters : (int)rint(num / denom);
 }
 
-// ---- polynomial real roots by bracketing between the critical points ---------------------------
-__device__ __forceinline__ double peval(const double* c, int deg, double x)
-{
-    double v = c[deg];
-    for (int i = deg - 1; i >= 0; i--) v = v * x + c[i];
-    return v;
-}
-
-__device__ double bracket_root(const double* c, int deg, double lo, double hi, double flo)
-{
-    double d[4];
-    for (int i = 1; i <= deg; i++) d[i - 1] = c[i] * i;
-    double x = 0.5 * (lo + hi);
-    for (int it = 0; it < 200; it++) {
-        const double f = peval(c, deg, x);
-        if (f == 0.) return x;
-        if ((f < 0.) == (flo < 0.)) lo = x; else hi = x;
-        const double df = peval(d, deg - 1, x);
-        double xn = df != 0. ? x - f / df : 0.5 * (lo + hi);
-        if (!(xn > lo && xn < hi)) xn = 0.5 * (lo + hi);
-        if (fabs(xn - x) <= 4e-16 * fabs(x) || hi - lo <= 4e-16 * fabs(x)) return xn;
-        x = xn;
-    }
-    return x;
-}
-
-// real roots of c[0..deg] (deg <= 4) in (lo, hi], ascending
-__device__ int real_roots(const double* cin, int deg, double lo, double hi, double* roots)
-{
-    double big = 0.;
-    for (int i = 0; i <= deg; i++) big = fmax(big, fabs(cin[i]));
-    while (deg > 0 && fabs(cin[deg]) <= 1e-14 * big) deg--;
-    if (deg == 0) return 0;
-    double der[4][5];
-    int degs[4];
-    for (int i = 0; i <= deg; i++) der[0][i] = cin[i];
-    degs[0] = deg;
-    int nd = 1;
-    while (degs[nd - 1] > 1) {
-        for (int i = 1; i <= degs[nd - 1]; i++) der[nd][i - 1] = der[nd - 1][i] * i;
-        degs[nd] = degs[nd - 1] - 1;
-        nd++;
-    }
-    double r[4], prev[4];
-    int nprev = 0;
-    {
-        const double x = -der[nd - 1][0] / der[nd - 1][1];
-        if (x > lo && x <= hi) prev[nprev++] = x;
-    }
-    for (int k = nd - 2; k >= 0; k--) {
-        const double* p = der[k];
-        const int dg = degs[k];
-        int nr = 0;
-        double a = lo, fa = peval(p, dg, a);
-        for (int i = 0; i <= nprev; i++) {
-            const double b = i < nprev ? prev[i] : hi;
-            const double fb = peval(p, dg, b);
-            if (b > a) {
-                if (fb == 0.) r[nr++] = b;
-                else if (fa != 0. && (fa < 0.) != (fb < 0.)) r[nr++] = bracket_root(p, dg, a, b, fa);
-            }
-            a = b; fa = fb;
-        }
-        nprev = nr;
-        for (int i = 0; i < nr; i++) prev[i] = r[i];
-    }
-    for (int i = 0; i < nprev; i++) roots[i] = prev[i];
-    return nprev;
-}
-
 __device__ __forceinline__ void cross3(const double* a, const double* b, double* c)
 {
     c[0] = a[1] * b[2] - a[2] * b[1];
@@ -210,126 +140,75 @@ __device__ __forceinline__ float reproj_err2(const double* R, const double* t, c
     return __fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy));
 }
 
-// ---- 4-lane cooperative root isolation -----------------------------------------------------------
-// The serial chain of real_roots/p3p4 is what bounds a RANSAC chunk (every hypothesis CTA waits
-// for its pose), so one hypothesis is solved by a quad of lanes: the <=4 bracketing intervals of a
-// derivative level, and later the <=4 quartic roots, are independent and run one per lane.  The
-// arithmetic per interval / per root is the same as in the serial code (same expressions, same
-// order), so both give identical bits.
-template <int DEG>
-__device__ __forceinline__ double peval_t(const double* c, double x)
-{
-    double v = c[DEG];
-#pragma unroll
-    for (int i = DEG - 1; i >= 0; i--) v = v * x + c[i];
-    return v;
-}
+// ---- P3P ---------------------------------------------------------------------------------------
+// The serial chain of the minimal solver bounds a RANSAC chunk (every hypothesis CTA waits for
+// its pose, and a lone warp retires one dependent FP64 instruction every ~14 cycles), so the
+// solver is chosen for the shortest dependent chain and spread over a quad of lanes:
+//   - depths l1,l2,l3 along the unit bearings satisfy  li^2 + bij li lj + lj^2 = aij.  The two
+//     homogeneous conics D1 = a23 M12 - a12 M23, D2 = a23 M13 - a13 M23 share the solutions; one
+//     real root g of det(D1 + g D2) = 0 (a cubic: Newton from the stationary-point expansion, no
+//     bracketing) gives a degenerate conic = a pair of planes (e1 +- s e2).L = 0, each of which
+//     turns one distance equation into a quadratic in tau = l3/l2 ("lambda twist", Persson &
+//     Nordberg 2018): at most 4 depth triples with no quartic to isolate;
+//   - lane q of the quad takes (plane q>>1, quadratic root q&1), polishes its triple by
+//     Gauss-Newton on the three distance equations (so the result does not depend on how the
+//     start was obtained: it agrees with the Grunert-quartic oracle to rounding), aligns the
+//     triangles exactly and scores the 4th point; the quad keeps the smallest pixel error.
 
-// d = coefficients of the derivative of c (degree DEG-1)
-template <int DEG>
-__device__ __forceinline__ double bracket_root_t(const double* c, const double* d, double lo, double hi, double flo)
+// one real root of x^3 + b x^2 + c x + d
+__device__ __forceinline__ double cubic_root(double b, double c, double d)
 {
-    double x = 0.5 * (lo + hi);
-    for (int it = 0; it < 200; it++) {
-        const double f = peval_t<DEG>(c, x);
-        if (f == 0.) return x;
-        if ((f < 0.) == (flo < 0.)) lo = x; else hi = x;
-        const double df = peval_t<DEG - 1>(d, x);
-        double xn = df != 0. ? x - f / df : 0.5 * (lo + hi);
-        if (!(xn > lo && xn < hi)) xn = 0.5 * (lo + hi);
-        if (fabs(xn - x) <= 4e-16 * fabs(x) || hi - lo <= 4e-16 * fabs(x)) return xn;
-        x = xn;
-    }
-    return x;
-}
-
-__device__ __forceinline__ double sel4(int i, double a0, double a1, double a2, double a3)
-{
-    return i == 0 ? a0 : (i == 1 ? a1 : (i == 2 ? a2 : a3));
-}
-
-// one derivative level: lane q of the quad takes interval q of (lo, prev..., hi]; the roots found
-// are gathered back, ascending, into prev[0..return)
-template <int DEG>
-__device__ __forceinline__ int quad_level(const double* p, const double* dp, double lo, double hi, double* prev,
-                                          int nprev, int q, unsigned qmask)
-{
-    bool has = false;
-    double root = 0.;
-    if (q <= nprev) {
-        const double a = q == 0 ? lo : sel4(q - 1, prev[0], prev[1], prev[2], prev[3]);
-        const double b = q < nprev ? sel4(q, prev[0], prev[1], prev[2], prev[3]) : hi;
-        const double fa = peval_t<DEG>(p, a), fb = peval_t<DEG>(p, b);
-        if (b > a) {
-            if (fb == 0.) { has = true; root = b; }
-            else if (fa != 0. && (fa < 0.) != (fb < 0.)) { has = true; root = bracket_root_t<DEG>(p, dp, a, b, fa); }
+    double r0;
+    const double disc = b * b - 3. * c;
+    if (disc >= 0.) {   // start beyond the outer root on the convex side of a stationary point
+        const double v = sqrt(disc);
+        const double t1 = (-b - v) * (1. / 3.);
+        double k = ((t1 + b) * t1 + c) * t1 + d;
+        if (k > 0.) r0 = t1 - sqrt(-k / (3. * t1 + b));
+        else {
+            const double t2 = (-b + v) * (1. / 3.);
+            k = ((t2 + b) * t2 + c) * t2 + d;
+            r0 = t2 + sqrt(-k / (3. * t2 + b));
         }
+    } else {
+        r0 = -b * (1. / 3.);
+        if (fabs((3. * r0 + 2. * b) * r0 + c) < 1e-4) r0 += 1.;
     }
-    int n = 0;
-#pragma unroll
-    for (int s = 0; s < 4; s++) {
-        const int hs = __shfl_sync(qmask, (int)has, s, 4);
-        const double rs = __shfl_sync(qmask, root, s, 4);
-        if (hs) {
-            if (n == 0) prev[0] = rs; else if (n == 1) prev[1] = rs; else if (n == 2) prev[2] = rs; else prev[3] = rs;
-            n++;
-        }
+    for (int it = 0; it < 50; it++) {
+        const double fx = ((r0 + b) * r0 + c) * r0 + d;
+        const double fpx = (3. * r0 + 2. * b) * r0 + c;
+        if (fpx == 0.) break;
+        const double dx = fx / fpx;
+        r0 -= dx;
+        if (fabs(dx) <= 1e-15 * fabs(r0)) break;
     }
-    return n;
+    return r0;
 }
 
-// real roots of the quartic c[0..4] in (lo, hi], ascending, by a quad of lanes (all 4 lanes get
-// the full result).  Same result as real_roots(c, 4, lo, hi, roots).
-__device__ int real_roots4_quad(const double* cin, double lo, double hi, double* roots, int q, unsigned qmask)
+// unit vector spanning the null space of the symmetric rank-2 matrix M - s I (largest of the
+// three row cross products)
+__device__ __forceinline__ void null_vector(const double* M, double s, double* e)
 {
-    double big = 0.;
+    const double r0[3] = { M[0] - s, M[1], M[2] }, r1[3] = { M[1], M[3] - s, M[4] }, r2[3] = { M[2], M[4], M[5] - s };
+    double c0[3], c1[3], c2[3];
+    cross3(r0, r1, c0); cross3(r0, r2, c1); cross3(r1, r2, c2);
+    const double n0 = dot3(c0, c0), n1 = dot3(c1, c1), n2 = dot3(c2, c2);
+    const bool u1 = n1 > n0 && n1 >= n2, u2 = n2 > n0 && n2 > n1;
+    const double n = u2 ? n2 : (u1 ? n1 : n0);
+    const double inv = rsqrt(n);
 #pragma unroll
-    for (int i = 0; i <= 4; i++) big = fmax(big, fabs(cin[i]));
-    if (fabs(cin[4]) <= 1e-14 * big) {   // degenerate leading coefficient: rare, serial path on lane 0
-        int nv = 0;
-        double r[4] = { 0., 0., 0., 0. };
-        if (q == 0) nv = real_roots(cin, 4, lo, hi, r);
-        nv = __shfl_sync(qmask, nv, 0, 4);
-#pragma unroll
-        for (int i = 0; i < 4; i++) roots[i] = __shfl_sync(qmask, r[i], 0, 4);
-        return nv;
-    }
-    // Cauchy bound: every (complex) root, hence by Gauss-Lucas every critical point of every
-    // derivative, has modulus < 1 + max|c_i/c_4|.  Shrinking the search interval from 1e6 to the
-    // bound keeps the root set and saves the ~40 Newton steps a start at 5e5 spends coming down.
-    {
-        double m = 0.;
-#pragma unroll
-        for (int i = 0; i < 4; i++) m = fmax(m, fabs(cin[i]));
-        hi = fmin(hi, 1. + m / fabs(cin[4]));
-    }
-    double d1[4], d2[3], d3[2];
-#pragma unroll
-    for (int i = 1; i <= 4; i++) d1[i - 1] = cin[i] * i;
-#pragma unroll
-    for (int i = 1; i <= 3; i++) d2[i - 1] = d1[i] * i;
-#pragma unroll
-    for (int i = 1; i <= 2; i++) d3[i - 1] = d2[i] * i;
-    double prev[4] = { 0., 0., 0., 0. };
-    int nprev = 0;
-    {
-        const double x = -d3[0] / d3[1];
-        if (x > lo && x <= hi) prev[nprev++] = x;
-    }
-    nprev = quad_level<2>(d2, d3, lo, hi, prev, nprev, q, qmask);
-    nprev = quad_level<3>(d1, d2, lo, hi, prev, nprev, q, qmask);
-    nprev = quad_level<4>(cin, d1, lo, hi, prev, nprev, q, qmask);
-#pragma unroll
-    for (int i = 0; i < 4; i++) roots[i] = prev[i];
-    return nprev;
+    for (int i = 0; i < 3; i++) e[i] = (u2 ? c2[i] : (u1 ? c1[i] : c0[i])) * inv;
 }
 
-// P3P (Grunert quartic; roots isolated by bracketing; distances polished by Gauss-Newton; exact
-// 3-point alignment).  X: 4 world points (rows), p: 4 pixel points.  Roots come from the first
-// three correspondences, the fourth picks the root with the smallest pixel error.  Called by the
-// 4 lanes of a quad (q = lane in quad) with identical inputs; returns true on the ONE lane that
-// holds the selected solution in Rt = [R|t] (12 doubles: R row-major then t); *found is set on all
-// four lanes.
+__device__ __forceinline__ double det3(const double* a, const double* b, const double* c)
+{
+    return a[0] * (b[1] * c[2] - b[2] * c[1]) - a[1] * (b[0] * c[2] - b[2] * c[0]) + a[2] * (b[0] * c[1] - b[1] * c[0]);
+}
+
+// X: 4 world points (rows), p: 4 pixel points.  Solutions come from the first three
+// correspondences, the fourth picks the one with the smallest pixel error.  Called by the 4 lanes
+// of a quad (q = lane in quad) with identical inputs; returns true on the ONE lane that holds the
+// selected solution in Rt = [R|t] (12 doubles: R row-major then t); *found_any is set on all four.
 __device__ bool p3p4_quad(const double* X, const double* p, const double* K, double* Rt, int q, unsigned qmask,
                           bool* found_any)
 {
@@ -338,16 +217,17 @@ __device__ bool p3p4_quad(const double* X, const double* p, const double* K, dou
 #pragma unroll
     for (int i = 0; i < 3; i++) {
         const double x = (p[2 * i] - K[2]) / K[0], y = (p[2 * i + 1] - K[5]) / K[4];
-        const double n = sqrt(x * x + y * y + 1.);
-        j[3 * i] = x / n; j[3 * i + 1] = y / n; j[3 * i + 2] = 1. / n;
+        const double n = rsqrt(x * x + y * y + 1.);
+        j[3 * i] = x * n; j[3 * i + 1] = y * n; j[3 * i + 2] = n;
     }
     const double* X1 = X; const double* X2 = X + 3; const double* X3 = X + 6;
     double d12[3], d13[3], d23[3];
 #pragma unroll
     for (int i = 0; i < 3; i++) { d12[i] = X1[i] - X2[i]; d13[i] = X1[i] - X3[i]; d23[i] = X2[i] - X3[i]; }
-    const double a2 = dot3(d23, d23), b2 = dot3(d13, d13), c2 = dot3(d12, d12);
-    if (!(a2 > 0. && b2 > 0. && c2 > 0.)) return false;
-    const double ca = dot3(j + 3, j + 6), cb = dot3(j, j + 6), cg = dot3(j, j + 3);
+    const double a12 = dot3(d12, d12), a13 = dot3(d13, d13), a23 = dot3(d23, d23);
+    if (!(a23 > 0. && a13 > 0. && a12 > 0.)) return false;
+    const double c12 = dot3(j, j + 3), c13 = dot3(j, j + 6), c23 = dot3(j + 3, j + 6);
+    const double b12 = -2. * c12, b13 = -2. * c13, b23 = -2. * c23;
     double nX[3], XmInv[9];
     cross3(d12, d13, nX);
     {
@@ -360,81 +240,86 @@ __device__ bool p3p4_quad(const double* X, const double* p, const double* K, dou
 #pragma unroll
         for (int i = 0; i < 3; i++) { XmInv[i] = bc[i] * id; XmInv[3 + i] = cA[i] * id; XmInv[6 + i] = ab[i] * id; }
     }
-    // u = N(v)/D(v); quartic  N^2 - 2 cg N D + (1 - k W) D^2 = 0  in v = s3/s1
-    const double qq = (a2 - c2) / b2, k = c2 / b2;
-    const double N[3] = { 1. + qq, -2. * qq * cb, qq - 1. };
-    const double D[2] = { 2. * cg, -2. * ca };
-    const double W[3] = { 1., -2. * cb, 1. };
-    double NN[5] = { 0, 0, 0, 0, 0 }, ND[4] = { 0, 0, 0, 0 }, DD[3] = { 0, 0, 0 }, G[3], GDD[5] = { 0, 0, 0, 0, 0 }, Q[5];
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-#pragma unroll
-        for (int b = 0; b < 3; b++) NN[a + b] += N[a] * N[b];
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-#pragma unroll
-        for (int b = 0; b < 2; b++) ND[a + b] += N[a] * D[b];
-#pragma unroll
-    for (int a = 0; a < 2; a++)
-#pragma unroll
-        for (int b = 0; b < 2; b++) DD[a + b] += D[a] * D[b];
-#pragma unroll
-    for (int a = 0; a < 3; a++) G[a] = (a == 0 ? 1. : 0.) - k * W[a];
-#pragma unroll
-    for (int a = 0; a < 3; a++)
-#pragma unroll
-        for (int b = 0; b < 3; b++) GDD[a + b] += G[a] * DD[b];
-    double big = 0.;
-#pragma unroll
-    for (int a = 0; a < 5; a++) { Q[a] = NN[a] + GDD[a] - (a < 4 ? 2. * cg * ND[a] : 0.); big = fmax(big, fabs(Q[a])); }
-    if (!(big > 0.) || !isfinite(big)) return false;
-    double vr[4];
-    const int nv = real_roots4_quad(Q, 0., 1e6, vr, q, qmask);
+    // rows of the symmetric conics
+    const double A0[3] = { a23, a23 * b12 * .5, 0. }, A1[3] = { a23 * b12 * .5, a23 - a12, -a12 * b23 * .5 },
+                 A2[3] = { 0., -a12 * b23 * .5, -a12 };
+    const double B0[3] = { a23, 0., a23 * b13 * .5 }, B1[3] = { 0., -a13, -a13 * b23 * .5 },
+                 B2[3] = { a23 * b13 * .5, -a13 * b23 * .5, a23 - a13 };
+    const double k0 = det3(A0, A1, A2);
+    const double k1 = det3(B0, A1, A2) + det3(A0, B1, A2) + det3(A0, A1, B2);
+    const double k2 = det3(B0, B1, A2) + det3(B0, A1, B2) + det3(A0, B1, B2);
+    const double k3 = det3(B0, B1, B2);
+    if (!(fabs(k3) > 0.) || !isfinite(k3)) return false;
+    const double ik3 = 1. / k3;
+    const double g = cubic_root(k2 * ik3, k1 * ik3, k0 * ik3);
+    // M = D1 + g D2, upper triangle (00 01 02 11 12 22)
+    const double M[6] = { A0[0] + g * B0[0], A0[1] + g * B0[1], A0[2] + g * B0[2],
+                          A1[1] + g * B1[1], A1[2] + g * B1[2], A2[2] + g * B2[2] };
+    const double tr = M[0] + M[3] + M[5];
+    const double m2 = M[0] * M[3] - M[1] * M[1] + M[0] * M[5] - M[2] * M[2] + M[3] * M[5] - M[4] * M[4];
+    const double dsc = tr * tr - 4. * m2;
+    if (!(dsc >= 0.)) return false;
+    const double sq = sqrt(dsc);
+    const double s1 = .5 * (tr + (tr >= 0. ? sq : -sq));   // larger-magnitude eigenvalue first
+    if (s1 == 0.) return false;
+    const double s2 = m2 / s1;
+    if (!(s1 * s2 < 0.)) return false;   // a real plane pair needs eigenvalues of opposite sign
+    double e1[3], e2[3];
+    null_vector(M, s1, e1);
+    null_vector(M, s2, e2);
+    const double sv = sqrt(-s2 / s1);
 
-    // lane q evaluates root q
+    // lane q: plane (q >> 1), quadratic root (q & 1)
     bool mine = false;
     double e = 0.;
     do {
-        if (q >= nv) break;
-        const double v = sel4(q, vr[0], vr[1], vr[2], vr[3]);
-        const double Wv = 1. + v * (v - 2. * cb);
-        if (!(Wv > 0.)) break;
-        const double Dv = D[0] + D[1] * v;
-        double u;
-        if (fabs(Dv) > 1e-9) {
-            u = (N[0] + v * (N[1] + v * N[2])) / Dv;
+        const double ss = (q & 2) ? -sv : sv;
+        const double u0 = e1[0] + ss * e2[0], u1 = e1[1] + ss * e2[1], u2 = e1[2] + ss * e2[2];
+        if (!(fabs(u0) > 0.)) break;
+        const double iu = -1. / u0;
+        const double w0 = u1 * iu, w1 = u2 * iu;   // l1 = w0 l2 + w1 l3
+        const double qa = (a13 - a12) * w1 * w1 - a12 * b13 * w1 - a12;
+        const double qb = a13 * b12 * w1 - a12 * b13 * w0 - 2. * w0 * w1 * (a12 - a13);
+        const double qc = (a13 - a12) * w0 * w0 + a13 * b12 * w0 + a13;
+        double tau;
+        if (fabs(qa) > 0.) {
+            const double dd = qb * qb - 4. * qa * qc;
+            if (!(dd >= 0.)) break;
+            const double sd = sqrt(dd), q2 = -.5 * (qb + (qb >= 0. ? sd : -sd));
+            if (q & 1) { if (q2 == 0.) break; tau = qc / q2; }
+            else tau = q2 / qa;
         } else {
-            const double cc = 1. - k * Wv, disc = cg * cg - cc;
-            if (!(disc >= 0.)) break;
-            const double sq = sqrt(disc), u0 = cg + sq, u1 = cg - sq;
-            const double e0 = fabs(u0 * u0 + v * v - 2. * u0 * v * ca - (a2 / b2) * Wv);
-            const double e1 = fabs(u1 * u1 + v * v - 2. * u1 * v * ca - (a2 / b2) * Wv);
-            u = e0 <= e1 ? u0 : u1;
+            if ((q & 1) || !(fabs(qb) > 0.)) break;
+            tau = -qc / qb;
         }
-        if (!(u > 0.)) break;
-        double s1 = sqrt(b2 / Wv), s2 = u * s1, s3 = v * s1;
+        if (!(tau > 0.)) break;
+        const double den = tau * (b23 + tau) + 1.;
+        if (!(den > 0.)) break;
+        double l2 = sqrt(a23 / den), l3 = tau * l2, l1 = w0 * l2 + w1 * l3;
+        if (!(l1 > 0.)) break;
         for (int it = 0; it < 5; it++) {
-            const double r12 = s1 * s1 + s2 * s2 - 2. * s1 * s2 * cg - c2;
-            const double r13 = s1 * s1 + s3 * s3 - 2. * s1 * s3 * cb - b2;
-            const double r23 = s2 * s2 + s3 * s3 - 2. * s2 * s3 * ca - a2;
-            const double J00 = 2. * (s1 - s2 * cg), J01 = 2. * (s2 - s1 * cg);
-            const double J10 = 2. * (s1 - s3 * cb), J12 = 2. * (s3 - s1 * cb);
-            const double J21 = 2. * (s2 - s3 * ca), J22 = 2. * (s3 - s2 * ca);
+            const double r12 = l1 * l1 + l2 * l2 - 2. * l1 * l2 * c12 - a12;
+            const double r13 = l1 * l1 + l3 * l3 - 2. * l1 * l3 * c13 - a13;
+            const double r23 = l2 * l2 + l3 * l3 - 2. * l2 * l3 * c23 - a23;
+            const double J00 = 2. * (l1 - l2 * c12), J01 = 2. * (l2 - l1 * c12);
+            const double J10 = 2. * (l1 - l3 * c13), J12 = 2. * (l3 - l1 * c13);
+            const double J21 = 2. * (l2 - l3 * c23), J22 = 2. * (l3 - l2 * c23);
             const double det = -J00 * J12 * J21 - J01 * J10 * J22;
             if (!(fabs(det) > 1e-300)) break;
-            const double ds1 = (-J12 * J21 * r12 - J01 * J22 * r13 + J01 * J12 * r23) / det;
-            const double ds2 = (-J10 * J22 * r12 + J00 * J22 * r13 - J00 * J12 * r23) / det;
-            const double ds3 = (J10 * J21 * r12 - J00 * J21 * r13 - J01 * J10 * r23) / det;
-            s1 -= ds1; s2 -= ds2; s3 -= ds3;
-            if (fabs(ds1) + fabs(ds2) + fabs(ds3) <= 1e-15 * (s1 + s2 + s3)) break;
+            const double id = 1. / det;
+            const double dl1 = (-J12 * J21 * r12 - J01 * J22 * r13 + J01 * J12 * r23) * id;
+            const double dl2 = (-J10 * J22 * r12 + J00 * J22 * r13 - J00 * J12 * r23) * id;
+            const double dl3 = (J10 * J21 * r12 - J00 * J21 * r13 - J01 * J10 * r23) * id;
+            l1 -= dl1; l2 -= dl2; l3 -= dl3;
+            if (fabs(dl1) + fabs(dl2) + fabs(dl3) <= 1e-15 * (l1 + l2 + l3)) break;
         }
-        if (!(s1 > 0. && s2 > 0. && s3 > 0.)) break;
+        if (!(l1 > 0. && l2 > 0. && l3 > 0.)) break;
         double e12[3], e13[3], nY[3], Y1[3];
 #pragma unroll
         for (int i = 0; i < 3; i++) {
-            Y1[i] = s1 * j[i];
-            e12[i] = Y1[i] - s2 * j[3 + i];
-            e13[i] = Y1[i] - s3 * j[6 + i];
+            Y1[i] = l1 * j[i];
+            e12[i] = Y1[i] - l2 * j[3 + i];
+            e13[i] = Y1[i] - l3 * j[6 + i];
         }
         cross3(e12, e13, nY);
         bool fin = true;
@@ -458,7 +343,6 @@ __device__ bool p3p4_quad(const double* X, const double* p, const double* K, dou
         e = du * du + dv * dv;
         mine = true;
     } while (false);
-    // the serial loop keeps the first root (ascending) with the strictly smallest error
     int win = -1;
     double beste = 0.;
 #pragma unroll
