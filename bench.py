@@ -188,6 +188,7 @@ def run_gpu(args, rank, world, local_rank):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     tracks = 0
     klt_iters = 0
+    lm_iters = ransac_iters = inliers = promoted = 0
     sampler = ClockSampler(local_rank)
     barrier(world)
     torch.cuda.synchronize()
@@ -208,6 +209,7 @@ def run_gpu(args, rank, world, local_rank):
         if s >= warmup:
             ev[s - warmup][1].record(stream)
             klt_iters += cnt.klt_iters
+            lm_iters += cnt.lm_iters; ransac_iters += cnt.ransac_iters; inliers += cnt.n_inliers; promoted += cnt.n_promoted
     torch.cuda.synchronize()
     barrier(world)
     t_wall = time.perf_counter() - t_wall0
@@ -240,7 +242,9 @@ def run_gpu(args, rank, world, local_rank):
     return dict(total_ms=total_ms, step_ms=step_ms, t_wall=t_wall, launches=launches, tracks_per_step=tracks / steps,
                 klt_iters_per_land=prof_iters_land / max(prof_land, 1), stage_ms=stage_ms,
                 prof_tracks_per_step=prof_tracks / max(nfr, 1), clocks=sampler.summary(), e2e=e2e,
-                final_counts=final_counts, frame_bytes=w * h)
+                final_counts=final_counts, frame_bytes=w * h,
+                per_frame=dict(lm_iters=lm_iters / steps, ransac_iters=ransac_iters / steps, pnp_inliers=inliers / steps,
+                               promoted=promoted / steps))
 
 
 def barrier(world):
@@ -303,7 +307,7 @@ def run_e2e(pkg, sq, steps, warmup, local_rank, world):
         # sizes for the next feed from the scalars the PnP sync already brought back (no extra sync):
         # inliers now, candidates as they were after the previous frame's append
         c = vo._runtime().ctx.counters(sync=False)
-        n_land, n_cand = c["n_inliers"], c["n_candidates"] + len(feed)
+        n_land, n_cand = c["n_landmarks"], c["n_candidates"] + len(feed)
         h2d += w * h + feed.nbytes + 128
         d2h += 256
     vo._runtime().ctx.synchronize()
@@ -404,7 +408,7 @@ def main():
                              "so the HBM fraction is small by construction (SURVEY.md 8d)"},
         "stage_ms": r["stage_ms"], "wall_ms_per_step_incl_flush": 1e3 * r["t_wall"] / args.steps,
         "state": {"landmarks": r["final_counts"][0], "candidates": r["final_counts"][1],
-                  "lk_iterations_per_track": iters},
+                  "lk_iterations_per_track": iters, **r["per_frame"]},
     })
     line["config"]["l2"] = "flushed between steps (256 MiB memset outside the per-step events)"
     if world == 1 and not args.no_cpu_baseline:

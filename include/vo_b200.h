@@ -126,6 +126,10 @@ int vo_set_state(vo_ctx* ctx, const float* P, const double* X, int n);
 /* Host mirror of state['P'], state['X'] (main.py:248 reads state['X'] every frame).  P/X may be
  * NULL to query n only.  Synchronises. */
 int vo_get_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
+/* The landmarks as they were before the last vo_klt_track_landmarks / vo_process_frame; a third
+ * landmark buffer keeps them on the device until the next tracking step (main.py:248 reads the
+ * previous frame's state['X'] after the current frame's associate + estimatePose).  Synchronises. */
+int vo_get_prev_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
 /* Asynchronous pinned-host snapshot of P/X as they are now, readable after later calls have
  * replaced them on the device (main.py:248 reads the previous frame's state['X'] after the next
  * frame's associate/estimatePose).  vo_get_snapshot synchronises. */
@@ -151,6 +155,21 @@ int vo_klt_track_landmarks(vo_ctx* ctx, int64_t prev_key, int64_t next_key, cons
  * vo_pipeline.py:274-324.  Synchronises. */
 int vo_pnp_ransac(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, double T44[16], int* n_inliers,
                   int* ok);
+/* a3 + a6 with ONE synchronisation: vo_pnp_ransac, then - speculatively, before the pose is back on
+ * the host - the promotion step of vo_track_triangulate_promote with the pose taken from the device
+ * (the class API forces a sync inside estimatePose; with the promotion enqueued ahead of it the GPU
+ * does not idle while the host walks from estimatePose to triangulate_landmark).  Needs the
+ * candidates tracked with the landmarks (vo_klt_track_landmarks on this frame pair).  Afterwards the
+ * caller confirms (vo_promote_commit: triangulate_landmark got the pose/alpha assumed here) or
+ * undoes it (vo_promote_rollback: state as after vo_pnp_ransac, candidate tracking still pending).
+ * ok=0 is rolled back internally.  Until then the promoted rows sit behind the n_inliers rows of P/X. */
+int vo_pnp_ransac_promote(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, double alpha_deg,
+                          double T44[16], int* n_inliers, int* ok, int* n_promoted);
+int vo_promote_commit(vo_ctx* ctx);
+int vo_promote_rollback(vo_ctx* ctx);
+int vo_promote_pending(vo_ctx* ctx);
+/* 1 if the candidates were tracked over (prev, next) together with the landmarks and not consumed yet */
+int vo_candidates_tracked(vo_ctx* ctx, int64_t prev_key, int64_t next_key);
 /* a6  LandmarkTriangulator.triangulate_landmark, steps 1 and 3 (vo_pipeline.py:489-545, 608-721):
  * track C, drop lost rows of C/F/T, alpha(C,F) > alpha_deg => DLT with (T_first, T44) and append to
  * P/X, remove from C/F/T.  prev_key = next_key = -1 runs the promotion step without tracking.

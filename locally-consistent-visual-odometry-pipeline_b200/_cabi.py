@@ -79,6 +79,12 @@ SIGNATURES = {
     "vo_peek_counters": (c_int, [c_void_p, ctypes.POINTER(Counters)]),
     "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
+    "vo_pnp_ransac_promote": (c_int, [c_void_p, c_void_p, _PP, c_double, c_void_p, _PI, _PI, _PI]),
+    "vo_promote_commit": (c_int, [c_void_p]),
+    "vo_promote_rollback": (c_int, [c_void_p]),
+    "vo_promote_pending": (c_int, [c_void_p]),
+    "vo_candidates_tracked": (c_int, [c_void_p, c_i64, c_i64]),
+    "vo_get_prev_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
     "vo_add_candidates": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "vo_track_candidates": (c_int, [c_void_p, c_i64, c_i64, _PK]),
@@ -311,6 +317,36 @@ class Context:
         self._check(self.lib.vo_pnp_ransac(self.h, _ptr(K), ctypes.byref(params) if params is not None else None,
                                            _ptr(T), ctypes.byref(ninl), ctypes.byref(ok)))
         return bool(ok.value), T, ninl.value
+
+    def pnp_ransac_promote(self, K, params, alpha_deg):
+        """estimatePose + speculative promotion with the device pose, one sync (vo_pnp_ransac_promote)."""
+        K = np.ascontiguousarray(K, np.float64)
+        T = np.empty((4, 4), np.float64)
+        ninl, ok, nprom = c_int(), c_int(), c_int()
+        self._check(self.lib.vo_pnp_ransac_promote(self.h, _ptr(K), ctypes.byref(params) if params is not None else None,
+                                                   float(alpha_deg), _ptr(T), ctypes.byref(ninl), ctypes.byref(ok),
+                                                   ctypes.byref(nprom)))
+        return bool(ok.value), T, ninl.value, nprom.value
+
+    def promote_commit(self):
+        self._check(self.lib.vo_promote_commit(self.h))
+
+    def promote_rollback(self):
+        self._check(self.lib.vo_promote_rollback(self.h))
+
+    def candidates_tracked(self, prev_key, next_key):
+        return bool(self.lib.vo_candidates_tracked(self.h, prev_key, next_key))
+
+    def promote_pending(self):
+        return bool(self.lib.vo_promote_pending(self.h))
+
+    def get_prev_state(self):
+        n = c_int()
+        self._check(self.lib.vo_get_prev_state(self.h, None, None, 0, ctypes.byref(n)))
+        P = np.empty((n.value, 2), np.float32)
+        X = np.empty((n.value, 3), np.float64)
+        self._check(self.lib.vo_get_prev_state(self.h, _ptr(P), _ptr(X), n.value, ctypes.byref(n)))
+        return P, X
 
     def track_triangulate_promote(self, prev_key, next_key, K, T44, alpha_deg, params=None, sync=False):
         K = np.ascontiguousarray(K, np.float64)

@@ -169,7 +169,8 @@ int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int6
         for (int y = 0; y < h; y++) memcpy(c->pinned_stage + (size_t)y * w, img + (size_t)y * pitch, w);
         VO_CUDA(c, cudaMemcpyAsync(s->raw, c->pinned_stage, bytes, cudaMemcpyHostToDevice, c->stream));
     } else {
-        VO_CUDA(c, cudaMemcpy2DAsync(s->raw, w, img, pitch, w, h, cudaMemcpyDefault, c->stream));
+        if (pitch == w) VO_CUDA(c, cudaMemcpyAsync(s->raw, img, bytes, cudaMemcpyDefault, c->stream));
+        else VO_CUDA(c, cudaMemcpy2DAsync(s->raw, w, img, pitch, w, h, cudaMemcpyDefault, c->stream));
     }
     s->w = w; s->h = h;
     VO_TRY(build_pyramid(c, *s, 3));

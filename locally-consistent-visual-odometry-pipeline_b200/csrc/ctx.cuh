@@ -141,6 +141,10 @@ struct DevScalars {
     int32_t klt_iters;     // sum of LK iterations (roofline accounting)
     int32_t rng_exhausted; // the RNG draw table ran out (host reports VO_ERR_CAPACITY)
     int32_t ticket;        // multi-CTA kernels: last-block-done counter (always 0 between kernels)
+    int32_t prev_n_land;   // |P| before the last tracking step (rows of the `prev` landmark buffer)
+    // values before the last promotion step (rollback of a speculative promotion)
+    int32_t spec_n_land, spec_n_cand, spec_cf_alias, spec_cand_was_empty;
+    int32_t pad_;
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -148,10 +152,13 @@ struct DevScalars {
 
 struct Pipeline {
     int track_capacity = 0, hyp_capacity = 0;
-    // landmarks, ping-pong (cur = index of the live buffers)
+    // landmarks, three buffers in rotation (cur = index of the live ones): the post-KLT compaction
+    // writes cur+1, the inlier pruning cur+2, so the state a frame started from (prev) stays intact
+    // until the next frame's compaction - main.py:248 reads it after estimatePose
     int cur = 0;
-    DevBuf<float> P[2];     // n x 2
-    DevBuf<double> X[2];    // n x 3
+    int prev = -1;          // buffer holding the state before the last tracking step (-1: none)
+    DevBuf<float> P[3];     // n x 2
+    DevBuf<double> X[3];    // n x 3
     int n_land_upper = 0;   // host-known upper bound of n_land
     // candidates, ping-pong
     int ccur = 0;
@@ -185,6 +192,9 @@ struct Pipeline {
     DevBuf<int32_t> stage_i;
     int klt_b_off = 0;      // offset of the candidate results inside the klt_* buffers
     bool packed_valid = false;  // q4/qv hold the current landmarks (set by the post-KLT compaction)
+    // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
+    bool spec_pending = false;
+    int64_t spec_prev_key = -1, spec_next_key = -1;
     DevScalars* d_sc = nullptr;
     DevScalars* h_sc = nullptr;  // pinned mirror
     // pinned snapshot of the landmarks before a tracking step (serves main.py:248)

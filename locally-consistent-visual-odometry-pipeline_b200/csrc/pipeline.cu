@@ -18,8 +18,8 @@ int pipeline_init(Ctx* c, int track_capacity, int hyp_capacity)
     VO_CUDA(c, cudaMallocHost((void**)&p->h_sc, sizeof(DevScalars)));
     memset(p->h_sc, 0, sizeof(DevScalars));
     const size_t n = p->track_capacity;
+    for (int k = 0; k < 3; k++) { VO_TRY(ensure(c, p->P[k], n * 2)); VO_TRY(ensure(c, p->X[k], n * 3)); }
     for (int k = 0; k < 2; k++) {
-        VO_TRY(ensure(c, p->P[k], n * 2)); VO_TRY(ensure(c, p->X[k], n * 3));
         VO_TRY(ensure(c, p->C[k], n * 2)); VO_TRY(ensure(c, p->F[k], n * 2)); VO_TRY(ensure(c, p->Ti[k], n));
     }
     VO_TRY(ensure(c, p->klt_out, n * 4)); VO_TRY(ensure(c, p->klt_err, n * 2));
@@ -36,9 +36,8 @@ void pipeline_free(Ctx* c)
 {
     Pipeline* p = c->pipe;
     if (!p) return;
-    for (int k = 0; k < 2; k++) {
-        cudaFree(p->P[k].p); cudaFree(p->X[k].p); cudaFree(p->C[k].p); cudaFree(p->F[k].p); cudaFree(p->Ti[k].p);
-    }
+    for (int k = 0; k < 3; k++) { cudaFree(p->P[k].p); cudaFree(p->X[k].p); }
+    for (int k = 0; k < 2; k++) { cudaFree(p->C[k].p); cudaFree(p->F[k].p); cudaFree(p->Ti[k].p); }
     cudaFree(p->poses.p); cudaFree(p->klt_in.p); cudaFree(p->klt_out.p); cudaFree(p->klt_err.p);
     cudaFree(p->klt_status.p); cudaFree(p->klt_iters.p); cudaFree(p->lost.p); cudaFree(p->q4.p); cudaFree(p->qv.p);
     cudaFree(p->sets.p); cudaFree(p->hyp.p); cudaFree(p->counts.p); cudaFree(p->mask.p); cudaFree(p->promote.p);
@@ -136,6 +135,7 @@ int vo_set_state(vo_ctx* c, const float* P, const double* X, int n)
     p->n_land_upper = n;
     p->cand_tracked_valid = false;
     p->packed_valid = false;
+    p->spec_pending = false;
     // the caller's buffers may be pageable and go away: finish the copies before returning
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     return VO_OK;
@@ -155,6 +155,24 @@ int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
     return VO_OK;
 }
 
+
+// The landmarks as they were before the last vo_klt_track_landmarks / vo_process_frame: the third
+// landmark buffer keeps them until the next tracking step (main.py:248 reads the previous frame's
+// state['X'] after the current frame's associate + estimatePose).  Synchronises.
+int vo_get_prev_state(vo_ctx* c, float* P, double* X, int cap, int* n)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    if (p->prev < 0) return set_error(c, VO_ERR_STATE, "no previous state is held");
+    VO_TRY(read_scalars(c));
+    const int m = p->h_sc->prev_n_land;
+    if (n) *n = m;
+    if (m > cap) return (P || X) ? set_error(c, VO_ERR_CAPACITY, "previous state has %d rows, buffer %d", m, cap) : VO_OK;
+    if (m > 0 && P) VO_CUDA(c, cudaMemcpyAsync(P, p->P[p->prev].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && X) VO_CUDA(c, cudaMemcpyAsync(X, p->X[p->prev].p, sizeof(double) * 3 * m, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    return VO_OK;
+}
 
 // main.py:248 reads the PREVIOUS frame's state['X'] after the next frame's associate/estimatePose
 // have already replaced it on the device: keep an asynchronous pinned-host snapshot (64 KB at 2k
@@ -323,6 +341,91 @@ int vo_pnp_ransac(vo_ctx* c, const double K[9], const vo_pnp_params* params, dou
     if (n_inliers) *n_inliers = p->h_sc->n_inliers;
     if (ok) *ok = p->h_sc->ok;
     return VO_OK;
+}
+
+__global__ void promote_rollback_kernel(DevScalars* sc)
+{
+    sc->n_land = sc->spec_n_land; sc->n_cand = sc->spec_n_cand; sc->cf_alias = sc->spec_cf_alias;
+    sc->cand_was_empty = sc->spec_cand_was_empty; sc->n_promoted = 0; sc->n_cand_lost = 0;
+}
+
+static int promote_rollback(Ctx* c)
+{
+    Pipeline* p = c->pipe;
+    promote_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
+    c->launches++;
+    p->ccur ^= 1;                                  // the pre-promotion candidate buffers are intact
+    p->n_land_upper = p->h_sc->spec_n_land;        // h_sc is current: every speculation ends in a sync
+    p->n_cand_upper = p->h_sc->spec_n_cand;
+    p->h_sc->n_land = p->h_sc->spec_n_land; p->h_sc->n_cand = p->h_sc->spec_n_cand;
+    p->h_sc->n_promoted = 0; p->h_sc->n_cand_lost = 0;
+    p->cand_tracked_prev = p->spec_prev_key; p->cand_tracked_next = p->spec_next_key;
+    p->cand_tracked_valid = true;                  // the KLT results of the candidates are still there
+    p->spec_pending = false;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+// a3 + a6 in one enqueue, ONE synchronisation: estimatePose, then - speculatively, before the pose
+// is back on the host - the promotion step of triangulate_landmark with the pose taken from the
+// device.  The class API forces a sync in estimatePose (it returns T); with the promotion already
+// behind it, the GPU has no idle gap while the host walks from estimatePose to
+// triangulate_landmark.  Needs the candidates tracked together with the landmarks
+// (vo_klt_track_landmarks).  The caller then either confirms (vo_promote_commit: the arguments of
+// triangulate_landmark were the ones assumed) or undoes it (vo_promote_rollback).  No model (ok=0):
+// rolled back here, the state is as after vo_pnp_ransac.  The promoted rows sit behind the
+// n_inliers rows of P/X.
+int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* params, double alpha_deg, double T44[16],
+                          int* n_inliers, int* ok, int* n_promoted)
+{
+    VO_NEED(c);
+    if (!K) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    if (!p->cand_tracked_valid || !p->packed_valid)
+        return set_error(c, VO_ERR_STATE, "speculative promotion needs vo_klt_track_landmarks on this frame pair first");
+    PnpLaunch L{};
+    if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
+    L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
+    L.d_sets_in = nullptr; L.compact = true;
+    memcpy(L.K, K, sizeof(L.K));
+    VO_TRY(launch_pnp(c, L));
+    p->packed_valid = false;
+    p->spec_prev_key = p->cand_tracked_prev; p->spec_next_key = p->cand_tracked_next;
+    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+    p->cand_tracked_valid = false;
+    p->spec_pending = true;
+    VO_TRY(read_scalars(c));
+    VO_TRY(check_rng(c));
+    if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
+    if (n_inliers) *n_inliers = p->h_sc->n_inliers;
+    if (ok) *ok = p->h_sc->ok;
+    if (n_promoted) *n_promoted = p->h_sc->n_promoted;
+    if (!p->h_sc->ok) VO_TRY(promote_rollback(c));
+    return VO_OK;
+}
+
+int vo_promote_commit(vo_ctx* c)
+{
+    VO_NEED(c);
+    if (!c->pipe->spec_pending) return set_error(c, VO_ERR_STATE, "no speculative promotion pending");
+    c->pipe->spec_pending = false;
+    return VO_OK;
+}
+
+int vo_promote_rollback(vo_ctx* c)
+{
+    VO_NEED(c);
+    if (!c->pipe->spec_pending) return set_error(c, VO_ERR_STATE, "no speculative promotion pending");
+    return promote_rollback(c);
+}
+
+int vo_promote_pending(vo_ctx* c) { return c && c->pipe && c->pipe->spec_pending ? 1 : 0; }
+
+int vo_candidates_tracked(vo_ctx* c, int64_t prev_key, int64_t next_key)
+{
+    if (!c || !c->pipe) return 0;
+    const Pipeline* p = c->pipe;
+    return p->cand_tracked_valid && p->packed_valid && p->cand_tracked_prev == prev_key && p->cand_tracked_next == next_key;
 }
 
 // ---- a6 (second half): append new candidates, F := C, T := pose (vo_pipeline.py:574-591)

@@ -790,11 +790,18 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
     FinalizeBufs fb{};
     if (L.compact) {
         fb.P_in = p->P[p->cur].p; fb.X_in = p->X[p->cur].p;
-        fb.P_out = p->P[p->cur ^ 1].p; fb.X_out = p->X[p->cur ^ 1].p;
+        const int nxt = (p->cur + 1) % 3;
+        VO_TRY(ensure(c, p->P[nxt], (size_t)(L.n_upper > 0 ? L.n_upper : 1) * 2));
+        VO_TRY(ensure(c, p->X[nxt], (size_t)(L.n_upper > 0 ? L.n_upper : 1) * 3));
+        fb.P_out = p->P[nxt].p; fb.X_out = p->X[nxt].p;
     }
     pnp_finalize_kernel<<<1, kFinThreads, 0, c->stream>>>(p->d_sc, p->hyp.p, (const float4*)L.q4, L.qv, p->mask.p, a, fb);
     c->launches++;
-    if (L.compact) p->cur ^= 1;
+    if (L.compact) {
+        const int nxt = (p->cur + 1) % 3;
+        if (nxt == p->prev) p->prev = -1;   // pruning without a preceding tracking step reuses that buffer
+        p->cur = nxt;
+    }
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
 }

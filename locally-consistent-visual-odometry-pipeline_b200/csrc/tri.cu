@@ -76,7 +76,7 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
     it = __reduce_add_sync(0xffffffffu, it);
     if ((tid & 31) == 0) atomicAdd(&sIter, it);
     __syncthreads();
-    if (tid == 0) { sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
+    if (tid == 0) { sc->prev_n_land = n; sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
 }
 
 // ---- DLT ---------------------------------------------------------------------------------------
@@ -278,6 +278,8 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
         pr = __reduce_add_sync(0xffffffffu, pr);
         if (lane == 0) {
             const int kept = st + pr, n_lost = n - kept;
+            sc->spec_n_land = n_land; sc->spec_n_cand = sc->n_cand; sc->spec_cf_alias = sc->cf_alias;
+            sc->spec_cand_was_empty = sc->cand_was_empty;
             sc->n_cand = st;
             sc->n_promoted = pr;
             sc->n_cand_lost = n_lost;
@@ -338,16 +340,18 @@ int launch_landmark_compact(Ctx* c, int n_upper)
 {
     Pipeline* p = c->pipe;
     const size_t n = n_upper > 0 ? n_upper : 1;
-    VO_TRY(ensure(c, p->P[p->cur ^ 1], n * 2));
-    VO_TRY(ensure(c, p->X[p->cur ^ 1], n * 3));
+    const int nxt = (p->cur + 1) % 3;
+    VO_TRY(ensure(c, p->P[nxt], n * 2));
+    VO_TRY(ensure(c, p->X[nxt], n * 3));
     VO_TRY(ensure(c, p->q4, n * 4));
     VO_TRY(ensure(c, p->qv, n));
     VO_TRY(ensure(c, p->lost, n * 2));
     landmark_compact_kernel<<<1, kScanThreads, 0, c->stream>>>(
         p->d_sc, n_upper, (const float2*)p->klt_out.p, p->klt_status.p, p->klt_iters.p, p->X[p->cur].p,
-        (float2*)p->P[p->cur ^ 1].p, p->X[p->cur ^ 1].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p);
+        (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p);
     c->launches++;
-    p->cur ^= 1;
+    p->prev = p->cur;
+    p->cur = nxt;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
 }

@@ -23,6 +23,7 @@ Differences a caller can observe (DESIGN.md lists them with reasons):
 import os
 import sys
 import time
+import zlib
 from typing import Dict
 
 import numpy as np
@@ -68,6 +69,7 @@ _DEFAULTS = {
     'pnp_refine_iters': 20,
     'klt_fb_check': False,       # the reference has no forward-backward check
     'klt_fb_thresh': 1.0,
+    'speculative_promotion': True,   # enqueue the promotion step ahead of estimatePose's sync
     'emulate_cf_alias': True,    # reference quirk App. B-5 (first candidate batch: F follows C)
     'device': 0,
 }
@@ -89,7 +91,10 @@ class _Runtime:
         self.state_version = 0    # bumped whenever the device landmarks change
         self.ext_version = 0      # bumped whenever the device candidates change
         self.timers = {}
-        self.snap_id = 0
+        self.prev_token = 0       # bumped at every tracking step (whose input state stays readable)
+        self.pair = None          # (old_frame, new_frame, k_old, k_new) of the last associate call
+        self.pending_add = None   # (points, pose) of a deferred vo_add_candidates
+        self.spec = None          # assumptions of a pending speculative promotion
 
     # frames arrive as host uint8 arrays; the same object is passed to several stages and then
     # becomes the "old" frame of the next iteration (main.py:293), so upload + pyramid happen once
@@ -98,7 +103,8 @@ class _Runtime:
             raise ValueError("frames must be 2-D uint8 (cv2.IMREAD_GRAYSCALE) arrays")
         if img.strides[1] != 1:
             img = np.ascontiguousarray(img)
-        fp = (img.shape, img.ctypes.data, int(img[::max(1, img.shape[0] // 8), ::max(1, img.shape[1] // 16)].sum()))
+        # cheap content fingerprint: catches a buffer that was refilled in place
+        fp = (img.shape, img.__array_interface__['data'][0], zlib.adler32(img[img.shape[0] >> 1]))
         ent = self.frames.get(id(img))
         if ent is not None and ent[2] == fp and self.ctx.has_frame(ent[0]):
             return ent[0]
@@ -110,6 +116,30 @@ class _Runtime:
             for k in sorted(self.frames, key=lambda i: self.frames[i][0])[:-3]:
                 del self.frames[k]
         return key
+
+    def pair_keys(self, old_frame, new_frame):
+        """Keys of a frame pair; the pair the last associate call saw is recognised by identity."""
+        pr = self.pair
+        if pr is not None and pr[0] is old_frame and pr[1] is new_frame and self.ctx.has_frame(pr[2]) \
+                and self.ctx.has_frame(pr[3]):
+            return pr[2], pr[3]
+        return self.frame_key(old_frame), self.frame_key(new_frame)
+
+    # the append of new candidates is deferred until the next frame's upload is on the stream (the
+    # copy engine and the pyramid kernels then start ~20 us earlier); anything that looks at the
+    # candidates flushes it first
+    def flush_pending_add(self):
+        if self.pending_add is not None:
+            pts, pose = self.pending_add
+            self.pending_add = None
+            self.ctx.add_candidates(pts, pose)
+
+    def drop_speculation(self):
+        """Undo a speculative promotion whose assumptions were not confirmed."""
+        if self.spec is not None:
+            self.spec = None
+            if self.ctx.promote_pending():
+                self.ctx.promote_rollback()
 
 
 _rt = None
@@ -145,8 +175,11 @@ class DeviceState(dict):
         if not dict.__contains__(self, 'P'):
             if self._current():
                 P, X = self._rt.ctx.get_state()
-            elif self._rt is _rt and getattr(self, '_snap', None) == self._rt.snap_id:
-                P, X = self._rt.ctx.get_snapshot()   # previous frame's state (main.py:248)
+                lim = getattr(self, '_limit', None)
+                if lim is not None and self._rt.spec is not None:   # speculatively promoted rows are not visible yet
+                    P, X = P[:lim], X[:lim]
+            elif self._rt is _rt and getattr(self, '_prev', None) == self._rt.prev_token:
+                P, X = self._rt.ctx.get_prev_state()   # previous frame's state (main.py:248)
             else:
                 raise RuntimeError("stale DeviceState: the device landmarks have moved on to a later frame")
             dict.__setitem__(self, 'P', P)
@@ -191,6 +224,7 @@ class DeviceState(dict):
     def _rebind(self, version):
         dict.clear(self)
         self._version, self._dirty = version, False
+        self._limit = None
 
 
 class DeviceExtendedState(dict):
@@ -207,6 +241,8 @@ class DeviceExtendedState(dict):
         if not dict.__contains__(self, 'C'):
             if not self._current():
                 raise RuntimeError("stale DeviceExtendedState: the device candidates have moved on")
+            self._rt.drop_speculation()
+            self._rt.flush_pending_add()
             C, F, T = self._rt.ctx.get_candidates()
             dict.__setitem__(self, 'C', C.astype(np.float64))
             dict.__setitem__(self, 'F', F)
@@ -261,6 +297,7 @@ def _sync_state_to_device(rt, state):
 def _sync_ext_to_device(rt, ext):
     if isinstance(ext, DeviceExtendedState) and ext._current():
         return
+    rt.pending_add = None     # superseded: the caller's arrays are the authority now
     C = np.asarray(ext['C'], np.float64).reshape(-1, 2)
     F = np.asarray(ext['F'], np.float64).reshape(-1, 2)
     T = np.asarray(ext['T'], np.float64).reshape(-1, 4, 4)
@@ -345,15 +382,18 @@ class KeypointsToLandmarksAssociator():
         """KLT of state['P'] from old_frame to new_frame; returns (new_state, points_tracking_lost)
         with new_state = rows of P (new positions, float32) and X whose status is 1."""
         rt = _runtime(new_frame)
-        k_old, k_new = rt.frame_key(old_frame), rt.frame_key(new_frame)
+        rt.drop_speculation()      # estimatePose without a matching triangulate_landmark
+        k_old, k_new = rt.frame_key(old_frame), rt.frame_key(new_frame)   # upload + pyramid first
+        rt.pair = (old_frame, new_frame, k_old, k_new)
+        rt.flush_pending_add()     # last frame's new candidates must be tracked from this frame on
         _sync_state_to_device(rt, state)
+        rt.prev_token += 1
         if not isinstance(state, DeviceState):
             state['P'] = np.asarray(state['P']).astype(np.float32)   # reference side effect (vo:214)
         elif not dict.__contains__(state, 'P'):
-            # the caller may still read this (now previous) state after the device has moved on
-            rt.ctx.snapshot_state()
-            rt.snap_id += 1
-            state._snap = rt.snap_id
+            # the caller may still read this (now previous) state after the device has moved on:
+            # the third landmark buffer keeps it until the next tracking step
+            state._prev = rt.prev_token
         rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt)
         rt.state_version += 1
         return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
@@ -412,19 +452,37 @@ class PoseEstimator():
         """PnP-RANSAC + LM refit over associations{'P','X'}; prunes associations to the inliers in
         place and returns the 4x4 world->camera pose (host ndarray: main.py:239 inverts it)."""
         rt = _runtime()
+        rt.drop_speculation()
+        uploaded = not (isinstance(associations, DeviceState) and associations._current())
         _sync_state_to_device(rt, associations)
-        ok, T, n_inl = rt.ctx.pnp_ransac(self.K, self._params())
+        # The promotion step of triangulate_landmark does not need the host: enqueue it ahead of the
+        # sync this method ends in, with the pose taken from the device, and let triangulate_landmark
+        # confirm it when its arguments are the ones assumed (main.py always passes them).
+        method = config['find_new_candidates_method']
+        speculate = (bool(_cfg('speculative_promotion')) and not uploaded and method in ('feed', 'sift-sift')
+                     and rt.pair is not None and rt.ctx.candidates_tracked(rt.pair[2], rt.pair[3]))
+        if speculate:
+            alpha = float(_alpha_threshold())
+            ok, T, n_inl, _ = rt.ctx.pnp_ransac_promote(self.K, self._params(), alpha)
+        else:
+            ok, T, n_inl = rt.ctx.pnp_ransac(self.K, self._params())
         self.last = {'ok': ok, 'n_inliers': n_inl}
         if config.get('debug'):
             print('len inliers', n_inl)
         if not ok or n_inl < 4:
+            rt.drop_speculation()      # (no model: already rolled back inside the library)
             return self._rebootstrap(associations, img_idx)
         rt.state_version += 1
         if isinstance(associations, DeviceState):
             associations._rebind(rt.state_version)
         else:   # a plain dict was passed: prune it on the host too
             P, X = rt.ctx.get_state()
-            associations['P'], associations['X'] = P, X
+            associations['P'], associations['X'] = P[:n_inl], X[:n_inl]
+        if speculate:
+            rt.spec = {'T': T.copy(), 'alpha': alpha, 'K': np.array(self.K, np.float64), 'pair': rt.pair,
+                       'state_version': rt.state_version, 'ext_version': rt.ext_version}
+            if isinstance(associations, DeviceState):
+                associations._limit = n_inl
         return T
 
     def _rebootstrap(self, associations, img_idx):
@@ -514,27 +572,42 @@ class LandmarkTriangulator():
         with (T, new_pose), append it to state P/X and remove it from C/F/T.
         Returns (state, extended_state, cur_des)."""
         rt = _runtime(new_frame)
-        k_old, k_new = rt.frame_key(old_frame), rt.frame_key(new_frame)
-        _sync_state_to_device(rt, state)
-        if not isinstance(extended_state, DeviceExtendedState) and len(np.asarray(extended_state['C'])) == 0:
-            extended_state = {'C': np.zeros((0, 2)), 'F': np.zeros((0, 2)), 'T': np.zeros((0, 4, 4))}   # main.py:185-188
-        _sync_ext_to_device(rt, extended_state)
         method = config['find_new_candidates_method']
-        threshold = 1
-        if method == 'sift-sift':
-            threshold = config['sift_alpha']
-        if method == 'shi-mask':
-            threshold = config['shi_alpha']
+        threshold = _alpha_threshold()
         new_pose = np.ascontiguousarray(new_pose, np.float64)
+        sp = rt.spec
+        if isinstance(extended_state, DeviceExtendedState):
+            ext_ok = extended_state._current()
+        else:   # first frame: main.py passes empty numpy arrays (main.py:185-188); the ctx is fresh and empty too
+            ext_ok = rt.ext_version == 0 and len(np.asarray(extended_state['C'])) == 0
+        confirmed = (sp is not None and ext_ok and sp['ext_version'] == rt.ext_version
+                     and isinstance(state, DeviceState) and state._current()
+                     and state._version == sp['state_version'] and sp['pair'] is rt.pair
+                     and rt.pair[0] is old_frame and rt.pair[1] is new_frame
+                     and float(threshold) == sp['alpha'] and np.array_equal(new_pose, sp['T'])
+                     and np.array_equal(np.asarray(self.K, np.float64), sp['K']))
+        if confirmed:
+            # the promotion ran ahead of estimatePose's sync with exactly these arguments
+            rt.spec = None
+            rt.ctx.promote_commit()
+        else:
+            rt.drop_speculation()
+            k_old, k_new = rt.pair_keys(old_frame, new_frame)
+            rt.flush_pending_add()
+            _sync_state_to_device(rt, state)
+            if not isinstance(extended_state, DeviceExtendedState) and len(np.asarray(extended_state['C'])) == 0:
+                extended_state = {'C': np.zeros((0, 2)), 'F': np.zeros((0, 2)), 'T': np.zeros((0, 4, 4))}   # main.py:185-188
+            _sync_ext_to_device(rt, extended_state)
 
-        # 1) + 3) on the device: candidate KLT (already done with the landmarks' launch when the same
-        # frame pair went through associateKeypointsToLandmarks), removal, bearing test, DLT, promotion
-        rt.ctx.track_candidates(k_old, k_new, rt.klt)
+            # 1) + 3) on the device: candidate KLT (already done with the landmarks' launch when the same
+            # frame pair went through associateKeypointsToLandmarks), removal, bearing test, DLT, promotion
+            rt.ctx.track_candidates(k_old, k_new, rt.klt)
         well_tracked_prev = []
         if method in ('shi-mask', 'sift-mask'):
             prev, _, st = rt.ctx.candidate_tracks()          # the detectors mask these pixels
             well_tracked_prev = prev[st == 1]
-        rt.ctx.track_triangulate_promote(k_old, k_new, self.K, new_pose, float(threshold), rt.klt)
+        if not confirmed:
+            rt.ctx.track_triangulate_promote(k_old, k_new, self.K, new_pose, float(threshold), rt.klt)
 
         # 2) new candidates: CPU detectors run while the GPU works on the promotion
         new_candidates_list, cur_des = [], []
@@ -547,7 +620,8 @@ class LandmarkTriangulator():
         elif method == 'feed':   # pre-generated candidate feed (benchmarks / tests)
             new_candidates_list = _candidate_feed.pop(0) if _candidate_feed else []
         if len(new_candidates_list) > 0:
-            rt.ctx.add_candidates(np.asarray(new_candidates_list, np.float64), np.eye(4) @ new_pose)
+            # appended on the device when the next frame has been uploaded (or when someone looks)
+            rt.pending_add = (np.array(new_candidates_list, np.float64), np.eye(4) @ new_pose)
 
         rt.state_version += 1
         rt.ext_version += 1
@@ -560,6 +634,16 @@ class LandmarkTriangulator():
         else:
             extended_state = DeviceExtendedState(rt, rt.ext_version)
         return (state, extended_state, cur_des)
+
+
+def _alpha_threshold():
+    """Bearing-angle threshold in degrees (reference vo_pipeline.py:608-612)."""
+    method = config['find_new_candidates_method']
+    if method == 'sift-sift':
+        return config['sift_alpha']
+    if method == 'shi-mask':
+        return config['shi_alpha']
+    return 1
 
 
 # candidate feed for find_new_candidates_method == 'feed': a list of (n x 2) arrays, one per frame

@@ -39,6 +39,7 @@ def drive_dropin(vo, sq, read_prev_state=True):
         vision.state, vision.extended_state = new_state, ext
         img1 = img2
         Ts.append(new_pose)
+        vo._runtime().flush_pending_add()      # the append is deferred to the next frame's upload
         cnt = vo._runtime().ctx.counters()
         nP.append(cnt["n_landmarks"]); nC.append(cnt["n_candidates"])
     return np.array(Ts), np.array(nP), np.array(nC), vision
@@ -122,6 +123,105 @@ def test_fused_frame_equals_staged_calls(pkg, scene_mod):
             assert np.array_equal(u, v)
     finally:
         a.close(); b.close()
+
+
+def test_speculative_promotion_commit_and_rollback(pkg, scene_mod):
+    """vo_pnp_ransac_promote (+commit) == vo_pnp_ransac + vo_track_triangulate_promote, bit for bit; a
+    rollback restores the state exactly as vo_pnp_ransac leaves it, and the staged promotion can then
+    still run on the pending candidate tracking."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    K = sq.K
+    pnp = pkg.pnp_defaults()
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)   # staged
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)   # speculative, alternating commit / rollback
+    try:
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        for k in range(1, 14):
+            for c in (a, b):
+                c.upload_frame(sq.frames[k], k + 1)
+                c.klt_track_landmarks(k, k + 1)
+            ok, Ta, ninl = a.pnp_ransac(K, pnp)
+            Pa0, Xa0 = a.get_state()                     # pruned to the inliers, nothing promoted yet
+            Ca0 = a.get_candidates()
+            assert b.candidates_tracked(k, k + 1)
+            okb, Tb, ninlb, nprom = b.pnp_ransac_promote(K, pnp, 1.0)
+            assert ok and okb and ninl == ninlb and np.array_equal(Ta, Tb) and b.promote_pending()
+            if k % 2 == 0:
+                b.promote_rollback()
+                assert not b.promote_pending()
+                Pb0, Xb0 = b.get_state()
+                assert np.array_equal(Pa0, Pb0) and np.array_equal(Xa0, Xb0)
+                for u, v in zip(Ca0, b.get_candidates()):
+                    assert np.array_equal(u, v)
+                b.track_triangulate_promote(k, k + 1, K, Tb, 1.0)
+            else:
+                Pb, Xb = b.get_state()                   # promoted rows sit behind the inlier rows
+                assert np.array_equal(Pb[:ninl], Pa0) and np.array_equal(Xb[:ninl], Xa0) and len(Pb) == ninl + nprom
+                b.promote_commit()
+            a.track_triangulate_promote(k, k + 1, K, Ta, 1.0)
+            for c in (a, b):
+                c.add_candidates(sq.feeds[k], Ta)
+            ca, cb = a.counters(), b.counters()
+            for key in ("n_landmarks", "n_candidates", "n_promoted", "n_candidates_lost", "cf_alias"):
+                assert ca[key] == cb[key], (k, key)
+            Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+            assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+            for u, v in zip(a.get_candidates(), b.get_candidates()):
+                assert np.array_equal(u, v)
+            # the state this frame started from is still readable (main.py:248)
+            Pp, Xp = b.get_prev_state()
+            assert len(Pp) == prev_rows if k > 1 else len(Pp) == len(sq.P0)
+            assert np.array_equal(Xp, prev_X)  if k > 1 else np.array_equal(Xp, sq.X0)
+            prev_rows, prev_X = len(Pb), Xb
+    finally:
+        a.close(); b.close()
+
+
+def test_dropin_speculation_is_transparent(dropin, scene_mod):
+    """The drop-in classes give the same poses and states with the speculative promotion on and off,
+    and the previous frame's state (main.py:248) is served with the right content either way."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    runs = []
+    for spec in (True, False):
+        dropin.config['speculative_promotion'] = spec
+        dropin._reset_runtime()
+        dropin.set_candidate_feed([f.copy() for f in sq.feeds[1:]])
+        vision = dropin.BestVision(sq.K)
+        vision.state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+        vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+        associate = dropin.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+        pose_estimator = dropin.PoseEstimator(sq.K)
+        Ts, prevX, endX = [], [], []
+        img1 = sq.frames[0]
+        for k in range(1, 16):
+            img2 = sq.frames[k]
+            new_state, _ = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
+            new_pose = pose_estimator.estimatePose(new_state, k)
+            prevX.append(np.array(vision.state["X"]))            # previous state, read late
+            if k % 5 == 0:
+                mid = np.array(new_state["X"])                       # inlier rows only, even while a speculation is pending
+                assert len(mid) == pose_estimator.last['n_inliers']
+            tri = dropin.LandmarkTriangulator(sq.K, None)
+            vision.state, vision.extended_state, _ = tri.triangulate_landmark(img1, img2, new_state, vision.extended_state, new_pose)
+            if k % 3 == 0:
+                endX.append(np.array(vision.state["X"]))         # current state, read early
+            img1 = img2
+            Ts.append(new_pose)
+        C, F, T = (np.array(vision.extended_state[key]) for key in "CFT")
+        runs.append((np.array(Ts), prevX, endX, np.array(vision.state["P"]), C, F, T))
+    dropin.config.pop('speculative_promotion')
+    on, off = runs
+    assert np.array_equal(on[0], off[0])
+    for u, v in zip(on[1] + on[2], off[1] + off[2]):
+        assert np.array_equal(u, v)
+    for i in range(3, 7):
+        assert np.array_equal(on[i], off[i])
+    # content of the late read: frame k's previous state == frame k-1's end state
+    assert np.array_equal(on[1][3], on[2][0]) and np.array_equal(on[1][6], on[2][1])
+    assert np.array_equal(on[1][0], sq.X0)
 
 
 def test_state_roundtrip_and_edge_cases(ctx):
