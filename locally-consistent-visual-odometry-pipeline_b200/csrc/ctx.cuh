@@ -236,6 +236,8 @@ struct PnpLaunch {
     bool compact;                       // prune landmark buffers to the inliers (estimatePose)
 };
 int launch_pnp(Ctx* c, const PnpLaunch& L);
+// raw cv::RNG output table on the device, large enough for H iterations (grows, never shrinks)
+int ensure_rng_table(Ctx* c, int H);
 // tri.cu
 int launch_landmark_compact(Ctx* c, int n_upper);   // after KLT: keep status==1, pack q4/qv
 // Tnew == nullptr: take the pose the last PnP left on the device (fused per-frame call)

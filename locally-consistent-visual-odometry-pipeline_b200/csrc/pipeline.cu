@@ -3,6 +3,7 @@
 // plus unit-level entry points that mirror the cv2 signatures for differential tests.
 #include <math.h>
 #include "ctx.cuh"
+#include "pnp_sets.cuh"
 
 namespace vo {
 
@@ -103,15 +104,19 @@ __global__ void expand_poses_kernel(const int32_t* __restrict__ Ti, const double
 }
 
 __global__ void pack_points_kernel(DevScalars* sc, const double* __restrict__ X, const float2* __restrict__ P, int n,
-                                   int from_state, float4* __restrict__ q4, float* __restrict__ qv)
+                                   int from_state, float4* __restrict__ q4, float* __restrict__ qv,
+                                   int32_t* __restrict__ sets, vo::RngTab rt)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int m = from_state ? min(sc->n_land, n) : n;
     if (i == 0) sc->n_tracked = m;
-    if (i >= m) return;
-    const float2 p = P[i];
-    q4[i] = make_float4((float)X[3 * (size_t)i], (float)X[3 * (size_t)i + 1], (float)X[3 * (size_t)i + 2], p.x);
-    qv[i] = p.y;
+    if (i < m) {
+        const float2 p = P[i];
+        q4[i] = make_float4((float)X[3 * (size_t)i], (float)X[3 * (size_t)i + 1], (float)X[3 * (size_t)i + 2], p.x);
+        qv[i] = p.y;
+    }
+    // the point count of the coming PnP-RANSAC is known: draw its first minimal sets here
+    if (blockIdx.x == 0 && threadIdx.x < 32) vo::pnp_prepare_sets(sc, sets, rt, m);
 }
 
 #define VO_NEED(c) do { if (!(c) || !(c)->pipe) return VO_ERR_INVALID; } while (0)
@@ -326,8 +331,10 @@ int vo_pnp_ransac(vo_ctx* c, const double K[9], const vo_pnp_params* params, dou
     if (!p->packed_valid) {   // no tracking step preceded (state set directly): pack P/X now
         const size_t m = p->n_land_upper > 0 ? p->n_land_upper : 1;
         VO_TRY(ensure(c, p->q4, m * 4)); VO_TRY(ensure(c, p->qv, m));
+        VO_TRY(ensure_rng_table(c, p->hyp_capacity));
         pack_points_kernel<<<(int)((m + 255) / 256), 256, 0, c->stream>>>(p->d_sc, p->X[p->cur].p, (const float2*)p->P[p->cur].p,
-                                                                          p->n_land_upper, 1, (float4*)p->q4.p, p->qv.p);
+                                                                          p->n_land_upper, 1, (float4*)p->q4.p, p->qv.p, p->sets.p,
+                                                                          RngTab{ p->rng_tab.p, p->rng_tab_len });
         c->launches++;
     }
     L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
@@ -631,8 +638,10 @@ int vo_solve_pnp_ransac(vo_ctx* c, const double* X, const float* P, int n, const
         VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p, X, sizeof(double) * 3 * n, cudaMemcpyDefault, c->stream));
         VO_CUDA(c, cudaMemcpyAsync(p->stage_f.p, P, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
     }
+    VO_TRY(ensure_rng_table(c, p->hyp_capacity));
     pack_points_kernel<<<(int)((m + 255) / 256), 256, 0, c->stream>>>(p->d_sc, p->stage_d.p, (const float2*)p->stage_f.p, n, 0,
-                                                                      (float4*)p->q4.p, p->qv.p);
+                                                                      (float4*)p->q4.p, p->qv.p, p->sets.p,
+                                                                      RngTab{ p->rng_tab.p, p->rng_tab_len });
     c->launches++;
     if (minimal_sets) {
         const size_t H = L.prm.max_iters > 0 ? L.prm.max_iters : 1;

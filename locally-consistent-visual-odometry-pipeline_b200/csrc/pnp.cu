@@ -18,13 +18,14 @@
 // No tensor cores: FP64 CUDA-core work (P3P, projection) and FP32 compares.
 #include <float.h>
 #include "ctx.cuh"
+#include "pnp_sets.cuh"
 
 namespace vo {
 
 namespace {
 
-constexpr int kHypThreads = 256;
-constexpr int kFinThreads = 512;
+constexpr int kHypThreads = 256;      // threads of a RANSAC CTA (hypothesis scoring, and the refit by the last CTA)
+constexpr int kFinThreads = kHypThreads;
 
 struct PnpArgs {
     double K[9];
@@ -36,71 +37,6 @@ struct PnpArgs {
     int explicit_sets;
     int compact;
 };
-
-// ---- cv::RNG -----------------------------------------------------------------------------------
-// cv::RNG is a multiply-with-carry generator: strictly sequential, but its raw 32-bit output
-// stream does not depend on the data (the seed is fixed at 2^64-1 inside RANSAC's run()).  The
-// host tabulates the stream once (rng_table_host); the device turns it into minimal sets with
-// `% n` and the duplicate re-draws of getSubset, 32 sets per step.
-struct RngTab { const uint32_t* tab; int len; };
-
-// rows [sc->sets_ready, to) of the minimal-set table, exactly as getSubset draws them.
-// Called by one full warp.  Optimistic step: lane l assumes sets h..h+l-1 needed no re-draw and
-// reads draws pos+4l..pos+4l+3; the prefix of lanes for which that held is committed, the first
-// set with a duplicate is drawn serially by lane 0.
-__device__ void gen_sets_warp(DevScalars* sc, int32_t* sets, RngTab rt, int n, int to)
-{
-    const int lane = threadIdx.x & 31;
-    int h = sc->sets_ready;
-    long long pos = (long long)sc->rng;
-    int exhausted = 0;
-    while (h < to && !exhausted) {
-        const int cnt = min(32, to - h);
-        bool ok = false;
-        int4 v = make_int4(0, 0, 0, 0);
-        const long long p0 = pos + 4 * lane;
-        if (lane < cnt && p0 + 3 < rt.len) {
-            v.x = (int)(rt.tab[p0] % (unsigned)n);
-            v.y = (int)(rt.tab[p0 + 1] % (unsigned)n);
-            v.z = (int)(rt.tab[p0 + 2] % (unsigned)n);
-            v.w = (int)(rt.tab[p0 + 3] % (unsigned)n);
-            ok = v.y != v.x && v.z != v.x && v.z != v.y && v.w != v.x && v.w != v.y && v.w != v.z;
-        }
-        const unsigned bad = __ballot_sync(0xffffffffu, lane < cnt && !ok);
-        const int good = bad ? __ffs(bad) - 1 : cnt;
-        if (lane < good) reinterpret_cast<int4*>(sets)[h + lane] = v;
-        h += good; pos += 4 * good;
-        if (good < cnt) {   // set h: serial draw with re-draws (or the table ran out)
-            long long np = pos;
-            int fail = 0;
-            if (lane == 0) {
-                int idx[kMinimal];
-#pragma unroll
-                for (int i = 0; i < kMinimal; i++) {
-                    for (;;) {
-                        if (np >= rt.len) { fail = 1; break; }
-                        const int x = (int)(rt.tab[np++] % (unsigned)n);
-                        bool dup = false;
-#pragma unroll
-                        for (int j = 0; j < kMinimal; j++) dup |= (j < i) && idx[j] == x;
-                        if (!dup) { idx[i] = x; break; }
-                    }
-                    if (fail) break;
-                }
-                if (!fail) reinterpret_cast<int4*>(sets)[h] = make_int4(idx[0], idx[1], idx[2], idx[3]);
-            }
-            exhausted = __shfl_sync(0xffffffffu, fail, 0);
-            pos = __shfl_sync(0xffffffffu, np, 0);
-            if (!exhausted) h++;
-        }
-    }
-    __syncwarp();
-    if (lane == 0) {
-        sc->rng = (uint64_t)pos;
-        sc->sets_ready = exhausted ? to : h;   // rows past h stay unset; rng_exhausted aborts the run
-        if (exhausted) sc->rng_exhausted = 1;
-    }
-}
 
 // RANSACUpdateNumIters
 __device__ int update_num_iters(double p, double ep, int model_points, int max_iters)
@@ -355,100 +291,36 @@ __device__ bool p3p4_quad(const double* X, const double* p, const double* K, dou
     return win == q;
 }
 
-// ---- kernels -----------------------------------------------------------------------------------
-__global__ void pnp_init_kernel(DevScalars* sc, int32_t* sets, const int32_t* d_n, PnpArgs a, RngTab rt, int chunk0_end)
+// ---- RANSAC bookkeeping ------------------------------------------------------------------------
+// One warp: the sequential rule of the reference loop (first strictly-better model wins, the
+// iteration budget shrinks with every new best) replayed over the counts of hypotheses [h0, h1).
+// `first` initialises the run; when the budget is not exhausted the minimal sets of the next
+// chunk are drawn.
+__device__ void ransac_select(DevScalars* sc, int32_t* sets, const int32_t* counts, const PnpArgs& a, RngTab rt,
+                              int n, int first, int h0, int h1, int next_end, int last)
 {
-    // one warp
-    const int n = d_n ? min(*d_n, a.n_upper) : a.n_upper;
-    __syncwarp();
-    if (threadIdx.x == 0) {
-        sc->n_tracked = n;
-        sc->niters = a.max_iters; sc->best_count = 0; sc->best_hyp = -1; sc->iters_run = 0; sc->done = 0;
-        sc->sets_ready = 0; sc->rng = 0; sc->ok = 0; sc->n_inliers = 0; sc->lm_iters = 0; sc->rng_exhausted = 0;
-        if (n < kMinimal || a.max_iters <= 0) { sc->niters = 0; sc->done = 1; }
-        else if (n == kMinimal) {   // cv2: count == modelPoints -> one direct solve on all points
-            reinterpret_cast<int4*>(sets)[0] = make_int4(0, 1, 2, 3);
-            sc->niters = 1; sc->sets_ready = a.max_iters;
-        }
+    const int lane = threadIdx.x & 31;
+    int niters, best, best_hyp, done;
+    if (first) {
+        niters = (n < kMinimal || a.max_iters <= 0) ? 0 : (n == kMinimal ? 1 : a.max_iters);
+        best = 0; best_hyp = -1; done = niters == 0;
+    } else {
+        niters = sc->niters; best = sc->best_count; best_hyp = sc->best_hyp; done = sc->done;
     }
-    __syncwarp();
-    if (n > kMinimal && a.max_iters > 0 && !a.explicit_sets) gen_sets_warp(sc, sets, rt, n, chunk0_end);
-}
-
-// one CTA per hypothesis: lanes 0-3 solve P3P, the CTA scores all points
-__global__ void __launch_bounds__(kHypThreads)
-pnp_hyp_kernel(const DevScalars* __restrict__ sc, const int32_t* __restrict__ sets, const float4* __restrict__ q4,
-               const float* __restrict__ qv, double* __restrict__ hyp, int32_t* __restrict__ counts, PnpArgs a, int h0)
-{
-    const int h = h0 + blockIdx.x;
-    if (h >= sc->niters) return;   // beyond the (shrinking) iteration budget: never looked at
-    const int n = sc->n_tracked;
-    __shared__ double sRt[12];
-    __shared__ int sValid;
-    __shared__ int sCount[kHypThreads / 32];
-    if (threadIdx.x < 4) {   // a quad of lanes solves the minimal problem
-        const int4 s = reinterpret_cast<const int4*>(sets)[h];
-        const int idx[4] = { s.x, s.y, s.z, s.w };
-        double X[12], p[8];
-        bool ok = true;
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            ok &= idx[k] >= 0 && idx[k] < n;
-            const int i = ok ? idx[k] : 0;
-            const float4 q = q4[i];
-            X[3 * k] = q.x; X[3 * k + 1] = q.y; X[3 * k + 2] = q.z;
-            p[2 * k] = q.w; p[2 * k + 1] = qv[i];
-        }
-        double Rt[12];
-        bool found = false;
-        const bool winner = ok && p3p4_quad(X, p, a.K, Rt, threadIdx.x, 0xFu, &found);
-        if (threadIdx.x == 0) sValid = ok && found;
-        if (winner) {
-#pragma unroll
-            for (int i = 0; i < 12; i++) { sRt[i] = Rt[i]; hyp[(size_t)h * 12 + i] = Rt[i]; }
-        }
+    if (done) {
+        if (lane == 0 && first) { sc->niters = 0; sc->best_count = 0; sc->best_hyp = -1; sc->done = 1; sc->iters_run = 0; }
+        return;
     }
-    __syncthreads();
-    if (!sValid) { if (threadIdx.x == 0) counts[h] = -1; return; }
-    double R[9], t[3];
-#pragma unroll
-    for (int i = 0; i < 9; i++) R[i] = sRt[i];
-#pragma unroll
-    for (int i = 0; i < 3; i++) t[i] = sRt[9 + i];
-    int good = 0;
-    for (int i = threadIdx.x; i < n; i += kHypThreads) {
-        const float4 q = q4[i];
-        good += reproj_err2(R, t, a.K, q.x, q.y, q.z, q.w, qv[i]) <= a.thr2;
-    }
-    good = __reduce_add_sync(0xffffffffu, good);
-    if ((threadIdx.x & 31) == 0) sCount[threadIdx.x >> 5] = good;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int s = 0;
-#pragma unroll
-        for (int w = 0; w < kHypThreads / 32; w++) s += sCount[w];
-        counts[h] = s;
-    }
-}
-
-// one warp: sequential RANSAC bookkeeping over the counts of hypotheses [h0, h1)
-__global__ void pnp_select_kernel(DevScalars* sc, int32_t* sets, const int32_t* __restrict__ counts, PnpArgs a,
-                                  RngTab rt, int h0, int h1, int next_end, int last)
-{
-    if (sc->done) return;
-    const int lane = threadIdx.x;
-    const int n = sc->n_tracked;
-    int niters = sc->niters, best = sc->best_count, best_hyp = sc->best_hyp;
-    int h = h0, done = 0;
+    int h = h0;
     while (h < h1) {
         if (h >= niters) { done = 1; break; }
         const int lim = min(h1, niters);
-        const int c = (h + lane < lim) ? counts[h + lane] : -1;
+        const int c = (h + lane < lim) ? __ldcg(counts + h + lane) : -1;
         const unsigned m = __ballot_sync(0xffffffffu, c > max(best, kMinimal - 1));
         if (!m) { h += 32; continue; }
-        const int first = __ffs(m) - 1;
-        best = __shfl_sync(0xffffffffu, c, first);
-        best_hyp = h + first;
+        const int f = __ffs(m) - 1;
+        best = __shfl_sync(0xffffffffu, c, f);
+        best_hyp = h + f;
         niters = n == kMinimal ? niters : update_num_iters(a.confidence, (double)(n - best) / n, kMinimal, niters);
         h = best_hyp + 1;
     }
@@ -471,10 +343,15 @@ struct FinalizeBufs {
 
 __device__ __forceinline__ void so3_exp(const double* w, double* R)
 {
-    const double th2 = dot3(w, w), th = sqrt(th2);
+    const double th2 = dot3(w, w);
     double A, B;
-    if (th < 1e-8) { A = 1. - th2 / 6.; B = 0.5 - th2 / 24.; }
-    else { A = sin(th) / th; B = (1. - cos(th)) / th2; }
+    if (th2 < 1e-4) {   // LM steps are small: series to th^8 (error < 1e-21), no sqrt / sin / cos on the chain
+        A = 1. + th2 * (-1. / 6. + th2 * (1. / 120. + th2 * (-1. / 5040. + th2 * (1. / 362880.))));
+        B = 0.5 + th2 * (-1. / 24. + th2 * (1. / 720. + th2 * (-1. / 40320. + th2 * (1. / 3628800.))));
+    } else {
+        const double th = sqrt(th2);
+        A = sin(th) / th; B = (1. - cos(th)) / th2;
+    }
     const double wx = w[0], wy = w[1], wz = w[2];
     R[0] = 1. - B * (wy * wy + wz * wz); R[1] = B * wx * wy - A * wz;       R[2] = B * wx * wz + A * wy;
     R[3] = B * wx * wy + A * wz;        R[4] = 1. - B * (wx * wx + wz * wz); R[5] = B * wy * wz - A * wx;
@@ -523,7 +400,7 @@ constexpr int kAcc = 28;  // 21 (lower triangle of JtJ) + 6 (Jt r) + 1 (cost)
 // accumulate JtJ, Jt r and the cost at pose Rt over the masked points; result in sAcc (all threads
 // see it after the trailing __syncthreads)
 __device__ void lm_accumulate(const double* Rt, const double* K, const float4* __restrict__ q4,
-                              const float* __restrict__ qv, const uint8_t* __restrict__ mask, int n,
+                              const float* __restrict__ qv, const uint8_t* mask, int n,
                               double (*sPart)[kAcc], double* sAcc)
 {
     double acc[32];   // kAcc used, padded to the warp width for the halving reduction
@@ -579,9 +456,8 @@ __device__ void lm_accumulate(const double* Rt, const double* K, const float4* _
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(kFinThreads)
-pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4* __restrict__ q4,
-                    const float* __restrict__ qv, uint8_t* __restrict__ mask, PnpArgs a, FinalizeBufs fb)
+__device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __restrict__ q4,
+                             const float* __restrict__ qv, uint8_t* mask, const PnpArgs& a, const FinalizeBufs& fb, int n)
 {
     __shared__ double sPart[kFinThreads / 32][kAcc];
     __shared__ double sAcc[kAcc];
@@ -592,13 +468,12 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
     __shared__ int sWarpTot[kFinThreads / 32];
     __shared__ int sBase;
     const int tid = threadIdx.x;
-    const int n = sc->n_tracked;
     const int best = sc->best_hyp;
     const bool ok = best >= 0;
 
     int ninl = 0;
     if (ok) {
-        if (tid < 12) sRt[tid] = hyp[(size_t)best * 12 + tid];
+        if (tid < 12) sRt[tid] = __ldcg(hyp + (size_t)best * 12 + tid);
         __syncthreads();
         double R[9], t[3];
 #pragma unroll
@@ -617,7 +492,7 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
         if (tid == 0) {
             for (int i = 0; i < 21; i++) sH[i] = sAcc[i];
             for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
-            sCost = sAcc[27]; sLambda = 1e-3; sState = 0; sFails = 0; sIters = 0;
+            sCost = sAcc[27]; sLambda = 1e-6; sState = 0; sFails = 0; sIters = 0;
         }
         __syncthreads();
         while (sIters < a.refine_iters) {
@@ -685,12 +560,13 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
                 sc->T[4 * r + 3] = sRt[9 + r];
             }
             sc->T[12] = 0.; sc->T[13] = 0.; sc->T[14] = 0.; sc->T[15] = 1.;
-            for (int i = 0; i < 12; i++) sc->Th[i] = hyp[(size_t)best * 12 + i];
+            for (int i = 0; i < 12; i++) sc->Th[i] = __ldcg(hyp + (size_t)best * 12 + i);
             sc->cost = sCost; sc->lm_iters = sIters;
         }
     } else {
         for (int i = tid; i < n; i += kFinThreads) mask[i] = 0;
         if (tid < 16) sc->T[tid] = 0.;
+        if (tid == 0) sc->lm_iters = 0;
         __syncthreads();
     }
     if (tid == 0) { sc->ok = ok; sc->n_inliers = ninl; }
@@ -722,12 +598,94 @@ pnp_finalize_kernel(DevScalars* sc, const double* __restrict__ hyp, const float4
     if (tid == 0) sc->n_land = sBase;
 }
 
+// ---- the RANSAC kernel -----------------------------------------------------------------------------
+// One CTA per hypothesis of the chunk [h0, h0 + gridDim.x): lanes 0-3 solve P3P, the CTA scores all
+// points.  The last CTA to finish (ticket) replays the sequential bookkeeping over the chunk's
+// counts and, for the final chunk, goes on to the refit and the pruning - so a RANSAC that ends
+// inside its first chunk (the usual case) is ONE launch, with no set-up, selection or refit
+// launches around it.
+__global__ void __launch_bounds__(kHypThreads)
+pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, const float* __restrict__ qv,
+                 double* hyp, int32_t* counts, uint8_t* mask, PnpArgs a, RngTab rt, FinalizeBufs fb,
+                 int h0, int h1, int next_end, int first, int last)
+{
+    __shared__ double sRt[12];
+    __shared__ int sValid, sLast;
+    __shared__ int sCount[kHypThreads / 32];
+    const int tid = threadIdx.x;
+    const int h = h0 + blockIdx.x;
+    const int n = min(sc->n_tracked, a.n_upper);
+    // the first chunk lies inside the initial budget by construction; later chunks see the budget the
+    // previous chunk's bookkeeping left (hypotheses beyond it are never looked at)
+    const bool active = first ? (n >= kMinimal && h < (n == kMinimal ? 1 : a.max_iters)) : (!sc->done && h < sc->niters);
+    if (active) {
+        if (tid < 4) {   // a quad of lanes solves the minimal problem
+            int4 s = n == kMinimal ? make_int4(0, 1, 2, 3) : reinterpret_cast<const int4*>(sets)[h];
+            const int idx[4] = { s.x, s.y, s.z, s.w };
+            double X[12], p[8];
+            bool ok = true;
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                ok &= idx[k] >= 0 && idx[k] < n;
+                const int i = ok ? idx[k] : 0;
+                const float4 q = q4[i];
+                X[3 * k] = q.x; X[3 * k + 1] = q.y; X[3 * k + 2] = q.z;
+                p[2 * k] = q.w; p[2 * k + 1] = qv[i];
+            }
+            double Rt[12];
+            bool found = false;
+            const bool winner = ok && p3p4_quad(X, p, a.K, Rt, tid, 0xFu, &found);
+            if (tid == 0) sValid = ok && found;
+            if (winner) {
+#pragma unroll
+                for (int i = 0; i < 12; i++) { sRt[i] = Rt[i]; hyp[(size_t)h * 12 + i] = Rt[i]; }
+            }
+        }
+        __syncthreads();
+        if (sValid) {
+            double R[9], t[3];
+#pragma unroll
+            for (int i = 0; i < 9; i++) R[i] = sRt[i];
+#pragma unroll
+            for (int i = 0; i < 3; i++) t[i] = sRt[9 + i];
+            int good = 0;
+            for (int i = tid; i < n; i += kHypThreads) {
+                const float4 q = q4[i];
+                good += reproj_err2(R, t, a.K, q.x, q.y, q.z, q.w, qv[i]) <= a.thr2;
+            }
+            good = __reduce_add_sync(0xffffffffu, good);
+            if ((tid & 31) == 0) sCount[tid >> 5] = good;
+            __syncthreads();
+            if (tid == 0) {
+                int s = 0;
+#pragma unroll
+                for (int w = 0; w < kHypThreads / 32; w++) s += sCount[w];
+                counts[h] = s;
+            }
+        } else if (tid == 0) counts[h] = -1;
+    }
+    // ---- chunk bookkeeping by the last CTA to get here --------------------------------------------
+    __syncthreads();
+    if (tid == 0) {
+        __threadfence();
+        sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
+    }
+    __syncthreads();
+    if (!sLast) return;
+    __threadfence();
+    if (tid < 32) ransac_select(sc, sets, counts, a, rt, n, first, h0, h1, next_end, last);
+    __syncthreads();
+    if (tid == 0) sc->ticket = 0;
+    if (!last) return;
+    pnp_finalize(sc, hyp, q4, qv, mask, a, fb, n);
+}
+
 }  // namespace
 
 // raw outputs of cv::RNG(2^64-1) in draw order; 16 draws per iteration + slack covers the re-draws
 // of getSubset with overwhelming margin (4 + O(1/n) are used); if it ever runs out the device sets
 // rng_exhausted and the host reports VO_ERR_CAPACITY
-static int ensure_rng_table(Ctx* c, int H)
+int ensure_rng_table(Ctx* c, int H)
 {
     Pipeline* p = c->pipe;
     const size_t need = (size_t)(H > 0 ? H : 1) * 16 + 1024;
@@ -764,28 +722,13 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
     VO_TRY(ensure(c, p->counts, (size_t)(H > 0 ? H : 1)));
     VO_TRY(ensure(c, p->mask, (size_t)(L.n_upper > 0 ? L.n_upper : 1)));
     int32_t* sets = const_cast<int32_t*>(L.d_sets_in);
-    if (!sets) {
-        VO_TRY(ensure(c, p->sets, (size_t)(H > 0 ? H : 1) * kMinimal));
-        sets = p->sets.p;
-    }
     RngTab rt{ nullptr, 0 };
-    if (!L.d_sets_in) {
+    if (!sets) {
+        // rows [0, kPnpChunk0) were drawn by the kernel that fixed the point count (compaction / packing)
+        VO_TRY(ensure(c, p->sets, (size_t)(H > kPnpChunk0 ? H : kPnpChunk0) * kMinimal, true));
+        sets = p->sets.p;
         VO_TRY(ensure_rng_table(c, H));
         rt.tab = p->rng_tab.p; rt.len = p->rng_tab_len;
-    }
-    // chunk boundaries: small first chunk (the adaptive stop usually ends inside it)
-    int bounds[kPnpChunks + 1] = { 0, H < 128 ? H : 128, H < 512 ? H : 512, H };
-    pnp_init_kernel<<<1, 32, 0, c->stream>>>(p->d_sc, sets, L.d_n, a, rt, bounds[1]);
-    c->launches++;
-    for (int k = 0; k < kPnpChunks; k++) {
-        const int h0 = bounds[k], h1 = bounds[k + 1];
-        if (h1 <= h0) continue;
-        const bool last = (h1 == H);
-        pnp_hyp_kernel<<<h1 - h0, kHypThreads, 0, c->stream>>>(p->d_sc, sets, (const float4*)L.q4, L.qv, p->hyp.p,
-                                                               p->counts.p, a, h0);
-        pnp_select_kernel<<<1, 32, 0, c->stream>>>(p->d_sc, sets, p->counts.p, a, rt, h0, h1,
-                                                   k + 2 <= kPnpChunks ? bounds[k + 2] : H, last ? 1 : 0);
-        c->launches += 2;
     }
     FinalizeBufs fb{};
     if (L.compact) {
@@ -795,8 +738,20 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         VO_TRY(ensure(c, p->X[nxt], (size_t)(L.n_upper > 0 ? L.n_upper : 1) * 3));
         fb.P_out = p->P[nxt].p; fb.X_out = p->X[nxt].p;
     }
-    pnp_finalize_kernel<<<1, kFinThreads, 0, c->stream>>>(p->d_sc, p->hyp.p, (const float4*)L.q4, L.qv, p->mask.p, a, fb);
-    c->launches++;
+    // chunks: the first is small (the adaptive stop usually ends inside it: one launch for the whole
+    // RANSAC), the others take up to 2048 hypotheses each
+    for (int h0 = 0, k = 0; k == 0 || h0 < H; k++) {
+        const int h1 = k == 0 ? (H < kPnpChunk0 ? H : kPnpChunk0) : (H - h0 < 2048 ? H : h0 + 2048);
+        const int next_end = H - h1 < 2048 ? H : h1 + 2048;
+        const int last = h1 >= H;
+        const int grid = h1 - h0 > 0 ? h1 - h0 : 1;
+        pnp_chunk_kernel<<<grid, kHypThreads, 0, c->stream>>>(p->d_sc, sets, (const float4*)L.q4, L.qv, p->hyp.p,
+                                                              p->counts.p, p->mask.p, a, rt, fb, h0, h1, next_end,
+                                                              k == 0 ? 1 : 0, last);
+        c->launches++;
+        h0 = h1;
+        if (last) break;
+    }
     if (L.compact) {
         const int nxt = (p->cur + 1) % 3;
         if (nxt == p->prev) p->prev = -1;   // pruning without a preceding tracking step reuses that buffer

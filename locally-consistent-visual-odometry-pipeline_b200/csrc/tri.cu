@@ -12,6 +12,7 @@
 // vector of the smallest singular value; here one-sided Jacobi in FP64 (FP32 misses the 1e-4 gate).
 // All compactions are order-preserving (prefix sums), so row order equals the reference's.
 #include "ctx.cuh"
+#include "pnp_sets.cuh"
 
 namespace vo {
 
@@ -46,7 +47,8 @@ __global__ void __launch_bounds__(kScanThreads)
 landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ klt_out,
                         const uint8_t* __restrict__ status, const int32_t* __restrict__ iters,
                         const double* __restrict__ X_in, float2* __restrict__ P_out, double* __restrict__ X_out,
-                        float4* __restrict__ q4, float* __restrict__ qv, float2* __restrict__ lost)
+                        float4* __restrict__ q4, float* __restrict__ qv, float2* __restrict__ lost,
+                        int32_t* __restrict__ sets, RngTab rt)
 {
     __shared__ int sWarp[kScanThreads / 32];
     __shared__ int sKeep, sLost, sIter;
@@ -77,6 +79,8 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
     if ((tid & 31) == 0) atomicAdd(&sIter, it);
     __syncthreads();
     if (tid == 0) { sc->prev_n_land = n; sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
+    // the point count of the coming PnP-RANSAC is known: draw its first minimal sets here
+    if (tid < 32) pnp_prepare_sets(sc, sets, rt, sKeep);
 }
 
 // ---- DLT ---------------------------------------------------------------------------------------
@@ -291,32 +295,40 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
     }
 }
 
-// append n_new candidates: C := F := pts, T := pose (vo_pipeline.py:574-591)
+// append n_new candidates: C := F := pts, T := pose (vo_pipeline.py:574-591); the last CTA to
+// finish publishes the new size (every CTA has read the old one by then)
 __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts, int n_new, int use_dev_T,
                                 const double* __restrict__ Thost, float2* __restrict__ C, double2* __restrict__ F,
                                 int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap)
 {
+    __shared__ int sLast;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n0 = sc->n_cand;
-    if (use_dev_T && !sc->ok) return;   // no pose this frame: nothing is added
-    if (i < 16) poses[16 * (size_t)pose_idx + i] = use_dev_T ? sc->T[i] : Thost[i];
-    if (i < n_new && n0 + i < cand_cap) {
-        const double2 p = pts[i];
-        C[n0 + i] = make_float2((float)p.x, (float)p.y);
-        F[n0 + i] = p;
-        Ti[n0 + i] = pose_idx;
+    const bool skip = use_dev_T && !sc->ok;   // no pose this frame: nothing is added
+    if (!skip) {
+        if (i < 16) poses[16 * (size_t)pose_idx + i] = use_dev_T ? sc->T[i] : Thost[i];
+        if (i < n_new && n0 + i < cand_cap) {
+            const double2 p = pts[i];
+            C[n0 + i] = make_float2((float)p.x, (float)p.y);
+            F[n0 + i] = p;
+            Ti[n0 + i] = pose_idx;
+        }
     }
-}
-
-__global__ void cand_add_commit_kernel(DevScalars* sc, int n_new, int use_dev_T, int cand_cap)
-{
-    if (use_dev_T && !sc->ok) return;
-    if (n_new <= 0) return;
-    // C empty when the batch arrives: the reference binds C and F to one ndarray (App. B-5);
-    // otherwise np.concatenate allocates fresh arrays and any aliasing ends
-    sc->cf_alias = sc->cand_was_empty ? 1 : 0;
-    sc->n_cand = min(sc->n_cand + n_new, cand_cap);
-    sc->cand_was_empty = 0;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
+        if (sLast) {
+            sc->ticket = 0;
+            if (!skip && n_new > 0) {
+                // C empty when the batch arrives: the reference binds C and F to one ndarray (App. B-5);
+                // otherwise np.concatenate allocates fresh arrays and any aliasing ends
+                sc->cf_alias = sc->cand_was_empty ? 1 : 0;
+                sc->n_cand = min(n0 + n_new, cand_cap);
+                sc->cand_was_empty = 0;
+            }
+        }
+    }
 }
 
 __global__ void triangulate_kernel(const double* __restrict__ M1, const double* __restrict__ M2, int per_point,
@@ -346,9 +358,11 @@ int launch_landmark_compact(Ctx* c, int n_upper)
     VO_TRY(ensure(c, p->q4, n * 4));
     VO_TRY(ensure(c, p->qv, n));
     VO_TRY(ensure(c, p->lost, n * 2));
+    VO_TRY(ensure_rng_table(c, p->hyp_capacity));
     landmark_compact_kernel<<<1, kScanThreads, 0, c->stream>>>(
         p->d_sc, n_upper, (const float2*)p->klt_out.p, p->klt_status.p, p->klt_iters.p, p->X[p->cur].p,
-        (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p);
+        (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p, p->sets.p,
+        RngTab{ p->rng_tab.p, p->rng_tab_len });
     c->launches++;
     p->prev = p->cur;
     p->cur = nxt;
@@ -409,8 +423,7 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
     cand_add_kernel<<<blocks, threads, 0, c->stream>>>(p->d_sc, (const double2*)d_pts, n_new, d_Thost == nullptr,
                                                        d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
                                                        p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap);
-    cand_add_commit_kernel<<<1, 1, 0, c->stream>>>(p->d_sc, n_new, d_Thost == nullptr, cap);
-    c->launches += 2;
+    c->launches++;
     p->n_poses++;
     p->n_cand_upper += n_new > 0 ? n_new : 0;
     VO_CUDA(c, cudaGetLastError());
