@@ -466,7 +466,6 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
     __shared__ int sFails, sIters;
     __shared__ int sState;   // 0 = continue with trial, 1 = stop
     __shared__ int sWarpTot[kFinThreads / 32];
-    __shared__ int sBase;
     const int tid = threadIdx.x;
     const int best = sc->best_hyp;
     const bool ok = best >= 0;
@@ -480,12 +479,19 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
         for (int i = 0; i < 9; i++) R[i] = sRt[i];
 #pragma unroll
         for (int i = 0; i < 3; i++) t[i] = sRt[9 + i];
+        int c = 0;
         for (int i = tid; i < n; i += kFinThreads) {
             const float4 q = q4[i];
             const uint8_t f = n == kMinimal ? 1 : (reproj_err2(R, t, a.K, q.x, q.y, q.z, q.w, qv[i]) <= a.thr2);
             mask[i] = f;
+            c += f;
         }
+        c = __reduce_add_sync(0xffffffffu, c);
+        if ((tid & 31) == 0) sWarpTot[tid >> 5] = c;
+        if (tid < 12) sc->Th[tid] = sRt[tid];   // the winning unrefined hypothesis
         __syncthreads();
+#pragma unroll
+        for (int w = 0; w < kFinThreads / 32; w++) ninl += sWarpTot[w];
 
         // ---- LM: evaluate at the current pose, then trial steps ------------------------------------
         lm_accumulate(sRt, a.K, q4, qv, mask, n, sPart, sAcc);
@@ -518,9 +524,9 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
                     double step = 0.;
                     for (int r = 0; r < 6; r++) step += d[r] * d[r];
                     sStep = step;
-                    // a step below 1e-11 (rad / scene units) cannot move the pose at the 1e-9 level:
-                    // converged, no trial evaluation needed
-                    sState = step < 1e-22 ? 1 : 0;
+                    // a step below 1e-9 (rad / scene units) cannot move the pose at the level any gate
+                    // looks at: converged, no trial evaluation needed
+                    sState = step < 1e-18 ? 1 : 0;
                 }
             }
             __syncthreads();
@@ -535,7 +541,11 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
                     for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
                     sCost = cn; sLambda = fmax(sLambda * 0.1, 1e-12);
                     sFails = 0; sIters++;
-                    sState = (sStep < 1e-22 || dec <= 1e-13 * cn) ? 1 : 0;   // 1 = converged
+                    // Gauss-Newton contracts the error by orders of magnitude per step: after an accepted
+                    // step below 1e-7 the next one would be far below 1e-9
+                    sState = (sStep < 1e-14 || dec <= 1e-13 * cn) ? 1 : 0;   // 1 = converged
+                } else if (sStep < 1e-14) {
+                    sState = 1;   // a rejected step this small: the cost is at its rounding floor
                 } else {
                     sLambda *= 10.;
                     if (++sFails >= 12) sState = 1;
@@ -546,21 +556,12 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
             __syncthreads();
             if (st) break;
         }
-        // inlier count
-        int c = 0;
-        for (int i = tid; i < n; i += kFinThreads) c += mask[i];
-        c = __reduce_add_sync(0xffffffffu, c);
-        if ((tid & 31) == 0) sWarpTot[tid >> 5] = c;
-        __syncthreads();
-        for (int w = 0; w < kFinThreads / 32; w++) ninl += sWarpTot[w];
-        __syncthreads();
         if (tid == 0) {
             for (int r = 0; r < 3; r++) {
                 for (int cc = 0; cc < 3; cc++) { sc->T[4 * r + cc] = sRt[3 * r + cc]; }
                 sc->T[4 * r + 3] = sRt[9 + r];
             }
             sc->T[12] = 0.; sc->T[13] = 0.; sc->T[14] = 0.; sc->T[15] = 1.;
-            for (int i = 0; i < 12; i++) sc->Th[i] = __ldcg(hyp + (size_t)best * 12 + i);
             sc->cost = sCost; sc->lm_iters = sIters;
         }
     } else {
@@ -573,29 +574,36 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
 
     if (!a.compact) return;
     // ---- prune landmarks to the inliers, order preserved (no model: state left as it is) -------
-    if (tid == 0) sBase = 0;
-    __syncthreads();
+    int base = 0;
     for (int i0 = 0; i0 < n; i0 += kFinThreads) {
         const int i = i0 + tid;
         const bool keep = i < n && (!ok || mask[i]);
+        float2 pp = make_float2(0.f, 0.f);
+        double x0 = 0., x1 = 0., x2 = 0.;
+        if (keep) {   // issued before the barrier: the load latency overlaps the rank computation
+            pp = reinterpret_cast<const float2*>(fb.P_in)[i];
+            x0 = fb.X_in[3 * (size_t)i]; x1 = fb.X_in[3 * (size_t)i + 1]; x2 = fb.X_in[3 * (size_t)i + 2];
+        }
         const unsigned bal = __ballot_sync(0xffffffffu, keep);
         const int wpre = __popc(bal & ((1u << (tid & 31)) - 1));
         if ((tid & 31) == 0) sWarpTot[tid >> 5] = __popc(bal);
         __syncthreads();
-        int off = sBase;
-        for (int w = 0; w < (tid >> 5); w++) off += sWarpTot[w];
+        int off = base, tot = 0;
+#pragma unroll
+        for (int w = 0; w < kFinThreads / 32; w++) {
+            const int cw = sWarpTot[w];
+            if (w < (tid >> 5)) off += cw;
+            tot += cw;
+        }
         if (keep) {
             const int o = off + wpre;
-            reinterpret_cast<float2*>(fb.P_out)[o] = reinterpret_cast<const float2*>(fb.P_in)[i];
-            fb.X_out[3 * (size_t)o] = fb.X_in[3 * (size_t)i];
-            fb.X_out[3 * (size_t)o + 1] = fb.X_in[3 * (size_t)i + 1];
-            fb.X_out[3 * (size_t)o + 2] = fb.X_in[3 * (size_t)i + 2];
+            reinterpret_cast<float2*>(fb.P_out)[o] = pp;
+            fb.X_out[3 * (size_t)o] = x0; fb.X_out[3 * (size_t)o + 1] = x1; fb.X_out[3 * (size_t)o + 2] = x2;
         }
-        __syncthreads();
-        if (tid == 0) { int s = 0; for (int w = 0; w < kFinThreads / 32; w++) s += sWarpTot[w]; sBase += s; }
+        base += tot;
         __syncthreads();
     }
-    if (tid == 0) sc->n_land = sBase;
+    if (tid == 0) sc->n_land = base;
 }
 
 // ---- the RANSAC kernel -----------------------------------------------------------------------------
