@@ -222,7 +222,7 @@ def run_gpu(args, rank, world, local_rank):
     # ---- roofline leg: stage timers (CUDA events inside the library) over the same steps ---------------
     n_land, n_cand = reset_state()
     ctx.set_profiling(False)
-    prof_tracks, prof_iters_land, prof_land = 0, 0, 0
+    prof_tracks, prof_iters_land, prof_land, prof_iters_cand, prof_cand = 0, 0, 0, 0, 0
     for s in range(steps + warmup):
         if s == warmup:
             ctx.set_profiling(True)
@@ -230,9 +230,11 @@ def run_gpu(args, rank, world, local_rank):
         if s >= warmup:
             prof_tracks += n_land + n_cand
             prof_land += n_land
+            prof_cand += n_cand
         n_land, n_cand = dev_step(s, order, n_land, n_cand)
         if s >= warmup:
             prof_iters_land += cnt.klt_iters
+            prof_iters_cand += cnt.klt_iters_candidates
     stage_ms, nfr = ctx.stage_times()
     ctx.set_profiling(False)
 
@@ -241,6 +243,8 @@ def run_gpu(args, rank, world, local_rank):
     ctx.close()
     return dict(total_ms=total_ms, step_ms=step_ms, t_wall=t_wall, launches=launches, tracks_per_step=tracks / steps,
                 klt_iters_per_land=prof_iters_land / max(prof_land, 1), stage_ms=stage_ms,
+                klt=dict(land_tracks=prof_land / max(nfr, 1), land_iters=prof_iters_land / max(nfr, 1),
+                         cand_tracks=prof_cand / max(nfr, 1), cand_iters=prof_iters_cand / max(nfr, 1)),
                 prof_tracks_per_step=prof_tracks / max(nfr, 1), clocks=sampler.summary(), e2e=e2e,
                 final_counts=final_counts, frame_bytes=w * h,
                 per_frame=dict(lm_iters=lm_iters / steps, ransac_iters=ransac_iters / steps, pnp_inliers=inliers / steps,
@@ -384,12 +388,15 @@ def main():
         pass
     peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json)") if "hbm_gbs" in peaks else (6650.0, "fallback")
     # KLT algorithmic bytes per track: 4 levels x (w+3)^2 template+derivative window
-    # fetch, (w+1)^2 per Gauss-Newton step, one (w+1)^2 error pass, 21 B of point I/O
-    iters = r["klt_iters_per_land"]
-    bytes_per_track = 4 * 576 + 484 * iters + 505
-    klt_ms = r["stage_ms"]["klt"]
-    alg_bytes = bytes_per_track * r["prof_tracks_per_step"]
+    # fetch, (w+1)^2 per Gauss-Newton step, one (w+1)^2 error pass, 21 B of point I/O.  The dominant
+    # launch is the candidates' KLT (side stream); tracks and iterations are the kernel's own counters.
+    k = r["klt"]
+    iters = (k["land_iters"] + k["cand_iters"]) / max(k["land_tracks"] + k["cand_tracks"], 1)
+    klt_ms = r["stage_ms"]["klt_candidates"]
+    alg_bytes = (4 * 576 + 505) * k["cand_tracks"] + 484 * k["cand_iters"]
     achieved = alg_bytes / (klt_ms * 1e-3) / 1e9 if klt_ms > 0 else 0.0
+    land_ms = r["stage_ms"]["klt_landmarks"]
+    land_bytes = (4 * 576 + 505) * k["land_tracks"] + 484 * k["land_iters"]
     traffic = None
     try:
         traffic = json.load(open(os.path.join(ROOT, "profiles", "klt_traffic.json")))["dram_bytes_per_launch"]
@@ -401,9 +408,12 @@ def main():
         "e2e": {"value": world * e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": r["e2e"]["h2d"], "d2h_bytes_per_step": r["e2e"]["d2h"]},
         "gpu_launches": int(r["launches"]), "klt_tracks_per_s": r["tracks_per_step"] * fps,
         "clocks": r["clocks"],
-        "roofline": {"bound": "hbm", "kernel": "klt_track_kernel<21>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "klt_track_kernel<21> (candidates' launch, side stream)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": klt_ms,
+                     "tracks_per_launch": k["cand_tracks"], "lk_iterations_per_launch": k["cand_iters"],
+                     "landmark_launch": {"kernel_ms": land_ms, "tracks": k["land_tracks"], "lk_iterations": k["land_iters"],
+                                         "achieved": land_bytes / (land_ms * 1e-3) / 1e9 if land_ms > 0 else 0.0},
                      "note": "latency regime: ~2000 warps on 148 SMs is <1 wave; the window gathers are served by L1/L2, "
                              "so the HBM fraction is small by construction (SURVEY.md 8d)"},
         "stage_ms": r["stage_ms"], "wall_ms_per_step_incl_flush": 1e3 * r["t_wall"] / args.steps,

@@ -118,6 +118,7 @@ typedef struct vo_counters {
     int32_t ransac_iters, best_hypothesis, lm_iters;
     int32_t n_promoted, n_candidates_lost, cf_alias;
     int32_t klt_iters;                   /* sum of LK iterations over the last landmark KLT */
+    int32_t klt_iters_candidates;        /* same over the last candidate KLT (set by the promotion step) */
     double reproj_cost;                  /* sum of squared reprojection errors of the refit */
 } vo_counters;
 
@@ -196,10 +197,11 @@ int vo_process_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, i
                      const double* new_candidates, int n_new, double T44[16], vo_counters* counters);
 
 /* Stage timers of vo_process_frame (CUDA events on the ctx stream; bench.py's roofline leg).
- * ms[5] = {upload+pyramid, KLT, landmark compaction, PnP-RANSAC+LM, promotion+append} summed over
- * `frames` frames since vo_set_profiling(ctx, 1). */
+ * ms[6] = {upload+pyramid, landmark KLT, landmark compaction, PnP-RANSAC+LM, promotion+append (incl.
+ * the wait for the candidates' KLT), candidates' KLT on the side stream (overlaps stages 1-3)} summed
+ * over `frames` frames since vo_set_profiling(ctx, 1). */
 int vo_set_profiling(vo_ctx* ctx, int enable);
-int vo_get_stage_times(vo_ctx* ctx, double ms[5], int* frames);
+int vo_get_stage_times(vo_ctx* ctx, double ms[6], int* frames);
 
 /* ---- unit-level entry point mirroring cv2.solvePnPRansac (vo_pipeline.py:258-264) with P3P
  * hypotheses.  minimal_sets: max_iters x 4 int32 or NULL (cv::RNG(2^64-1) emulation = what cv2

@@ -36,7 +36,8 @@ class PnpParams(ctypes.Structure):
 class Counters(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "n_landmarks", "n_candidates", "n_tracked", "n_lost", "n_inliers", "pnp_ok", "ransac_iters",
-        "best_hypothesis", "lm_iters", "n_promoted", "n_candidates_lost", "cf_alias", "klt_iters")] + [
+        "best_hypothesis", "lm_iters", "n_promoted", "n_candidates_lost", "cf_alias", "klt_iters",
+        "klt_iters_candidates")] + [
         ("reproj_cost", c_double)]
 
     def as_dict(self):
@@ -399,10 +400,10 @@ class Context:
         self._check(self.lib.vo_set_profiling(self.h, int(enable)))
 
     def stage_times(self):
-        ms = np.zeros(5)
+        ms = np.zeros(6)
         n = c_int()
         self._check(self.lib.vo_get_stage_times(self.h, _ptr(ms), ctypes.byref(n)))
-        names = ("upload_pyramid", "klt", "compact", "pnp", "promote")
+        names = ("upload_pyramid", "klt_landmarks", "compact", "pnp", "promote", "klt_candidates")
         return {k: float(v) / max(n.value, 1) for k, v in zip(names, ms)}, n.value
 
     # ---- unit-level: cv2.solvePnPRansac / cv2.triangulatePoints ------------------------------------

@@ -28,6 +28,14 @@ static FrameSlot* find_slot(Ctx* c, int64_t key)
 
 FrameSlot* get_frame(Ctx* c, int64_t key) { return find_slot(c, key); }
 
+int join_side_stream(Ctx* c)
+{
+    if (!c->side_inflight) return VO_OK;
+    c->side_inflight = false;
+    VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    return VO_OK;
+}
+
 }  // namespace vo
 
 using namespace vo;
@@ -78,6 +86,12 @@ int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity
         if (e != cudaSuccess) { delete c; return set_error(nullptr, VO_ERR_CUDA, "cudaStreamCreate failed: %s", cudaGetErrorString(e)); }
         c->own_stream = true;
     }
+    if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
+        delete c;
+        return set_error(nullptr, VO_ERR_CUDA, "side stream creation failed: %s", cudaGetErrorString(cudaGetLastError()));
+    }
     c->pinned_stage_bytes = (size_t)max_w * max_h;
     e = cudaMallocHost((void**)&c->pinned_stage, c->pinned_stage_bytes);
     if (e != cudaSuccess) { delete c; return set_error(nullptr, VO_ERR_NOMEM, "cudaMallocHost failed: %s", cudaGetErrorString(e)); }
@@ -92,12 +106,16 @@ int vo_destroy(vo_ctx* c)
     if (!c) return VO_OK;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
+    if (c->stream2) cudaStreamSynchronize(c->stream2);
     pipeline_free(c);
     for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); }
     cudaFree(c->u_pts.p); cudaFree(c->u_out.p); cudaFree(c->u_err.p); cudaFree(c->u_status.p);
     cudaFree(c->u_iters.p); cudaFree(c->u_n.p);
     cudaFreeHost(c->pinned_stage);
     if (c->own_stream) cudaStreamDestroy(c->stream);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
+    if (c->ev_join) cudaEventDestroy(c->ev_join);
     delete c;
     return VO_OK;
 }
@@ -107,6 +125,7 @@ const char* vo_last_error(vo_ctx* c) { return c ? c->err.c_str() : g_create_erro
 int vo_synchronize(vo_ctx* c)
 {
     if (!c) return VO_ERR_INVALID;
+    VO_TRY(join_side_stream(c));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     return VO_OK;
 }
@@ -137,6 +156,7 @@ int vo_has_frame(vo_ctx* c, int64_t key)
 int vo_drop_frames(vo_ctx* c)
 {
     if (!c) return VO_ERR_INVALID;
+    VO_TRY(join_side_stream(c));
     for (auto& s : c->slots) s.valid = false;
     return VO_OK;
 }
@@ -147,6 +167,7 @@ int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int6
     if (w <= 0 || h <= 0 || w > c->max_w || h > c->max_h || pitch < w)
         return set_error(c, VO_ERR_INVALID, "frame %dx%d (pitch %d) outside ctx limits %dx%d", w, h, pitch, c->max_w, c->max_h);
     if (find_slot(c, key)) return VO_OK;
+    VO_TRY(join_side_stream(c));   // a pyramid slot may be recycled under the side stream's reads
     FrameSlot* s = nullptr;
     for (auto& t : c->slots) if (!t.valid) { s = &t; break; }
     if (!s) { s = &c->slots[0]; for (auto& t : c->slots) if (t.stamp < s->stamp) s = &t; }

@@ -50,6 +50,11 @@ struct Ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    // side stream: the candidates' KLT runs here, concurrently with the landmark chain
+    // (landmark KLT -> compaction -> PnP-RANSAC) on `stream`; joined before the promotion step
+    cudaStream_t stream2 = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    bool side_inflight = false;
     int max_w = 0, max_h = 0;
     int sm_count = 148;
     std::string err;
@@ -144,6 +149,8 @@ struct DevScalars {
     int32_t prev_n_land;   // |P| before the last tracking step (rows of the `prev` landmark buffer)
     // values before the last promotion step (rollback of a speculative promotion)
     int32_t spec_n_land, spec_n_cand, spec_cf_alias, spec_cand_was_empty;
+    int32_t finalized;     // the refit of the current RANSAC run has been done
+    int32_t klt_iters_cand; // sum of LK iterations over the candidates (roofline accounting)
     int32_t pad_;
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
@@ -201,7 +208,7 @@ struct Pipeline {
     float* h_snapP = nullptr; double* h_snapX = nullptr; DevScalars* h_snap_sc = nullptr;
     size_t snap_cap = 0; int snap_rows = 0;
     // optional stage timers (vo_set_profiling)
-    bool profiling = false; cudaEvent_t ev[6] = {}; double stage_ms[5] = {}; int stage_frames = 0;
+    bool profiling = false; cudaEvent_t ev[6] = {}; cudaEvent_t ev_side[2] = {}; double stage_ms[6] = {}; int stage_frames = 0;
 };
 
 // ---- stage launchers implemented in the .cu files -------------------------------------------
@@ -214,7 +221,9 @@ int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const f
 int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_ptsA,
                 const int32_t* d_nA, int nA_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
-                const vo_klt_params& prm);
+                const vo_klt_params& prm, cudaStream_t st = nullptr);
+// make `stream` wait for the work in flight on the side stream (no-op if there is none)
+int join_side_stream(Ctx* c);
 
 // optional extra (off in parity mode): track `out` back into `prev` and clear status where the
 // round trip misses the start point by more than prm.fb_thresh

@@ -313,8 +313,9 @@ int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const f
 int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
                 const int32_t* d_n, int n_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
-                const vo_klt_params& prm)
+                const vo_klt_params& prm, cudaStream_t st)
 {
+    if (!st) st = c->stream;
     if (n_upper < 0) n_upper = 0;
     if (nB_upper < 0) nB_upper = 0;
     if (n_upper + nB_upper <= 0) return VO_OK;
@@ -331,7 +332,7 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
     const double eps = prm.epsilon < 0. ? 0. : (prm.epsilon > 10. ? 10. : prm.epsilon);
     const double eps2 = eps * eps;
     const int blocks = (n_upper + nB_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, c->stream>>>(
+    klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
         prev, next, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
         (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr);
     c->launches++;

@@ -47,6 +47,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->d_sc);
     cudaFreeHost(p->h_sc);
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
+    for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
     delete p;
     c->pipe = nullptr;
@@ -85,8 +86,22 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
     const size_t tot = (size_t)nA + nB > 0 ? (size_t)nA + nB : 1;
     VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
     VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
-    VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, p->C[p->ccur].p, &p->d_sc->n_cand, nB,
-                       nA, p->klt_out.p, p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm));
+    if (nB > 0) {
+        // fork: the candidates (usually most of the tracks, and with them the slowest stragglers) are
+        // tracked on the side stream while the landmark chain - the only thing the pose depends on -
+        // goes ahead on the main stream; the promotion step joins the two
+        VO_TRY(join_side_stream(c));
+        VO_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
+        VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+        if (p->profiling) cudaEventRecord(p->ev_side[0], c->stream2);
+        VO_TRY(launch_klt2(c, a->pyr, b->pyr, nullptr, nullptr, 0, p->C[p->ccur].p, &p->d_sc->n_cand, nB, nA, p->klt_out.p,
+                           p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, c->stream2));
+        if (p->profiling) cudaEventRecord(p->ev_side[1], c->stream2);
+        VO_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
+        c->side_inflight = true;
+    }
+    VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, nullptr, nullptr, 0, 0, p->klt_out.p,
+                       p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm));
     p->klt_b_off = nA;
     return VO_OK;
 }
@@ -190,6 +205,7 @@ int vo_snapshot_state(vo_ctx* c)
     if (n > p->snap_cap) {
         VO_CUDA(c, cudaStreamSynchronize(c->stream));
         for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
+    for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX);
         p->h_snapP = nullptr; p->h_snapX = nullptr; p->snap_cap = 0;
         size_t cap = 4096;
@@ -227,6 +243,7 @@ int vo_get_snapshot(vo_ctx* c, float* P, double* X, int cap, int* n)
 int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* T, int n, int cf_alias)
 {
     VO_NEED(c);
+    VO_TRY(join_side_stream(c));
     if (n < 0 || (n > 0 && (!C || !F || !T))) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
     const size_t m = n > 0 ? n : 1;
@@ -253,6 +270,7 @@ int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* 
 int vo_get_candidates(vo_ctx* c, float* C, double* F, double* T, int cap, int* n)
 {
     VO_NEED(c);
+    VO_TRY(join_side_stream(c));
     Pipeline* p = c->pipe;
     VO_TRY(read_scalars(c));
     const int m = p->h_sc->n_cand;
@@ -292,7 +310,8 @@ static int fill_counters(vo_ctx* c, vo_counters* out, bool sync)
     out->n_landmarks = s->n_land; out->n_candidates = s->n_cand; out->n_tracked = s->n_tracked; out->n_lost = s->n_lost;
     out->n_inliers = s->n_inliers; out->pnp_ok = s->ok; out->ransac_iters = s->iters_run; out->best_hypothesis = s->best_hyp;
     out->lm_iters = s->lm_iters; out->n_promoted = s->n_promoted; out->n_candidates_lost = s->n_cand_lost;
-    out->cf_alias = s->cf_alias; out->klt_iters = s->klt_iters; out->reproj_cost = s->cost;
+    out->cf_alias = s->cf_alias; out->klt_iters = s->klt_iters; out->klt_iters_candidates = s->klt_iters_cand;
+    out->reproj_cost = s->cost;
     return VO_OK;
 }
 
@@ -454,6 +473,7 @@ int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
 int vo_track_candidates(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params)
 {
     VO_NEED(c);
+    VO_TRY(join_side_stream(c));
     Pipeline* p = c->pipe;
     if (p->cand_tracked_valid && p->cand_tracked_prev == prev_key && p->cand_tracked_next == next_key) return VO_OK;
     vo_klt_params prm;
@@ -478,6 +498,7 @@ int vo_track_candidates(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_
 int vo_get_candidate_tracks(vo_ctx* c, float* prev_pts, float* next_pts, uint8_t* status, int cap, int* n)
 {
     VO_NEED(c);
+    VO_TRY(join_side_stream(c));
     Pipeline* p = c->pipe;
     if (!p->cand_tracked_valid) return set_error(c, VO_ERR_STATE, "no pending candidate tracking");
     const int off = p->klt_b_off;
@@ -556,6 +577,8 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
             float ms = 0.f;
             if (cudaEventElapsedTime(&ms, p->ev[k], p->ev[k + 1]) == cudaSuccess) p->stage_ms[k] += ms;
         }
+        float ms = 0.f;   // the candidates' KLT on the side stream (overlaps stages 1-3)
+        if (cudaEventElapsedTime(&ms, p->ev_side[0], p->ev_side[1]) == cudaSuccess) p->stage_ms[5] += ms;
         p->stage_frames++;
     }
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
@@ -565,7 +588,7 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
         counters->n_lost = s->n_lost; counters->n_inliers = s->n_inliers; counters->pnp_ok = s->ok;
         counters->ransac_iters = s->iters_run; counters->best_hypothesis = s->best_hyp; counters->lm_iters = s->lm_iters;
         counters->n_promoted = s->n_promoted; counters->n_candidates_lost = s->n_cand_lost; counters->cf_alias = s->cf_alias;
-        counters->klt_iters = s->klt_iters; counters->reproj_cost = s->cost;
+        counters->klt_iters = s->klt_iters; counters->klt_iters_candidates = s->klt_iters_cand; counters->reproj_cost = s->cost;
     }
     return VO_OK;
 }
@@ -577,18 +600,21 @@ int vo_set_profiling(vo_ctx* c, int enable)
 {
     VO_NEED(c);
     Pipeline* p = c->pipe;
-    if (enable && !p->ev[0]) for (int k = 0; k < 6; k++) VO_CUDA(c, cudaEventCreate(&p->ev[k]));
+    if (enable && !p->ev[0]) {
+        for (int k = 0; k < 6; k++) VO_CUDA(c, cudaEventCreate(&p->ev[k]));
+        for (int k = 0; k < 2; k++) VO_CUDA(c, cudaEventCreate(&p->ev_side[k]));
+    }
     p->profiling = enable != 0;
-    for (int k = 0; k < 5; k++) p->stage_ms[k] = 0.;
+    for (int k = 0; k < 6; k++) p->stage_ms[k] = 0.;
     p->stage_frames = 0;
     return VO_OK;
 }
 
-int vo_get_stage_times(vo_ctx* c, double ms[5], int* frames)
+int vo_get_stage_times(vo_ctx* c, double ms[6], int* frames)
 {
     VO_NEED(c);
     if (!ms) return VO_ERR_INVALID;
-    for (int k = 0; k < 5; k++) ms[k] = c->pipe->stage_ms[k];
+    for (int k = 0; k < 6; k++) ms[k] = c->pipe->stage_ms[k];
     if (frames) *frames = c->pipe->stage_frames;
     return VO_OK;
 }

@@ -304,6 +304,7 @@ __device__ void ransac_select(DevScalars* sc, int32_t* sets, const int32_t* coun
     if (first) {
         niters = (n < kMinimal || a.max_iters <= 0) ? 0 : (n == kMinimal ? 1 : a.max_iters);
         best = 0; best_hyp = -1; done = niters == 0;
+        if (lane == 0) sc->finalized = 0;
     } else {
         niters = sc->niters; best = sc->best_count; best_hyp = sc->best_hyp; done = sc->done;
     }
@@ -621,12 +622,13 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
     __shared__ int sValid, sLast;
     __shared__ int sCount[kHypThreads / 32];
     const int tid = threadIdx.x;
-    const int h = h0 + blockIdx.x;
     const int n = min(sc->n_tracked, a.n_upper);
-    // the first chunk lies inside the initial budget by construction; later chunks see the budget the
-    // previous chunk's bookkeeping left (hypotheses beyond it are never looked at)
-    const bool active = first ? (n >= kMinimal && h < (n == kMinimal ? 1 : a.max_iters)) : (!sc->done && h < sc->niters);
-    if (active) {
+    // the first chunk lies inside the initial budget by construction (one CTA per hypothesis); later
+    // chunks run on a fixed small grid that strides over whatever budget the previous chunk's
+    // bookkeeping left (hypotheses beyond it are never looked at; usually there are none)
+    const int lim = first ? ((n >= kMinimal && a.max_iters > 0) ? (n == kMinimal ? 1 : h1) : 0)
+                          : (sc->done ? 0 : min(h1, sc->niters));
+    for (int h = h0 + blockIdx.x; h < lim; h += gridDim.x) {
         if (tid < 4) {   // a quad of lanes solves the minimal problem
             int4 s = n == kMinimal ? make_int4(0, 1, 2, 3) : reinterpret_cast<const int4*>(sets)[h];
             const int idx[4] = { s.x, s.y, s.z, s.w };
@@ -671,6 +673,7 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
                 counts[h] = s;
             }
         } else if (tid == 0) counts[h] = -1;
+        __syncthreads();   // sRt / sValid / sCount are reused by the next hypothesis of this CTA
     }
     // ---- chunk bookkeeping by the last CTA to get here --------------------------------------------
     __syncthreads();
@@ -684,7 +687,10 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
     if (tid < 32) ransac_select(sc, sets, counts, a, rt, n, first, h0, h1, next_end, last);
     __syncthreads();
     if (tid == 0) sc->ticket = 0;
-    if (!last) return;
+    // the run is over (budget reached, or this was the last chunk) and not refitted yet: refit here
+    if (!sc->done || sc->finalized) return;
+    __syncthreads();
+    if (tid == 0) sc->finalized = 1;
     pnp_finalize(sc, hyp, q4, qv, mask, a, fb, n);
 }
 
@@ -752,7 +758,8 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         const int h1 = k == 0 ? (H < kPnpChunk0 ? H : kPnpChunk0) : (H - h0 < 2048 ? H : h0 + 2048);
         const int next_end = H - h1 < 2048 ? H : h1 + 2048;
         const int last = h1 >= H;
-        const int grid = h1 - h0 > 0 ? h1 - h0 : 1;
+        int grid = h1 - h0 > 0 ? h1 - h0 : 1;
+        if (k > 0 && grid > 2 * c->sm_count) grid = 2 * c->sm_count;   // later chunks: fixed grid, strided
         pnp_chunk_kernel<<<grid, kHypThreads, 0, c->stream>>>(p->d_sc, sets, (const float4*)L.q4, L.qv, p->hyp.p,
                                                               p->counts.p, p->mask.p, a, rt, fb, h0, h1, next_end,
                                                               k == 0 ? 1 : 0, last);

@@ -78,7 +78,7 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
     it = __reduce_add_sync(0xffffffffu, it);
     if ((tid & 31) == 0) atomicAdd(&sIter, it);
     __syncthreads();
-    if (tid == 0) { sc->prev_n_land = n; sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
+    if (tid == 0) { sc->klt_iters_cand = 0; sc->prev_n_land = n; sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
     // the point count of the coming PnP-RANSAC is known: draw its first minimal sets here
     if (tid < 32) pnp_prepare_sets(sc, sets, rt, sKeep);
 }
@@ -199,9 +199,10 @@ __device__ __forceinline__ CandRow load_cand(const PromoteArgs& a, bool alias, i
 }
 
 __global__ void __launch_bounds__(kCandThreads)
-cand_classify_kernel(const DevScalars* __restrict__ sc, PromoteArgs a, const float2* __restrict__ klt_out,
+cand_classify_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out,
                      const uint8_t* __restrict__ status, const float2* __restrict__ C_in,
-                     const double2* __restrict__ F_in, uint8_t* __restrict__ flag, int32_t* __restrict__ blk_counts)
+                     const double2* __restrict__ F_in, uint8_t* __restrict__ flag, int32_t* __restrict__ blk_counts,
+                     const int32_t* __restrict__ klt_iters)
 {
     const int n = min(sc->n_cand, a.ncand_upper);
     const bool alias = sc->cf_alias != 0;
@@ -216,6 +217,11 @@ cand_classify_kernel(const DevScalars* __restrict__ sc, PromoteArgs a, const flo
             if (have_pose && bearing_angle_deg((double)r.c.x, (double)r.c.y, r.f.x, r.f.y) > a.alpha_deg) f = kCandPromote;
         }
         flag[i] = f;
+    }
+    if (a.use_klt && klt_iters) {   // roofline accounting: iterations spent on the candidates
+        int it = i < n ? klt_iters[a.b_off + i] : 0;
+        it = __reduce_add_sync(0xffffffffu, it);
+        if ((threadIdx.x & 31) == 0 && it) atomicAdd(&sc->klt_iters_cand, it);
     }
     const int n_stay = __syncthreads_count(f == kCandStay);
     const int n_prom = __syncthreads_count(f == kCandPromote);
@@ -374,6 +380,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
                    int b_off)
 {
     Pipeline* p = c->pipe;
+    VO_TRY(join_side_stream(c));   // the candidates' KLT results come from the side stream
     PromoteArgs a;
     memcpy(a.K, K, sizeof(a.K));
     if (Tnew) memcpy(a.Tnew, Tnew, sizeof(a.Tnew)); else memset(a.Tnew, 0, sizeof(a.Tnew));
@@ -396,7 +403,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
     cand_classify_kernel<<<nb, kCandThreads, 0, c->stream>>>(
         p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p);
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, p->klt_iters.p);
     cand_apply_kernel<<<nb, kCandThreads, 0, c->stream>>>(
         p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
         (const double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, p->cand_flag.p, p->blk_counts.p,
@@ -413,6 +420,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
 int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost)
 {
     Pipeline* p = c->pipe;
+    VO_TRY(join_side_stream(c));
     const size_t need = (size_t)p->n_cand_upper + (n_new > 0 ? n_new : 0) + 1;
     VO_TRY(ensure(c, p->C[p->ccur], need * 2, true));
     VO_TRY(ensure(c, p->F[p->ccur], need * 2, true));
