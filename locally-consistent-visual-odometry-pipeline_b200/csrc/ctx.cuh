@@ -94,6 +94,33 @@ int set_error(Ctx* c, int code, const char* fmt, ...);
         if (_r != VO_OK) return _r; \
     } while (0)
 
+// ---- programmatic dependent launch ---------------------------------------------------------------
+// The frame is a chain of small dependent kernels, so the ~2 us a kernel boundary costs (drain,
+// launch, ramp-up) is paid a dozen times per frame.  Kernels launched through launch_pdl may be
+// made resident while their predecessor in the stream is still running; every such kernel starts
+// with pdl_prologue(), which lets ITS successor do the same and then blocks until the predecessor
+// grid has completed and its writes are visible (griddepcontrol.wait) - before touching any data.
+// Without the launch attribute both instructions are no-ops.
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_prologue()
+{
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, cudaStream_t st, Args... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 template <typename T>
 int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
 {

@@ -113,6 +113,7 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
     constexpr int RPR = WIN / kRun;            // runs per row
     constexpr int NRUNS = WIN * RPR;           // 63
     constexpr int NR = (NRUNS + 31) / 32;      // runs per lane
+    pdl_prologue();
     const int lane = threadIdx.x & 31;
     int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     // two track lists share one launch: landmarks (A) then candidates (B, written at b_off)

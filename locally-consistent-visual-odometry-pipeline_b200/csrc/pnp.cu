@@ -621,6 +621,7 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
     __shared__ double sRt[12];
     __shared__ int sValid, sLast;
     __shared__ int sCount[kHypThreads / 32];
+    pdl_prologue();
     const int tid = threadIdx.x;
     const int n = min(sc->n_tracked, a.n_upper);
     // the first chunk lies inside the initial budget by construction (one CTA per hypothesis); later
@@ -760,9 +761,8 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         const int last = h1 >= H;
         int grid = h1 - h0 > 0 ? h1 - h0 : 1;
         if (k > 0 && grid > 2 * c->sm_count) grid = 2 * c->sm_count;   // later chunks: fixed grid, strided
-        pnp_chunk_kernel<<<grid, kHypThreads, 0, c->stream>>>(p->d_sc, sets, (const float4*)L.q4, L.qv, p->hyp.p,
-                                                              p->counts.p, p->mask.p, a, rt, fb, h0, h1, next_end,
-                                                              k == 0 ? 1 : 0, last);
+        VO_CUDA(c, launch_pdl(pnp_chunk_kernel, dim3(grid), dim3(kHypThreads), c->stream, p->d_sc, sets, (const float4*)L.q4,
+                              L.qv, p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, h0, h1, next_end, k == 0 ? 1 : 0, last));
         c->launches++;
         h0 = h1;
         if (last) break;

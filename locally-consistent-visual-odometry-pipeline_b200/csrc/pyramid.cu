@@ -45,6 +45,7 @@ __global__ void __launch_bounds__(TX* TY)
 build_level_kernel(const uint8_t* __restrict__ src, int sstride, LevelDesc dst)
 {
     __shared__ uint8_t tile[TY + 2][TX + 2 + 2];
+    pdl_prologue();
     const int X0 = blockIdx.x * TX - kPad, Y0 = blockIdx.y * TY - kPad;
     const int tid = threadIdx.y * TX + threadIdx.x;
     for (int i = tid; i < (TY + 2) * (TX + 2); i += TX * TY) {
@@ -110,9 +111,10 @@ int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap)
         const LevelDesc& d = s.pyr.lv[l];
         dim3 grid((d.w + 2 * kPad + TX - 1) / TX, (d.h + 2 * kPad + TY - 1) / TY), block(TX, TY);
         if (l == 0)
-            build_level_kernel<true><<<grid, block, 0, c->stream>>>(s.raw, s.w, d);
+            VO_CUDA(c, launch_pdl(build_level_kernel<true>, grid, block, c->stream, (const uint8_t*)s.raw, s.w, d));
         else
-            build_level_kernel<false><<<grid, block, 0, c->stream>>>(s.pyr.lv[l - 1].img, s.pyr.lv[l - 1].stride, d);
+            VO_CUDA(c, launch_pdl(build_level_kernel<false>, grid, block, c->stream, (const uint8_t*)s.pyr.lv[l - 1].img,
+                                  s.pyr.lv[l - 1].stride, d));
         c->launches++;
     }
     VO_CUDA(c, cudaGetLastError());

@@ -52,6 +52,7 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
 {
     __shared__ int sWarp[kScanThreads / 32];
     __shared__ int sKeep, sLost, sIter;
+    pdl_prologue();
     const int tid = threadIdx.x;
     const int n = min(sc->n_land, n_upper);
     if (tid == 0) { sKeep = 0; sLost = 0; sIter = 0; }
@@ -204,6 +205,7 @@ cand_classify_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ k
                      const double2* __restrict__ F_in, uint8_t* __restrict__ flag, int32_t* __restrict__ blk_counts,
                      const int32_t* __restrict__ klt_iters)
 {
+    pdl_prologue();
     const int n = min(sc->n_cand, a.ncand_upper);
     const bool alias = sc->cf_alias != 0;
     const bool have_pose = a.use_dev_T ? sc->ok != 0 : true;
@@ -238,6 +240,7 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
     __shared__ int sWarpStay[kCandThreads / 32], sWarpProm[kCandThreads / 32];
     __shared__ int sBaseStay, sBaseProm, sLast;
     __shared__ double sM2[12];
+    pdl_prologue();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(sc->n_cand, a.ncand_upper);
     const int n_land = sc->n_land;
@@ -308,6 +311,7 @@ __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts,
                                 int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap)
 {
     __shared__ int sLast;
+    pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n0 = sc->n_cand;
     const bool skip = use_dev_T && !sc->ok;   // no pose this frame: nothing is added
@@ -365,10 +369,10 @@ int launch_landmark_compact(Ctx* c, int n_upper)
     VO_TRY(ensure(c, p->qv, n));
     VO_TRY(ensure(c, p->lost, n * 2));
     VO_TRY(ensure_rng_table(c, p->hyp_capacity));
-    landmark_compact_kernel<<<1, kScanThreads, 0, c->stream>>>(
-        p->d_sc, n_upper, (const float2*)p->klt_out.p, p->klt_status.p, p->klt_iters.p, p->X[p->cur].p,
-        (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p, p->sets.p,
-        RngTab{ p->rng_tab.p, p->rng_tab_len });
+    VO_CUDA(c, launch_pdl(landmark_compact_kernel, dim3(1), dim3(kScanThreads), c->stream,
+        p->d_sc, n_upper, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const int32_t*)p->klt_iters.p,
+        (const double*)p->X[p->cur].p, (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p,
+        p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }));
     c->launches++;
     p->prev = p->cur;
     p->cur = nxt;
@@ -401,14 +405,14 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     const int nb = ncand_upper > 0 ? (ncand_upper + kCandThreads - 1) / kCandThreads : 1;
     VO_TRY(ensure(c, p->cand_flag, nc));
     VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
-    cand_classify_kernel<<<nb, kCandThreads, 0, c->stream>>>(
-        p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, p->klt_iters.p);
-    cand_apply_kernel<<<nb, kCandThreads, 0, c->stream>>>(
-        p->d_sc, a, (const float2*)p->klt_out.p, p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, p->cand_flag.p, p->blk_counts.p,
-        (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p, p->Ti[p->ccur ^ 1].p, p->poses.p,
-        (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap);
+    VO_CUDA(c, launch_pdl(cand_classify_kernel, dim3(nb), dim3(kCandThreads), c->stream,
+        p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p));
+    VO_CUDA(c, launch_pdl(cand_apply_kernel, dim3(nb), dim3(kCandThreads), c->stream,
+        p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
+        (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
+        (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
+        p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap));
     c->launches++;
     c->launches++;
     p->ccur ^= 1;
@@ -428,9 +432,9 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
     VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));
     const int cap = (int)(p->C[p->ccur].cap / 2);
     const int threads = 256, blocks = ((n_new > 16 ? n_new : 16) + threads - 1) / threads;
-    cand_add_kernel<<<blocks, threads, 0, c->stream>>>(p->d_sc, (const double2*)d_pts, n_new, d_Thost == nullptr,
-                                                       d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
-                                                       p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap);
+    VO_CUDA(c, launch_pdl(cand_add_kernel, dim3(blocks), dim3(threads), c->stream, p->d_sc, (const double2*)d_pts, n_new,
+                          (int)(d_Thost == nullptr), d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
+                          p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap));
     c->launches++;
     p->n_poses++;
     p->n_cand_upper += n_new > 0 ? n_new : 0;
