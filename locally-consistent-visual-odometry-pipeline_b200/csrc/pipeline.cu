@@ -131,7 +131,11 @@ __global__ void pack_points_kernel(DevScalars* sc, const double* __restrict__ X,
         qv[i] = p.y;
     }
     // the point count of the coming PnP-RANSAC is known: draw its first minimal sets here
-    if (blockIdx.x == 0 && threadIdx.x < 32) vo::pnp_prepare_sets(sc, sets, rt, m);
+    if (blockIdx.x == 0 && threadIdx.x < 32) {
+        vo::RngPreload pre;
+        vo::pnp_preload_draws(rt, pre);
+        vo::pnp_prepare_sets(sc, sets, rt, m, pre);
+    }
 }
 
 #define VO_NEED(c) do { if (!(c) || !(c)->pipe) return VO_ERR_INVALID; } while (0)

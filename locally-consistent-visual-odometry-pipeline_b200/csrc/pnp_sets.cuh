@@ -72,21 +72,53 @@ __device__ inline void gen_sets_warp(DevScalars* sc, int32_t* sets, RngTab rt, i
     }
 }
 
+// The first kPnpChunk0 sets start at draw 0, so their raw draws can be fetched before the point count
+// is known (the table is cold in L2 after anything large has run): lane l, batch b holds draws
+// 128 b + 4 l .. + 3.
+struct RngPreload { uint4 v[kPnpChunk0 / 32]; };
+
+__device__ inline void pnp_preload_draws(RngTab rt, RngPreload& pre)
+{
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int b = 0; b < kPnpChunk0 / 32; b++) {
+        pre.v[b] = make_uint4(0, 0, 0, 0);
+        if (rt.tab && 128 * b + 4 * lane + 3 < rt.len) pre.v[b] = reinterpret_cast<const uint4*>(rt.tab)[32 * b + lane];
+    }
+}
+
 // Called by ONE full warp of the kernel that fixes the point count n of the next RANSAC: resets the
 // draw position and pre-generates the minimal sets of the first chunk, so the RANSAC needs no
-// set-up launch of its own.
-__device__ inline void pnp_prepare_sets(DevScalars* sc, int32_t* sets, RngTab rt, int n)
+// set-up launch of its own.  Batches are served from the preloaded draws as long as no set needed
+// a re-draw (then the draw position is no longer 128 b and the generic path takes over).
+__device__ inline void pnp_prepare_sets(DevScalars* sc, int32_t* sets, RngTab rt, int n, const RngPreload& pre)
 {
+    const int lane = threadIdx.x & 31;
     __syncwarp();
-    if ((threadIdx.x & 31) == 0) {
-        sc->sets_ready = 0; sc->rng = 0; sc->rng_exhausted = 0;
+    int h = 0;
+    if (n > kMinimal && rt.tab && rt.len >= 4 * kPnpChunk0) {
+#pragma unroll
+        for (int b = 0; b < kPnpChunk0 / 32; b++) {
+            if (h != 32 * b) break;
+            const uint4 r = pre.v[b];
+            const int4 v = make_int4((int)(r.x % (unsigned)n), (int)(r.y % (unsigned)n), (int)(r.z % (unsigned)n),
+                                     (int)(r.w % (unsigned)n));
+            const bool ok = v.y != v.x && v.z != v.x && v.z != v.y && v.w != v.x && v.w != v.y && v.w != v.z;
+            const unsigned bad = __ballot_sync(0xffffffffu, !ok);
+            const int good = bad ? __ffs(bad) - 1 : 32;
+            if (lane < good) reinterpret_cast<int4*>(sets)[h + lane] = v;
+            h += good;
+        }
+    }
+    if (lane == 0) {
+        sc->sets_ready = h; sc->rng = (uint64_t)(4 * h); sc->rng_exhausted = 0;
         if (n == kMinimal) {   // cv2: count == modelPoints -> one direct solve on all points
             reinterpret_cast<int4*>(sets)[0] = make_int4(0, 1, 2, 3);
             sc->sets_ready = 0x7fffffff;
         }
     }
     __syncwarp();
-    if (n > kMinimal && rt.tab) gen_sets_warp(sc, sets, rt, n, kPnpChunk0);
+    if (n > kMinimal && rt.tab && h < kPnpChunk0) gen_sets_warp(sc, sets, rt, n, kPnpChunk0);
 }
 
 }  // namespace vo

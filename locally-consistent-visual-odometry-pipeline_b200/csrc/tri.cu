@@ -42,7 +42,10 @@ __device__ __forceinline__ int tile_rank(bool flag, int* sWarp, int* sBase)
     return off + wpre;
 }
 
-// after KLT on the landmarks: keep status==1 rows (new position, X), pack the float32 PnP inputs
+// after KLT on the landmarks: keep status==1 rows (new position, X), pack the float32 PnP inputs.
+// One CTA, one barrier: 31 warps own contiguous segments of the rows (count, barrier, then
+// order-preserving writes from warp-local ranks); the 32nd warp, which after the barrier knows the
+// point count of the coming PnP-RANSAC, draws its first minimal sets meanwhile.
 __global__ void __launch_bounds__(kScanThreads)
 landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ klt_out,
                         const uint8_t* __restrict__ status, const int32_t* __restrict__ iters,
@@ -50,22 +53,54 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
                         float4* __restrict__ q4, float* __restrict__ qv, float2* __restrict__ lost,
                         int32_t* __restrict__ sets, RngTab rt)
 {
-    __shared__ int sWarp[kScanThreads / 32];
-    __shared__ int sKeep, sLost, sIter;
+    constexpr int NW = kScanThreads / 32 - 1;   // data warps
+    __shared__ int sKeepW[32], sLostW[32], sIterW[32];
     pdl_prologue();
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(sc->n_land, n_upper);
-    if (tid == 0) { sKeep = 0; sLost = 0; sIter = 0; }
+    const int seg = ((n + NW - 1) / NW + 31) & ~31;   // rows per data warp, a multiple of the warp width
+    const int lo = warp * seg, hi = min(n, lo + seg);
+    int ck = 0, cl = 0, it = 0;
+    RngPreload pre;
+    if (warp == NW) pnp_preload_draws(rt, pre);   // in flight while the data warps count
+    if (warp < NW) {
+        for (int i0 = lo; i0 < hi; i0 += 32) {
+            const int i = i0 + lane;
+            const bool in = i < hi;
+            const bool keep = in && status[i] != 0;
+            if (in && iters) it += iters[i];
+            const unsigned bk = __ballot_sync(0xffffffffu, keep);
+            const unsigned bi = __ballot_sync(0xffffffffu, in);
+            ck += __popc(bk); cl += __popc(bi & ~bk);
+        }
+        it = __reduce_add_sync(0xffffffffu, it);
+    }
+    if (lane == 0) { sKeepW[warp] = ck; sLostW[warp] = cl; sIterW[warp] = it; }
     __syncthreads();
-    int it = 0;
-    for (int i0 = 0; i0 < n; i0 += kScanThreads) {
-        const int i = i0 + tid;
-        const bool in = i < n;
+    // every warp: exclusive scan of the per-warp counts across lanes
+    const int kw = sKeepW[lane], lw = sLostW[lane];
+    int ks = kw, ls = lw;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int a = __shfl_up_sync(0xffffffffu, ks, o), b = __shfl_up_sync(0xffffffffu, ls, o);
+        if (lane >= o) { ks += a; ls += b; }
+    }
+    const int n_keep = __shfl_sync(0xffffffffu, ks, 31), n_lost = __shfl_sync(0xffffffffu, ls, 31);
+    int ok_ = __shfl_sync(0xffffffffu, ks - kw, warp), ol_ = __shfl_sync(0xffffffffu, ls - lw, warp);
+    if (warp == NW) {
+        // the point count of the coming PnP-RANSAC is known: draw its first minimal sets here
+        pnp_prepare_sets(sc, sets, rt, n_keep, pre);
+        return;
+    }
+    for (int i0 = lo; i0 < hi; i0 += 32) {
+        const int i = i0 + lane;
+        const bool in = i < hi;
         const bool keep = in && status[i] != 0;
-        if (in && iters) it += iters[i];
-        const int o = tile_rank<kScanThreads>(keep, sWarp, &sKeep);
-        const int ol = tile_rank<kScanThreads>(in && !keep, sWarp, &sLost);
+        const unsigned bk = __ballot_sync(0xffffffffu, keep);
+        const unsigned bi = __ballot_sync(0xffffffffu, in);
+        const unsigned below = (1u << lane) - 1;
         if (keep) {
+            const int o = ok_ + __popc(bk & below);
             const float2 p = klt_out[i];
             const double x = X_in[3 * (size_t)i], y = X_in[3 * (size_t)i + 1], z = X_in[3 * (size_t)i + 2];
             P_out[o] = p;
@@ -73,15 +108,18 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
             q4[o] = make_float4((float)x, (float)y, (float)z, p.x);   // cv2 converts X to float32
             qv[o] = p.y;
         } else if (in) {
-            lost[ol] = klt_out[i];
+            lost[ol_ + __popc(bi & ~bk & below)] = klt_out[i];
+        }
+        ok_ += __popc(bk); ol_ += __popc(bi & ~bk);
+    }
+    if (warp == 0) {
+        int its = sIterW[lane];
+        its = __reduce_add_sync(0xffffffffu, its);
+        if (lane == 0) {
+            sc->klt_iters_cand = 0; sc->prev_n_land = n; sc->n_land = n_keep; sc->n_tracked = n_keep; sc->n_lost = n_lost;
+            sc->klt_iters = its;
         }
     }
-    it = __reduce_add_sync(0xffffffffu, it);
-    if ((tid & 31) == 0) atomicAdd(&sIter, it);
-    __syncthreads();
-    if (tid == 0) { sc->klt_iters_cand = 0; sc->prev_n_land = n; sc->n_land = sKeep; sc->n_tracked = sKeep; sc->n_lost = sLost; sc->klt_iters = sIter; }
-    // the point count of the coming PnP-RANSAC is known: draw its first minimal sets here
-    if (tid < 32) pnp_prepare_sets(sc, sets, rt, sKeep);
 }
 
 // ---- DLT ---------------------------------------------------------------------------------------
