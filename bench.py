@@ -137,7 +137,7 @@ def run_reference(sq, steps, warmup):
 def run_gpu(args, rank, world, local_rank):
     import torch
     pkg = importlib.import_module(PKG)
-    scene, sq = build_sequence(seed=11 + rank)
+    scene, sq = build_sequence(seed=stream_seed(rank))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     stream = torch.cuda.Stream(device=dev)
@@ -257,6 +257,25 @@ def barrier(world):
         dist.barrier()
 
 
+def stream_seed(rank):
+    """One independent sequence per rank: the stream a rank processes is a function
+    of its rank only, so no rank needs anything from another one on the data path."""
+    return 11 + rank
+
+
+def job_throughput(total_ms, e2e_fps, steps, world, device=None):
+    """Whole-job frames/s from per-rank timings: the slowest rank defines the job's time (MAX over
+    ranks of the device time and of the e2e time per frame), the job's work is world x steps frames.
+    The only collective of the multi-GPU path; it is outside the timed region."""
+    if world > 1:
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor([total_ms, 1.0 / e2e_fps], dtype=torch.float64, device=device or "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_fps = float(t[0]), 1.0 / float(t[1])
+    return world * steps / (total_ms * 1e-3), world * e2e_fps, total_ms
+
+
 def run_e2e(pkg, sq, steps, warmup, local_rank, world):
     """Public API end to end: KeypointsToLandmarksAssociator / PoseEstimator / LandmarkTriangulator
     exactly as main.py:229-294 calls them; every step uploads its frame from pinned host memory and
@@ -369,17 +388,11 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     r = run_gpu(args, rank, world, local_rank)
-    total_ms, e2e_fps = r["total_ms"], r["e2e"]["fps"]
-    if world > 1:
-        import torch.distributed as dist
-        t = torch.tensor([total_ms, 1.0 / e2e_fps], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)      # slowest rank defines the job's time
-        total_ms, e2e_fps = float(t[0]), 1.0 / float(t[1])
+    fps, e2e_job_fps, total_ms = job_throughput(r["total_ms"], r["e2e"]["fps"], args.steps, world, "cuda")
     if rank != 0:
         if world > 1:
             torch.distributed.destroy_process_group()
         return
-    fps = world * args.steps / (total_ms * 1e-3)
 
     peaks = {}
     try:
@@ -405,7 +418,7 @@ def main():
     line = dict(base)
     line.update({
         "value": fps, "ms_per_step": total_ms / args.steps, "dtype": "u8/i32 (KLT), f64 (P3P, projection, DLT), f32 (inlier test)",
-        "e2e": {"value": world * e2e_fps, "unit": "frames/s", "h2d_bytes_per_step": r["e2e"]["h2d"], "d2h_bytes_per_step": r["e2e"]["d2h"]},
+        "e2e": {"value": e2e_job_fps, "unit": "frames/s", "h2d_bytes_per_step": r["e2e"]["h2d"], "d2h_bytes_per_step": r["e2e"]["d2h"]},
         "gpu_launches": int(r["launches"]), "klt_tracks_per_s": r["tracks_per_step"] * fps,
         "clocks": r["clocks"],
         "roofline": {"bound": "hbm", "kernel": "klt_track_kernel<21> (candidates' launch, side stream)", "achieved": achieved, "peak": peak, "unit": "GB/s",
