@@ -111,6 +111,7 @@ def tri():
 SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, n_feed, seed)
     "kitti_half": ("kitti", 0.5, 36, 600, 80, 3),
     "parking_half": ("parking", 0.5, 24, 300, 60, 4),
+    "malaga_half": ("malaga", 0.5, 20, 900, 100, 5),
 }
 
 

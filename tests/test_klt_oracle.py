@@ -13,6 +13,7 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 KLT_CASES = {  # name: (h, w, seed, n)
     "kitti": (376, 1241, 1, 2000),
     "parking": (480, 640, 2, 500),
+    "malaga": (768, 1024, 3, 3000),
     "small": (120, 160, 4, 300),
     "tiny": (40, 60, 5, 100),
 }

@@ -15,6 +15,7 @@ GOLD = os.path.join(os.path.dirname(__file__), "golden")
 SEQ_CASES = {  # must match tests/golden/make_golden.py
     "kitti_half": ("kitti", 0.5, 36, 600, 80, 3),
     "parking_half": ("parking", 0.5, 24, 300, 60, 4),
+    "malaga_half": ("malaga", 0.5, 20, 900, 100, 5),
 }
 _seq_cache = {}
 
