@@ -189,6 +189,33 @@ int vo_get_candidate_tracks(vo_ctx* ctx, float* prev_pts, float* next_pts, uint8
  * frame they arrive, so the order does not change results). */
 int vo_add_candidates(vo_ctx* ctx, const double* pts, int n, const double T44[16]);
 
+/* ---- SURVEY.md 8f-1 (first "next" row): the Shi-Tomasi candidate detector on the device.
+ * Replaces cv2.goodFeaturesToTrack(new_frame, maxCorners=500, qualityLevel=0.03, minDistance=10,
+ * mask=mask, blockSize=4, gradientSize=3, useHarrisDetector=False) at vo_pipeline.py:381
+ * (LandmarkTriangulator.find_new_candidates_shi, vo_pipeline.py:357-390). */
+typedef struct vo_gftt_params {
+    int max_corners;       /* 500 (<= 0: no limit) */
+    double quality_level;  /* 0.03 */
+    double min_distance;   /* 10 */
+    int block_size;        /* 4 (1..8); gradientSize is 3 */
+    int vec_cols;          /* columns the OpenCV build evaluates with its fused SIMD row filter;
+                            * -1 = width & ~31, what the pinned build does (oracle/gftt.c) */
+} vo_gftt_params;
+void vo_gftt_params_default(vo_gftt_params* p);
+/* Unit-level mirror of cv2.goodFeaturesToTrack on a resident frame.  mask: w*h u8 (host or device)
+ * or NULL; alternatively exclude_pts (n x 2 float32): the reference's mask, 255 everywhere and 0 at
+ * int(x), int(y) of every point (vo_pipeline.py:371-378).  corners: cap x 2 float32 (x, y) in cv2's
+ * order.  eig_out: optional w*h float32 = cv2.cornerMinEigenVal(frame, blockSize, ksize=3).
+ * info = {candidates sorted, grid overflow, max key, 0}.  Synchronises. */
+int vo_good_features_to_track(vo_ctx* ctx, int64_t frame_key, const uint8_t* mask, const float* exclude_pts,
+                              int n_exclude, const vo_gftt_params* params, float* corners, int cap, int* n_corners,
+                              float* eig_out, int32_t info[4]);
+/* find_new_candidates_shi + the append of vo_pipeline.py:564-591 without leaving the device: corners
+ * of frame_key, masked at the previous-frame positions of the candidates the last KLT kept, become
+ * candidates C := F := corners, T := T44 (NULL = the pose the last PnP left on the device).
+ * No synchronisation.  Call after the promotion step of the same frame. */
+int vo_detect_add_candidates_shi(vo_ctx* ctx, int64_t frame_key, const vo_gftt_params* params, const double T44[16]);
+
 /* One frame of main.py:216-284 with a single host synchronisation: upload (img may be NULL if
  * next_key is resident), KLT of P and C, PnP-RANSAC + LM + pruning, promotion, append of
  * new_candidates (n_new x 2 float64; the reference's detectors stay on the CPU). */

@@ -10,8 +10,8 @@ The directory name carries a hyphen (it mirrors the upstream repository name), s
 directory on sys.path ahead of the reference's src/ to get the drop-in `vo_pipeline` module.
 """
 from . import _build  # noqa: F401
-from ._cabi import (Context, Counters, KltParams, PnpParams, PinnedArray, VoError, klt_defaults,  # noqa: F401
-                    pnp_defaults, load, lib_path)
+from ._cabi import (Context, Counters, GfttParams, KltParams, PnpParams, PinnedArray, VoError, gftt_defaults,  # noqa: F401
+                    klt_defaults, pnp_defaults, load, lib_path)
 
 __all__ = ["Context", "KltParams", "PnpParams", "PinnedArray", "VoError", "load", "lib_path", "build"]
 

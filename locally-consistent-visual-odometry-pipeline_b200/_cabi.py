@@ -33,6 +33,11 @@ class PnpParams(ctypes.Structure):
                 ("refine_iters", c_int), ("min_inliers", c_int)]
 
 
+class GfttParams(ctypes.Structure):
+    _fields_ = [("max_corners", c_int), ("quality_level", c_double), ("min_distance", c_double),
+                ("block_size", c_int), ("vec_cols", c_int)]
+
+
 class Counters(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "n_landmarks", "n_candidates", "n_tracked", "n_lost", "n_inliers", "pnp_ok", "ransac_iters",
@@ -96,6 +101,10 @@ SIGNATURES = {
     "vo_get_stage_times": (c_int, [c_void_p, c_void_p, _PI]),
     "vo_solve_pnp_ransac": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _PI]),
+    "vo_gftt_params_default": (None, [ctypes.POINTER(GfttParams)]),
+    "vo_good_features_to_track": (c_int, [c_void_p, c_i64, c_void_p, c_void_p, c_int, ctypes.POINTER(GfttParams),
+                                          c_void_p, c_int, _PI, c_void_p, c_void_p]),
+    "vo_detect_add_candidates_shi": (c_int, [c_void_p, c_i64, ctypes.POINTER(GfttParams), c_void_p]),
     "vo_triangulate_points": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
 }
 
@@ -131,6 +140,12 @@ def _ptr(a):
 def klt_defaults():
     p = KltParams()
     load().vo_klt_params_default(ctypes.byref(p))
+    return p
+
+
+def gftt_defaults():
+    p = GfttParams()
+    load().vo_gftt_params_default(ctypes.byref(p))
     return p
 
 
@@ -437,3 +452,33 @@ class Context:
         out = np.zeros((n, 4))
         self._check(self.lib.vo_triangulate_points(self.h, _ptr(M1), _ptr(M2), per_point, _ptr(p1), _ptr(p2), n, _ptr(out)))
         return out
+
+    # ---- unit-level: cv2.goodFeaturesToTrack (reference vo_pipeline.py:381) ---------------------------
+    def good_features_to_track(self, frame_key, mask=None, exclude_pts=None, params=None, want_eig=False, shape=None):
+        """Shi-Tomasi corners of a resident frame in cv2's order: (n, 2) float32 (x, y).  `mask` is a
+        (h, w) uint8 image or None; `exclude_pts` (n, 2) builds the reference's single-pixel mask."""
+        prm = params if params is not None else gftt_defaults()
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, np.uint8)
+            shape = mask.shape
+        ex = None
+        if exclude_pts is not None and len(exclude_pts):
+            ex = np.ascontiguousarray(exclude_pts, np.float32).reshape(-1, 2)
+        if want_eig and shape is None:
+            raise ValueError("want_eig needs the frame shape")
+        cap = prm.max_corners if prm.max_corners > 0 else int(shape[0] * shape[1])
+        out = np.zeros((max(cap, 1), 2), np.float32)
+        eig = np.empty(shape, np.float32) if want_eig else None
+        n = c_int()
+        info = np.zeros(4, np.int32)
+        self._check(self.lib.vo_good_features_to_track(self.h, frame_key, _ptr(mask), _ptr(ex), 0 if ex is None else len(ex),
+                                                       ctypes.byref(prm), _ptr(out), cap, ctypes.byref(n), _ptr(eig), _ptr(info)))
+        if want_eig:
+            return out[:n.value].copy(), eig, int(info[0])
+        return out[:n.value].copy()
+
+    def detect_add_candidates_shi(self, frame_key, params=None, T=None):
+        """find_new_candidates_shi + the candidate append on the device, no synchronisation."""
+        prm = params if params is not None else gftt_defaults()
+        T = None if T is None else np.ascontiguousarray(T, np.float64).reshape(4, 4)
+        self._check(self.lib.vo_detect_add_candidates_shi(self.h, frame_key, ctypes.byref(prm), _ptr(T)))

@@ -108,6 +108,7 @@ int vo_destroy(vo_ctx* c)
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     pipeline_free(c);
+    detector_free(c);
     for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); }
     cudaFree(c->u_pts.p); cudaFree(c->u_out.p); cudaFree(c->u_err.p); cudaFree(c->u_status.p);
     cudaFree(c->u_iters.p); cudaFree(c->u_n.p);

@@ -46,6 +46,27 @@ struct DevBuf {
     size_t cap = 0;  // elements
 };
 
+// ---- Shi-Tomasi detector (det.cu; reference vo_pipeline.py:357-390) -----------------------------
+struct DetScalars {
+    unsigned max_key;   // order-preserving key of the masked maximum of the min-eigenvalue map (0: none)
+    int32_t n_cand;     // local maxima above the quality threshold
+    int32_t n_out;      // corners accepted
+    int32_t overflow;   // an accepted-corner grid cell overflowed (cannot happen for minDistance >= cell)
+    int32_t n_sorted;   // candidates the selection kernel sorted
+};
+
+struct Detector {
+    DevBuf<float> eig;                  // w*h min-eigenvalue map
+    DevBuf<uint8_t> mask;               // w*h
+    DevBuf<unsigned long long> keys;    // (value key << 32 | pixel index), power-of-two capacity >= w*h
+    DevBuf<int> grid_cnt;               // accepted corners per minDistance cell
+    DevBuf<unsigned> grid_pts;          // 4 packed (x | y << 16) per cell
+    DevBuf<float> out;                  // accepted corners, float2, cv2's order
+    DetScalars* d_sc = nullptr;
+    DetScalars* h_sc = nullptr;         // pinned mirror
+    int out_cap = 0;
+};
+
 struct Ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -72,6 +93,8 @@ struct Ctx {
     // forward-backward check scratch
     DevBuf<float> fb_pts;
     DevBuf<uint8_t> fb_status;
+
+    Detector det;
 
     struct Pipeline* pipe = nullptr;  // device-resident Markov state + PnP scratch
 };
@@ -226,6 +249,9 @@ struct Pipeline {
     DevBuf<int32_t> stage_i;
     int klt_b_off = 0;      // offset of the candidate results inside the klt_* buffers
     bool packed_valid = false;  // q4/qv hold the current landmarks (set by the post-KLT compaction)
+    // the last promotion step consumed a candidate KLT: C[ccur ^ 1] holds the candidates' previous
+    // positions, klt_status + mask_src_off their status, d_sc->spec_n_cand their number (detector mask)
+    bool mask_src_valid = false; int mask_src_off = 0;
     // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
     bool spec_pending = false;
     int64_t spec_prev_key = -1, spec_next_key = -1;
@@ -280,7 +306,14 @@ int launch_landmark_compact(Ctx* c, int n_upper);   // after KLT: keep status==1
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper,
                    bool use_klt, int b_off);
 // d_pts: n_new x 2 doubles on the device; d_Thost: 16 doubles on the device or nullptr (= device pose)
-int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost);
+// d_n_new: optional device count (the rows actually appended are min(*d_n_new, n_new))
+int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new = nullptr);
+// det.cu
+void gftt_defaults(vo_gftt_params* p);
+int detector_free(Ctx* c);
+int launch_gftt(Ctx* c, const FrameSlot& f, const uint8_t* d_mask, const vo_gftt_params& prm);
+int build_point_mask(Ctx* c, int w, int h, const float* d_pts, const uint8_t* d_status, const int32_t* d_n, int n_upper);
+int corners_to_stage(Ctx* c, double* d_stage);
 int launch_triangulate(Ctx* c, const double* d_M1, const double* d_M2, int per_point, const double* d_p1,
                        const double* d_p2, int n, double* d_X4);
 

@@ -472,6 +472,37 @@ int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
     return VO_OK;
 }
 
+// ---- 8f-1: find_new_candidates_shi on the device (vo_pipeline.py:357-390 + :564-591) ---------------
+// Shi-Tomasi corners of the resident frame, masked at the truncated PREVIOUS-frame positions of the
+// candidates the last KLT kept (the reference's mask, :371-378), appended as candidates C := F :=
+// corners, T := T44 (NULL: the pose the last PnP left on the device).  Nothing comes back to the
+// host: no synchronisation.  Call after the promotion step of the same frame.
+int vo_detect_add_candidates_shi(vo_ctx* c, int64_t frame_key, const vo_gftt_params* params, const double T44[16])
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    vo_gftt_params prm;
+    if (params) prm = *params; else vo_gftt_params_default(&prm);
+    if (prm.max_corners <= 0) return set_error(c, VO_ERR_INVALID, "vo_detect_add_candidates_shi needs maxCorners > 0");
+    FrameSlot* f = get_frame(c, frame_key);
+    if (!f) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)frame_key);
+    VO_TRY(join_side_stream(c));
+    const uint8_t* d_mask = nullptr;
+    if (p->mask_src_valid) {
+        // upper bound of the pre-promotion candidate count: what the promotion step was sized with
+        const int n_upper = (int)(p->C[p->ccur ^ 1].cap / 2);
+        VO_TRY(build_point_mask(c, f->w, f->h, p->C[p->ccur ^ 1].p, p->klt_status.p + p->mask_src_off,
+                                &p->d_sc->spec_n_cand, n_upper));
+        d_mask = c->det.mask.p;
+    }
+    VO_TRY(launch_gftt(c, *f, d_mask, prm));
+    VO_TRY(ensure(c, p->stage_d, (size_t)prm.max_corners * 2 + 16));
+    if (T44) VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p, T44, sizeof(double) * 16, cudaMemcpyDefault, c->stream));
+    VO_TRY(corners_to_stage(c, p->stage_d.p + 16));
+    VO_TRY(launch_cand_add(c, p->stage_d.p + 16, prm.max_corners, T44 ? p->stage_d.p : nullptr, &c->det.d_sc->n_out));
+    return VO_OK;
+}
+
 // Tracks the candidates C over (prev, next) unless vo_klt_track_landmarks already did for this
 // frame pair; the result is consumed by vo_track_triangulate_promote.  (vo_pipeline.py:501)
 int vo_track_candidates(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params)

@@ -344,7 +344,8 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
 
 // append n_new candidates: C := F := pts, T := pose (vo_pipeline.py:574-591); the last CTA to
 // finish publishes the new size (every CTA has read the old one by then)
-__global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts, int n_new, int use_dev_T,
+__global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts, int n_new_upper,
+                                const int32_t* __restrict__ n_new_dev, int use_dev_T,
                                 const double* __restrict__ Thost, float2* __restrict__ C, double2* __restrict__ F,
                                 int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap)
 {
@@ -352,6 +353,7 @@ __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts,
     pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n0 = sc->n_cand;
+    const int n_new = n_new_dev ? min(*n_new_dev, n_new_upper) : n_new_upper;
     const bool skip = use_dev_T && !sc->ok;   // no pose this frame: nothing is added
     if (!skip) {
         if (i < 16) poses[16 * (size_t)pose_idx + i] = use_dev_T ? sc->T[i] : Thost[i];
@@ -454,12 +456,13 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     c->launches++;
     c->launches++;
     p->ccur ^= 1;
+    p->mask_src_valid = use_klt; p->mask_src_off = b_off;
     p->n_land_upper += ncand_upper;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
 }
 
-int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost)
+int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new)
 {
     Pipeline* p = c->pipe;
     VO_TRY(join_side_stream(c));
@@ -471,7 +474,7 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
     const int cap = (int)(p->C[p->ccur].cap / 2);
     const int threads = 256, blocks = ((n_new > 16 ? n_new : 16) + threads - 1) / threads;
     VO_CUDA(c, launch_pdl(cand_add_kernel, dim3(blocks), dim3(threads), c->stream, p->d_sc, (const double2*)d_pts, n_new,
-                          (int)(d_Thost == nullptr), d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
+                          d_n_new, (int)(d_Thost == nullptr), d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
                           p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap));
     c->launches++;
     p->n_poses++;

@@ -198,3 +198,52 @@ def bearing_triangulate(C, F, T, Tnew, K, alpha_deg):
         _p(C), _p(F), _p(T), n, _p(np.ascontiguousarray(Tnew, np.float64)), _p(np.ascontiguousarray(K, np.float64)),
         alpha_deg, _p(promote), _p(X), _p(alpha))
     return promote, X, alpha
+
+
+def corner_min_eigen_val(img, block=4, vec_cols=-1):
+    """cv2.cornerMinEigenVal(img, block, ksize=3) restated (oracle/gftt.c)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    eig = np.empty((h, w), np.float32)
+    f = lib().vo_oracle_corner_min_eigen_val
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+    f(_p(img), w, h, block, vec_cols, _p(eig))
+    return eig
+
+
+def sobel_scaled(img, block=4, vec_cols=-1):
+    """cv2.Sobel(img, CV_32F, 1|0, 0|1, ksize=3, scale=1/(4*block*255)) restated (oracle/gftt.c)."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    dx, dy = np.empty((h, w), np.float32), np.empty((h, w), np.float32)
+    f = lib().vo_oracle_sobel_scaled
+    f.restype = None
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    f(_p(img), w, h, block, vec_cols, _p(dx), _p(dy))
+    return dx, dy
+
+
+def good_features_to_track(img, max_corners=500, quality=0.03, min_distance=10.0, mask=None, block=4,
+                           vec_cols=-1, want_eig=False):
+    """cv2.goodFeaturesToTrack(img, max_corners, quality, min_distance, mask=mask, blockSize=block,
+    gradientSize=3, useHarrisDetector=False) restated (oracle/gftt.c; reference vo_pipeline.py:381).
+    Returns (n, 2) float32 corners (x, y) in cv2's order."""
+    img = np.ascontiguousarray(img, np.uint8)
+    h, w = img.shape
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, np.uint8)
+    cap = max_corners if max_corners > 0 else w * h
+    corners = np.zeros((cap, 2), np.float32)
+    eig = np.empty((h, w), np.float32) if want_eig else None
+    nc = ctypes.c_int()
+    f = lib().vo_oracle_good_features_to_track
+    f.restype = ctypes.c_int
+    f.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
+                  ctypes.c_double, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p,
+                  ctypes.POINTER(ctypes.c_int)]
+    n = f(_p(img), w, h, _p(mask), max_corners, quality, min_distance, block, vec_cols, _p(corners), cap, _p(eig),
+          ctypes.byref(nc))
+    if want_eig:
+        return corners[:n].copy(), eig, nc.value
+    return corners[:n].copy()

@@ -108,6 +108,29 @@ def tri():
     np.savez_compressed(os.path.join(HERE, "tri.npz"), **out)
 
 
+from make_golden_cases import GFTT_CASES, gftt_image, reference_mask  # noqa: E402
+
+
+def gftt():
+    """cv2.goodFeaturesToTrack exactly as the reference calls it (vo_pipeline.py:381), with the
+    reference's mask, plus cv2.cornerMinEigenVal (the map behind it) as a checksum + samples."""
+    import hashlib
+    out = {"cv2_version": cv2.__version__}
+    for name in GFTT_CASES:
+        img, pts = gftt_image(name)
+        mask = reference_mask(img, pts)
+        c = cv2.goodFeaturesToTrack(img, maxCorners=500, qualityLevel=0.03, minDistance=10, mask=mask, blockSize=4,
+                                    gradientSize=3, useHarrisDetector=False, k=0.04)
+        out[name + "_corners"] = np.zeros((0, 2), np.float32) if c is None else c.reshape(-1, 2)
+        c = cv2.goodFeaturesToTrack(img, maxCorners=0, qualityLevel=0.01, minDistance=5, blockSize=4)
+        out[name + "_all_corners"] = c.reshape(-1, 2).astype(np.uint16)
+        eig = cv2.cornerMinEigenVal(img, 4, ksize=3)
+        out[name + "_eig_sha1"] = np.frombuffer(hashlib.sha1(eig.tobytes()).digest(), np.uint8)
+        out[name + "_eig_rows"] = eig[:: max(1, img.shape[0] // 6)]
+        out[name + "_img_sum"] = img.astype(np.int64).sum()
+    np.savez_compressed(os.path.join(HERE, "gftt.npz"), **out)
+
+
 SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, n_feed, seed)
     "kitti_half": ("kitti", 0.5, 36, 600, 80, 3),
     "parking_half": ("parking", 0.5, 24, 300, 60, 4),
@@ -203,7 +226,7 @@ def seq():
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["klt", "pnp", "tri", "seq"]
+    which = sys.argv[1:] or ["klt", "pnp", "tri", "gftt", "seq"]
     for w in which:
         globals()[w]()
     print("golden vectors written with cv2", cv2.__version__)
