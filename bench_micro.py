@@ -73,7 +73,7 @@ def main():
     sm_mhz = pk.get("sm_max_mhz", 1965.0)
     fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12      # TFLOP/s, CUDA-core FMA
     ptr = lambda t: ctypes.c_void_p(t.data_ptr())
-    want = set(args.only.split(",")) if args.only else {"klt", "pyramid", "ransac", "dlt"}
+    want = set(args.only.split(",")) if args.only else {"klt", "pyramid", "ransac", "dlt", "gftt"}
 
     def check(r):
         if r != 0:
@@ -175,6 +175,43 @@ def main():
         print(json.dumps({"kernel": "triangulate_kernel (4x4 Jacobi SVD, FP64)", "regime": "saturation", "points": n, "ms": med,
                           "ms_min": best, "points_per_s": n / (med * 1e-3), "achieved_gflops_fp64": n * 3000.0 / (med * 1e-3) / 1e9,
                           "algorithmic_bytes": byt, "achieved_gbs": byt / (med * 1e-3) / 1e9, "hbm_peak_gbs": hbm}))
+    if "gftt" in want:
+        # cv2.goodFeaturesToTrack replacement on a KITTI-shaped frame, mask of 1500 points,
+        # corners left on the device (the pipeline appends them there); cv2 on the host cores beside it
+        import time
+        scene = importlib.import_module(PKG + ".scene")
+        img = scene.Sequence("kitti", n_frames=2, n_tracks=50, n_feed=10, seed=25).frames[1]
+        rng = np.random.default_rng(3)
+        pts = np.stack([rng.uniform(0, 1241, 1500), rng.uniform(0, 376, 1500)], 1).astype(np.float32)
+        ctx.upload_frame(img, 900)
+        d_pts = torch.from_numpy(pts).to(dev)
+        d_out = torch.empty((500, 2), dtype=torch.float32, device=dev)
+        prm = pkg.gftt_defaults()
+        n = ctypes.c_int()
+
+        def run():
+            check(lib.vo_good_features_to_track(h, 900, None, ptr(d_pts), len(pts), ctypes.byref(prm), ptr(d_out), 500,
+                                                ctypes.byref(n), None, None))
+        med, best = timed(torch, stream, run, args.reps)
+        line = {"kernel": "shi_eig + shi_nms + shi_select (Shi-Tomasi, 500 corners, minDistance 10)", "regime": "one 1241x376 frame",
+                "ms": med, "ms_min": best, "corners": n.value, "frames_per_s": 1e3 / med,
+                "algorithmic_bytes": 1241 * 376 * (1 + 1 + 4 + 4 + 1), "note": "u8 frame + mask in, float32 map out and back in for the NMS"}
+        try:
+            import cv2
+            mask = np.full(img.shape, 255, np.uint8)
+            mask[pts[:, 1].astype(int), pts[:, 0].astype(int)] = 0
+            ts = []
+            for _ in range(12):
+                t0 = time.perf_counter()
+                c = cv2.goodFeaturesToTrack(img, maxCorners=500, qualityLevel=0.03, minDistance=10, mask=mask, blockSize=4,
+                                            gradientSize=3, useHarrisDetector=False, k=0.04)
+                ts.append((time.perf_counter() - t0) * 1e3)
+            line["cv2_ms"] = float(np.median(ts[2:]))
+            line["cv2_threads"] = cv2.getNumThreads()
+            line["same_corners_as_cv2"] = bool(np.array_equal(c.reshape(-1, 2), d_out[:n.value].cpu().numpy()))
+        except ImportError:
+            pass
+        print(json.dumps(line))
     ctx.close()
 
 

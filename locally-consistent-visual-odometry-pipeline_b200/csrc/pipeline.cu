@@ -385,6 +385,7 @@ static int promote_rollback(Ctx* c)
     promote_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
     c->launches++;
     p->ccur ^= 1;                                  // the pre-promotion candidate buffers are intact
+    p->mask_src_valid = false;
     p->n_land_upper = p->h_sc->spec_n_land;        // h_sc is current: every speculation ends in a sync
     p->n_cand_upper = p->h_sc->spec_n_cand;
     p->h_sc->n_land = p->h_sc->spec_n_land; p->h_sc->n_cand = p->h_sc->spec_n_cand;

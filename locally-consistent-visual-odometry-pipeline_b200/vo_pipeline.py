@@ -72,6 +72,7 @@ _DEFAULTS = {
     'speculative_promotion': True,   # enqueue the promotion step ahead of estimatePose's sync
     'emulate_cf_alias': True,    # reference quirk App. B-5 (first candidate batch: F follows C)
     'device': 0,
+    'gpu_detector': True,        # find_new_candidates_shi on the device (csrc/det.cu); False: cv2 on the CPU
 }
 
 
@@ -459,7 +460,8 @@ class PoseEstimator():
         # sync this method ends in, with the pose taken from the device, and let triangulate_landmark
         # confirm it when its arguments are the ones assumed (main.py always passes them).
         method = config['find_new_candidates_method']
-        speculate = (bool(_cfg('speculative_promotion')) and not uploaded and method in ('feed', 'sift-sift')
+        speculate = (bool(_cfg('speculative_promotion')) and not uploaded
+                     and (method in ('feed', 'sift-sift') or (method == 'shi-mask' and _device_shi()))
                      and rt.pair is not None and rt.ctx.candidates_tracked(rt.pair[2], rt.pair[3]))
         if speculate:
             alpha = float(_alpha_threshold())
@@ -537,6 +539,12 @@ class LandmarkTriangulator():
     def find_new_candidates_shi(self, new_frame: np.ndarray, state: dict, keypoints_well_tracked):
         """Shi-Tomasi corners (500, quality 0.03, min distance 10, block 4) outside the single pixels
         of the well-tracked candidates (reference vo_pipeline.py:357-390)."""
+        if _cfg('gpu_detector'):
+            # same corners in the same order as cv2.goodFeaturesToTrack with the reference's mask
+            # (tests/test_gftt_gpu.py); the mask is built on the device from the point list
+            rt = _runtime(new_frame)
+            pts = np.asarray(keypoints_well_tracked, np.float64).reshape(-1, 2)
+            return rt.ctx.good_features_to_track(rt.frame_key(new_frame), exclude_pts=pts).astype(np.float64)
         VOInitializer._need_cv2()
         mask = self._pixel_mask(new_frame, keypoints_well_tracked)
         corners = cv2.goodFeaturesToTrack(new_frame, maxCorners=500, qualityLevel=0.03, minDistance=10, mask=mask,
@@ -603,7 +611,10 @@ class LandmarkTriangulator():
             # frame pair went through associateKeypointsToLandmarks), removal, bearing test, DLT, promotion
             rt.ctx.track_candidates(k_old, k_new, rt.klt)
         well_tracked_prev = []
-        if method in ('shi-mask', 'sift-mask'):
+        # shi-mask with the stock detector method: detection, mask and append stay on the device
+        device_shi = (method == 'shi-mask' and _device_shi()
+                      and type(self).find_new_candidates_shi is LandmarkTriangulator.find_new_candidates_shi)
+        if method in ('shi-mask', 'sift-mask') and not device_shi:
             prev, _, st = rt.ctx.candidate_tracks()          # the detectors mask these pixels
             well_tracked_prev = prev[st == 1]
         if not confirmed:
@@ -611,7 +622,11 @@ class LandmarkTriangulator():
 
         # 2) new candidates: CPU detectors run while the GPU works on the promotion
         new_candidates_list, cur_des = [], []
-        if method == 'shi-mask':
+        if device_shi:
+            # vo_pipeline.py:381 + :574-591 in one enqueue: corners masked at the previous positions of
+            # the candidates KLT kept, appended with T = new_pose; nothing returns to the host
+            rt.ctx.detect_add_candidates_shi(rt.pair[3] if confirmed else k_new, T=np.eye(4) @ new_pose)
+        elif method == 'shi-mask':
             new_candidates_list = self.find_new_candidates_shi(new_frame, state, well_tracked_prev)
         elif method == 'sift-mask':
             new_candidates_list = self.find_new_candidates_sift_mask(new_frame, state, well_tracked_prev)
@@ -634,6 +649,10 @@ class LandmarkTriangulator():
         else:
             extended_state = DeviceExtendedState(rt, rt.ext_version)
         return (state, extended_state, cur_des)
+
+
+def _device_shi():
+    return bool(_cfg('gpu_detector'))
 
 
 def _alpha_threshold():

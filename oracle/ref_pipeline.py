@@ -23,7 +23,11 @@ except Exception:   # pragma: no cover
 
 
 class RefPipeline:
-    def __init__(self, K, confidence=0.99999, reproj=2.0, alpha=1.0, pnp="p3p", max_iters=100, row_match="isin"):
+    def __init__(self, K, confidence=0.99999, reproj=2.0, alpha=1.0, pnp="p3p", max_iters=100, row_match="isin",
+                 detector=None):
+        # detector="shi": config find_new_candidates_method 'shi-mask' (vo_pipeline.py:357-390, :519-520):
+        # cv2.goodFeaturesToTrack with the reference's single-pixel mask instead of a candidate feed
+        self.detector = detector
         self.K = np.asarray(K, np.float64)
         self.confidence, self.reproj, self.alpha, self.pnp, self.max_iters = confidence, reproj, alpha, pnp, max_iters
         self.row_match = row_match
@@ -60,14 +64,29 @@ class RefPipeline:
         return np.concatenate([np.concatenate([R, t], axis=-1), np.array([[0, 0, 0, 1]])], axis=0)
 
     # vo_pipeline.py:470-750 with the detector replaced by `new_candidates`
+    # vo_pipeline.py:357-390
+    def find_new_candidates_shi(self, new_frame, keypoints_well_tracked):
+        mask = np.full(new_frame.shape[:2], 255, np.uint8)
+        for i in range(len(keypoints_well_tracked)):
+            y, x = int(keypoints_well_tracked[i][1]), int(keypoints_well_tracked[i][0])
+            if 0 <= y < mask.shape[0] and 0 <= x < mask.shape[1]:
+                mask[y, x] = 0
+        kp = cv2.goodFeaturesToTrack(new_frame, maxCorners=500, qualityLevel=0.03, minDistance=10, mask=mask, blockSize=4,
+                                     gradientSize=3, useHarrisDetector=False, k=0.04)
+        return np.array([cv2.KeyPoint(x=pt[0][0], y=pt[0][1], size=20).pt for pt in kp])
+
     def triangulate(self, old_frame, new_frame, state, ext, new_pose, new_candidates):
         c1 = ext['C'].astype(np.float32)
+        c1_ok = []
         if len(c1) > 0:
             c2, st, err = cv2.calcOpticalFlowPyrLK(old_frame, new_frame, c1, None)
             st = np.hstack(st).astype(np.bool_)
             c2_ok, c1_ok, c1_lost = c2[st == 1], c1[st == 1], c1[st == 0]
             if self.row_match == "isin":      # the reference's element-wise "row" matching (App. B-4)
-                mask = np.isin(ext['C'], c1_ok).all(axis=1)
+                if self.detector == "shi":
+                    mask = np.isin(c2, c2_ok).all(axis=1)        # vo_pipeline.py:519-520
+                else:
+                    mask = np.isin(ext['C'], c1_ok).all(axis=1)  # vo_pipeline.py:521-522
                 ext['C'][mask] = c2_ok
                 mask = np.isin(ext['C'], c1_lost).all(axis=1)
             else:                              # what it means: status-mask selection
@@ -78,6 +97,8 @@ class RefPipeline:
                 ext['C'] = np.delete(ext['C'], rm, axis=0)
                 ext['F'] = np.delete(ext['F'], rm, axis=0)
                 ext['T'] = np.delete(ext['T'], rm, axis=0)
+        if self.detector == "shi" and new_candidates is None:
+            new_candidates = self.find_new_candidates_shi(new_frame, c1_ok)
         if len(new_candidates) > 0:
             newT = np.stack([(np.eye(4) @ new_pose) for _ in range(len(new_candidates))])
             if len(ext['C']) == 0:

@@ -55,6 +55,19 @@ def scene_mod():
 
 
 @pytest.fixture()
+def dropin_shi(tmp_path, monkeypatch):
+    """The drop-in configured as the reference's 'shi-mask' mode (Shi-Tomasi candidates every frame)."""
+    (tmp_path / "config.yaml").write_text(CONFIG_YAML % "shi-mask")
+    monkeypatch.chdir(tmp_path)
+    monkeypatch.syspath_prepend(os.path.join(ROOT, PKG_NAME))
+    sys.modules.pop("vo_pipeline", None)
+    mod = importlib.import_module("vo_pipeline")
+    yield mod
+    mod._reset_runtime()
+    sys.modules.pop("vo_pipeline", None)
+
+
+@pytest.fixture()
 def dropin(tmp_path, monkeypatch):
     """The drop-in module imported the way main.py does it: as top-level `vo_pipeline`, with the
     package directory ahead on sys.path and config.yaml in the CWD (method 'feed' = candidate feed)."""

@@ -138,6 +138,11 @@ SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, n_feed, seed)
 }
 
 
+SHI_SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, seed)
+    "kitti_half_shi": ("kitti", 0.5, 14, 300, 6),
+}
+
+
 def _import_reference(workdir, method="sift-sift"):
     """Import the reference's own src/vo_pipeline.py (config.yaml in CWD, matplotlib stubbed)."""
     import importlib
@@ -222,6 +227,35 @@ def seq():
             print(name, variant, "ATE %.4f m over %.1f m" % (scene_mod.ate(Ts, gt), sq.scene.step * (nf - 1)),
                   "nP", nP[0], nP[-1], "nC", nC[0], nC[-1])
         ref.cv2.solvePnPRansac = real_ransac
+    # config find_new_candidates_method 'shi-mask': the reference's own Shi-Tomasi detector, mask,
+    # alpha (shi_alpha) and RANSAC confidence (shi_ransac_confidence) - SURVEY.md 8f-1
+    ref.config['find_new_candidates_method'] = 'shi-mask'
+    for name, (shape, scale, nf, nt, seed) in SHI_SEQ_CASES.items():
+        sq = scene_mod.Sequence(shape, n_frames=nf, n_tracks=nt, n_feed=1, seed=seed, scale=scale)
+        out[name + "_checksum"] = sq.checksum()
+        for variant in ("literal", "p3p"):
+            ref.cv2.solvePnPRansac = p3p_ransac if variant == "p3p" else real_ransac
+            state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+            ext = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+            assoc = ref.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+            pe = ref.PoseEstimator(sq.K)
+            Ts, nP, nC = [], [], []
+            with contextlib.redirect_stdout(io.StringIO()):
+                for k in range(1, nf):
+                    new_state, _ = assoc.associateKeypointsToLandmarks(sq.frames[k - 1], sq.frames[k], state)
+                    T = pe.estimatePose(new_state, k)
+                    tri = ref.LandmarkTriangulator(sq.K, None)
+                    state, ext, _ = tri.triangulate_landmark(sq.frames[k - 1], sq.frames[k], new_state, ext, T)
+                    Ts.append(T); nP.append(len(state["P"])); nC.append(len(ext["C"]))
+            out["%s_%s_T" % (name, variant)] = np.array(Ts)
+            out["%s_%s_nP" % (name, variant)] = np.array(nP)
+            out["%s_%s_nC" % (name, variant)] = np.array(nC)
+            if variant == "p3p":
+                out[name + "_p3p_C_last"] = np.asarray(ext["C"], np.float64)
+            print(name, variant, "ATE %.4f m over %.1f m" % (scene_mod.ate(Ts, sq.poses[1:]), sq.scene.step * (nf - 1)),
+                  "nP", nP[0], nP[-1], "nC", nC[0], nC[-1])
+        ref.cv2.solvePnPRansac = real_ransac
+    ref.config['find_new_candidates_method'] = 'sift-sift'
     np.savez_compressed(os.path.join(HERE, "seq.npz"), **out)
 
 

@@ -56,7 +56,7 @@ def test_gftt_vs_cv2_live(ctx):
     k = upload(ctx, img)
     agree = []
     for md, mc, q, bs in ((10, 500, 0.03, 4), (10.4, 0, 0.03, 4), (3, 100, 0.2, 4), (0, 50, 0.01, 4), (7, 300, 0.05, 3), (10, 500, 0.03, 5)):
-        c = cv2.goodFeaturesToTrack(img, maxCorners=mc, qualityLevel=q, minDistance=md, blockSize=bs, gradientSize=3)
+        c = cv2.goodFeaturesToTrack(img, maxCorners=mc, qualityLevel=q, minDistance=md, mask=None, blockSize=bs, gradientSize=3)
         c = c.reshape(-1, 2)
         o = ctx.good_features_to_track(k, params=ctx_params(ctx, mc, q, md, bs), shape=img.shape)
         agree.append(len(c) == len(o) and np.array_equal(c, o))

@@ -9,7 +9,7 @@ import os
 import numpy as np
 import pytest
 
-from test_pipeline_oracle import GOLD, SEQ_CASES, get_sequence, run_port
+from test_pipeline_oracle import GOLD, SEQ_CASES, SHI_SEQ_CASES, get_sequence, get_shi_sequence, run_port, run_port_shi
 from test_pnp_oracle import rot_angle
 
 pytestmark = pytest.mark.gpu
@@ -90,6 +90,45 @@ def test_dropin_sequence_vs_reference_classes(dropin, scene_mod, name):
     assert len(P) == len(X) == nP[-1] and P.dtype == np.float32 and X.dtype == np.float64
     C, F, T = (vision.extended_state[k] for k in "CFT")
     assert len(C) == len(F) == len(T) == nC[-1] and T.shape[1:] == (4, 4)
+
+
+@pytest.mark.parametrize("name", list(SHI_SEQ_CASES))
+@pytest.mark.parametrize("gpu_detector", [True, False])
+def test_dropin_shi_mask_sequence_vs_reference_classes(dropin_shi, scene_mod, name, gpu_detector):
+    """config 'shi-mask' end to end: candidates come from the Shi-Tomasi detector every frame -
+    on the device (detect + mask + append without a host round trip, csrc/det.cu) or, with
+    gpu_detector False, from cv2 on the CPU as before - against the reference's own classes run in
+    that mode (golden).  The detector is bit-exact, so both must give the same candidate sets."""
+    vo = dropin_shi
+    vo.config["gpu_detector"] = gpu_detector
+    if not gpu_detector:
+        pytest.importorskip("cv2")
+    g = np.load(os.path.join(GOLD, "seq.npz"))
+    sq = get_shi_sequence(scene_mod, name)
+    Ts, nP, nC, vision = drive_dropin(vo, sq)
+    if sq.checksum() == int(g[name + "_checksum"]):
+        Tg, nPg, nCg, Cg = g[name + "_p3p_T"], g[name + "_p3p_nP"], g[name + "_p3p_nC"], g[name + "_p3p_C_last"]
+        Tl = g[name + "_literal_T"]
+    else:
+        pytest.importorskip("cv2")
+        Tg, nPg, nCg, _, e = run_port_shi(sq, "p3p")
+        Cg = np.asarray(e["C"], np.float64)
+        Tl = run_port_shi(sq, "literal")[0]
+    gt = sq.poses[1:]
+    same = (nP == nPg) & (nC == nCg)
+    first_diff = int(np.argmin(same)) if not same.all() else len(same)
+    print("%s gpu_detector=%s: state sizes identical for the first %d of %d frames; nC %s vs %s" % (
+        name, gpu_detector, first_diff, len(same), nC[-3:], nCg[-3:]))
+    assert first_diff >= len(same) // 2
+    assert np.abs(nP - nPg).max() <= 0.15 * nPg.max() and np.abs(nC - nCg).max() <= 0.05 * nCg.max()
+    m = max(first_diff, 1)
+    dR0 = max(rot_angle(a[:3, :3], b[:3, :3]) for a, b in zip(Ts[:m], Tg[:m]))
+    dt0 = max(np.linalg.norm(a[:3, 3] - b[:3, 3]) / np.linalg.norm(b[:3, 3]) for a, b in zip(Ts[:m], Tg[:m]))
+    assert dR0 <= 1e-4 and dt0 <= 1e-4
+    assert scene_mod.ate(Ts, gt) <= 1.01 * max(scene_mod.ate(Tl, gt), scene_mod.ate(Tg, gt)) + 1e-3
+    if first_diff == len(same):      # identical inputs all the way: the candidate sets are the same rows
+        C = np.asarray(vision.extended_state["C"], np.float64)
+        assert C.shape == Cg.shape and np.abs(C - Cg).max() <= 0.05
 
 
 def test_fused_frame_equals_staged_calls(pkg, scene_mod):

@@ -17,6 +17,9 @@ SEQ_CASES = {  # must match tests/golden/make_golden.py
     "parking_half": ("parking", 0.5, 24, 300, 60, 4),
     "malaga_half": ("malaga", 0.5, 20, 900, 100, 5),
 }
+SHI_SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, seed) - must match tests/golden/make_golden.py
+    "kitti_half_shi": ("kitti", 0.5, 14, 300, 6),
+}
 _seq_cache = {}
 
 
@@ -25,6 +28,26 @@ def get_sequence(scene_mod, name):
         shape, scale, nf, nt, nfeed, seed = SEQ_CASES[name]
         _seq_cache[name] = scene_mod.Sequence(shape, n_frames=nf, n_tracks=nt, n_feed=nfeed, seed=seed, scale=scale)
     return _seq_cache[name]
+
+
+def get_shi_sequence(scene_mod, name):
+    if name not in _seq_cache:
+        shape, scale, nf, nt, seed = SHI_SEQ_CASES[name]
+        _seq_cache[name] = scene_mod.Sequence(shape, n_frames=nf, n_tracks=nt, n_feed=1, seed=seed, scale=scale)
+    return _seq_cache[name]
+
+
+def run_port_shi(sq, variant):
+    """config 'shi-mask': the port detects with cv2.goodFeaturesToTrack (shi_alpha 1.5, shi confidence)."""
+    from oracle.ref_pipeline import RefPipeline
+    rp = RefPipeline(sq.K, pnp=variant, confidence=0.999993, alpha=1.5, detector="shi")
+    state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+    ext = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+    Ts, nP, nC = [], [], []
+    for k in range(1, len(sq.frames)):
+        state, ext, T = rp.frame(sq.frames[k - 1], sq.frames[k], state, ext, None)
+        Ts.append(T); nP.append(len(state["P"])); nC.append(len(ext["C"]))
+    return np.array(Ts), np.array(nP), np.array(nC), state, ext
 
 
 def run_port(sq, variant, row_match="isin"):
@@ -53,6 +76,23 @@ def test_port_reproduces_reference_classes(scene_mod, name, variant):
     assert np.allclose(Ts, g["%s_%s_T" % (name, variant)], rtol=0, atol=1e-9)
     if variant == "p3p":
         assert np.allclose(state["X"], g[name + "_p3p_X_last"], rtol=1e-9, atol=1e-9)
+
+
+@pytest.mark.parametrize("name", list(SHI_SEQ_CASES))
+@pytest.mark.parametrize("variant", ["literal", "p3p"])
+def test_port_reproduces_reference_classes_shi_mask(scene_mod, name, variant):
+    """The reference run with find_new_candidates_method 'shi-mask' (its own detector)."""
+    pytest.importorskip("cv2")
+    g = np.load(os.path.join(GOLD, "seq.npz"))
+    sq = get_shi_sequence(scene_mod, name)
+    if sq.checksum() != int(g[name + "_checksum"]):
+        pytest.skip("rendered frames differ from the golden generator's on this machine (libm)")
+    Ts, nP, nC, state, ext = run_port_shi(sq, variant)
+    assert np.array_equal(nP, g["%s_%s_nP" % (name, variant)])
+    assert np.array_equal(nC, g["%s_%s_nC" % (name, variant)])
+    assert np.allclose(Ts, g["%s_%s_T" % (name, variant)], rtol=0, atol=1e-9)
+    if variant == "p3p":
+        assert np.array_equal(np.asarray(ext["C"], np.float64), g[name + "_p3p_C_last"])
 
 
 def test_status_mask_equals_isin_row_matching(scene_mod):
