@@ -188,13 +188,15 @@ def main():
         d_out = torch.empty((500, 2), dtype=torch.float32, device=dev)
         prm = pkg.gftt_defaults()
         n = ctypes.c_int()
+        ginfo = np.zeros(4, np.int32)
 
         def run():
             check(lib.vo_good_features_to_track(h, 900, None, ptr(d_pts), len(pts), ctypes.byref(prm), ptr(d_out), 500,
-                                                ctypes.byref(n), None, None))
+                                                ctypes.byref(n), None, ginfo.ctypes.data))
         med, best = timed(torch, stream, run, args.reps)
         line = {"kernel": "shi_eig + shi_nms + shi_select (Shi-Tomasi, 500 corners, minDistance 10)", "regime": "one 1241x376 frame",
-                "ms": med, "ms_min": best, "corners": n.value, "frames_per_s": 1e3 / med,
+                "ms": med, "ms_min": best, "corners": n.value, "candidates": int(ginfo[0]), "selection_rounds": int(ginfo[2]),
+                "selection_kcycles": {"sort": int(ginfo[3] % 1000), "bucketing": int(ginfo[3] // 1000 % 1000), "rounds": int(ginfo[3] // 1000000)}, "frames_per_s": 1e3 / med,
                 "algorithmic_bytes": 1241 * 376 * (1 + 1 + 4 + 4 + 1), "note": "u8 frame + mask in, float32 map out and back in for the NMS"}
         try:
             import cv2

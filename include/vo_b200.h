@@ -200,13 +200,17 @@ typedef struct vo_gftt_params {
     int block_size;        /* 4 (1..8); gradientSize is 3 */
     int vec_cols;          /* columns the OpenCV build evaluates with its fused SIMD row filter;
                             * -1 = width & ~31, what the pinned build does (oracle/gftt.c) */
+    int use_cluster;       /* 1: corner selection on a thread-block cluster of 8 CTAs (default);
+                            * 0: single-CTA kernel only (same result; tests) */
 } vo_gftt_params;
 void vo_gftt_params_default(vo_gftt_params* p);
 /* Unit-level mirror of cv2.goodFeaturesToTrack on a resident frame.  mask: w*h u8 (host or device)
  * or NULL; alternatively exclude_pts (n x 2 float32): the reference's mask, 255 everywhere and 0 at
  * int(x), int(y) of every point (vo_pipeline.py:371-378).  corners: cap x 2 float32 (x, y) in cv2's
  * order.  eig_out: optional w*h float32 = cv2.cornerMinEigenVal(frame, blockSize, ksize=3).
- * info = {candidates sorted, grid overflow, max key, 0}.  Synchronises. */
+ * info = {candidates (local maxima above the threshold), candidates sorted (+ 2^30 if the single-CTA
+ * kernel produced the result), selection rounds, selection-kernel kilocycles packed as
+ * sort + 1000 * bucketing + 1000000 * rounds}.  Synchronises. */
 int vo_good_features_to_track(vo_ctx* ctx, int64_t frame_key, const uint8_t* mask, const float* exclude_pts,
                               int n_exclude, const vo_gftt_params* params, float* corners, int cap, int* n_corners,
                               float* eig_out, int32_t info[4]);

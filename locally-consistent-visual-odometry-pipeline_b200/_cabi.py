@@ -35,7 +35,7 @@ class PnpParams(ctypes.Structure):
 
 class GfttParams(ctypes.Structure):
     _fields_ = [("max_corners", c_int), ("quality_level", c_double), ("min_distance", c_double),
-                ("block_size", c_int), ("vec_cols", c_int)]
+                ("block_size", c_int), ("vec_cols", c_int), ("use_cluster", c_int)]
 
 
 class Counters(ctypes.Structure):

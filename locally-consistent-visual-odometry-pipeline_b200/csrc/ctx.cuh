@@ -51,16 +51,22 @@ struct DetScalars {
     unsigned max_key;   // order-preserving key of the masked maximum of the min-eigenvalue map (0: none)
     int32_t n_cand;     // local maxima above the quality threshold
     int32_t n_out;      // corners accepted
-    int32_t overflow;   // an accepted-corner grid cell overflowed (cannot happen for minDistance >= cell)
+    int32_t overflow;   // reserved (0)
     int32_t n_sorted;   // candidates the selection kernel sorted
+    int32_t rounds;     // parallel rounds the greedy selection needed
+    int32_t cyc[3];     // SM cycles of the selection kernel's phases: sort, bucketing, rounds + compaction
+    int32_t fallback;   // the cluster kernel left the selection to the single-CTA kernel
 };
 
 struct Detector {
     DevBuf<float> eig;                  // w*h min-eigenvalue map
     DevBuf<uint8_t> mask;               // w*h
     DevBuf<unsigned long long> keys;    // (value key << 32 | pixel index), power-of-two capacity >= w*h
-    DevBuf<int> grid_cnt;               // accepted corners per minDistance cell
-    DevBuf<unsigned> grid_pts;          // 4 packed (x | y << 16) per cell
+    DevBuf<int> cell_cnt, cell_start;   // candidates per minDistance cell, exclusive prefix sum
+    DevBuf<int> items;                  // candidate ranks bucketed by cell
+    DevBuf<unsigned> xy;                // (x | y << 16) of the candidates in sorted order
+    DevBuf<uint8_t> state;              // 0 undecided, 1 accepted, 2 rejected
+    DevBuf<int> ghist;                  // key histogram + round flags of the cluster kernel
     DevBuf<float> out;                  // accepted corners, float2, cv2's order
     DetScalars* d_sc = nullptr;
     DetScalars* h_sc = nullptr;         // pinned mirror

@@ -14,9 +14,10 @@
 //   shi_nms_kernel     threshold (quality x max), 3x3 non-maximum test on the thresholded map, interior
 //                      and mask rules; survivors appended as 64-bit keys (value | pixel index).
 //   shi_select_kernel  one CTA: bitonic sort of the keys (value descending, address descending - the
-//                      order cv2 sorts in), then the greedy minimum-distance acceptance in that order:
-//                      a warp decides 32 candidates per step (accepted-corner grid of minDistance cells
-//                      + an in-batch dependency resolution with ballots), identical to the sequential scan.
+//                      order cv2 sorts in), then cv2's greedy minimum-distance acceptance evaluated for
+//                      all candidates in parallel rounds over a cell-bucketed candidate list (a
+//                      candidate depends on earlier ones only, so the fixed point is the sequential scan).
+#include <cooperative_groups.h>
 #include "ctx.cuh"
 
 namespace vo {
@@ -27,8 +28,6 @@ constexpr int TX = 32, TY = 16;
 constexpr int kMaxBlock = 8;
 constexpr int SW = TX + kMaxBlock + 1, SH = TY + kMaxBlock + 1;   // source tile (virtual coordinates)
 constexpr int DW = TX + kMaxBlock - 1, DH = TY + kMaxBlock - 1;   // derivative tile
-constexpr int kSortSmem = 16384;                                  // keys sorted in shared memory (128 KB)
-constexpr int kCellCap = 4;
 
 __device__ __forceinline__ int reflect101(int p, int n)
 {
@@ -188,104 +187,434 @@ __device__ void bitonic_desc(Ptr a, int n2)
         }
 }
 
+// exclusive prefix sum over the CTA (blockDim.x == 1024); *total = sum of all v
+__device__ __forceinline__ int block_excl_scan(int v, int* total)
+{
+    __shared__ int wsum[32];
+    __shared__ int tot;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) wsum[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = wsum[lane], winc = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, winc, d);
+            if (lane >= d) winc += t;
+        }
+        wsum[lane] = winc - w;
+        if (lane == 31) tot = winc;
+    }
+    __syncthreads();
+    const int r = wsum[wid] + inc - v;
+    *total = tot;
+    __syncthreads();      // wsum/tot may be reused by the next call
+    return r;
+}
+
+struct SelArrays {
+    unsigned* xy;      // (x | y << 16) in sorted order
+    uint8_t* state;    // 0 undecided, 1 accepted, 2 rejected
+    int* items;        // candidate ranks bucketed by cell
+    int* cell_cnt;     // gw*gh
+    int* cell_start;   // gw*gh + 1
+};
+
+// cv2's greedy minimum-distance acceptance - "take a candidate unless an accepted one lies closer than
+// minDistance inside the 3x3 minDistance-cells around it", scanned in sorted order - evaluated for all
+// n candidates in parallel: candidates are bucketed by cell (counting sort) and, in rounds, every
+// undecided candidate looks at the EARLIER candidates around it: one of them accepted => rejected;
+// none of them undecided => accepted.  A candidate's fate depends on earlier ones only, so the fixed
+// point is exactly the sequential result whatever the schedule.  Writes the first `limit` accepted
+// candidates (sorted order) to out and returns how many were accepted (counting stops at limit).
+// A.xy must hold the n positions; all pointers may be shared or global memory.
+__device__ int greedy_select(int n, const SelArrays& A, bool use_dist, int cell, int gw, int gh, float md2, int limit,
+                             float2* __restrict__ out, int* rounds_out)
+{
+    const int T = threadIdx.x, NT = blockDim.x;
+    const int ncell = gw * gh;
+    int rounds = 0;
+    if (use_dist) {
+        for (int i = T; i < ncell; i += NT) A.cell_cnt[i] = 0;
+        __syncthreads();
+        for (int i = T; i < n; i += NT) {
+            const unsigned p = A.xy[i];
+            A.state[i] = 0;
+            atomicAdd(&A.cell_cnt[(int)((p >> 16) / cell) * gw + (int)((p & 0xffffu) / cell)], 1);
+        }
+        __syncthreads();
+        int running = 0;
+        for (int base = 0; base < ncell; base += NT) {
+            const int c = base + T;
+            const int v = c < ncell ? A.cell_cnt[c] : 0;
+            int total;
+            const int ex = block_excl_scan(v, &total);
+            if (c < ncell) A.cell_start[c] = running + ex;
+            running += total;
+        }
+        if (T == 0) A.cell_start[ncell] = running;
+        __syncthreads();
+        for (int i = T; i < n; i += NT) {
+            const unsigned p = A.xy[i];
+            const int c = (int)((p >> 16) / cell) * gw + (int)((p & 0xffffu) / cell);
+            A.items[A.cell_start[c] + atomicSub(&A.cell_cnt[c], 1) - 1] = i;
+        }
+        __syncthreads();
+        int pending;
+        do {
+            pending = 0;
+            rounds++;
+            for (int i = T; i < n; i += NT) {
+                if (A.state[i]) continue;
+                const unsigned p = A.xy[i];
+                const int x = p & 0xffffu, y = p >> 16;
+                const int cx = x / cell, cy = y / cell;
+                const int x1 = max(cx - 1, 0), x2 = min(cx + 1, gw - 1), y1 = max(cy - 1, 0), y2 = min(cy + 1, gh - 1);
+                int verdict = 1;      // accepted unless an earlier neighbour says otherwise
+                for (int yy = y1; yy <= y2 && verdict != 2; yy++) {
+                    // the cells of one grid row are adjacent in the item list
+                    const int pb = A.cell_start[yy * gw + x1], pe = A.cell_start[yy * gw + x2 + 1];
+                    for (int q = pb; q < pe; q++) {
+                        const int j = A.items[q];
+                        if (j >= i) continue;
+                        const unsigned pj = A.xy[j];
+                        const float dx = (float)(x - (int)(pj & 0xffffu)), dy = (float)(y - (int)(pj >> 16));
+                        if (dx * dx + dy * dy < md2) {
+                            const int sj = A.state[j];
+                            if (sj == 1) { verdict = 2; break; }
+                            if (sj == 0) verdict = 0;
+                        }
+                    }
+                }
+                if (verdict) A.state[i] = (uint8_t)verdict;
+                else pending = 1;
+            }
+        } while (__syncthreads_or(pending));
+    }
+    int running = 0;
+    for (int base = 0; base < n && running < limit; base += NT) {
+        const int i = base + T;
+        const int a = i < n && (!use_dist || A.state[i] == 1);
+        int total;
+        const int ex = block_excl_scan(a, &total);
+        if (a && running + ex < limit) {
+            const unsigned p = A.xy[i];
+            out[running + ex] = make_float2((float)(p & 0xffffu), (float)(p >> 16));
+        }
+        running += total;
+    }
+    *rounds_out = rounds;
+    return running;
+}
+
+constexpr int kTopSmem = 8192;     // candidates the shared-memory path sorts and selects (64 KB of keys)
+constexpr int kHistBins = 2048;
+
+// One CTA.  Sorts the candidate keys descending (= cv2's order: value, then address) and runs the
+// greedy selection.  Only the best-valued candidates can end up among the first maxCorners accepted,
+// so a first attempt takes the top ~4 x maxCorners candidates by value (threshold from a histogram of
+// the keys), sorts and selects them in shared memory; the result is exact when it yields maxCorners
+// corners.  Otherwise (few corners, or no limit) everything is redone on all candidates - in shared
+// memory if they fit, else in global memory.
 __global__ void __launch_bounds__(1024, 1)
 shi_select_kernel(unsigned long long* __restrict__ keys, int key_cap, int w, int h, int max_corners, float min_dist,
-                  int cell, int gw, int gh, int* __restrict__ grid_cnt, unsigned* __restrict__ grid_pts,
+                  double quality, int cell, int gw, int gh, int cells_in_smem, SelArrays G,
                   float2* __restrict__ out, int out_cap, DetScalars* sc)
 {
     extern __shared__ unsigned long long skeys[];
+    __shared__ int hist[kHistBins];
+    __shared__ int s_m, s_bin;
+    const int T = threadIdx.x, NT = blockDim.x;
+    if (!sc->fallback) return;         // the cluster kernel has produced the result
     const int n = min(sc->n_cand, key_cap);
-    int n2 = 1;
-    while (n2 < n) n2 <<= 1;
-    const bool in_smem = n2 <= kSortSmem;
     const bool use_dist = min_dist >= 1.f;
-    if (use_dist)
-        for (int i = threadIdx.x; i < gw * gh; i += blockDim.x) grid_cnt[i] = 0;
-    if (in_smem) {
-        for (int i = threadIdx.x; i < n2; i += blockDim.x) skeys[i] = i < n ? keys[i] : 0ull;
-        __syncthreads();
-        bitonic_desc(skeys, n2);
-    } else {
-        for (int i = n + threadIdx.x; i < n2; i += blockDim.x) keys[i] = 0ull;   // key buffer is a power of two
-        __syncthreads();
-        bitonic_desc(keys, n2);
-    }
-    __syncthreads();
-    if (threadIdx.x >= 32) return;
-    const unsigned long long* sorted = in_smem ? skeys : keys;
-    const int lane = threadIdx.x;
-    const unsigned lt = (1u << lane) - 1u;
+    const int ncell = gw * gh;
     const float md2 = min_dist * min_dist;
     const int limit = max_corners > 0 ? min(max_corners, out_cap) : out_cap;
-    volatile const int* vcnt = grid_cnt;
-    volatile const unsigned* vpts = grid_pts;
-    int accepted = 0, overflow = 0;
-    for (int pos = 0; pos < n && accepted < limit; pos += 32) {
-        const int k = pos + lane;
-        const bool valid = k < n;
-        const unsigned idx = valid ? (unsigned)(sorted[k] & 0xffffffffull) : 0u;
-        const int y = idx / w, x = idx - y * w;
-        const int cx = x / cell, cy = y / cell;
-        bool alive = valid;
-        unsigned nb = 0;
-        if (use_dist) {
-            if (alive) {
-                const int x1 = max(cx - 1, 0), x2 = min(cx + 1, gw - 1), y1 = max(cy - 1, 0), y2 = min(cy + 1, gh - 1);
-                for (int yy = y1; yy <= y2 && alive; yy++)
-                    for (int xx = x1; xx <= x2 && alive; xx++) {
-                        const int c = yy * gw + xx;
-                        const int cnt = min(vcnt[c], kCellCap);
-                        for (int e = 0; e < cnt; e++) {
-                            const unsigned p = vpts[c * kCellCap + e];
-                            const float dx = (float)(x - (int)(p & 0xffffu)), dy = (float)(y - (int)(p >> 16));
-                            if (dx * dx + dy * dy < md2) { alive = false; break; }
-                        }
-                    }
+    const long long t0 = clock64();
+    // shared-memory arrays: [keys 8 B x kTopSmem -> reused as xy + items][state][cell_cnt][cell_start]
+    SelArrays S;
+    S.xy = reinterpret_cast<unsigned*>(skeys);
+    S.items = reinterpret_cast<int*>(skeys) + kTopSmem;
+    S.state = reinterpret_cast<uint8_t*>(skeys + kTopSmem);
+    S.cell_cnt = cells_in_smem ? reinterpret_cast<int*>(S.state + kTopSmem) : G.cell_cnt;
+    S.cell_start = cells_in_smem ? S.cell_cnt + ncell : G.cell_start;
+
+    unsigned long long th = 0ull;      // keys >= th take part in this attempt
+    int m = n;
+    if (n > 1024 && limit < n) {
+        const unsigned kmax = sc->max_key;
+        const float maxv = kmax ? key_value(kmax) : 0.f;
+        const unsigned kmin = ordered_key((float)((double)maxv * quality));
+        int shift = 0;
+        while (((kmax > kmin ? kmax - kmin : 0u) >> shift) >= (unsigned)kHistBins) shift++;
+        for (int i = T; i < kHistBins; i += NT) hist[i] = 0;
+        __syncthreads();
+        for (int i = T; i < n; i += NT) {
+            const unsigned k32 = (unsigned)(keys[i] >> 32);
+            atomicAdd(&hist[min((k32 > kmin ? k32 - kmin : 0u) >> shift, (unsigned)kHistBins - 1u)], 1);
+        }
+        __syncthreads();
+        if (T < 32) {      // lowest bin whose suffix count reaches the target
+            const int target = min(max(4 * limit, 1024), kTopSmem * 3 / 4);
+            constexpr int SEG = kHistBins / 32;
+            const int hi = kHistBins - 1 - T * SEG;          // lane 0 owns the top segment
+            int seg = 0;
+            for (int b = 0; b < SEG; b++) seg += hist[hi - b];
+            int inc = seg;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, d);
+                if (T >= d) inc += t;
             }
-            // earlier candidates of this batch that would block this one if accepted
-            const unsigned me = (unsigned)x | ((unsigned)y << 16);
-            for (int j = 0; j < 31; j++) {
-                const unsigned pj = __shfl_sync(0xffffffffu, me, j);
-                const int xj = pj & 0xffffu, yj = pj >> 16;
-                const float dx = (float)(x - xj), dy = (float)(y - yj);
-                // cv2 only looks into the 3x3 cells around the candidate
-                const bool near = abs(xj / cell - cx) <= 1 && abs(yj / cell - cy) <= 1 && dx * dx + dy * dy < md2;
-                if (j < lane && near) nb |= 1u << j;
+            const unsigned reach = __ballot_sync(0xffffffffu, inc >= target);
+            if (reach == 0u) { if (T == 0) { s_bin = 0; s_m = n; } }
+            else if (T == __ffs(reach) - 1) {
+                int cum = inc - seg, b = 0;
+                for (; b < SEG; b++) { cum += hist[hi - b]; if (cum >= target) break; }
+                s_bin = hi - b; s_m = cum;
             }
         }
-        bool undecided = alive, acc = false;
-        for (;;) {
-            const unsigned accm = __ballot_sync(0xffffffffu, acc);
-            const unsigned undm = __ballot_sync(0xffffffffu, undecided);
-            if (!undm) break;
-            if (undecided) {
-                if (nb & accm) undecided = false;
-                else if (!(nb & undm)) { acc = true; undecided = false; }
-            }
-        }
-        const unsigned accm = __ballot_sync(0xffffffffu, acc);
-        const int rank = __popc(accm & lt);
-        const bool take = acc && accepted + rank < limit;
-        if (take) {
-            out[accepted + rank] = make_float2((float)x, (float)y);
-            if (use_dist) {
-                const int c = cy * gw + cx;
-                const int slot = atomicAdd(&grid_cnt[c], 1);
-                if (slot < kCellCap) grid_pts[c * kCellCap + slot] = (unsigned)x | ((unsigned)y << 16);
-                else overflow = 1;
-            }
-        }
-        accepted += __popc(__ballot_sync(0xffffffffu, take));
-        __threadfence_block();
-        __syncwarp();
+        __syncthreads();
+        if (s_bin > 0 && s_m <= kTopSmem) { th = (unsigned long long)(kmin + ((unsigned)s_bin << shift)) << 32; m = s_m; }
     }
-    overflow = __any_sync(0xffffffffu, overflow);
-    if (lane == 0) { sc->n_out = accepted; sc->overflow = overflow; sc->n_sorted = n; }
+    int rounds = 0, accepted = 0;
+    long long t1 = t0, t2 = t0;
+    for (int attempt = 0; attempt < 2; attempt++) {
+        if (m <= kTopSmem) {
+            int m2 = 1;
+            while (m2 < m) m2 <<= 1;
+            if (T == 0) s_m = 0;
+            __syncthreads();
+            if (th == 0ull) { for (int i = T; i < n; i += NT) skeys[i] = keys[i]; }
+            else {
+                for (int i = T; i < n; i += NT) {
+                    const unsigned long long k = keys[i];
+                    if (k >= th) skeys[atomicAdd(&s_m, 1)] = k;
+                }
+            }
+            for (int i = m + T; i < m2; i += NT) skeys[i] = 0ull;
+            __syncthreads();
+            bitonic_desc(skeys, m2);
+            t1 = clock64();
+            // keys -> positions, in place (every key is in registers before anything is overwritten)
+            unsigned pos[kTopSmem / 1024];
+#pragma unroll
+            for (int r = 0; r < kTopSmem / 1024; r++) {
+                const int i = T + r * 1024;
+                if (i < m) {
+                    const unsigned idx = (unsigned)(skeys[i] & 0xffffffffull);
+                    const unsigned y = idx / (unsigned)w;
+                    pos[r] = (idx - y * w) | (y << 16);
+                }
+            }
+            __syncthreads();
+#pragma unroll
+            for (int r = 0; r < kTopSmem / 1024; r++) {
+                const int i = T + r * 1024;
+                if (i < m) S.xy[i] = pos[r];
+            }
+            __syncthreads();
+            accepted = greedy_select(m, S, use_dist, cell, gw, gh, md2, limit, out, &rounds);
+        } else {
+            int n2 = 1;
+            while (n2 < n) n2 <<= 1;
+            for (int i = n + T; i < n2; i += NT) keys[i] = 0ull;   // the key buffer is a power of two
+            __syncthreads();
+            bitonic_desc(keys, n2);
+            t1 = clock64();
+            for (int i = T; i < n; i += NT) {
+                const unsigned idx = (unsigned)(keys[i] & 0xffffffffull);
+                const unsigned y = idx / (unsigned)w;
+                G.xy[i] = (idx - y * w) | (y << 16);
+            }
+            __syncthreads();
+            accepted = greedy_select(n, G, use_dist, cell, gw, gh, md2, limit, out, &rounds);
+        }
+        t2 = clock64();
+        if (accepted >= limit || m >= n) break;
+        th = 0ull; m = n;       // the best candidates did not yield maxCorners corners: take them all
+        __syncthreads();
+    }
+    if (T == 0) {
+        sc->n_out = min(accepted, limit); sc->overflow = 0; sc->n_sorted = m; sc->rounds = rounds;
+        sc->cyc[0] = (int)(t1 - t0); sc->cyc[1] = 0; sc->cyc[2] = (int)(t2 - t1);
+    }
 }
 
-__global__ void det_reset_kernel(DetScalars* sc)
+// ---- fast path: the same selection on a thread-block cluster of 8 CTAs (8 SMs) -------------------
+// The single-CTA kernel above is instruction-bound on one SM (~190 warp instructions per candidate).
+// Here the candidates are partitioned by VALUE into 8 slabs of about n/8 keys (boundaries from a
+// 2048-bin histogram of the keys, like a sample sort); CTA r sorts slab r in its shared memory, so the
+// concatenation of the slabs is the globally sorted list; positions, states and per-cell linked lists
+// (head/next) live in global memory (L2), and the parallel rounds of the greedy selection run on all
+// 8 SMs with a cluster barrier (which also invalidates L1) between rounds.  Anything outside its
+// limits (no maxCorners, no distance, a slab that does not fit, > 60 rounds) is left to the single-CTA
+// kernel, which runs right after and returns at once unless sc->fallback is set.
+constexpr int kCl = 8;
+constexpr int kSlabCap = 8192;
+
+__global__ void __cluster_dims__(kCl, 1, 1) __launch_bounds__(1024, 1)
+shi_select_cluster_kernel(const unsigned long long* __restrict__ keys, int key_cap, int w, int h, int max_corners,
+                          float min_dist, double quality, int cell, int gw, int gh, SelArrays G, int* __restrict__ ghist,
+                          float2* __restrict__ out, int out_cap, DetScalars* sc)
 {
-    sc->max_key = 0; sc->n_cand = 0; sc->n_out = 0; sc->overflow = 0; sc->n_sorted = 0;
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    extern __shared__ unsigned long long skeys[];
+    __shared__ int hist[kHistBins];
+    __shared__ uint8_t slab_of[kHistBins];
+    __shared__ int slab_cnt[kCl], slab_off[kCl];
+    __shared__ int s_m;
+    const int T = threadIdx.x, NT = blockDim.x;
+    const int r = (int)cluster.block_rank();
+    const int gT = r * NT + T, GN = kCl * NT;
+    const int n = min(sc->n_cand, key_cap);
+    const int ncell = gw * gh;
+    const int limit = max_corners > 0 ? min(max_corners, out_cap) : out_cap;
+    int* head = G.cell_cnt;      // per cell: rank of the most recently linked candidate, -1 = empty
+    int* next = G.items;         // per candidate: the next one in its cell
+    int* gflag = ghist + kHistBins;   // 3 rotating "somebody is still undecided" flags
+    const long long t0 = clock64();
+    if (max_corners <= 0 || min_dist < 1.f || n > kCl * kSlabCap) {   // uniform over the cluster
+        if (gT == 0) sc->fallback = 1;
+        return;
+    }
+    const unsigned kmax = sc->max_key;
+    const float maxv = kmax ? key_value(kmax) : 0.f;
+    const unsigned kmin = ordered_key((float)((double)maxv * quality));
+    int shift = 0;
+    while (((kmax > kmin ? kmax - kmin : 0u) >> shift) >= (unsigned)kHistBins) shift++;
+    // ---- histogram of the keys (ghist was zeroed by det_reset_kernel) and empty cell lists
+    for (int i = T; i < kHistBins; i += NT) hist[i] = 0;
+    if (T < kCl) { slab_cnt[T] = 0; slab_off[T] = 0x7fffffff; }
+    __syncthreads();
+    for (int i = gT; i < n; i += GN) {
+        const unsigned k32 = (unsigned)(keys[i] >> 32);
+        atomicAdd(&hist[min((k32 > kmin ? k32 - kmin : 0u) >> shift, (unsigned)kHistBins - 1u)], 1);
+    }
+    for (int i = gT; i < ncell; i += GN) head[i] = -1;
+    __syncthreads();
+    for (int i = T; i < kHistBins; i += NT)
+        if (hist[i]) atomicAdd(&ghist[i], hist[i]);
+    cluster.sync();
+    // ---- slabs: bin b belongs to slab min(7, (#keys in bins above b) / ceil(n/8)); every CTA computes all
+    const int per = max((n + kCl - 1) / kCl, 1);
+    {
+        int running = 0;
+        for (int base = 0; base < kHistBins; base += NT) {
+            const int b = kHistBins - 1 - (base + T);          // descending bins
+            const int v = __ldcg(&ghist[b]);
+            int total;
+            const int above = running + block_excl_scan(v, &total);
+            const int sl = min(kCl - 1, above / per);
+            slab_of[b] = (uint8_t)sl;
+            hist[b] = v;
+            if (v) { atomicAdd(&slab_cnt[sl], v); atomicMin(&slab_off[sl], above); }
+            running += total;
+        }
+    }
+    if (T == 0) s_m = 0;
+    __syncthreads();
+    bool bad = false;
+    for (int k = 0; k < kCl; k++) bad |= slab_cnt[k] > kSlabCap;
+    if (bad) {                                                  // same decision in every CTA
+        if (gT == 0) sc->fallback = 1;
+        return;
+    }
+    const int m = slab_cnt[r], off = m ? slab_off[r] : 0;
+    // ---- my slab: gather, sort in shared memory, publish positions, link into the cell lists
+    for (int i = T; i < n; i += NT) {
+        const unsigned long long k = keys[i];
+        const unsigned k32 = (unsigned)(k >> 32);
+        if (slab_of[min((k32 > kmin ? k32 - kmin : 0u) >> shift, (unsigned)kHistBins - 1u)] == r) skeys[atomicAdd(&s_m, 1)] = k;
+    }
+    int m2 = 1;
+    while (m2 < m) m2 <<= 1;
+    for (int i = m + T; i < m2; i += NT) skeys[i] = 0ull;
+    __syncthreads();
+    bitonic_desc(skeys, m2);
+    for (int i = T; i < m; i += NT) {
+        const unsigned idx = (unsigned)(skeys[i] & 0xffffffffull);
+        const unsigned y = idx / (unsigned)w, x = idx - y * w;
+        G.xy[off + i] = x | (y << 16);
+        G.state[off + i] = 0;
+        next[off + i] = atomicExch(&head[(int)(y / cell) * gw + (int)(x / cell)], off + i);
+    }
+    const long long t1 = clock64();
+    cluster.sync();
+    // ---- rounds on all 8 SMs
+    const float md2 = min_dist * min_dist;
+    int rounds = 0;
+    bool give_up = false;
+    for (;;) {
+        int pending = 0;
+        if (gT == 0) gflag[(rounds + 1) % 3] = 0;
+        for (int i = gT; i < n; i += GN) {
+            if (G.state[i]) continue;
+            const unsigned p = G.xy[i];
+            const int x = p & 0xffffu, y = p >> 16;
+            const int cx = x / cell, cy = y / cell;
+            const int x1 = max(cx - 1, 0), x2 = min(cx + 1, gw - 1), y1 = max(cy - 1, 0), y2 = min(cy + 1, gh - 1);
+            int verdict = 1;
+            for (int yy = y1; yy <= y2 && verdict != 2; yy++)
+                for (int xx = x1; xx <= x2 && verdict != 2; xx++)
+                    for (int j = head[yy * gw + xx]; j >= 0; j = next[j]) {
+                        if (j >= i) continue;
+                        const unsigned pj = G.xy[j];
+                        const float dx = (float)(x - (int)(pj & 0xffffu)), dy = (float)(y - (int)(pj >> 16));
+                        if (dx * dx + dy * dy < md2) {
+                            const int sj = __ldcg(&G.state[j]);
+                            if (sj == 1) { verdict = 2; break; }
+                            if (sj == 0) verdict = 0;
+                        }
+                    }
+            if (verdict) G.state[i] = (uint8_t)verdict;
+            else pending = 1;
+        }
+        pending = __syncthreads_or(pending);
+        if (pending && T == 0) atomicOr(&gflag[rounds % 3], 1);
+        cluster.sync();
+        const int any = __ldcg(&gflag[rounds % 3]);
+        rounds++;
+        if (!any) break;
+        if (rounds >= 60) { give_up = true; break; }
+    }
+    if (give_up) {
+        if (gT == 0) sc->fallback = 1;
+        return;
+    }
+    if (r != 0) return;
+    // ---- CTA 0: the first `limit` accepted candidates in sorted order
+    int running = 0;
+    for (int base = 0; base < n && running < limit; base += NT) {
+        const int i = base + T;
+        const int a = i < n && __ldcg(&G.state[i]) == 1;
+        int total;
+        const int ex = block_excl_scan(a, &total);
+        if (a && running + ex < limit) {
+            const unsigned p = G.xy[i];
+            out[running + ex] = make_float2((float)(p & 0xffffu), (float)(p >> 16));
+        }
+        running += total;
+    }
+    if (T == 0) {
+        sc->n_out = min(running, limit); sc->overflow = 0; sc->n_sorted = n; sc->rounds = rounds; sc->fallback = 0;
+        sc->cyc[0] = (int)(t1 - t0); sc->cyc[1] = 0; sc->cyc[2] = (int)(clock64() - t1);
+    }
+}
+
+__global__ void det_reset_kernel(DetScalars* sc, int* __restrict__ ghist, int fallback)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) { sc->max_key = 0; sc->n_cand = 0; sc->n_out = 0; sc->overflow = 0; sc->n_sorted = 0; sc->rounds = 0; sc->fallback = fallback; }
+    if (i < kHistBins + 8) ghist[i] = 0;
 }
 
 // corners (float2) -> the double2 staging layout cand_add_kernel reads
@@ -297,15 +626,18 @@ __global__ void corners_to_f64_kernel(const float2* __restrict__ in, const DetSc
 
 }  // namespace
 
+constexpr int kSelSmemMax = 200 * 1024;
+
 void gftt_defaults(vo_gftt_params* p)
 {
     p->max_corners = 500; p->quality_level = 0.03; p->min_distance = 10.0; p->block_size = 4; p->vec_cols = -1;
+    p->use_cluster = 1;
 }
 
 int detector_free(Ctx* c)
 {
     Detector& d = c->det;
-    cudaFree(d.eig.p); cudaFree(d.mask.p); cudaFree(d.keys.p); cudaFree(d.grid_cnt.p); cudaFree(d.grid_pts.p);
+    cudaFree(d.eig.p); cudaFree(d.mask.p); cudaFree(d.keys.p); cudaFree(d.cell_cnt.p); cudaFree(d.cell_start.p); cudaFree(d.items.p); cudaFree(d.xy.p); cudaFree(d.state.p); cudaFree(d.ghist.p);
     cudaFree(d.out.p); cudaFree(d.d_sc);
     if (d.h_sc) cudaFreeHost(d.h_sc);
     d = Detector();
@@ -332,23 +664,40 @@ int launch_gftt(Ctx* c, const FrameSlot& f, const uint8_t* d_mask, const vo_gftt
     VO_TRY(ensure(c, d.out, (size_t)out_cap * 2));
     const int cell = prm.min_distance >= 1. ? (int)lrint(prm.min_distance) : 1;
     const int gw = (w + cell - 1) / cell, gh = (h + cell - 1) / cell;
-    VO_TRY(ensure(c, d.grid_cnt, (size_t)gw * gh));
-    VO_TRY(ensure(c, d.grid_pts, (size_t)gw * gh * kCellCap));
+    VO_TRY(ensure(c, d.cell_cnt, (size_t)gw * gh));
+    VO_TRY(ensure(c, d.cell_start, (size_t)gw * gh + 1));
+    VO_TRY(ensure(c, d.items, kcap));
+    VO_TRY(ensure(c, d.xy, kcap));
+    VO_TRY(ensure(c, d.state, kcap));
     if (!d.d_sc) {
         VO_CUDA(c, cudaMalloc((void**)&d.d_sc, sizeof(DetScalars)));
         VO_CUDA(c, cudaMallocHost((void**)&d.h_sc, sizeof(DetScalars)));
-        VO_CUDA(c, cudaFuncSetAttribute(shi_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSortSmem * 8));
+        VO_CUDA(c, cudaFuncSetAttribute(shi_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSelSmemMax));
+        VO_CUDA(c, cudaFuncSetAttribute(shi_select_cluster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSlabCap * 8));
     }
     const double scale = 1.0 / ((double)(1 << 2) * prm.block_size) / 255.0;
     const int vec_cols = prm.vec_cols < 0 ? (w & ~31) : prm.vec_cols;
-    det_reset_kernel<<<1, 1, 0, c->stream>>>(d.d_sc);
+    VO_TRY(ensure(c, d.ghist, (size_t)kHistBins + 8));
+    const bool use_cluster = prm.use_cluster != 0;
+    det_reset_kernel<<<(kHistBins + 8 + 255) / 256, 256, 0, c->stream>>>(d.d_sc, d.ghist.p, use_cluster ? 0 : 1);
     shi_eig_kernel<<<dim3((w + TX - 1) / TX, (h + TY - 1) / TY), dim3(TX, TY), 0, c->stream>>>(
         f.raw, w, h, w, prm.block_size, vec_cols, (float)scale, (float)(2.0 * scale), d_mask, d.eig.p, d.d_sc);
     shi_nms_kernel<<<dim3((w + 31) / 32, (h + 7) / 8), dim3(32, 8), 0, c->stream>>>(
         d.eig.p, w, h, d_mask, prm.quality_level, (unsigned long long*)d.keys.p, d.d_sc);
-    shi_select_kernel<<<1, 1024, kSortSmem * 8, c->stream>>>(
-        (unsigned long long*)d.keys.p, (int)kcap, w, h, prm.max_corners, (float)prm.min_distance, cell, gw, gh,
-        d.grid_cnt.p, d.grid_pts.p, (float2*)d.out.p, out_cap, d.d_sc);
+    // dynamic shared memory: keys (reused as positions + bucket items), states, and the cell arrays if they fit
+    const size_t base_smem = (size_t)kTopSmem * 8 + kTopSmem;
+    const size_t cell_smem = ((size_t)gw * gh * 2 + 1) * sizeof(int);
+    const int cells_in_smem = base_smem + cell_smem <= (size_t)kSelSmemMax;
+    SelArrays G{ d.xy.p, d.state.p, d.items.p, d.cell_cnt.p, d.cell_start.p };
+    if (use_cluster) {
+        shi_select_cluster_kernel<<<kCl, 1024, (size_t)kSlabCap * 8, c->stream>>>(
+            (const unsigned long long*)d.keys.p, (int)kcap, w, h, prm.max_corners, (float)prm.min_distance, prm.quality_level,
+            cell, gw, gh, G, d.ghist.p, (float2*)d.out.p, out_cap, d.d_sc);
+        c->launches++;
+    }
+    shi_select_kernel<<<1, 1024, base_smem + (cells_in_smem ? cell_smem : 0), c->stream>>>(
+        (unsigned long long*)d.keys.p, (int)kcap, w, h, prm.max_corners, (float)prm.min_distance, prm.quality_level,
+        cell, gw, gh, cells_in_smem, G, (float2*)d.out.p, out_cap, d.d_sc);
     c->launches += 4;
     VO_CUDA(c, cudaGetLastError());
     d.out_cap = out_cap;
@@ -414,7 +763,7 @@ int vo_good_features_to_track(vo_ctx* c, int64_t frame_key, const uint8_t* mask,
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     const int n = d.h_sc->n_out;
     if (n_corners) *n_corners = n;
-    if (info) { info[0] = d.h_sc->n_sorted; info[1] = d.h_sc->overflow; info[2] = (int32_t)d.h_sc->max_key; info[3] = 0; }
+    if (info) { info[0] = d.h_sc->n_cand; info[1] = d.h_sc->n_sorted + (d.h_sc->fallback ? 1 << 30 : 0); info[2] = d.h_sc->rounds; info[3] = d.h_sc->cyc[0] / 1000 + 1000 * (d.h_sc->cyc[1] / 1000) + 1000000 * (d.h_sc->cyc[2] / 1000); }
     if (d.h_sc->overflow) return set_error(c, VO_ERR_CAPACITY, "accepted-corner grid cell overflow");
     if (n > cap) return set_error(c, VO_ERR_CAPACITY, "%d corners, buffer %d", n, cap);
     if (n > 0) VO_CUDA(c, cudaMemcpyAsync(corners, d.out.p, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));

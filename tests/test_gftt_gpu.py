@@ -23,30 +23,33 @@ def upload(ctx, img):
     return _key[0]
 
 
+@pytest.mark.parametrize("use_cluster", [1, 0])
 @pytest.mark.parametrize("name", list(GFTT_CASES))
-def test_gftt_vs_golden_and_oracle(ctx, oracle, name):
+def test_gftt_vs_golden_and_oracle(ctx, oracle, name, use_cluster):
     g = np.load(os.path.join(GOLD, "gftt.npz"))
     img, pts = gftt_image(name)
     k = upload(ctx, img)
     mask = reference_mask(img, pts)
     # the reference's mask given as the point list it is built from, and as an image
-    c_pts, eig, ncand = ctx.good_features_to_track(k, exclude_pts=pts, want_eig=True, shape=img.shape)
-    c_img = ctx.good_features_to_track(k, mask=mask)
+    dflt = ctx_params(ctx, use_cluster=use_cluster)
+    c_pts, eig, ncand = ctx.good_features_to_track(k, exclude_pts=pts, params=dflt, want_eig=True, shape=img.shape)
+    c_img = ctx.good_features_to_track(k, mask=mask, params=dflt)
     o_c, o_eig, o_ncand = oracle.good_features_to_track(img, mask=mask, want_eig=True)
     assert np.array_equal(eig, o_eig)                      # cv2.cornerMinEigenVal, bit for bit
     assert ncand == o_ncand
     assert np.array_equal(c_pts, g[name + "_corners"]) and np.array_equal(c_img, g[name + "_corners"])
     assert np.array_equal(c_pts, o_c)
-    prm = ctx_params(ctx, max_corners=0, quality=0.01, min_distance=5)
+    prm = ctx_params(ctx, max_corners=0, quality=0.01, min_distance=5, use_cluster=use_cluster)
     allc = ctx.good_features_to_track(k, params=prm, shape=img.shape)
     assert np.array_equal(allc.astype(np.uint16), g[name + "_all_corners"])
 
 
-def ctx_params(ctx, max_corners=500, quality=0.03, min_distance=10.0, block=4):
+def ctx_params(ctx, max_corners=500, quality=0.03, min_distance=10.0, block=4, use_cluster=1):
     import importlib
     pkg = importlib.import_module("locally-consistent-visual-odometry-pipeline_b200")
     p = pkg.gftt_defaults()
     p.max_corners, p.quality_level, p.min_distance, p.block_size = max_corners, quality, min_distance, block
+    p.use_cluster = use_cluster
     return p
 
 
@@ -71,10 +74,10 @@ def test_gftt_large_candidate_sets_and_sort_paths(ctx, oracle):
     """> 16384 candidates: the selection kernel sorts in global memory instead of shared memory."""
     img = synth.texture(768, 1024, 31, radius=1, passes=1)
     k = upload(ctx, img)
-    for md, q in ((0, 0.0005), (2, 0.0005), (10, 0.0005)):
-        prm = ctx_params(ctx, 0, q, md)
+    for md, q, mc in ((0, 0.0005, 0), (2, 0.0005, 0), (10, 0.0005, 0), (10, 0.0005, 3000), (3, 0.0005, 20000), (25, 0.0005, 500)):
+        prm = ctx_params(ctx, mc, q, md)
         c, _, ncand = ctx.good_features_to_track(k, params=prm, want_eig=True, shape=img.shape)
-        o, _, o_ncand = oracle.good_features_to_track(img, max_corners=0, quality=q, min_distance=md, want_eig=True)
+        o, _, o_ncand = oracle.good_features_to_track(img, max_corners=mc, quality=q, min_distance=md, want_eig=True)
         assert ncand == o_ncand and ncand > 16384
         assert np.array_equal(c, o)
 
