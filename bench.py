@@ -170,6 +170,12 @@ def run_gpu(args, rank, world, local_rank):
 
     def dev_step(s, order, n_land, n_cand):
         b = order[s + 1]
+        if args.prefetch:
+            # frame ingest: the NEXT step's frame goes to the ingest stream now (inside this step's timed
+            # region: the ingest is ordered behind the step's start event) and overlaps this step's stages
+            r = lib.vo_prefetch_frame(hnd, ctypes.c_void_p(d_frames[order[s + 2]].data_ptr()), w, h, w, s + 3)
+            if r != 0:
+                raise RuntimeError(lib.vo_last_error(hnd).decode())
         want = int(np.clip(TARGET_TRACKS - n_land - n_cand, 0, FEED_MAX))
         fd = d_feeds[b]
         want = 0 if fd is None else min(want, fd.shape[0])
@@ -183,7 +189,7 @@ def run_gpu(args, rank, world, local_rank):
         return cnt.n_landmarks, cnt.n_candidates
 
     # ---- value: device-resident inputs, per-step CUDA events, L2 flush between steps -------------------
-    order = frame_order(F, steps + warmup)
+    order = frame_order(F, steps + warmup + 1)
     n_land, n_cand = reset_state()
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     tracks = 0
@@ -239,7 +245,7 @@ def run_gpu(args, rank, world, local_rank):
     ctx.set_profiling(False)
 
     # ---- e2e: the drop-in classes in main.py's order, frames in pinned host memory ---------------------
-    e2e = run_e2e(pkg, sq, steps, warmup, local_rank, world)
+    e2e = run_e2e(pkg, sq, steps, warmup, local_rank, world, args.prefetch)
     ctx.close()
     return dict(total_ms=total_ms, step_ms=step_ms, t_wall=t_wall, launches=launches, tracks_per_step=tracks / steps,
                 klt_iters_per_land=prof_iters_land / max(prof_land, 1), stage_ms=stage_ms,
@@ -276,7 +282,7 @@ def job_throughput(total_ms, e2e_fps, steps, world, device=None):
     return world * steps / (total_ms * 1e-3), world * e2e_fps, total_ms
 
 
-def run_e2e(pkg, sq, steps, warmup, local_rank, world):
+def run_e2e(pkg, sq, steps, warmup, local_rank, world, prefetch=True):
     """Public API end to end: KeypointsToLandmarksAssociator / PoseEstimator / LandmarkTriangulator
     exactly as main.py:229-294 calls them; every step uploads its frame from pinned host memory and
     reads the pose back (np.linalg.inv of it, as main.py:239 does)."""
@@ -300,7 +306,7 @@ def run_e2e(pkg, sq, steps, warmup, local_rank, world):
     pinned = [pkg.PinnedArray((h, w), np.uint8) for _ in range(F)]
     for p, f in zip(pinned, sq.frames):
         p.array[...] = f
-    order = frame_order(F, steps + warmup)
+    order = frame_order(F, steps + warmup + 1)
     vision = vo.BestVision(sq.K)
     vision.state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
     vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
@@ -322,6 +328,8 @@ def run_e2e(pkg, sq, steps, warmup, local_rank, world):
         img2 = pinned[b].array[:]
         feed = pick_feed(sq, b, n_land, n_cand)
         vo.set_candidate_feed([feed])
+        if prefetch:   # frame ingest: hand the next iteration's frame over before this one is processed
+            vo.prefetch_frame(pinned[order[s + 2]].array)
         new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
         new_pose = pose_estimator.estimatePose(new_state, s)
         pos = np.linalg.inv(new_pose)[0:3, 3]
@@ -349,6 +357,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefetch", dest="prefetch", action="store_false",
+                    help="upload + pyramid of a frame inside its own step (no frame ingest one step ahead)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -434,6 +444,8 @@ def main():
                   "lk_iterations_per_track": iters, **r["per_frame"]},
     })
     line["config"]["l2"] = "flushed between steps (256 MiB memset outside the per-step events)"
+    line["config"]["ingest"] = ("frame k+1 uploaded and its pyramid built on the ingest stream during step k (vo_prefetch_frame), "
+                                "every step still copies and builds exactly one frame inside the timed region") if args.prefetch else "in-step upload + pyramid"
     if world == 1 and not args.no_cpu_baseline:
         _, sq = build_sequence(seed=11)
         n = 60

@@ -92,6 +92,14 @@ int vo_free_pinned(void* p);
  * calls (vo_pipeline.py:215, :501); one upload + one pyramid per frame, cached by key -------- */
 /* img: host or device, 8-bit gray, `pitch` bytes per row.  No-op if frame_key is resident. */
 int vo_upload_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t frame_key);
+/* SURVEY.md 8f-2, frame ingest (main.py:216-223 reads frame k+1 only after frame k is done; here the
+ * NEXT frame can be handed over early): same as vo_upload_frame but enqueued on the ctx's ingest
+ * stream, so the H2D copy and the pyramid kernels run under the tracking of the current frame.  The
+ * first stage that uses frame_key waits for it on the device; nothing synchronises the host.  Call it
+ * BEFORE enqueueing the current frame's stages: the ingest is ordered behind the work enqueued so far
+ * (its slot may still be read by it) and overlaps whatever is enqueued afterwards.  A pinned or
+ * device `img` must stay untouched until a stage using frame_key has been synchronised. */
+int vo_prefetch_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t frame_key);
 int vo_has_frame(vo_ctx* ctx, int64_t frame_key);
 int vo_drop_frames(vo_ctx* ctx);
 /* test hook: copy pyramid level `level` of a resident frame (unpadded, w*h bytes) to the host;
@@ -163,7 +171,10 @@ int vo_pnp_ransac(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, d
  * candidates tracked with the landmarks (vo_klt_track_landmarks on this frame pair).  Afterwards the
  * caller confirms (vo_promote_commit: triangulate_landmark got the pose/alpha assumed here) or
  * undoes it (vo_promote_rollback: state as after vo_pnp_ransac, candidate tracking still pending).
- * ok=0 is rolled back internally.  Until then the promoted rows sit behind the n_inliers rows of P/X. */
+ * ok=0 is rolled back internally.  Until then the promoted rows sit behind the n_inliers rows of P/X.
+ * n_promoted == NULL: the host waits only for the pose (the scalar block is read back between the PnP
+ * and the promotion kernels), so the promotion step keeps the GPU busy while the host walks on to
+ * triangulate_landmark; vo_peek_counters then shows the counts as they were BEFORE the promotion. */
 int vo_pnp_ransac_promote(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, double alpha_deg,
                           double T44[16], int* n_inliers, int* ok, int* n_promoted);
 int vo_promote_commit(vo_ctx* ctx);

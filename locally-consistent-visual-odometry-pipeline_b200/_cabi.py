@@ -68,6 +68,7 @@ SIGNATURES = {
     "vo_alloc_pinned": (c_int, [ctypes.POINTER(c_void_p), c_u64]),
     "vo_free_pinned": (c_int, [c_void_p]),
     "vo_upload_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64]),
+    "vo_prefetch_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64]),
     "vo_has_frame": (c_int, [c_void_p, c_i64]),
     "vo_drop_frames": (c_int, [c_void_p]),
     "vo_get_pyramid_level": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p,
@@ -227,6 +228,13 @@ class Context:
         h, w = img.shape
         self._check(self.lib.vo_upload_frame(self.h, c_void_p(img.ctypes.data), w, h, img.strides[0], key))
 
+    def prefetch_frame(self, img, key):
+        """vo_prefetch_frame: upload + pyramid on the ingest stream (overlaps the stages enqueued after it)."""
+        if img.dtype != np.uint8 or img.ndim != 2 or img.strides[1] != 1:
+            raise ValueError("frames must be 2-D uint8 arrays with contiguous rows")
+        h, w = img.shape
+        self._check(self.lib.vo_prefetch_frame(self.h, c_void_p(img.ctypes.data), w, h, img.strides[0], key))
+
     def has_frame(self, key):
         return bool(self.lib.vo_has_frame(self.h, key))
 
@@ -334,15 +342,17 @@ class Context:
                                            _ptr(T), ctypes.byref(ninl), ctypes.byref(ok)))
         return bool(ok.value), T, ninl.value
 
-    def pnp_ransac_promote(self, K, params, alpha_deg):
-        """estimatePose + speculative promotion with the device pose, one sync (vo_pnp_ransac_promote)."""
+    def pnp_ransac_promote(self, K, params, alpha_deg, early=False):
+        """estimatePose + speculative promotion with the device pose, one sync (vo_pnp_ransac_promote).
+        early=True: wait for the pose only; the promotion step is still running when this returns
+        (n_promoted is then reported as None)."""
         K = np.ascontiguousarray(K, np.float64)
         T = np.empty((4, 4), np.float64)
         ninl, ok, nprom = c_int(), c_int(), c_int()
         self._check(self.lib.vo_pnp_ransac_promote(self.h, _ptr(K), ctypes.byref(params) if params is not None else None,
                                                    float(alpha_deg), _ptr(T), ctypes.byref(ninl), ctypes.byref(ok),
-                                                   ctypes.byref(nprom)))
-        return bool(ok.value), T, ninl.value, nprom.value
+                                                   None if early else ctypes.byref(nprom)))
+        return bool(ok.value), T, ninl.value, (None if early else nprom.value)
 
     def promote_commit(self):
         self._check(self.lib.vo_promote_commit(self.h))

@@ -22,7 +22,15 @@ int set_error(Ctx* c, int code, const char* fmt, ...)
 static FrameSlot* find_slot(Ctx* c, int64_t key)
 {
     for (auto& s : c->slots)
-        if (s.valid && s.key == key) { s.stamp = ++c->clock; return &s; }
+        if (s.valid && s.key == key) {
+            s.stamp = ++c->clock;
+            s.use_step = c->step_id; c->open_uses++;
+            if (s.pending) {   // filled by the ingest stream: everything enqueued from here on waits for it
+                s.pending = false;
+                if (cudaStreamWaitEvent(c->stream, s.ready, 0) != cudaSuccess) return nullptr;
+            }
+            return &s;
+        }
     return nullptr;
 }
 
@@ -33,6 +41,13 @@ int join_side_stream(Ctx* c)
     if (!c->side_inflight) return VO_OK;
     c->side_inflight = false;
     VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    return VO_OK;
+}
+
+int close_step(Ctx* c)
+{
+    VO_CUDA(c, cudaEventRecord(c->ev_step_end, c->stream));
+    c->step_id++; c->open_uses = 0;
     return VO_OK;
 }
 
@@ -87,6 +102,9 @@ int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity
         c->own_stream = true;
     }
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_ingest_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_step_end, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
         delete c;
@@ -94,6 +112,7 @@ int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity
     }
     c->pinned_stage_bytes = (size_t)max_w * max_h;
     e = cudaMallocHost((void**)&c->pinned_stage, c->pinned_stage_bytes);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&c->pinned_stage2, c->pinned_stage_bytes);
     if (e != cudaSuccess) { delete c; return set_error(nullptr, VO_ERR_NOMEM, "cudaMallocHost failed: %s", cudaGetErrorString(e)); }
     int r = pipeline_init(c, track_capacity, hyp_capacity);
     if (r != VO_OK) { g_create_error = c->err; vo_destroy(c); return r; }
@@ -107,12 +126,17 @@ int vo_destroy(vo_ctx* c)
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
+    if (c->stream3) cudaStreamSynchronize(c->stream3);
     pipeline_free(c);
     detector_free(c);
-    for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); }
+    for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); if (s.ready) cudaEventDestroy(s.ready); }
     cudaFree(c->u_pts.p); cudaFree(c->u_out.p); cudaFree(c->u_err.p); cudaFree(c->u_status.p);
     cudaFree(c->u_iters.p); cudaFree(c->u_n.p);
     cudaFreeHost(c->pinned_stage);
+    cudaFreeHost(c->pinned_stage2);
+    if (c->stream3) cudaStreamDestroy(c->stream3);
+    if (c->ev_ingest_fork) cudaEventDestroy(c->ev_ingest_fork);
+    if (c->ev_step_end) cudaEventDestroy(c->ev_step_end);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -128,6 +152,7 @@ int vo_synchronize(vo_ctx* c)
     if (!c) return VO_ERR_INVALID;
     VO_TRY(join_side_stream(c));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream3));
     return VO_OK;
 }
 
@@ -162,42 +187,94 @@ int vo_drop_frames(vo_ctx* c)
     return VO_OK;
 }
 
-int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
+// Upload + pyramid of one frame on `st` (the main stream, or the ingest stream for a prefetch).
+static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key, bool ingest)
 {
     if (!c || !img) return VO_ERR_INVALID;
     if (w <= 0 || h <= 0 || w > c->max_w || h > c->max_h || pitch < w)
         return set_error(c, VO_ERR_INVALID, "frame %dx%d (pitch %d) outside ctx limits %dx%d", w, h, pitch, c->max_w, c->max_h);
-    if (find_slot(c, key)) return VO_OK;
-    VO_TRY(join_side_stream(c));   // a pyramid slot may be recycled under the side stream's reads
+    if (ingest ? vo_has_frame(c, key) : (find_slot(c, key) != nullptr)) return VO_OK;
+    cudaStream_t st = ingest ? c->stream3 : c->stream;
+    if (!ingest) VO_TRY(join_side_stream(c));   // a pyramid slot may be recycled under the side stream's reads
+    // victim: a free slot, else the least recently used one - but not a frame that was handed over early
+    // and has not been used yet (its stamp is older than those of the frames tracked since), unless
+    // that hint is stale (two newer ingests) or nothing else is left
     FrameSlot* s = nullptr;
     for (auto& t : c->slots) if (!t.valid) { s = &t; break; }
-    if (!s) { s = &c->slots[0]; for (auto& t : c->slots) if (t.stamp < s->stamp) s = &t; }
+    if (!s) {
+        FrameSlot* any = &c->slots[0];
+        for (auto& t : c->slots) {
+            if (t.stamp < any->stamp) any = &t;
+            const bool fresh_hint = t.pending && c->ingest_seq - t.ingest_seq < 2;
+            if (!fresh_hint && (!s || t.stamp < s->stamp)) s = &t;
+        }
+        if (!s) s = any;
+    }
+    if (ingest) {
+        // The recycled slot may still be read by work that is enqueued but not finished.  If the stages
+        // of the current frame are already on the stream and none of them looked this slot up, its last
+        // readers belong to a closed step: wait for that step's end only, so the ingest runs UNDER the
+        // current frame's stages.  Otherwise order it behind everything enqueued so far (stages enqueued
+        // after this call then overlap it).
+        if (c->open_uses > 0 && s->use_step < c->step_id) {
+            VO_CUDA(c, cudaStreamWaitEvent(st, c->ev_step_end, 0));
+        } else {
+            VO_CUDA(c, cudaEventRecord(c->ev_ingest_fork, c->stream));
+            VO_CUDA(c, cudaStreamWaitEvent(st, c->ev_ingest_fork, 0));
+            if (c->side_inflight) VO_CUDA(c, cudaStreamWaitEvent(st, c->ev_join, 0));
+        }
+    }
     s->valid = false;
+    if (ingest) s->ingest_seq = ++c->ingest_seq;
+    if (s->pending) {   // an ingest into this very slot is still in flight: write behind it
+        VO_CUDA(c, cudaStreamWaitEvent(st, s->ready, 0));
+        s->pending = false;
+    }
     const size_t bytes = (size_t)w * h;
     if (bytes > s->raw_bytes) {
-        if (s->raw) { cudaStreamSynchronize(c->stream); cudaFree(s->raw); s->raw = nullptr; s->raw_bytes = 0; }
+        if (s->raw) { cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->stream3); cudaFree(s->raw); s->raw = nullptr; s->raw_bytes = 0; }
         VO_CUDA(c, cudaMalloc((void**)&s->raw, bytes));
         s->raw_bytes = bytes;
     }
-    // Pageable host memory is staged through the ctx's pinned buffer so the copy is a true
-    // async DMA; pinned host and device sources are copied directly.
+    // Pageable host memory is staged through a pinned buffer of the ctx (one per stream) so the copy
+    // is a true async DMA; pinned host and device sources are copied directly.
     cudaPointerAttributes at;
     cudaError_t e = cudaPointerGetAttributes(&at, img);
     bool pageable = (e != cudaSuccess) || at.type == cudaMemoryTypeUnregistered;
     if (e != cudaSuccess) cudaGetLastError();
     if (pageable) {
         // the previous async copy out of the staging buffer must have completed
-        VO_CUDA(c, cudaStreamSynchronize(c->stream));
-        for (int y = 0; y < h; y++) memcpy(c->pinned_stage + (size_t)y * w, img + (size_t)y * pitch, w);
-        VO_CUDA(c, cudaMemcpyAsync(s->raw, c->pinned_stage, bytes, cudaMemcpyHostToDevice, c->stream));
+        VO_CUDA(c, cudaStreamSynchronize(st));
+        uint8_t* stage = ingest ? c->pinned_stage2 : c->pinned_stage;
+        for (int y = 0; y < h; y++) memcpy(stage + (size_t)y * w, img + (size_t)y * pitch, w);
+        VO_CUDA(c, cudaMemcpyAsync(s->raw, stage, bytes, cudaMemcpyHostToDevice, st));
     } else {
-        if (pitch == w) VO_CUDA(c, cudaMemcpyAsync(s->raw, img, bytes, cudaMemcpyDefault, c->stream));
-        else VO_CUDA(c, cudaMemcpy2DAsync(s->raw, w, img, pitch, w, h, cudaMemcpyDefault, c->stream));
+        if (pitch == w) VO_CUDA(c, cudaMemcpyAsync(s->raw, img, bytes, cudaMemcpyDefault, st));
+        else VO_CUDA(c, cudaMemcpy2DAsync(s->raw, w, img, pitch, w, h, cudaMemcpyDefault, st));
     }
     s->w = w; s->h = h;
-    VO_TRY(build_pyramid(c, *s, 3));
+    if (!ingest) { s->use_step = c->step_id; c->open_uses++; }   // written on the main stream in the open step
+    VO_TRY(build_pyramid(c, *s, 3, st));
+    if (ingest) {
+        if (!s->ready) VO_CUDA(c, cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming));
+        VO_CUDA(c, cudaEventRecord(s->ready, st));
+        s->pending = true;
+    }
     s->key = key; s->valid = true; s->stamp = ++c->clock;
     return VO_OK;
+}
+
+int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
+{
+    return upload_impl(c, img, w, h, pitch, key, false);
+}
+
+// SURVEY.md 8f-2 (frame ingest): the same upload + pyramid, enqueued on the ctx's ingest stream so
+// that it runs under the tracking of the current frame; the first stage that uses `key` waits for it
+// on the device (no host synchronisation anywhere).
+int vo_prefetch_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
+{
+    return upload_impl(c, img, w, h, pitch, key, true);
 }
 
 int vo_get_pyramid_level(vo_ctx* c, int64_t key, int level, uint8_t* img, int16_t* deriv, int* w, int* h)

@@ -38,6 +38,12 @@ struct FrameSlot {
     short2* deriv_pool = nullptr;
     size_t raw_bytes = 0, img_bytes = 0, deriv_bytes = 0;
     PyramidDesc pyr{};
+    // frame ingest (vo_prefetch_frame): the slot is being filled on the ingest stream; `ready` is
+    // recorded there behind the last pyramid level and the first reader on the main stream waits on it
+    cudaEvent_t ready = nullptr;
+    bool pending = false;
+    uint64_t ingest_seq = 0;
+    uint64_t use_step = 0;   // Ctx::step_id when a stage last looked the slot up
 };
 
 template <typename T>
@@ -82,6 +88,16 @@ struct Ctx {
     cudaStream_t stream2 = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool side_inflight = false;
+    // ingest stream: upload + pyramid of the NEXT frame while the current one is tracked
+    cudaStream_t stream3 = nullptr;
+    cudaEvent_t ev_ingest_fork = nullptr;
+    uint64_t ingest_seq = 0;
+    // A "step" closes when the promotion stage has been enqueued (it joins the side stream): from then
+    // on no kernel of that step reads a frame slot, and ev_step_end (main stream) marks the point.
+    cudaEvent_t ev_step_end = nullptr;
+    uint64_t step_id = 1;        // id of the open step
+    int open_uses = 0;           // slot look-ups in the open step
+    uint8_t* pinned_stage2 = nullptr;   // pageable sources of the ingest stream are staged here
     int max_w = 0, max_h = 0;
     int sm_count = 148;
     std::string err;
@@ -260,6 +276,7 @@ struct Pipeline {
     bool mask_src_valid = false; int mask_src_off = 0;
     // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
     bool spec_pending = false;
+    cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion
     int64_t spec_prev_key = -1, spec_next_key = -1;
     DevScalars* d_sc = nullptr;
     DevScalars* h_sc = nullptr;  // pinned mirror
@@ -271,7 +288,7 @@ struct Pipeline {
 };
 
 // ---- stage launchers implemented in the .cu files -------------------------------------------
-int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap);
+int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap, cudaStream_t st = nullptr);
 int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
                const int32_t* d_n, int n_upper, float* d_out, uint8_t* d_status, float* d_err,
                int32_t* d_iters, const vo_klt_params& prm);
@@ -283,6 +300,8 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
                 const vo_klt_params& prm, cudaStream_t st = nullptr);
 // make `stream` wait for the work in flight on the side stream (no-op if there is none)
 int join_side_stream(Ctx* c);
+// the promotion stage of a frame has been enqueued: close the step (see Ctx::ev_step_end)
+int close_step(Ctx* c);
 
 // optional extra (off in parity mode): track `out` back into `prev` and clear status where the
 // round trip misses the start point by more than prm.fb_thresh

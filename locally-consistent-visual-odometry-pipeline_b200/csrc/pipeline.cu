@@ -48,6 +48,7 @@ void pipeline_free(Ctx* c)
     cudaFreeHost(p->h_sc);
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
+    if (p->ev_pose) cudaEventDestroy(p->ev_pose);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
     delete p;
     c->pipe = nullptr;
@@ -208,9 +209,7 @@ int vo_snapshot_state(vo_ctx* c)
     const size_t n = p->n_land_upper > 0 ? p->n_land_upper : 1;
     if (n > p->snap_cap) {
         VO_CUDA(c, cudaStreamSynchronize(c->stream));
-        for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
-    for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
-    cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX);
+        cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX);
         p->h_snapP = nullptr; p->h_snapX = nullptr; p->snap_cap = 0;
         size_t cap = 4096;
         while (cap < n) cap *= 2;
@@ -422,10 +421,30 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     VO_TRY(launch_pnp(c, L));
     p->packed_valid = false;
     p->spec_prev_key = p->cand_tracked_prev; p->spec_next_key = p->cand_tracked_next;
+    // n_promoted == NULL: the caller only needs the pose now.  The scalar block is read back between
+    // the PnP and the promotion kernels and the host waits for THAT copy only, so the promotion step
+    // (and whatever is enqueued next) runs while the host walks on to triangulate_landmark.
+    const bool early = n_promoted == nullptr;
+    const int ncand_before = p->n_cand_upper;
+    if (early) {
+        if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
+        VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+        VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));
+    }
     VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+    VO_TRY(close_step(c));
     p->cand_tracked_valid = false;
     p->spec_pending = true;
-    VO_TRY(read_scalars(c));
+    if (early) {
+        VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
+        DevScalars* s = p->h_sc;   // values BEFORE the promotion step: bounds stay upper bounds
+        p->n_land_upper = s->n_land + ncand_before;
+        p->n_cand_upper = s->n_cand;
+        s->spec_n_land = s->n_land; s->spec_n_cand = s->n_cand;   // what a rollback restores on the host side
+        s->n_promoted = 0; s->n_cand_lost = 0;
+    } else {
+        VO_TRY(read_scalars(c));
+    }
     VO_TRY(check_rng(c));
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
     if (n_inliers) *n_inliers = p->h_sc->n_inliers;
@@ -561,6 +580,7 @@ int vo_track_triangulate_promote(vo_ctx* c, int64_t prev_key, int64_t next_key, 
     if (use_klt) VO_TRY(vo_track_candidates(c, prev_key, next_key, params));
     p->cand_tracked_valid = false;
     VO_TRY(launch_promote(c, K, T44, alpha_deg, p->n_cand_upper, use_klt, p->klt_b_off));
+    VO_TRY(close_step(c));
     if (n_promoted) { VO_TRY(read_scalars(c)); *n_promoted = p->h_sc->n_promoted; }
     return VO_OK;
 }
@@ -602,6 +622,7 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
     VO_TRY(launch_pnp(c, L));
     if (prof) cudaEventRecord(p->ev[4], c->stream);
     VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+    VO_TRY(close_step(c));
     if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
     if (prof) cudaEventRecord(p->ev[5], c->stream);
     p->cand_tracked_valid = false;

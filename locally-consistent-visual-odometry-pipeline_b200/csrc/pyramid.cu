@@ -72,8 +72,9 @@ build_level_kernel(const uint8_t* __restrict__ src, int sstride, LevelDesc dst)
 
 }  // namespace
 
-int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap)
+int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap, cudaStream_t stream)
 {
+    if (!stream) stream = c->stream;
     // geometry
     int w = s.w, h = s.h, nl = 0;
     size_t img_total = 0;
@@ -89,7 +90,7 @@ int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap)
         w = (w + 1) / 2; h = (h + 1) / 2;
     }
     if (img_total > s.img_bytes) {
-        if (s.img_pool) { cudaStreamSynchronize(c->stream); cudaFree(s.img_pool); cudaFree(s.deriv_pool); }
+        if (s.img_pool) { cudaStreamSynchronize(c->stream); cudaStreamSynchronize(stream); cudaFree(s.img_pool); cudaFree(s.deriv_pool); }
         s.img_pool = nullptr; s.deriv_pool = nullptr; s.img_bytes = 0;
         VO_CUDA(c, cudaMalloc((void**)&s.img_pool, img_total));
         VO_CUDA(c, cudaMalloc((void**)&s.deriv_pool, img_total * sizeof(short2)));
@@ -99,7 +100,7 @@ int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap)
     // the derivative plane must be zero outside the image: clear whenever the geometry changes
     bool same = s.pyr.nlevels == nl;
     for (int l = 0; same && l < nl; l++) same = s.pyr.lv[l].w == ws[l] && s.pyr.lv[l].h == hs[l];
-    if (!same) VO_CUDA(c, cudaMemsetAsync(s.deriv_pool, 0, img_total * sizeof(short2), c->stream));
+    if (!same) VO_CUDA(c, cudaMemsetAsync(s.deriv_pool, 0, img_total * sizeof(short2), stream));
     s.pyr.nlevels = nl;
     for (int l = 0; l < nl; l++) {
         LevelDesc& d = s.pyr.lv[l];
@@ -111,9 +112,9 @@ int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap)
         const LevelDesc& d = s.pyr.lv[l];
         dim3 grid((d.w + 2 * kPad + TX - 1) / TX, (d.h + 2 * kPad + TY - 1) / TY), block(TX, TY);
         if (l == 0)
-            VO_CUDA(c, launch_pdl(build_level_kernel<true>, grid, block, c->stream, (const uint8_t*)s.raw, s.w, d));
+            VO_CUDA(c, launch_pdl(build_level_kernel<true>, grid, block, stream, (const uint8_t*)s.raw, s.w, d));
         else
-            VO_CUDA(c, launch_pdl(build_level_kernel<false>, grid, block, c->stream, (const uint8_t*)s.pyr.lv[l - 1].img,
+            VO_CUDA(c, launch_pdl(build_level_kernel<false>, grid, block, stream, (const uint8_t*)s.pyr.lv[l - 1].img,
                                   s.pyr.lv[l - 1].stride, d));
         c->launches++;
     }

@@ -88,6 +88,8 @@ class _Runtime:
         self.klt.fb_check = int(bool(_cfg('klt_fb_check')))
         self.klt.fb_thresh = float(_cfg('klt_fb_thresh'))
         self.frames = {}          # id(array) -> (key, strong ref, fingerprint)
+        self.hint = None          # frame passed to prefetch_frame, not yet on the ingest stream
+        self.prefetched = {}      # data pointer -> (key, strong ref, fingerprint) of frames handed over early
         self.next_key = 1
         self.state_version = 0    # bumped whenever the device landmarks change
         self.ext_version = 0      # bumped whenever the device candidates change
@@ -109,14 +111,41 @@ class _Runtime:
         ent = self.frames.get(id(img))
         if ent is not None and ent[2] == fp and self.ctx.has_frame(ent[0]):
             return ent[0]
-        key = self.next_key
-        self.next_key += 1
-        self.ctx.upload_frame(img, key)
+        if self.hint is not None and self.hint.__array_interface__['data'][0] == fp[1]:
+            self.hint = None      # needed right now: nothing left to hide the ingest under
+        pre = self.prefetched.pop(fp[1], None) if self.prefetched else None
+        if pre is not None and pre[2] == fp and self.ctx.has_frame(pre[0]):
+            key = pre[0]          # handed over early by prefetch_frame: already on its way / resident
+        else:
+            key = self.next_key
+            self.next_key += 1
+            self.ctx.upload_frame(img, key)
         self.frames[id(img)] = (key, img, fp)
         if len(self.frames) > 3:   # the ctx keeps 4 pyramids; drop the oldest host references
             for k in sorted(self.frames, key=lambda i: self.frames[i][0])[:-3]:
                 del self.frames[k]
         return key
+
+    def prefetch(self, img):
+        """Frame ingest: remember a FUTURE frame; its upload + pyramid go to the ingest
+        stream as soon as the current frame's tracking is on the main stream (issue_hint), so both the
+        host-side enqueue and the device-side work hide under the current frame's stages."""
+        if img.dtype != np.uint8 or img.ndim != 2 or img.strides[1] != 1:
+            raise ValueError("frames must be 2-D uint8 (cv2.IMREAD_GRAYSCALE) arrays with contiguous rows")
+        self.hint = img
+
+    def issue_hint(self):
+        img = self.hint
+        if img is None:
+            return
+        self.hint = None
+        fp = (img.shape, img.__array_interface__['data'][0], zlib.adler32(img[img.shape[0] >> 1]))
+        key = self.next_key
+        self.next_key += 1
+        self.ctx.prefetch_frame(img, key)
+        if len(self.prefetched) >= 2:    # hints that were never used
+            self.prefetched.pop(next(iter(self.prefetched)))
+        self.prefetched[fp[1]] = (key, img, fp)
 
     def pair_keys(self, old_frame, new_frame):
         """Keys of a frame pair; the pair the last associate call saw is recognised by identity."""
@@ -396,6 +425,7 @@ class KeypointsToLandmarksAssociator():
             # the third landmark buffer keeps it until the next tracking step
             state._prev = rt.prev_token
         rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt)
+        rt.issue_hint()            # next frame's ingest: under this frame's tracking and PnP
         rt.state_version += 1
         return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
 
@@ -454,6 +484,7 @@ class PoseEstimator():
         place and returns the 4x4 world->camera pose (host ndarray: main.py:239 inverts it)."""
         rt = _runtime()
         rt.drop_speculation()
+        rt.issue_hint()
         uploaded = not (isinstance(associations, DeviceState) and associations._current())
         _sync_state_to_device(rt, associations)
         # The promotion step of triangulate_landmark does not need the host: enqueue it ahead of the
@@ -465,7 +496,7 @@ class PoseEstimator():
                      and rt.pair is not None and rt.ctx.candidates_tracked(rt.pair[2], rt.pair[3]))
         if speculate:
             alpha = float(_alpha_threshold())
-            ok, T, n_inl, _ = rt.ctx.pnp_ransac_promote(self.K, self._params(), alpha)
+            ok, T, n_inl, _ = rt.ctx.pnp_ransac_promote(self.K, self._params(), alpha, early=True)
         else:
             ok, T, n_inl = rt.ctx.pnp_ransac(self.K, self._params())
         self.last = {'ok': ok, 'n_inliers': n_inl}
@@ -672,3 +703,84 @@ _candidate_feed = []
 def set_candidate_feed(feed):
     """Per-frame candidate positions used when config['find_new_candidates_method'] == 'feed'."""
     _candidate_feed[:] = list(feed)
+
+
+# ---- frame ingest (SURVEY.md 8f-2; the reference reads frame k+1 from disk only after frame k is done,
+# main.py:216-223) ---------------------------------------------------------------------------------------
+def prefetch_frame(img):
+    """Optional hint: `img` (2-D uint8, ideally pinned - see FrameIngest) will be passed as new_frame
+    soon.  Its H2D copy and pyramid are enqueued on the ingest stream right after the tracking of the
+    current frame (inside the next associateKeypointsToLandmarks / estimatePose call), so they run under
+    the stages of the current frame; the stage that first uses the frame waits for it on the device.
+    Results do not change."""
+    _runtime(img).prefetch(img)
+
+
+class FrameIngest:
+    """Pre-decoded frames in a ring of pinned host buffers, decoded one frame ahead by a worker
+    thread (cv2.imread releases the GIL) and handed to the device one frame ahead of their use:
+
+        for img2 in FrameIngest(paths):          # instead of cv2.imread(...) per iteration
+            new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
+
+    `source` is a sequence of file paths (read with cv2.IMREAD_GRAYSCALE, as main.py:217-223 does) or of
+    2-D uint8 arrays.  Yields numpy views over pinned memory; a view stays valid for `depth - 2` more
+    iterations (main.py keeps the previous frame as img1)."""
+
+    def __init__(self, source, depth=4, prefetch=True):
+        if depth < 3:
+            raise ValueError("FrameIngest needs depth >= 3 (previous, current and next frame are live)")
+        self.source, self.depth, self.do_prefetch = source, depth, prefetch
+        self.ring, self.shape = [], None
+
+    def _decode(self, item):
+        if isinstance(item, (str, os.PathLike)):
+            VOInitializer._need_cv2()
+            img = cv2.imread(os.fspath(item), cv2.IMREAD_GRAYSCALE)
+            if img is None:
+                raise FileNotFoundError(item)
+            return img
+        return np.asarray(item)
+
+    def _slot(self, i, img):
+        if img.dtype != np.uint8 or img.ndim != 2:
+            raise ValueError("frames must be 2-D uint8")
+        if self.shape != img.shape:   # (re)allocate the ring for this frame size
+            self.ring = [_cabi.PinnedArray(img.shape, np.uint8) for _ in range(self.depth)]
+            self.shape = img.shape
+        dst = self.ring[i % self.depth].array
+        dst[...] = img
+        return dst
+
+    def __len__(self):
+        return len(self.source)
+
+    def __iter__(self):
+        import threading
+        import queue
+        q = queue.Queue(maxsize=1)   # one decoded frame ahead; its ring slot is not live yet
+
+        def worker():
+            try:
+                for i, item in enumerate(self.source):
+                    q.put((i, self._decode(item)))
+                q.put(None)
+            except BaseException as e:   # surface decode errors in the consumer
+                q.put(e)
+
+        t = threading.Thread(target=worker, daemon=True)
+        t.start()
+
+        def take():
+            r = q.get()
+            if isinstance(r, BaseException):
+                raise r
+            return None if r is None else self._slot(*r)
+
+        cur = take()
+        while cur is not None:
+            nxt = take()
+            if nxt is not None and self.do_prefetch:
+                prefetch_frame(nxt)
+            yield cur
+            cur = nxt

@@ -164,8 +164,11 @@ def test_fused_frame_equals_staged_calls(pkg, scene_mod):
         a.close(); b.close()
 
 
-def test_speculative_promotion_commit_and_rollback(pkg, scene_mod):
-    """vo_pnp_ransac_promote (+commit) == vo_pnp_ransac + vo_track_triangulate_promote, bit for bit; a
+@pytest.mark.parametrize("early", [False, True])
+def test_speculative_promotion_commit_and_rollback(pkg, scene_mod, early):
+    """early: the host waits for the pose only (n_promoted == NULL), the promotion is still running when
+    the call returns and the peeked counters are those before it.
+    vo_pnp_ransac_promote (+commit) == vo_pnp_ransac + vo_track_triangulate_promote, bit for bit; a
     rollback restores the state exactly as vo_pnp_ransac leaves it, and the staged promotion can then
     still run on the pending candidate tracking."""
     sq = get_sequence(scene_mod, "kitti_half")
@@ -186,8 +189,13 @@ def test_speculative_promotion_commit_and_rollback(pkg, scene_mod):
             Pa0, Xa0 = a.get_state()                     # pruned to the inliers, nothing promoted yet
             Ca0 = a.get_candidates()
             assert b.candidates_tracked(k, k + 1)
-            okb, Tb, ninlb, nprom = b.pnp_ransac_promote(K, pnp, 1.0)
+            okb, Tb, ninlb, nprom = b.pnp_ransac_promote(K, pnp, 1.0, early=early)
             assert ok and okb and ninl == ninlb and np.array_equal(Ta, Tb) and b.promote_pending()
+            if early:
+                assert nprom is None
+                pk = b.counters(sync=False)              # as of the pose read-back: before the promotion
+                assert pk["n_landmarks"] == ninl and pk["n_candidates"] == len(Ca0[0]) and pk["n_promoted"] == 0
+                nprom = None
             if k % 2 == 0:
                 b.promote_rollback()
                 assert not b.promote_pending()
@@ -198,7 +206,8 @@ def test_speculative_promotion_commit_and_rollback(pkg, scene_mod):
                 b.track_triangulate_promote(k, k + 1, K, Tb, 1.0)
             else:
                 Pb, Xb = b.get_state()                   # promoted rows sit behind the inlier rows
-                assert np.array_equal(Pb[:ninl], Pa0) and np.array_equal(Xb[:ninl], Xa0) and len(Pb) == ninl + nprom
+                assert np.array_equal(Pb[:ninl], Pa0) and np.array_equal(Xb[:ninl], Xa0)
+                assert len(Pb) == ninl + (b.counters()["n_promoted"] if nprom is None else nprom)
                 b.promote_commit()
             a.track_triangulate_promote(k, k + 1, K, Ta, 1.0)
             for c in (a, b):
@@ -309,3 +318,93 @@ def test_cf_alias_quirk(ctx, scene_mod):
     assert not np.array_equal(F, sq.feeds[1][:len(F)])
     ctx.add_candidates(sq.feeds[2], sq.poses[2])                         # second batch: concatenate, no alias
     assert ctx.counters()["cf_alias"] == 0
+
+
+def test_frame_ingest_prefetch_is_bit_identical(pkg, scene_mod):
+    """frames handed over one step ahead on the ingest stream (vo_prefetch_frame) give the
+    same poses, landmarks and candidates, bit for bit, as in-step uploads - from pinned, pageable and
+    strided sources, across slot recycling, and when a prefetched frame is never used."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    K = sq.K
+    pnp = pkg.pnp_defaults()
+    h, w = sq.frames[0].shape
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)   # in-step uploads
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)   # ingest one frame ahead
+    n = 14
+    pinned = [pkg.PinnedArray((h, w), np.uint8) for _ in range(n + 2)]
+    wide = np.zeros((h, w + 24), np.uint8)               # strided pageable source
+    try:
+        for p, f in zip(pinned, sq.frames):
+            p.array[...] = f
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        b.prefetch_frame(pinned[1].array, 2)
+        for k in range(1, n):
+            # next frame to the ingest stream BEFORE this frame's stages: pinned / pageable / strided in turn
+            if k % 3 == 0:
+                src = pinned[k + 1].array
+            elif k % 3 == 1:
+                src = sq.frames[k + 1]
+            else:
+                wide[:, :w] = sq.frames[k + 1]
+                src = wide[:, :w]
+            b.prefetch_frame(src, k + 2)
+            if k == 5:
+                b.prefetch_frame(sq.frames[0], 1000)     # a hint that is never consumed
+            assert b.has_frame(k + 1)
+            Ta, ca = a.process_frame(sq.frames[k], k, k + 1, K, 1.0, sq.feeds[k], pnp=pnp)
+            Tb, cb = b.process_frame(None, k, k + 1, K, 1.0, sq.feeds[k], pnp=pnp)
+            assert ca["pnp_ok"] == 1 and np.array_equal(Ta, Tb), k
+            for key in ("n_landmarks", "n_candidates", "n_promoted", "n_inliers", "klt_iters"):
+                assert ca[key] == cb[key], (k, key)
+        Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+        assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+        for u, v in zip(a.get_candidates(), b.get_candidates()):
+            assert np.array_equal(u, v)
+        # the pyramid an ingest leaves behind is the one an upload builds
+        a.upload_frame(sq.frames[3], 77)
+        b.prefetch_frame(sq.frames[3], 77)
+        for lv in range(4):
+            ia, da = a.pyramid_level(77, lv)
+            ib, db = b.pyramid_level(77, lv)
+            assert np.array_equal(ia, ib) and np.array_equal(da, db)
+    finally:
+        a.close(); b.close()
+        for p in pinned:
+            p.free()
+
+
+def test_dropin_prefetch_hint_and_frame_ingest(dropin, scene_mod):
+    """vo_pipeline.prefetch_frame / FrameIngest: the drop-in classes driven with frames handed over one
+    iteration early return exactly the poses of the plain drive."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    Ts0, nP0, nC0, _ = drive_dropin(dropin, sq, read_prev_state=False)
+    dropin._reset_runtime()
+
+    vo = dropin
+    vo.set_candidate_feed([f.copy() for f in sq.feeds[1:]])
+    vision = vo.BestVision(sq.K)
+    vision.state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+    vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+    associate = vo.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+    pose_estimator = vo.PoseEstimator(sq.K)
+    Ts = []
+    img1 = None
+    ingest = vo.FrameIngest(sq.frames, depth=4)
+    assert len(ingest) == len(sq.frames)
+    for k, img2 in enumerate(ingest):
+        assert np.array_equal(img2, sq.frames[k])
+        if img1 is None:
+            img1 = img2
+            continue
+        new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
+        new_pose = pose_estimator.estimatePose(new_state, k)
+        tri = vo.LandmarkTriangulator(sq.K, None)
+        vision.state, vision.extended_state, _ = tri.triangulate_landmark(img1, img2, new_state, vision.extended_state, new_pose)
+        img1 = img2
+        Ts.append(new_pose)
+    assert np.array_equal(np.array(Ts), Ts0)
+    # every frame but the first two came in through the ingest stream: no key was uploaded twice
+    assert vo._runtime().next_key == len(sq.frames) + 1

@@ -12,13 +12,14 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 
-steps = int(sys.argv[1]) if len(sys.argv) > 1 else 300
+steps = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 300
 pkg = importlib.import_module(bench.PKG)
 _, sq = bench.build_sequence(seed=11)
 pr = cProfile.Profile()
-r0 = bench.run_e2e(pkg, sq, steps, 20, 0, 1)       # warm (also un-profiled reference number)
+PF = "--no-prefetch" not in sys.argv
+r0 = bench.run_e2e(pkg, sq, steps, 20, 0, 1, PF)       # warm (also un-profiled reference number)
 pr.enable()
-r = bench.run_e2e(pkg, sq, steps, 20, 0, 1)
+r = bench.run_e2e(pkg, sq, steps, 20, 0, 1, PF)
 pr.disable()
 print("e2e fps un-profiled %.1f, profiled %.1f" % (r0["fps"], r["fps"]))
 st = pstats.Stats(pr)
