@@ -158,6 +158,12 @@ int vo_peek_counters(vo_ctx* ctx, vo_counters* out);  /* as of the last synchron
  * n_kept may be NULL: then nothing synchronises. */
 int vo_klt_track_landmarks(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
                            int* n_kept);
+/* a1 with the PREVIOUS frame's append of new candidates (vo_pipeline.py:574-591) folded in: same result
+ * as vo_add_candidates(new_candidates, n_new, T44) followed by vo_klt_track_landmarks, but the rows
+ * travel on the side stream in front of the candidates' KLT, so neither their copy nor the append
+ * kernel sits between the caller and the landmark launch (the head of the chain the pose waits for). */
+int vo_klt_track_landmarks_add(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
+                               const double* new_candidates, int n_new, const double T44[16], int* n_kept);
 /* a3  PoseEstimator.estimatePose (vo_pipeline.py:245-335): PnP-RANSAC + LM refit, prunes P/X to
  * the inliers (vo_pipeline.py:327-331), T44 = 4x4 row-major world->camera (vo_pipeline.py:333).
  * ok=0 (no model / n<4) leaves the state untouched: the caller takes the re-bootstrap branch of

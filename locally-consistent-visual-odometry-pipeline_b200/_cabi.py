@@ -86,6 +86,7 @@ SIGNATURES = {
     "vo_peek_counters": (c_int, [c_void_p, ctypes.POINTER(Counters)]),
     "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
+    "vo_klt_track_landmarks_add": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, _PI]),
     "vo_pnp_ransac_promote": (c_int, [c_void_p, c_void_p, _PP, c_double, c_void_p, _PI, _PI, _PI]),
     "vo_promote_commit": (c_int, [c_void_p]),
     "vo_promote_rollback": (c_int, [c_void_p]),
@@ -327,11 +328,18 @@ class Context:
         return cnt.as_dict()
 
     # ---- per-frame stages ------------------------------------------------------------------------
-    def klt_track_landmarks(self, prev_key, next_key, params=None, sync=False):
+    def klt_track_landmarks(self, prev_key, next_key, params=None, sync=False, add=None):
+        """a1.  add=(pts n x 2 float64, T 4x4): the previous frame's new candidates, appended on the side
+        stream in front of the candidates' KLT (vo_klt_track_landmarks_add)."""
         n = c_int()
-        self._check(self.lib.vo_klt_track_landmarks(
-            self.h, prev_key, next_key, ctypes.byref(params) if params is not None else None,
-            ctypes.byref(n) if sync else None))
+        pk = ctypes.byref(params) if params is not None else None
+        if add is not None and len(add[0]) > 0:
+            pts = np.ascontiguousarray(add[0], np.float64).reshape(-1, 2)
+            T = np.ascontiguousarray(add[1], np.float64)
+            self._check(self.lib.vo_klt_track_landmarks_add(self.h, prev_key, next_key, pk, _ptr(pts), len(pts), _ptr(T),
+                                                            ctypes.byref(n) if sync else None))
+        else:
+            self._check(self.lib.vo_klt_track_landmarks(self.h, prev_key, next_key, pk, ctypes.byref(n) if sync else None))
         return n.value if sync else None
 
     def pnp_ransac(self, K, params=None):

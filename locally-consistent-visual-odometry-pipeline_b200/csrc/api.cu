@@ -39,7 +39,7 @@ FrameSlot* get_frame(Ctx* c, int64_t key) { return find_slot(c, key); }
 int join_side_stream(Ctx* c)
 {
     if (!c->side_inflight) return VO_OK;
-    c->side_inflight = false;
+    c->side_inflight = false; c->side_writes_counts = false;
     VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
     return VO_OK;
 }

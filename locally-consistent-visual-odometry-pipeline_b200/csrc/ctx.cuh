@@ -88,6 +88,7 @@ struct Ctx {
     cudaStream_t stream2 = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     bool side_inflight = false;
+    bool side_writes_counts = false;   // a deferred candidate append is part of the side stream's work
     // ingest stream: upload + pyramid of the NEXT frame while the current one is tracked
     cudaStream_t stream3 = nullptr;
     cudaEvent_t ev_ingest_fork = nullptr;
@@ -223,7 +224,7 @@ struct DevScalars {
     int32_t spec_n_land, spec_n_cand, spec_cf_alias, spec_cand_was_empty;
     int32_t finalized;     // the refit of the current RANSAC run has been done
     int32_t klt_iters_cand; // sum of LK iterations over the candidates (roofline accounting)
-    int32_t pad_;
+    int32_t ticket2;       // same for kernels enqueued on the side stream (they overlap main-stream kernels)
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -269,6 +270,9 @@ struct Pipeline {
     DevBuf<double> stage_d; // host->device staging (unit-level calls, candidate feed)
     DevBuf<float> stage_f;
     DevBuf<int32_t> stage_i;
+    // deferred append riding on the side stream (vo_klt_track_landmarks_add): double-buffered staging
+    double* h_add[2] = { nullptr, nullptr }; size_t h_add_cap = 0; int add_flip = 0;
+    DevBuf<double> d_add[2];
     int klt_b_off = 0;      // offset of the candidate results inside the klt_* buffers
     bool packed_valid = false;  // q4/qv hold the current landmarks (set by the post-KLT compaction)
     // the last promotion step consumed a candidate KLT: C[ccur ^ 1] holds the candidates' previous
@@ -332,7 +336,8 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
                    bool use_klt, int b_off);
 // d_pts: n_new x 2 doubles on the device; d_Thost: 16 doubles on the device or nullptr (= device pose)
 // d_n_new: optional device count (the rows actually appended are min(*d_n_new, n_new))
-int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new = nullptr);
+int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new = nullptr,
+                    bool on_side_stream = false);
 // det.cu
 void gftt_defaults(vo_gftt_params* p);
 int detector_free(Ctx* c);

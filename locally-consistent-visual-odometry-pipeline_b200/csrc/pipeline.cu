@@ -44,6 +44,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->sets.p); cudaFree(p->hyp.p); cudaFree(p->counts.p); cudaFree(p->mask.p); cudaFree(p->promote.p);
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
     cudaFree(p->rng_tab.p); cudaFree(p->blk_counts.p); cudaFree(p->cand_flag.p);
+    for (int k = 0; k < 2; k++) { cudaFree(p->d_add[k].p); if (p->h_add[k]) cudaFreeHost(p->h_add[k]); }
     cudaFree(p->d_sc);
     cudaFreeHost(p->h_sc);
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
@@ -58,6 +59,7 @@ void pipeline_free(Ctx* c)
 static int read_scalars(Ctx* c)
 {
     Pipeline* p = c->pipe;
+    if (c->side_writes_counts) VO_TRY(join_side_stream(c));   // n_cand is being updated over there
     VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     p->n_land_upper = p->h_sc->n_land;
@@ -79,21 +81,54 @@ __global__ void set_counts_kernel(DevScalars* sc, int n_land, int n_cand, int al
     if (n_cand >= 0) { sc->n_cand = n_cand; sc->cf_alias = alias; sc->cand_was_empty = n_cand == 0; }
 }
 
-// KLT of landmarks (list A) and candidates (list B, stored behind A at offset n_land_upper)
-static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& prm, bool with_candidates)
+// A deferred append of new candidates (vo_pipeline.py:574-591 of the PREVIOUS frame) that rides on the
+// side stream in front of the candidates' KLT: host rows, copied through pinned staging
+struct DeferredAdd { const double* pts; int n; const double* T44; };
+
+// KLT of landmarks (list A) and candidates (list B, stored behind A at offset n_land_upper).  The
+// landmark launch - the head of the chain the pose depends on - is enqueued FIRST; the candidates
+// (usually most of the tracks, and with them the slowest stragglers) follow on the side stream, behind
+// the optional deferred append, and are joined by the promotion step.
+static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& prm, bool with_candidates,
+                      const DeferredAdd* add = nullptr)
 {
     Pipeline* p = c->pipe;
-    const int nA = p->n_land_upper, nB = with_candidates ? p->n_cand_upper : 0;
+    const int nA = p->n_land_upper;
+    const int n_add = (add && with_candidates && add->n > 0) ? add->n : 0;
+    const int nB = with_candidates ? p->n_cand_upper + n_add : 0;
     const size_t tot = (size_t)nA + nB > 0 ? (size_t)nA + nB : 1;
+    VO_TRY(join_side_stream(c));
     VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
     VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
+    if (nB > 0) VO_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));   // the side stream forks BEFORE the landmark launch
+    VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, nullptr, nullptr, 0, 0, p->klt_out.p,
+                       p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm));
+    p->klt_b_off = nA;
     if (nB > 0) {
-        // fork: the candidates (usually most of the tracks, and with them the slowest stragglers) are
-        // tracked on the side stream while the landmark chain - the only thing the pose depends on -
-        // goes ahead on the main stream; the promotion step joins the two
-        VO_TRY(join_side_stream(c));
-        VO_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));
         VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+        if (n_add > 0) {
+            const size_t need = (size_t)n_add * 2 + 16;
+            if (need > p->h_add_cap) {
+                VO_CUDA(c, cudaStreamSynchronize(c->stream2));
+                size_t cap = 4096;
+                while (cap < need) cap *= 2;
+                for (int k = 0; k < 2; k++) {
+                    if (p->h_add[k]) cudaFreeHost(p->h_add[k]);
+                    p->h_add[k] = nullptr;
+                    VO_CUDA(c, cudaMallocHost((void**)&p->h_add[k], cap * sizeof(double)));
+                }
+                p->h_add_cap = cap;
+            }
+            // two staging buffers in turn: the copy out of the one used two frames ago was joined by that
+            // frame's promotion step, which the pose read-back of the frame after it has waited for
+            const int f = p->add_flip ^= 1;
+            VO_TRY(ensure(c, p->d_add[f], need));
+            memcpy(p->h_add[f], add->T44, 16 * sizeof(double));
+            memcpy(p->h_add[f] + 16, add->pts, (size_t)n_add * 2 * sizeof(double));
+            VO_CUDA(c, cudaMemcpyAsync(p->d_add[f].p, p->h_add[f], need * sizeof(double), cudaMemcpyHostToDevice, c->stream2));
+            VO_TRY(launch_cand_add(c, p->d_add[f].p + 16, n_add, p->d_add[f].p, nullptr, true));
+            c->side_writes_counts = true;
+        }
         if (p->profiling) cudaEventRecord(p->ev_side[0], c->stream2);
         VO_TRY(launch_klt2(c, a->pyr, b->pyr, nullptr, nullptr, 0, p->C[p->ccur].p, &p->d_sc->n_cand, nB, nA, p->klt_out.p,
                            p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, c->stream2));
@@ -101,9 +136,6 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
         VO_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
         c->side_inflight = true;
     }
-    VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, nullptr, nullptr, 0, 0, p->klt_out.p,
-                       p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm));
-    p->klt_b_off = nA;
     return VO_OK;
 }
 
@@ -323,7 +355,8 @@ int vo_get_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, 
 int vo_peek_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, false); }
 
 // ---- a1: KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227)
-int vo_klt_track_landmarks(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params, int* n_kept)
+static int track_landmarks_impl(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
+                                const DeferredAdd* add, int* n_kept)
 {
     VO_NEED(c);
     Pipeline* p = c->pipe;
@@ -332,14 +365,30 @@ int vo_klt_track_landmarks(vo_ctx* c, int64_t prev_key, int64_t next_key, const 
     FrameSlot* a = get_frame(c, prev_key);
     FrameSlot* b = get_frame(c, next_key);
     if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
-    // candidates ride along in the same launch: triangulate_landmark (vo:501) tracks them over the
-    // same frame pair, and their tracking does not depend on the pose
-    VO_TRY(track_both(c, a, b, prm, true));
+    // candidates ride along: triangulate_landmark (vo:501) tracks them over the same frame pair, and
+    // their tracking does not depend on the pose
+    VO_TRY(track_both(c, a, b, prm, true, add));
     p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
     VO_TRY(launch_landmark_compact(c, p->n_land_upper));
     p->packed_valid = true;
-    if (n_kept) { VO_TRY(read_scalars(c)); *n_kept = p->h_sc->n_land; }
+    if (n_kept) { VO_TRY(join_side_stream(c)); VO_TRY(read_scalars(c)); *n_kept = p->h_sc->n_land; }
     return VO_OK;
+}
+
+int vo_klt_track_landmarks(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params, int* n_kept)
+{
+    return track_landmarks_impl(c, prev_key, next_key, params, nullptr, n_kept);
+}
+
+// a1 with the previous frame's append of new candidates (vo_pipeline.py:574-591) folded in: the rows go
+// to the side stream in front of the candidates' KLT, so neither the copy nor the append kernel sits
+// between the host and the landmark launch.  Same result as vo_add_candidates + vo_klt_track_landmarks.
+int vo_klt_track_landmarks_add(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
+                               const double* new_candidates, int n_new, const double T44[16], int* n_kept)
+{
+    if (n_new < 0 || (n_new > 0 && (!new_candidates || !T44))) return VO_ERR_INVALID;
+    DeferredAdd add{ new_candidates, n_new, T44 };
+    return track_landmarks_impl(c, prev_key, next_key, params, n_new > 0 ? &add : nullptr, n_kept);
 }
 
 // ---- a3: PoseEstimator.estimatePose (vo_pipeline.py:245-335); synchronises
@@ -427,6 +476,7 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     const bool early = n_promoted == nullptr;
     const int ncand_before = p->n_cand_upper;
     if (early) {
+        VO_TRY(join_side_stream(c));   // a deferred append on the side stream writes n_cand (long done by now)
         if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
         VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
         VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));

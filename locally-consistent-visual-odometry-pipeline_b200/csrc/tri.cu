@@ -347,12 +347,14 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
 __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts, int n_new_upper,
                                 const int32_t* __restrict__ n_new_dev, int use_dev_T,
                                 const double* __restrict__ Thost, float2* __restrict__ C, double2* __restrict__ F,
-                                int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap)
+                                int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap,
+                                int side)
 {
     __shared__ int sLast;
     pdl_prologue();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n0 = sc->n_cand;
+    int32_t* ticket = side ? &sc->ticket2 : &sc->ticket;
     const int n_new = n_new_dev ? min(*n_new_dev, n_new_upper) : n_new_upper;
     const bool skip = use_dev_T && !sc->ok;   // no pose this frame: nothing is added
     if (!skip) {
@@ -367,9 +369,9 @@ __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts,
     __syncthreads();
     if (threadIdx.x == 0) {
         __threadfence();
-        sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
+        sLast = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
         if (sLast) {
-            sc->ticket = 0;
+            *ticket = 0;
             if (!skip && n_new > 0) {
                 // C empty when the batch arrives: the reference binds C and F to one ndarray (App. B-5);
                 // otherwise np.concatenate allocates fresh arrays and any aliasing ends
@@ -462,10 +464,11 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     return VO_OK;
 }
 
-int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new)
+int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new,
+                    bool on_side_stream)
 {
     Pipeline* p = c->pipe;
-    VO_TRY(join_side_stream(c));
+    if (!on_side_stream) VO_TRY(join_side_stream(c));
     const size_t need = (size_t)p->n_cand_upper + (n_new > 0 ? n_new : 0) + 1;
     VO_TRY(ensure(c, p->C[p->ccur], need * 2, true));
     VO_TRY(ensure(c, p->F[p->ccur], need * 2, true));
@@ -473,9 +476,9 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
     VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));
     const int cap = (int)(p->C[p->ccur].cap / 2);
     const int threads = 256, blocks = ((n_new > 16 ? n_new : 16) + threads - 1) / threads;
-    VO_CUDA(c, launch_pdl(cand_add_kernel, dim3(blocks), dim3(threads), c->stream, p->d_sc, (const double2*)d_pts, n_new,
-                          d_n_new, (int)(d_Thost == nullptr), d_Thost, (float2*)p->C[p->ccur].p, (double2*)p->F[p->ccur].p,
-                          p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap));
+    VO_CUDA(c, launch_pdl(cand_add_kernel, dim3(blocks), dim3(threads), on_side_stream ? c->stream2 : c->stream, p->d_sc,
+                          (const double2*)d_pts, n_new, d_n_new, (int)(d_Thost == nullptr), d_Thost, (float2*)p->C[p->ccur].p,
+                          (double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap, (int)on_side_stream));
     c->launches++;
     p->n_poses++;
     p->n_cand_upper += n_new > 0 ? n_new : 0;

@@ -413,9 +413,16 @@ class KeypointsToLandmarksAssociator():
         with new_state = rows of P (new positions, float32) and X whose status is 1."""
         rt = _runtime(new_frame)
         rt.drop_speculation()      # estimatePose without a matching triangulate_landmark
-        k_old, k_new = rt.frame_key(old_frame), rt.frame_key(new_frame)   # upload + pyramid first
+        pr = rt.pair
+        if pr is not None and pr[1] is old_frame and rt.ctx.has_frame(pr[3]):
+            k_old = pr[3]          # main.py:293 (img1 = img2): the frame tracked INTO last time, as uploaded then
+        else:
+            k_old = rt.frame_key(old_frame)
+        k_new = rt.frame_key(new_frame)   # upload + pyramid first (a no-op for a frame handed over early)
         rt.pair = (old_frame, new_frame, k_old, k_new)
-        rt.flush_pending_add()     # last frame's new candidates must be tracked from this frame on
+        # last frame's new candidates must be tracked from this frame on: they ride on the side stream in
+        # front of the candidates' KLT, behind the landmark launch
+        add, rt.pending_add = rt.pending_add, None
         _sync_state_to_device(rt, state)
         rt.prev_token += 1
         if not isinstance(state, DeviceState):
@@ -424,7 +431,7 @@ class KeypointsToLandmarksAssociator():
             # the caller may still read this (now previous) state after the device has moved on:
             # the third landmark buffer keeps it until the next tracking step
             state._prev = rt.prev_token
-        rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt)
+        rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt, add=add)
         rt.issue_hint()            # next frame's ingest: under this frame's tracking and PnP
         rt.state_version += 1
         return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
@@ -472,6 +479,14 @@ class PoseEstimator():
         self.last = {}
 
     def _params(self):
+        key = (int(_cfg('pnp_max_iters')), float(self.CONFIDENCE), float(self.REPOJ_THRESH), int(_cfg('pnp_refine_iters')))
+        if getattr(self, '_pcache', (None,))[0] == key:
+            return self._pcache[1]
+        p = self._build_params()
+        self._pcache = (key, p)
+        return p
+
+    def _build_params(self):
         p = _cabi.pnp_defaults()
         p.max_iters = int(_cfg('pnp_max_iters'))
         p.confidence = float(self.CONFIDENCE)
@@ -512,7 +527,7 @@ class PoseEstimator():
             P, X = rt.ctx.get_state()
             associations['P'], associations['X'] = P[:n_inl], X[:n_inl]
         if speculate:
-            rt.spec = {'T': T.copy(), 'alpha': alpha, 'K': np.array(self.K, np.float64), 'pair': rt.pair,
+            rt.spec = {'T': T.tobytes(), 'alpha': alpha, 'K': np.asarray(self.K, np.float64).tobytes(), 'pair': rt.pair,
                        'state_version': rt.state_version, 'ext_version': rt.ext_version}
             if isinstance(associations, DeviceState):
                 associations._limit = n_inl
@@ -623,8 +638,8 @@ class LandmarkTriangulator():
                      and isinstance(state, DeviceState) and state._current()
                      and state._version == sp['state_version'] and sp['pair'] is rt.pair
                      and rt.pair[0] is old_frame and rt.pair[1] is new_frame
-                     and float(threshold) == sp['alpha'] and np.array_equal(new_pose, sp['T'])
-                     and np.array_equal(np.asarray(self.K, np.float64), sp['K']))
+                     and float(threshold) == sp['alpha'] and new_pose.tobytes() == sp['T']
+                     and np.asarray(self.K, np.float64).tobytes() == sp['K'])
         if confirmed:
             # the promotion ran ahead of estimatePose's sync with exactly these arguments
             rt.spec = None

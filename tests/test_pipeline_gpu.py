@@ -408,3 +408,48 @@ def test_dropin_prefetch_hint_and_frame_ingest(dropin, scene_mod):
     assert np.array_equal(np.array(Ts), Ts0)
     # every frame but the first two came in through the ingest stream: no key was uploaded twice
     assert vo._runtime().next_key == len(sq.frames) + 1
+
+
+def test_track_with_folded_append_equals_add_then_track(pkg, scene_mod):
+    """vo_klt_track_landmarks_add (the previous frame's new candidates appended on the side stream, in
+    front of the candidates' KLT) == vo_add_candidates followed by vo_klt_track_landmarks, bit for bit,
+    including the C/F aliasing quirk of the first batch and state reads while the append is in flight."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    K = sq.K
+    pnp = pkg.pnp_defaults()
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)
+    try:
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        pend = None
+        for k in range(1, 12):
+            for c in (a, b):
+                c.upload_frame(sq.frames[k], k + 1)
+            if pend is not None:
+                a.add_candidates(*pend)
+            a.klt_track_landmarks(k, k + 1)
+            b.klt_track_landmarks(k, k + 1, add=pend)
+            if k % 4 == 0:      # a synchronising read while the side-stream append may still be running
+                assert a.counters()["n_candidates"] == b.counters()["n_candidates"]
+            oka, Ta, na = a.pnp_ransac(K, pnp)
+            if k % 2:
+                okb, Tb, nb, _ = b.pnp_ransac_promote(K, pnp, 1.0, early=True)
+                b.promote_commit()
+            else:
+                okb, Tb, nb = b.pnp_ransac(K, pnp)
+                b.track_triangulate_promote(k, k + 1, K, Tb, 1.0)
+            a.track_triangulate_promote(k, k + 1, K, Ta, 1.0)
+            assert oka and okb and na == nb and np.array_equal(Ta, Tb), k
+            pend = (sq.feeds[k].copy(), Ta.copy()) if len(sq.feeds[k]) else None
+            ca, cb = a.counters(), b.counters()
+            for key in ("n_landmarks", "n_candidates", "n_promoted", "n_candidates_lost", "cf_alias"):
+                assert ca[key] == cb[key], (k, key)
+        Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+        assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+        for u, v in zip(a.get_candidates(), b.get_candidates()):
+            assert np.array_equal(u, v)
+    finally:
+        a.close(); b.close()
