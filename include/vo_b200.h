@@ -237,6 +237,24 @@ int vo_good_features_to_track(vo_ctx* ctx, int64_t frame_key, const uint8_t* mas
  * No synchronisation.  Call after the promotion step of the same frame. */
 int vo_detect_add_candidates_shi(vo_ctx* ctx, int64_t frame_key, const vo_gftt_params* params, const double T44[16]);
 
+/* ---- trajectory / map bookkeeping of main.py:239-255 and a headless top-down plot
+ * (main.py:262-271, :296-305) on the device.
+ * vo_map_accumulate: pos = (inv(T) @ [0,0,0,1])[0:3] is appended to the path (poses_plotting), and the
+ * landmark rows X with r_min < ||X - pos|| < r_max (reference: 3 and 50) to the map (X_plotting), in
+ * order.  T44 NULL = the pose the last PnP left on the device.  use_prev_state 1 = the landmarks the
+ * current frame STARTED from (main.py:248 reads vision.state, which is the previous iteration's), 0 =
+ * the current ones.  n_added NULL and T44 NULL: nothing synchronises. */
+int vo_map_reset(vo_ctx* ctx);
+int vo_map_accumulate(vo_ctx* ctx, const double T44[16], double r_min, double r_max, int use_prev_state, int* n_added);
+/* traj: n_traj x 3, pts: n_pts x 3 float64 (either may be NULL to query the counts), pos: last camera
+ * position.  Synchronises. */
+int vo_map_get(vo_ctx* ctx, double* traj, int traj_cap, int* n_traj, double* pts, int pts_cap, int* n_pts, double pos[3]);
+/* X-Z plot into bgr (h x w x 3 u8, host or device): white canvas, black box `margin` px inside the
+ * border, landmarks as blue discs of `radius` px, path as a red 3 px polyline on top; axis limits =
+ * data range + 5 % (matplotlib's default margins), returned in bounds = {xlo, xhi, zlo, zhi}.  No text
+ * (no font rasteriser).  Synchronises. */
+int vo_map_render(vo_ctx* ctx, uint8_t* bgr, int w, int h, int margin, int radius, double bounds[4]);
+
 /* One frame of main.py:216-284 with a single host synchronisation: upload (img may be NULL if
  * next_key is resident), KLT of P and C, PnP-RANSAC + LM + pruning, promotion, append of
  * new_candidates (n_new x 2 float64; the reference's detectors stay on the CPU). */

@@ -87,6 +87,10 @@ SIGNATURES = {
     "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
     "vo_klt_track_landmarks_add": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, _PI]),
+    "vo_map_reset": (c_int, [c_void_p]),
+    "vo_map_accumulate": (c_int, [c_void_p, c_void_p, c_double, c_double, c_int, _PI]),
+    "vo_map_get": (c_int, [c_void_p, c_void_p, c_int, _PI, c_void_p, c_int, _PI, c_void_p]),
+    "vo_map_render": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "vo_pnp_ransac_promote": (c_int, [c_void_p, c_void_p, _PP, c_double, c_void_p, _PI, _PI, _PI]),
     "vo_promote_commit": (c_int, [c_void_p]),
     "vo_promote_rollback": (c_int, [c_void_p]),
@@ -428,6 +432,37 @@ class Context:
             ctypes.byref(pnp) if pnp is not None else None, float(alpha_deg),
             _ptr(new_candidates) if nn else None, nn, _ptr(T), ctypes.byref(cnt) if cnt is not None else None))
         return T, (cnt.as_dict() if cnt is not None else None)
+
+    # ---- trajectory / map bookkeeping (main.py:239-255, :262-271) ---------------------
+    def map_reset(self):
+        self._check(self.lib.vo_map_reset(self.h))
+
+    def map_accumulate(self, T=None, r_min=3.0, r_max=50.0, use_prev_state=True, sync=False):
+        """Append the camera position of pose T (None: the device pose of the last PnP) to the path and the
+        landmarks with r_min < |X - pos| < r_max to the map; returns the rows added when sync=True."""
+        n = c_int()
+        Tc = None if T is None else np.ascontiguousarray(T, np.float64)
+        self._check(self.lib.vo_map_accumulate(self.h, None if Tc is None else _ptr(Tc), float(r_min), float(r_max),
+                                               int(bool(use_prev_state)), ctypes.byref(n) if sync else None))
+        return n.value if sync else None
+
+    def map_get(self):
+        """(path n x 3, landmarks m x 3, last camera position)"""
+        nt, npts = c_int(), c_int()
+        pos = np.zeros(3)
+        self._check(self.lib.vo_map_get(self.h, None, 0, ctypes.byref(nt), None, 0, ctypes.byref(npts), _ptr(pos)))
+        traj = np.empty((nt.value, 3), np.float64)
+        pts = np.empty((npts.value, 3), np.float64)
+        self._check(self.lib.vo_map_get(self.h, _ptr(traj), nt.value, ctypes.byref(nt), _ptr(pts), npts.value,
+                                        ctypes.byref(npts), _ptr(pos)))
+        return traj, pts, pos
+
+    def map_render(self, w=1200, h=600, margin=40, radius=3):
+        """Top-down X-Z plot as an (h, w, 3) BGR uint8 image (cv2.imwrite-ready) and its axis limits."""
+        img = np.empty((h, w, 3), np.uint8)
+        bounds = np.zeros(4)
+        self._check(self.lib.vo_map_render(self.h, _ptr(img), w, h, margin, radius, _ptr(bounds)))
+        return img, bounds
 
     def set_profiling(self, enable):
         self._check(self.lib.vo_set_profiling(self.h, int(enable)))

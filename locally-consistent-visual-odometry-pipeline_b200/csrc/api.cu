@@ -127,6 +127,7 @@ int vo_destroy(vo_ctx* c)
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->stream3) cudaStreamSynchronize(c->stream3);
+    map_free(c);
     pipeline_free(c);
     detector_free(c);
     for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); if (s.ready) cudaEventDestroy(s.ready); }

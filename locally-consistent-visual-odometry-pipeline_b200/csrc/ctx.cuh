@@ -120,6 +120,7 @@ struct Ctx {
     Detector det;
 
     struct Pipeline* pipe = nullptr;  // device-resident Markov state + PnP scratch
+    struct MapState* map = nullptr;   // trajectory / landmark map accumulated on the device (map.cu)
 };
 
 extern thread_local std::string g_create_error;
@@ -240,6 +241,7 @@ struct Pipeline {
     DevBuf<float> P[3];     // n x 2
     DevBuf<double> X[3];    // n x 3
     int n_land_upper = 0;   // host-known upper bound of n_land
+    int prev_n_upper = 0;   // same for the rows of the `prev` buffer
     // candidates, ping-pong
     int ccur = 0;
     DevBuf<float> C[2];     // n x 2 (current observation; float32-exact)
@@ -338,6 +340,8 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
 // d_n_new: optional device count (the rows actually appended are min(*d_n_new, n_new))
 int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new = nullptr,
                     bool on_side_stream = false);
+// map.cu
+void map_free(Ctx* c);
 // det.cu
 void gftt_defaults(vo_gftt_params* p);
 int detector_free(Ctx* c);

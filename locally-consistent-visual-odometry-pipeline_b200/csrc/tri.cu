@@ -417,6 +417,7 @@ int launch_landmark_compact(Ctx* c, int n_upper)
         p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }));
     c->launches++;
     p->prev = p->cur;
+    p->prev_n_upper = n_upper;
     p->cur = nxt;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;

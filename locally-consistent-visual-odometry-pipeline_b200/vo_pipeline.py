@@ -799,3 +799,36 @@ class FrameIngest:
                 prefetch_frame(nxt)
             yield cur
             cur = nxt
+
+
+# ---- trajectory / map bookkeeping on the device (main.py:239-255, :262-271, :296-305) ----
+class TrajectoryMap:
+    """poses_plotting / X_plotting of main.py kept on the device.  Instead of
+
+        pos = (np.linalg.inv(new_pose) @ pos_h)[0:3]; X = vision.state['X']      # D2H of all landmarks
+        X_plotting = np.vstack((X_plotting, X[(norm(X - pos) < 50) & (norm(X - pos) > 3)]))
+
+    every frame, call `tmap.update(new_pose)` right after estimatePose: one small kernel appends the camera
+    position and the filtered landmarks (the ones the frame started from, as main.py:248 reads them);
+    nothing comes back to the host until `arrays()` / `savefig()`."""
+
+    def __init__(self, r_min=3.0, r_max=50.0):
+        self.r_min, self.r_max = float(r_min), float(r_max)
+        _runtime().ctx.map_reset()
+
+    def update(self, new_pose=None):
+        """new_pose None: the pose the last estimatePose left on the device."""
+        _runtime().ctx.map_accumulate(new_pose, self.r_min, self.r_max, use_prev_state=True)
+
+    def arrays(self):
+        """(poses_plotting n x 3, X_plotting m x 3) as host arrays."""
+        traj, pts, _ = _runtime().ctx.map_get()
+        return traj, pts
+
+    def render(self, w=1200, h=600, margin=40, radius=3):
+        """The X-Z plot of main.py:262-271 as an (h, w, 3) BGR image: landmarks blue, travelled path red."""
+        return _runtime().ctx.map_render(w, h, margin, radius)[0]
+
+    def savefig(self, path, **kw):
+        VOInitializer._need_cv2()
+        cv2.imwrite(path, self.render(**kw))
