@@ -18,6 +18,11 @@ pre-generated feed sized so that landmarks + candidates stay at ~2000 KLT tracks
   cpu_baseline / --impl reference   the port of the reference's three methods over cv2
          (oracle/ref_pipeline.py) on the host cores, same frames, same feed
 
+Frame ingest: in both legs the frame of step k+1 is handed to the library during step k
+(vo_prefetch_frame / vo_pipeline.prefetch_frame): its copy and pyramid run on the ingest stream under step
+k's stages.  Every step still copies and builds exactly one frame inside the timed region;
+--no-prefetch restores the in-step upload.
+
 N > 1 (torchrun): one independent stream per GPU, no collective on the data path (weak scaling).
 """
 import argparse
