@@ -107,7 +107,7 @@ class ClockSampler(threading.Thread):
 
 
 def pick_feed(sq, k, n_land, n_cand):
-    want = int(np.clip(TARGET_TRACKS - n_land - n_cand, 0, FEED_MAX))
+    want = min(max(TARGET_TRACKS - n_land - n_cand, 0), FEED_MAX)
     return sq.feeds[k][:want]
 
 

@@ -100,6 +100,10 @@ int vo_upload_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, in
  * (its slot may still be read by it) and overlaps whatever is enqueued afterwards.  A pinned or
  * device `img` must stay untouched until a stage using frame_key has been synchronised. */
 int vo_prefetch_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t frame_key);
+/* The same, announced now and put on the ingest stream by the next pose call (vo_pnp_ransac[_promote])
+ * between its last launch and its wait - the ~20 us the enqueue costs on the host then hide under the
+ * GPU's PnP - or by the first call that asks for frame_key.  img must stay valid until then. */
+int vo_prefetch_frame_deferred(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t frame_key);
 int vo_has_frame(vo_ctx* ctx, int64_t frame_key);
 int vo_drop_frames(vo_ctx* ctx);
 /* test hook: copy pyramid level `level` of a resident frame (unpadded, w*h bytes) to the host;
@@ -164,6 +168,12 @@ int vo_klt_track_landmarks(vo_ctx* ctx, int64_t prev_key, int64_t next_key, cons
  * kernel sits between the caller and the landmark launch (the head of the chain the pose waits for). */
 int vo_klt_track_landmarks_add(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
                                const double* new_candidates, int n_new, const double T44[16], int* n_kept);
+/* Undo the last vo_klt_track_landmarks[_add], provided nothing but that tracking step has run since:
+ * the drop-in enqueues the tracking of a frame it was handed early (vo_prefetch_frame) right behind the
+ * previous frame's promotion, BEFORE associateKeypointsToLandmarks is called for it, and takes it back
+ * if that call then comes with other arguments.  P/X are again what the step started from; a folded
+ * append stays; the state vo_get_prev_state served before is gone. */
+int vo_track_rollback(vo_ctx* ctx);
 /* a3  PoseEstimator.estimatePose (vo_pipeline.py:245-335): PnP-RANSAC + LM refit, prunes P/X to
  * the inliers (vo_pipeline.py:327-331), T44 = 4x4 row-major world->camera (vo_pipeline.py:333).
  * ok=0 (no model / n<4) leaves the state untouched: the caller takes the re-bootstrap branch of

@@ -69,6 +69,7 @@ SIGNATURES = {
     "vo_free_pinned": (c_int, [c_void_p]),
     "vo_upload_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64]),
     "vo_prefetch_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64]),
+    "vo_prefetch_frame_deferred": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64]),
     "vo_has_frame": (c_int, [c_void_p, c_i64]),
     "vo_drop_frames": (c_int, [c_void_p]),
     "vo_get_pyramid_level": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p,
@@ -87,6 +88,7 @@ SIGNATURES = {
     "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
     "vo_klt_track_landmarks_add": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, _PI]),
+    "vo_track_rollback": (c_int, [c_void_p]),
     "vo_map_reset": (c_int, [c_void_p]),
     "vo_map_accumulate": (c_int, [c_void_p, c_void_p, c_double, c_double, c_int, _PI]),
     "vo_map_get": (c_int, [c_void_p, c_void_p, c_int, _PI, c_void_p, c_int, _PI, c_void_p]),
@@ -233,12 +235,15 @@ class Context:
         h, w = img.shape
         self._check(self.lib.vo_upload_frame(self.h, c_void_p(img.ctypes.data), w, h, img.strides[0], key))
 
-    def prefetch_frame(self, img, key):
-        """vo_prefetch_frame: upload + pyramid on the ingest stream (overlaps the stages enqueued after it)."""
+    def prefetch_frame(self, img, key, deferred=False):
+        """vo_prefetch_frame: upload + pyramid on the ingest stream (overlaps the stages enqueued after it).
+        deferred=True: enqueued by the next pose call, under the GPU's PnP (vo_prefetch_frame_deferred);
+        the caller keeps `img` alive until then."""
         if img.dtype != np.uint8 or img.ndim != 2 or img.strides[1] != 1:
             raise ValueError("frames must be 2-D uint8 arrays with contiguous rows")
         h, w = img.shape
-        self._check(self.lib.vo_prefetch_frame(self.h, c_void_p(img.ctypes.data), w, h, img.strides[0], key))
+        fn = self.lib.vo_prefetch_frame_deferred if deferred else self.lib.vo_prefetch_frame
+        self._check(fn(self.h, c_void_p(img.ctypes.data), w, h, img.strides[0], key))
 
     def has_frame(self, key):
         return bool(self.lib.vo_has_frame(self.h, key))
@@ -365,6 +370,9 @@ class Context:
                                                    float(alpha_deg), _ptr(T), ctypes.byref(ninl), ctypes.byref(ok),
                                                    None if early else ctypes.byref(nprom)))
         return bool(ok.value), T, ninl.value, (None if early else nprom.value)
+
+    def track_rollback(self):
+        self._check(self.lib.vo_track_rollback(self.h))
 
     def promote_commit(self):
         self._check(self.lib.vo_promote_commit(self.h))

@@ -21,6 +21,7 @@ int set_error(Ctx* c, int code, const char* fmt, ...)
 
 static FrameSlot* find_slot(Ctx* c, int64_t key)
 {
+    if (c->hint.set && c->hint.key == key) flush_frame_hint(c);
     for (auto& s : c->slots)
         if (s.valid && s.key == key) {
             s.stamp = ++c->clock;
@@ -46,7 +47,7 @@ int join_side_stream(Ctx* c)
 
 int close_step(Ctx* c)
 {
-    VO_CUDA(c, cudaEventRecord(c->ev_step_end, c->stream));
+    VO_CUDA(c, cudaEventRecord(c->ev_step_end[c->step_id & 3], c->stream));
     c->step_id++; c->open_uses = 0;
     return VO_OK;
 }
@@ -104,7 +105,10 @@ int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_ingest_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->ev_step_end, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_step_end[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_step_end[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_step_end[2], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_step_end[3], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_join, cudaEventDisableTiming) != cudaSuccess) {
         delete c;
@@ -137,7 +141,7 @@ int vo_destroy(vo_ctx* c)
     cudaFreeHost(c->pinned_stage2);
     if (c->stream3) cudaStreamDestroy(c->stream3);
     if (c->ev_ingest_fork) cudaEventDestroy(c->ev_ingest_fork);
-    if (c->ev_step_end) cudaEventDestroy(c->ev_step_end);
+    for (auto& e : c->ev_step_end) if (e) cudaEventDestroy(e);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->ev_fork) cudaEventDestroy(c->ev_fork);
@@ -151,6 +155,7 @@ const char* vo_last_error(vo_ctx* c) { return c ? c->err.c_str() : g_create_erro
 int vo_synchronize(vo_ctx* c)
 {
     if (!c) return VO_ERR_INVALID;
+    VO_TRY(flush_frame_hint(c));
     VO_TRY(join_side_stream(c));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     VO_CUDA(c, cudaStreamSynchronize(c->stream3));
@@ -176,6 +181,7 @@ int vo_free_pinned(void* p)
 int vo_has_frame(vo_ctx* c, int64_t key)
 {
     if (!c) return 0;
+    if (c->hint.set && c->hint.key == key) flush_frame_hint(c);
     for (auto& s : c->slots) if (s.valid && s.key == key) return 1;
     return 0;
 }
@@ -183,13 +189,16 @@ int vo_has_frame(vo_ctx* c, int64_t key)
 int vo_drop_frames(vo_ctx* c)
 {
     if (!c) return VO_ERR_INVALID;
+    c->hint.set = false;
     VO_TRY(join_side_stream(c));
     for (auto& s : c->slots) s.valid = false;
     return VO_OK;
 }
 
+}  // extern "C"
+
 // Upload + pyramid of one frame on `st` (the main stream, or the ingest stream for a prefetch).
-static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key, bool ingest)
+static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key, bool ingest, bool overlap = false)
 {
     if (!c || !img) return VO_ERR_INVALID;
     if (w <= 0 || h <= 0 || w > c->max_w || h > c->max_h || pitch < w)
@@ -217,8 +226,11 @@ static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, i
         // readers belong to a closed step: wait for that step's end only, so the ingest runs UNDER the
         // current frame's stages.  Otherwise order it behind everything enqueued so far (stages enqueued
         // after this call then overlap it).
-        if (c->open_uses > 0 && s->use_step < c->step_id) {
-            VO_CUDA(c, cudaStreamWaitEvent(st, c->ev_step_end, 0));
+        // (`overlap`: called from inside a pose call, whose kernels - this frame's last - are on the stream.)
+        // The event of the step that last used the slot; a ring entry reused since belongs to a later
+        // step, which is only more conservative.
+        if ((c->open_uses > 0 || overlap) && s->use_step < c->step_id) {
+            VO_CUDA(c, cudaStreamWaitEvent(st, c->ev_step_end[s->use_step & 3], 0));
         } else {
             VO_CUDA(c, cudaEventRecord(c->ev_ingest_fork, c->stream));
             VO_CUDA(c, cudaStreamWaitEvent(st, c->ev_ingest_fork, 0));
@@ -265,6 +277,18 @@ static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, i
     return VO_OK;
 }
 
+namespace vo {
+int flush_frame_hint(Ctx* c, bool under_current_stages)
+{
+    if (!c->hint.set) return VO_OK;
+    c->hint.set = false;
+    return upload_impl(static_cast<vo_ctx*>(c), c->hint.img, c->hint.w, c->hint.h, c->hint.pitch, c->hint.key, true,
+                       under_current_stages);
+}
+}  // namespace vo
+
+extern "C" {
+
 int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
 {
     return upload_impl(c, img, w, h, pitch, key, false);
@@ -275,7 +299,22 @@ int vo_upload_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int6
 // on the device (no host synchronisation anywhere).
 int vo_prefetch_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
 {
+    if (c && c->hint.set) VO_TRY(flush_frame_hint(c));
     return upload_impl(c, img, w, h, pitch, key, true);
+}
+
+// The same, announced now and enqueued by the next pose call (vo_pnp_ransac / vo_pnp_ransac_promote)
+// between its last kernel launch and its wait for the pose - the host-side cost of the enqueue (~20 us)
+// then hides under the GPU's PnP - or earlier, by the first call that asks for frame_key.  img must
+// stay valid and unchanged until then (and, as for vo_prefetch_frame, until the copy has run).
+int vo_prefetch_frame_deferred(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key)
+{
+    if (!c || !img) return VO_ERR_INVALID;
+    if (w <= 0 || h <= 0 || w > c->max_w || h > c->max_h || pitch < w)
+        return set_error(c, VO_ERR_INVALID, "frame %dx%d (pitch %d) outside ctx limits %dx%d", w, h, pitch, c->max_w, c->max_h);
+    if (c->hint.set) VO_TRY(flush_frame_hint(c));
+    c->hint.set = true; c->hint.img = img; c->hint.w = w; c->hint.h = h; c->hint.pitch = pitch; c->hint.key = key;
+    return VO_OK;
 }
 
 int vo_get_pyramid_level(vo_ctx* c, int64_t key, int level, uint8_t* img, int16_t* deriv, int* w, int* h)

@@ -95,10 +95,13 @@ struct Ctx {
     uint64_t ingest_seq = 0;
     // A "step" closes when the promotion stage has been enqueued (it joins the side stream): from then
     // on no kernel of that step reads a frame slot, and ev_step_end (main stream) marks the point.
-    cudaEvent_t ev_step_end = nullptr;
+    cudaEvent_t ev_step_end[4] = {};   // ring: closing step S records ev_step_end[S & 3]
     uint64_t step_id = 1;        // id of the open step
     int open_uses = 0;           // slot look-ups in the open step
     uint8_t* pinned_stage2 = nullptr;   // pageable sources of the ingest stream are staged here
+    // a frame announced with vo_prefetch_frame_deferred: put on the ingest stream by the next pose call,
+    // between its enqueue and its wait (or by whoever asks for the key first)
+    struct { bool set = false; const uint8_t* img = nullptr; int w = 0, h = 0, pitch = 0; int64_t key = 0; } hint;
     int max_w = 0, max_h = 0;
     int sm_count = 148;
     std::string err;
@@ -282,6 +285,9 @@ struct Pipeline {
     bool mask_src_valid = false; int mask_src_off = 0;
     // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
     bool spec_pending = false;
+    // host-side values before the last tracking step (vo_track_rollback)
+    bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0;
+    double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
     cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion
     int64_t spec_prev_key = -1, spec_next_key = -1;
     DevScalars* d_sc = nullptr;
@@ -306,6 +312,8 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
                 const vo_klt_params& prm, cudaStream_t st = nullptr);
 // make `stream` wait for the work in flight on the side stream (no-op if there is none)
 int join_side_stream(Ctx* c);
+// put a deferred frame hint on the ingest stream now (no-op if there is none)
+int flush_frame_hint(Ctx* c, bool under_current_stages = false);
 // the promotion stage of a frame has been enqueued: close the step (see Ctx::ev_step_end)
 int close_step(Ctx* c);
 

@@ -2,6 +2,8 @@
 // stages of /root/reference/src/main.py:229-284 (associate -> estimatePose -> triangulate_landmark),
 // plus unit-level entry points that mirror the cv2 signatures for differential tests.
 #include <math.h>
+#include <stdlib.h>
+#include <time.h>
 #include "ctx.cuh"
 #include "pnp_sets.cuh"
 
@@ -369,7 +371,9 @@ static int track_landmarks_impl(vo_ctx* c, int64_t prev_key, int64_t next_key, c
     // their tracking does not depend on the pose
     VO_TRY(track_both(c, a, b, prm, true, add));
     p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
+    p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
     VO_TRY(launch_landmark_compact(c, p->n_land_upper));
+    p->rb_valid = true;
     p->packed_valid = true;
     if (n_kept) { VO_TRY(join_side_stream(c)); VO_TRY(read_scalars(c)); *n_kept = p->h_sc->n_land; }
     return VO_OK;
@@ -389,6 +393,29 @@ int vo_klt_track_landmarks_add(vo_ctx* c, int64_t prev_key, int64_t next_key, co
     if (n_new < 0 || (n_new > 0 && (!new_candidates || !T44))) return VO_ERR_INVALID;
     DeferredAdd add{ new_candidates, n_new, T44 };
     return track_landmarks_impl(c, prev_key, next_key, params, n_new > 0 ? &add : nullptr, n_kept);
+}
+
+__global__ void track_rollback_kernel(DevScalars* sc)
+{
+    sc->n_land = sc->prev_n_land; sc->n_tracked = 0; sc->n_lost = 0;
+}
+
+// Undo the last vo_klt_track_landmarks[_add] (nothing but the tracking step may have run since): the
+// landmarks are again the ones it started from - the compaction wrote into another buffer of the
+// rotation - and the candidates' pending KLT result is dropped.  A folded append stays (it is not part
+// of the tracking).  The state before the PREVIOUS tracking step (vo_get_prev_state) is gone.
+int vo_track_rollback(vo_ctx* c)
+{
+    VO_NEED(c);
+    Pipeline* p = c->pipe;
+    if (!p->rb_valid || !p->packed_valid) return set_error(c, VO_ERR_STATE, "no tracking step to undo");
+    VO_TRY(join_side_stream(c));
+    track_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
+    c->launches++;
+    VO_CUDA(c, cudaGetLastError());
+    p->cur = p->rb_cur; p->prev = -1; p->prev_n_upper = 0; p->n_land_upper = p->rb_n_land_upper;
+    p->rb_valid = false; p->packed_valid = false; p->cand_tracked_valid = false;
+    return VO_OK;
 }
 
 // ---- a3: PoseEstimator.estimatePose (vo_pipeline.py:245-335); synchronises
@@ -413,6 +440,7 @@ int vo_pnp_ransac(vo_ctx* c, const double K[9], const vo_pnp_params* params, dou
     memcpy(L.K, K, sizeof(L.K));
     VO_TRY(launch_pnp(c, L));
     p->packed_valid = false;
+    VO_TRY(flush_frame_hint(c, true));   // the next frame's ingest: enqueued while the GPU runs the PnP
     VO_TRY(read_scalars(c));
     VO_TRY(check_rng(c));
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
@@ -485,7 +513,21 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     VO_TRY(close_step(c));
     p->cand_tracked_valid = false;
     p->spec_pending = true;
+    VO_TRY(flush_frame_hint(c, true));   // the next frame's ingest: enqueued while the GPU runs the PnP
     if (early) {
+        static const bool trace = getenv("VO_TRACE") != nullptr;
+        if (trace) {   // host time blocked on the pose (tools/profile_e2e.py)
+            timespec t0, t1;
+            clock_gettime(CLOCK_MONOTONIC, &t0);
+            const bool ready = cudaEventQuery(p->ev_pose) == cudaSuccess;
+            cudaEventSynchronize(p->ev_pose);
+            clock_gettime(CLOCK_MONOTONIC, &t1);
+            p->trace_wait_us += (t1.tv_sec - t0.tv_sec) * 1e6 + (t1.tv_nsec - t0.tv_nsec) * 1e-3;
+            p->trace_ready += ready; p->trace_n++;
+            if (p->trace_n % 100 == 0)
+                fprintf(stderr, "[vo trace] pose wait %.1f us/frame, pose already there %d/%d\n", p->trace_wait_us / p->trace_n,
+                        p->trace_ready, p->trace_n);
+        }
         VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
         DevScalars* s = p->h_sc;   // values BEFORE the promotion step: bounds stay upper bounds
         p->n_land_upper = s->n_land + ncand_before;

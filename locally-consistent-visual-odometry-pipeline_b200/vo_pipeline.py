@@ -70,6 +70,7 @@ _DEFAULTS = {
     'klt_fb_check': False,       # the reference has no forward-backward check
     'klt_fb_thresh': 1.0,
     'speculative_promotion': True,   # enqueue the promotion step ahead of estimatePose's sync
+    'speculative_tracking': True,    # track into a frame handed over early right behind the promotion step
     'emulate_cf_alias': True,    # reference quirk App. B-5 (first candidate batch: F follows C)
     'device': 0,
     'gpu_detector': True,        # find_new_candidates_shi on the device (csrc/det.cu); False: cv2 on the CPU
@@ -98,6 +99,8 @@ class _Runtime:
         self.pair = None          # (old_frame, new_frame, k_old, k_new) of the last associate call
         self.pending_add = None   # (points, pose) of a deferred vo_add_candidates
         self.spec = None          # assumptions of a pending speculative promotion
+        self.spec_track = None    # assumptions of a tracking step enqueued ahead of its associate call
+        self.last_prefetch = None # (key, frame, fingerprint) of the newest frame on the ingest stream
 
     # frames arrive as host uint8 arrays; the same object is passed to several stages and then
     # becomes the "old" frame of the next iteration (main.py:293), so upload + pyramid happen once
@@ -114,6 +117,8 @@ class _Runtime:
         if self.hint is not None and self.hint.__array_interface__['data'][0] == fp[1]:
             self.hint = None      # needed right now: nothing left to hide the ingest under
         pre = self.prefetched.pop(fp[1], None) if self.prefetched else None
+        if pre is not None and self.last_prefetch is not None and pre[0] == self.last_prefetch[0]:
+            self.last_prefetch = None
         if pre is not None and pre[2] == fp and self.ctx.has_frame(pre[0]):
             key = pre[0]          # handed over early by prefetch_frame: already on its way / resident
         else:
@@ -134,7 +139,7 @@ class _Runtime:
             raise ValueError("frames must be 2-D uint8 (cv2.IMREAD_GRAYSCALE) arrays with contiguous rows")
         self.hint = img
 
-    def issue_hint(self):
+    def issue_hint(self, deferred=False):
         img = self.hint
         if img is None:
             return
@@ -142,10 +147,17 @@ class _Runtime:
         fp = (img.shape, img.__array_interface__['data'][0], zlib.adler32(img[img.shape[0] >> 1]))
         key = self.next_key
         self.next_key += 1
-        self.ctx.prefetch_frame(img, key)
+        self.ctx.prefetch_frame(img, key, deferred=deferred)   # (self.prefetched keeps img alive)
         if len(self.prefetched) >= 2:    # hints that were never used
             self.prefetched.pop(next(iter(self.prefetched)))
         self.prefetched[fp[1]] = (key, img, fp)
+        self.last_prefetch = (key, img, fp)
+
+    def drop_spec_track(self):
+        """Take back a tracking step that was enqueued ahead of an associate call that never came."""
+        if self.spec_track is not None:
+            self.spec_track = None
+            self.ctx.track_rollback()
 
     def pair_keys(self, old_frame, new_frame):
         """Keys of a frame pair; the pair the last associate call saw is recognised by identity."""
@@ -203,7 +215,10 @@ class DeviceState(dict):
 
     def _load(self):
         if not dict.__contains__(self, 'P'):
-            if self._current():
+            st = self._rt.spec_track
+            if st is not None and st['state'] is self and self._current():
+                P, X = self._rt.ctx.get_prev_state()   # the device is one tracking step ahead of this dict
+            elif self._current():
                 P, X = self._rt.ctx.get_state()
                 lim = getattr(self, '_limit', None)
                 if lim is not None and self._rt.spec is not None:   # speculatively promoted rows are not visible yet
@@ -413,6 +428,29 @@ class KeypointsToLandmarksAssociator():
         with new_state = rows of P (new positions, float32) and X whose status is 1."""
         rt = _runtime(new_frame)
         rt.drop_speculation()      # estimatePose without a matching triangulate_landmark
+        st = rt.spec_track
+        if st is not None:
+            # triangulate_landmark already enqueued this very tracking step behind its promotion (the frame
+            # had been handed over early): if the arguments are the ones it assumed, there is nothing to do
+            rt.spec_track = None
+            fp = (new_frame.shape, new_frame.__array_interface__['data'][0], zlib.adler32(new_frame[new_frame.shape[0] >> 1])) \
+                if new_frame.ndim == 2 and new_frame.dtype == np.uint8 and new_frame.strides[1] == 1 else None
+            if (st['old'] is old_frame and fp == st['fp'] and state is st['state'] and state._current()
+                    and rt.ctx.has_frame(st['k_new'])):
+                rt.prefetched.pop(fp[1], None)
+                rt.last_prefetch = None
+                rt.frames[id(new_frame)] = (st['k_new'], new_frame, fp)
+                if len(rt.frames) > 3:
+                    fr = rt.frames
+                    del fr[min(fr, key=lambda i: fr[i][0])]
+                rt.pair = (old_frame, new_frame, st['k_old'], st['k_new'])
+                rt.prev_token += 1
+                if not dict.__contains__(state, 'P'):
+                    state._prev = rt.prev_token
+                rt.issue_hint(deferred=True)   # goes out under the coming PnP
+                rt.state_version += 1
+                return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
+            rt.ctx.track_rollback()
         pr = rt.pair
         if pr is not None and pr[1] is old_frame and rt.ctx.has_frame(pr[3]):
             k_old = pr[3]          # main.py:293 (img1 = img2): the frame tracked INTO last time, as uploaded then
@@ -432,7 +470,7 @@ class KeypointsToLandmarksAssociator():
             # the third landmark buffer keeps it until the next tracking step
             state._prev = rt.prev_token
         rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt, add=add)
-        rt.issue_hint()            # next frame's ingest: under this frame's tracking and PnP
+        rt.issue_hint(deferred=True)   # next frame's ingest: enqueued by the pose call, under the GPU's PnP
         rt.state_version += 1
         return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
 
@@ -499,7 +537,8 @@ class PoseEstimator():
         place and returns the 4x4 world->camera pose (host ndarray: main.py:239 inverts it)."""
         rt = _runtime()
         rt.drop_speculation()
-        rt.issue_hint()
+        rt.drop_spec_track()
+        rt.issue_hint(deferred=True)
         uploaded = not (isinstance(associations, DeviceState) and associations._current())
         _sync_state_to_device(rt, associations)
         # The promotion step of triangulate_landmark does not need the host: enqueue it ahead of the
@@ -626,6 +665,7 @@ class LandmarkTriangulator():
         with (T, new_pose), append it to state P/X and remove it from C/F/T.
         Returns (state, extended_state, cur_des)."""
         rt = _runtime(new_frame)
+        rt.drop_spec_track()
         method = config['find_new_candidates_method']
         threshold = _alpha_threshold()
         new_pose = np.ascontiguousarray(new_pose, np.float64)
@@ -671,7 +711,7 @@ class LandmarkTriangulator():
         if device_shi:
             # vo_pipeline.py:381 + :574-591 in one enqueue: corners masked at the previous positions of
             # the candidates KLT kept, appended with T = new_pose; nothing returns to the host
-            rt.ctx.detect_add_candidates_shi(rt.pair[3] if confirmed else k_new, T=np.eye(4) @ new_pose)
+            rt.ctx.detect_add_candidates_shi(rt.pair[3] if confirmed else k_new, T=new_pose.copy())
         elif method == 'shi-mask':
             new_candidates_list = self.find_new_candidates_shi(new_frame, state, well_tracked_prev)
         elif method == 'sift-mask':
@@ -682,7 +722,7 @@ class LandmarkTriangulator():
             new_candidates_list = _candidate_feed.pop(0) if _candidate_feed else []
         if len(new_candidates_list) > 0:
             # appended on the device when the next frame has been uploaded (or when someone looks)
-            rt.pending_add = (np.array(new_candidates_list, np.float64), np.eye(4) @ new_pose)
+            rt.pending_add = (np.array(new_candidates_list, np.float64), new_pose.copy())   # T = eye(4) @ new_pose (vo:582)
 
         rt.state_version += 1
         rt.ext_version += 1
@@ -694,6 +734,16 @@ class LandmarkTriangulator():
             extended_state._rebind(rt.ext_version)
         else:
             extended_state = DeviceExtendedState(rt, rt.ext_version)
+        # The next frame is already on the ingest stream (prefetch_frame / FrameIngest): enqueue its
+        # tracking now, right behind the promotion step, instead of leaving the GPU idle until main.py
+        # comes round to associateKeypointsToLandmarks - which then finds the work done, or takes it back
+        # (vo_track_rollback) if it is called with anything else than (new_frame, that frame, this state).
+        pre = rt.last_prefetch
+        if (confirmed and pre is not None and bool(_cfg('speculative_tracking'))
+                and (method == 'feed' or device_shi) and rt.ctx.has_frame(pre[0])):
+            add, rt.pending_add = rt.pending_add, None
+            rt.ctx.klt_track_landmarks(rt.pair[3], pre[0], rt.klt, add=add)
+            rt.spec_track = {'old': new_frame, 'fp': pre[2], 'k_old': rt.pair[3], 'k_new': pre[0], 'state': state}
         return (state, extended_state, cur_des)
 
 

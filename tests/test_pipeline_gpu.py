@@ -453,3 +453,85 @@ def test_track_with_folded_append_equals_add_then_track(pkg, scene_mod):
             assert np.array_equal(u, v)
     finally:
         a.close(); b.close()
+
+
+def test_track_rollback_restores_the_tracking_input(pkg, scene_mod):
+    """vo_track_rollback: after tracking into a wrong frame and taking it back, the run continues bit for
+    bit like one that never did (landmarks, candidates incl. a folded append, poses)."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    K = sq.K
+    pnp = pkg.pnp_defaults()
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)
+    try:
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        pend = None
+        for k in range(1, 10):
+            for c in (a, b):
+                c.upload_frame(sq.frames[k], k + 1)
+            a.klt_track_landmarks(k, k + 1, add=pend)
+            if k % 2:
+                b.upload_frame(sq.frames[k + 2], 500 + k)
+                b.klt_track_landmarks(k, 500 + k, add=pend)       # wrong target frame
+                Pw, Xw = b.get_state()                            # (synchronises: the wrong step really ran)
+                b.track_rollback()
+                P0, X0 = b.get_state()
+                assert len(P0) >= len(Pw)
+                b.klt_track_landmarks(k, k + 1)                   # the append stays: not repeated
+            else:
+                b.klt_track_landmarks(k, k + 1, add=pend)
+            oka, Ta, na = a.pnp_ransac(K, pnp)
+            okb, Tb, nb = b.pnp_ransac(K, pnp)
+            assert oka and okb and na == nb and np.array_equal(Ta, Tb), k
+            for c in (a, b):
+                c.track_triangulate_promote(k, k + 1, K, Ta, 1.0)
+            pend = (sq.feeds[k].copy(), Ta.copy()) if len(sq.feeds[k]) else None
+            Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+            assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+            for u, v in zip(a.get_candidates(), b.get_candidates()):
+                assert np.array_equal(u, v)
+        with pytest.raises(pkg.VoError):
+            b.track_rollback()                                    # nothing to undo after a PnP
+    finally:
+        a.close(); b.close()
+
+
+def test_dropin_speculative_tracking_hit_and_miss(dropin, scene_mod):
+    """Frames hinted one iteration ahead: triangulate_landmark enqueues the next tracking step itself.
+    Right hints (consumed) and wrong hints (rolled back) both reproduce the plain drive's poses exactly,
+    and the state dict handed back in between still reads as the pre-tracking landmarks."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    Ts0, nP0, nC0, _ = drive_dropin(dropin, sq, read_prev_state=False)
+    for wrong_every in (0, 3):
+        dropin._reset_runtime()
+        vo = dropin
+        vo.set_candidate_feed([f.copy() for f in sq.feeds[1:]])
+        vision = vo.BestVision(sq.K)
+        vision.state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+        vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+        associate = vo.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+        pose_estimator = vo.PoseEstimator(sq.K)
+        Ts, hits = [], 0
+        img1 = sq.frames[0]
+        n = len(sq.frames)
+        for k in range(1, n):
+            img2 = sq.frames[k]
+            nxt = k + 1 if not (wrong_every and k % wrong_every == 0) else k + 2
+            if nxt < n:
+                vo.prefetch_frame(sq.frames[nxt])
+            hits += vo._runtime().spec_track is not None
+            new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
+            new_pose = pose_estimator.estimatePose(new_state, k)
+            tri = vo.LandmarkTriangulator(sq.K, None)
+            vision.state, vision.extended_state, _ = tri.triangulate_landmark(img1, img2, new_state, vision.extended_state, new_pose)
+            if k == 4:      # read the returned state while the next tracking step is already enqueued
+                assert vo._runtime().spec_track is not None
+                n_now = len(vision.state["X"])
+                assert n_now == len(vision.state["P"]) and n_now >= vo._runtime().ctx.counters()["n_landmarks"]
+            img1 = img2
+            Ts.append(new_pose)
+        assert np.array_equal(np.array(Ts), Ts0), wrong_every
+        assert hits >= n - 4
