@@ -9,9 +9,10 @@ A step is one frame through the whole hot path: KLT of landmarks and candidates 
 synthetic (ray-cast corridor, 1241x376, known trajectory); the candidate detector is replaced by a
 pre-generated feed sized so that landmarks + candidates stay at ~2000 KLT tracks per frame.
 
-  value  frames/s, frames and candidate feed already resident in HBM, vo_process_frame per step
-         (one host sync per frame for the pose), CUDA events per step on the ctx stream, L2 flushed
-         between steps outside the events
+  value  frames/s, frames and candidate feed already resident in HBM, vo_process_frame_pipelined per
+         step (the host waits for each frame's pose; the tracking of the next, already ingested frame is
+         enqueued behind the current frame's promotion), CUDA events per step on the ctx stream, L2
+         flushed between steps outside the events
   e2e    frames/s through the drop-in vo_pipeline classes in main.py's order, frames in pinned
          HOST memory (H2D every step), pose read back every step; wall clock between syncs
   roofline   the KLT kernel (dominant launch): algorithmic bytes per launch / its CUDA-event time
@@ -173,6 +174,8 @@ def run_gpu(args, rank, world, local_rank):
         ctx.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
         return len(sq.P0), 0
 
+    profiling = [False]
+
     def dev_step(s, order, n_land, n_cand):
         b = order[s + 1]
         if args.prefetch:
@@ -184,13 +187,18 @@ def run_gpu(args, rank, world, local_rank):
         want = int(np.clip(TARGET_TRACKS - n_land - n_cand, 0, FEED_MAX))
         fd = d_feeds[b]
         want = 0 if fd is None else min(want, fd.shape[0])
-        r = lib.vo_process_frame(hnd, ctypes.c_void_p(d_frames[b].data_ptr()), w, h, w, s + 1, s + 2, Kc.ctypes.data,
+        step_fn = lib.vo_process_frame_pipelined if (args.prefetch and not profiling[0]) else lib.vo_process_frame
+        r = step_fn(hnd, ctypes.c_void_p(d_frames[b].data_ptr()), w, h, w, s + 1, s + 2, Kc.ctypes.data,
                                  ctypes.byref(klt), ctypes.byref(pnp), ALPHA,
                                  ctypes.c_void_p(fd.data_ptr()) if want else None, want, T44.ctypes.data, ctypes.byref(cnt))
         if r != 0:
             raise RuntimeError(lib.vo_last_error(hnd).decode())
         if not cnt.pnp_ok:
             raise RuntimeError("PnP failed at step %d" % s)
+        if step_fn is lib.vo_process_frame_pipelined:
+            # counts as of the pose read-back (before this frame's promotion and append): the same
+            # bookkeeping as the e2e loop uses
+            return cnt.n_landmarks, cnt.n_candidates + want
         return cnt.n_landmarks, cnt.n_candidates
 
     # ---- value: device-resident inputs, per-step CUDA events, L2 flush between steps -------------------
@@ -233,6 +241,7 @@ def run_gpu(args, rank, world, local_rank):
     # ---- roofline leg: stage timers (CUDA events inside the library) over the same steps ---------------
     n_land, n_cand = reset_state()
     ctx.set_profiling(False)
+    profiling[0] = True    # stage timers bracket the stages of one frame: frames are not overlapped in this leg
     prof_tracks, prof_iters_land, prof_land, prof_iters_cand, prof_cand = 0, 0, 0, 0, 0
     for s in range(steps + warmup):
         if s == warmup:
@@ -434,7 +443,7 @@ def main():
     line.update({
         "value": fps, "ms_per_step": total_ms / args.steps, "dtype": "u8/i32 (KLT), f64 (P3P, projection, DLT), f32 (inlier test)",
         "e2e": {"value": e2e_job_fps, "unit": "frames/s", "h2d_bytes_per_step": r["e2e"]["h2d"], "d2h_bytes_per_step": r["e2e"]["d2h"]},
-        "gpu_launches": int(r["launches"]), "klt_tracks_per_s": r["tracks_per_step"] * fps,
+        "gpu_launches": int(r["launches"]), "klt_tracks_per_s": r["prof_tracks_per_step"] * fps,
         "clocks": r["clocks"],
         "roofline": {"bound": "hbm", "kernel": "klt_track_kernel<21> (candidates' launch, side stream)", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,

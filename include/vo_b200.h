@@ -272,6 +272,16 @@ int vo_process_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, i
                      const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
                      const double* new_candidates, int n_new, double T44[16], vo_counters* counters);
 
+/* The same with the frames overlapped: the host waits for the pose only, so `counters` holds the counts
+ * as they were BEFORE this frame's promotion and append (n_promoted = 0), and if a frame has been handed
+ * over with vo_prefetch_frame since the last call, the tracking step (next_key -> that frame) is enqueued
+ * right behind the append.  The next call for that frame pair finds it done; any other call takes it
+ * back (vo_track_rollback).  With the stage timers on it behaves like vo_process_frame. */
+int vo_process_frame_pipelined(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t prev_key,
+                               int64_t next_key, const double K[9], const vo_klt_params* kparams,
+                               const vo_pnp_params* pparams, double alpha_deg, const double* new_candidates, int n_new,
+                               double T44[16], vo_counters* counters);
+
 /* Stage timers of vo_process_frame (CUDA events on the ctx stream; bench.py's roofline leg).
  * ms[6] = {upload+pyramid, landmark KLT, landmark compaction, PnP-RANSAC+LM, promotion+append (incl.
  * the wait for the candidates' KLT), candidates' KLT on the side stream (overlaps stages 1-3)} summed

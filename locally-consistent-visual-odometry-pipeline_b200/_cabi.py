@@ -105,6 +105,8 @@ SIGNATURES = {
     "vo_get_candidate_tracks": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_process_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64, c_i64, c_void_p, _PK, _PP,
                                  c_double, c_void_p, c_int, c_void_p, ctypes.POINTER(Counters)]),
+    "vo_process_frame_pipelined": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64, c_i64, c_void_p, _PK, _PP,
+                                 c_double, c_void_p, c_int, c_void_p, ctypes.POINTER(Counters)]),
     "vo_set_profiling": (c_int, [c_void_p, c_int]),
     "vo_get_stage_times": (c_int, [c_void_p, c_void_p, _PI]),
     "vo_solve_pnp_ransac": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
@@ -422,7 +424,7 @@ class Context:
         self._check(self.lib.vo_add_candidates(self.h, _ptr(pts), len(pts), _ptr(T44)))
 
     def process_frame(self, img, prev_key, next_key, K, alpha_deg, new_candidates=None, klt=None, pnp=None,
-                      want_counters=True):
+                      want_counters=True, pipelined=False):
         K = np.ascontiguousarray(K, np.float64)
         T = np.empty((4, 4), np.float64)
         cnt = Counters() if want_counters else None
@@ -435,7 +437,8 @@ class Context:
         else:
             h = w = pitch = 0
             ip = None
-        self._check(self.lib.vo_process_frame(
+        fn = self.lib.vo_process_frame_pipelined if pipelined else self.lib.vo_process_frame
+        self._check(fn(
             self.h, ip, w, h, pitch, prev_key, next_key, _ptr(K), ctypes.byref(klt) if klt is not None else None,
             ctypes.byref(pnp) if pnp is not None else None, float(alpha_deg),
             _ptr(new_candidates) if nn else None, nn, _ptr(T), ctypes.byref(cnt) if cnt is not None else None))

@@ -28,6 +28,7 @@ static FrameSlot* find_slot(Ctx* c, int64_t key)
             s.use_step = c->step_id; c->open_uses++;
             if (s.pending) {   // filled by the ingest stream: everything enqueued from here on waits for it
                 s.pending = false;
+                if (c->last_ingest_valid && c->last_ingest_key == key) c->last_ingest_valid = false;
                 if (cudaStreamWaitEvent(c->stream, s.ready, 0) != cudaSuccess) return nullptr;
             }
             return &s;
@@ -272,6 +273,7 @@ static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, i
         if (!s->ready) VO_CUDA(c, cudaEventCreateWithFlags(&s->ready, cudaEventDisableTiming));
         VO_CUDA(c, cudaEventRecord(s->ready, st));
         s->pending = true;
+        c->last_ingest_key = key; c->last_ingest_valid = true;
     }
     s->key = key; s->valid = true; s->stamp = ++c->clock;
     return VO_OK;

@@ -93,6 +93,7 @@ struct Ctx {
     cudaStream_t stream3 = nullptr;
     cudaEvent_t ev_ingest_fork = nullptr;
     uint64_t ingest_seq = 0;
+    int64_t last_ingest_key = 0; bool last_ingest_valid = false;   // newest frame on the ingest stream, not used yet
     // A "step" closes when the promotion stage has been enqueued (it joins the side stream): from then
     // on no kernel of that step reads a frame slot, and ev_step_end (main stream) marks the point.
     cudaEvent_t ev_step_end[4] = {};   // ring: closing step S records ev_step_end[S & 3]
@@ -286,6 +287,8 @@ struct Pipeline {
     // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
     bool spec_pending = false;
     // host-side values before the last tracking step (vo_track_rollback)
+    // vo_process_frame_pipelined: the tracking step (ahead_prev -> ahead_next) is already enqueued
+    bool ahead_valid = false; int64_t ahead_prev = 0, ahead_next = 0;
     bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0;
     double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
     cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion

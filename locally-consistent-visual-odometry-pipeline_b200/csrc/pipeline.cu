@@ -681,29 +681,53 @@ int vo_track_triangulate_promote(vo_ctx* c, int64_t prev_key, int64_t next_key, 
 // upload + pyramid of the new frame, KLT of P and C (one launch), landmark compaction, PnP-RANSAC +
 // LM + pruning, candidate update + bearing test + DLT + promotion, append of the new candidates
 // (pose taken from the device), D2H of the pose and counters.
-int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
-                     const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
-                     const double* new_candidates, int n_new, double T44[16], vo_counters* counters)
+//
+// pipelined: the host waits for the pose only (scalars read back between the PnP and the promotion, so
+// the counters are those BEFORE the promotion and the append), and if a frame has been handed over with
+// vo_prefetch_frame since the last call, the tracking step into it is enqueued right behind the append
+// - the next call for (next_key, that frame) finds it done, any other call takes it back - so the GPU
+// runs the chain PnP -> promotion -> append -> KLT -> compaction without a gap across frames.
+static void fill_counters_from(const DevScalars* s, vo_counters* counters)
+{
+    counters->n_landmarks = s->n_land; counters->n_candidates = s->n_cand; counters->n_tracked = s->n_tracked;
+    counters->n_lost = s->n_lost; counters->n_inliers = s->n_inliers; counters->pnp_ok = s->ok;
+    counters->ransac_iters = s->iters_run; counters->best_hypothesis = s->best_hyp; counters->lm_iters = s->lm_iters;
+    counters->n_promoted = s->n_promoted; counters->n_candidates_lost = s->n_cand_lost; counters->cf_alias = s->cf_alias;
+    counters->klt_iters = s->klt_iters; counters->klt_iters_candidates = s->klt_iters_cand; counters->reproj_cost = s->cost;
+}
+
+static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
+                              const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
+                              const double* new_candidates, int n_new, double T44[16], vo_counters* counters, bool pipelined)
 {
     VO_NEED(c);
     if (!K || n_new < 0 || (n_new > 0 && !new_candidates)) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
     vo_klt_params kp;
     if (kparams) kp = *kparams; else vo_klt_params_default(&kp);
+    if (p->profiling) pipelined = false;   // the stage timers bracket the stages of ONE frame
     if (p->profiling) cudaEventRecord(p->ev[0], c->stream);
+    // a tracking step enqueued ahead by the previous pipelined call: ours, or to be taken back
+    const bool tracked = p->ahead_valid && p->ahead_prev == prev_key && p->ahead_next == next_key && p->packed_valid &&
+                         p->cand_tracked_valid;
+    if (p->ahead_valid && !tracked && p->rb_valid && p->packed_valid) VO_TRY(vo_track_rollback(c));
+    p->ahead_valid = false;
     if (img) VO_TRY(vo_upload_frame(c, img, w, h, pitch, next_key));
-    FrameSlot* a = get_frame(c, prev_key);
-    FrameSlot* b = get_frame(c, next_key);
-    if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    FrameSlot *a = nullptr, *b = nullptr;
+    if (!tracked) {
+        a = get_frame(c, prev_key);
+        b = get_frame(c, next_key);
+        if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    }
     if (n_new > 0) {   // stage the candidate feed early so the copy overlaps the tracking
         VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
         VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
     }
     const bool prof = p->profiling;
     if (prof) cudaEventRecord(p->ev[1], c->stream);
-    VO_TRY(track_both(c, a, b, kp, true));
+    if (!tracked) VO_TRY(track_both(c, a, b, kp, true));
     if (prof) cudaEventRecord(p->ev[2], c->stream);
-    VO_TRY(launch_landmark_compact(c, p->n_land_upper));
+    if (!tracked) VO_TRY(launch_landmark_compact(c, p->n_land_upper));
     p->packed_valid = true;
     PnpLaunch L{};
     if (pparams) L.prm = *pparams; else vo_pnp_params_default(&L.prm);
@@ -713,13 +737,45 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
     if (prof) cudaEventRecord(p->ev[3], c->stream);
     VO_TRY(launch_pnp(c, L));
     if (prof) cudaEventRecord(p->ev[4], c->stream);
+    const int ncand_before = p->n_cand_upper;
+    if (pipelined) {
+        VO_TRY(join_side_stream(c));
+        if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
+        VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+        VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));
+    }
     VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
     VO_TRY(close_step(c));
     if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
     if (prof) cudaEventRecord(p->ev[5], c->stream);
     p->cand_tracked_valid = false;
     p->packed_valid = false;
-    VO_TRY(read_scalars(c));
+    p->rb_valid = false;
+    if (pipelined) {
+        // the next frame is on the ingest stream already: its tracking goes right behind the append
+        if (c->last_ingest_valid && c->last_ingest_key != next_key && vo_has_frame(c, c->last_ingest_key)) {
+            const int64_t nk = c->last_ingest_key;
+            FrameSlot* a2 = get_frame(c, next_key);
+            FrameSlot* b2 = get_frame(c, nk);
+            if (a2 && b2) {
+                VO_TRY(track_both(c, a2, b2, kp, true));
+                p->cand_tracked_prev = next_key; p->cand_tracked_next = nk; p->cand_tracked_valid = true;
+                p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
+                VO_TRY(launch_landmark_compact(c, p->n_land_upper));
+                p->rb_valid = true; p->packed_valid = true;
+                p->ahead_valid = true; p->ahead_prev = next_key; p->ahead_next = nk;
+            }
+        }
+        VO_TRY(flush_frame_hint(c, true));
+        VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
+        DevScalars* s = p->h_sc;   // as of the PnP: before the promotion and the append
+        // (still upper bounds for what the promotion, the append and a tracking step enqueued above leave)
+        p->n_land_upper = s->n_land + ncand_before; p->n_cand_upper = s->n_cand + n_new;
+        s->n_promoted = 0; s->n_cand_lost = 0;
+        if (!s->ok && p->ahead_valid) { VO_TRY(vo_track_rollback(c)); p->ahead_valid = false; }
+    } else {
+        VO_TRY(read_scalars(c));
+    }
     VO_TRY(check_rng(c));
     if (prof) {   // accumulate stage times (ms): upload+pyramid, KLT, compaction, PnP, promotion
         for (int k = 0; k < 5; k++) {
@@ -731,15 +787,24 @@ int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int
         p->stage_frames++;
     }
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
-    if (counters) {
-        const DevScalars* s = p->h_sc;
-        counters->n_landmarks = s->n_land; counters->n_candidates = s->n_cand; counters->n_tracked = s->n_tracked;
-        counters->n_lost = s->n_lost; counters->n_inliers = s->n_inliers; counters->pnp_ok = s->ok;
-        counters->ransac_iters = s->iters_run; counters->best_hypothesis = s->best_hyp; counters->lm_iters = s->lm_iters;
-        counters->n_promoted = s->n_promoted; counters->n_candidates_lost = s->n_cand_lost; counters->cf_alias = s->cf_alias;
-        counters->klt_iters = s->klt_iters; counters->klt_iters_candidates = s->klt_iters_cand; counters->reproj_cost = s->cost;
-    }
+    if (counters) fill_counters_from(p->h_sc, counters);
     return VO_OK;
+}
+
+int vo_process_frame(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
+                     const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
+                     const double* new_candidates, int n_new, double T44[16], vo_counters* counters)
+{
+    return process_frame_impl(c, img, w, h, pitch, prev_key, next_key, K, kparams, pparams, alpha_deg, new_candidates, n_new,
+                              T44, counters, false);
+}
+
+int vo_process_frame_pipelined(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
+                               const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
+                               const double* new_candidates, int n_new, double T44[16], vo_counters* counters)
+{
+    return process_frame_impl(c, img, w, h, pitch, prev_key, next_key, K, kparams, pparams, alpha_deg, new_candidates, n_new,
+                              T44, counters, true);
 }
 
 // Stage timers of vo_process_frame (CUDA events on the ctx stream).  enable: 1 = on (resets the

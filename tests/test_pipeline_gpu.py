@@ -535,3 +535,42 @@ def test_dropin_speculative_tracking_hit_and_miss(dropin, scene_mod):
             Ts.append(new_pose)
         assert np.array_equal(np.array(Ts), Ts0), wrong_every
         assert hits >= n - 4
+
+
+def test_pipelined_frames_equal_the_synchronous_call(pkg, scene_mod):
+    """vo_process_frame_pipelined (pose-only wait, next frame's tracking enqueued behind the promotion when
+    that frame was handed over early) gives the poses and the final state of vo_process_frame bit for
+    bit - with hits (next call matches), a miss (taken back) and steps without a frame ahead."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    K = sq.K
+    pnp = pkg.pnp_defaults()
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)
+    n = 14
+    try:
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        for k in range(1, n):
+            Ta, ca = a.process_frame(sq.frames[k], k, k + 1, K, 1.0, sq.feeds[k], pnp=pnp)
+            if k % 5 == 3:
+                b.prefetch_frame(sq.frames[k + 2], 900 + k)        # a frame that is NOT the next one: miss
+            elif k % 5 != 4 and k + 1 < len(sq.frames):
+                b.prefetch_frame(sq.frames[k + 1], k + 2)          # the next frame, one step ahead
+            Tb, cb = b.process_frame(sq.frames[k], k, k + 1, K, 1.0, sq.feeds[k], pnp=pnp, pipelined=True)
+            assert ca["pnp_ok"] == 1 and cb["pnp_ok"] == 1 and np.array_equal(Ta, Tb), k
+            assert ca["n_inliers"] == cb["n_inliers"] and cb["n_promoted"] == 0
+            assert cb["n_landmarks"] == cb["n_inliers"]            # as of the pose: pruned, nothing promoted yet
+        # leave the pipelined mode: one synchronous call on both, then compare everything
+        Ta, ca = a.process_frame(sq.frames[n], n, n + 1, K, 1.0, sq.feeds[n], pnp=pnp)
+        Tb, cb = b.process_frame(sq.frames[n], n, n + 1, K, 1.0, sq.feeds[n], pnp=pnp)
+        assert np.array_equal(Ta, Tb)
+        for key in ("n_landmarks", "n_candidates", "n_promoted", "n_candidates_lost", "n_inliers", "cf_alias"):
+            assert ca[key] == cb[key], key
+        Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+        assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+        for u, v in zip(a.get_candidates(), b.get_candidates()):
+            assert np.array_equal(u, v)
+    finally:
+        a.close(); b.close()
