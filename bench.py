@@ -179,8 +179,9 @@ def run_gpu(args, rank, world, local_rank):
     def dev_step(s, order, n_land, n_cand):
         b = order[s + 1]
         if args.prefetch:
-            # frame ingest: the NEXT step's frame goes to the ingest stream now (inside this step's timed
-            # region: the ingest is ordered behind the step's start event) and overlaps this step's stages
+            # frame ingest: the NEXT step's frame goes to the ingest stream now, after this step's start
+            # event has been recorded; on the GPU it runs under the chain that is executing at that moment
+            # (previous frame's promotion / this frame's tracking, enqueued one call ahead) - timed stages
             r = lib.vo_prefetch_frame(hnd, ctypes.c_void_p(d_frames[order[s + 2]].data_ptr()), w, h, w, s + 3)
             if r != 0:
                 raise RuntimeError(lib.vo_last_error(hnd).decode())
@@ -459,7 +460,8 @@ def main():
     })
     line["config"]["l2"] = "flushed between steps (256 MiB memset outside the per-step events)"
     line["config"]["ingest"] = ("frame k+1 uploaded and its pyramid built on the ingest stream during step k (vo_prefetch_frame), "
-                                "every step still copies and builds exactly one frame inside the timed region") if args.prefetch else "in-step upload + pyramid"
+                                "every step still copies and builds exactly one frame; frames overlapped "
+                                "(vo_process_frame_pipelined: pose-only wait, next tracking enqueued behind the promotion)") if args.prefetch else "in-step upload + pyramid, synchronous vo_process_frame"
     if world == 1 and not args.no_cpu_baseline:
         _, sq = build_sequence(seed=11)
         n = 60
