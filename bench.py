@@ -229,7 +229,6 @@ def run_gpu(args, rank, world, local_rank):
         if s >= warmup:
             ev[s - warmup][1].record(stream)
             klt_iters += cnt.klt_iters
-            lm_iters += cnt.lm_iters; ransac_iters += cnt.ransac_iters; inliers += cnt.n_inliers; promoted += cnt.n_promoted
     torch.cuda.synchronize()
     barrier(world)
     t_wall = time.perf_counter() - t_wall0
@@ -256,6 +255,8 @@ def run_gpu(args, rank, world, local_rank):
         if s >= warmup:
             prof_iters_land += cnt.klt_iters
             prof_iters_cand += cnt.klt_iters_candidates
+            # per-frame state statistics from this (synchronous) leg: its counters are the final ones of each frame
+            lm_iters += cnt.lm_iters; ransac_iters += cnt.ransac_iters; inliers += cnt.n_inliers; promoted += cnt.n_promoted
     stage_ms, nfr = ctx.stage_times()
     ctx.set_profiling(False)
 
