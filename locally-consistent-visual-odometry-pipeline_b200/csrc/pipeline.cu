@@ -124,11 +124,12 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
             // two staging buffers in turn: the copy out of the one used two frames ago was joined by that
             // frame's promotion step, which the pose read-back of the frame after it has waited for
             const int f = p->add_flip ^= 1;
-            VO_TRY(ensure(c, p->d_add[f], need));
             memcpy(p->h_add[f], add->T44, 16 * sizeof(double));
             memcpy(p->h_add[f] + 16, add->pts, (size_t)n_add * 2 * sizeof(double));
-            VO_CUDA(c, cudaMemcpyAsync(p->d_add[f].p, p->h_add[f], need * sizeof(double), cudaMemcpyHostToDevice, c->stream2));
-            VO_TRY(launch_cand_add(c, p->d_add[f].p + 16, n_add, p->d_add[f].p, nullptr, true));
+            // the append kernel reads the rows straight out of the pinned buffer (unified addressing:
+            // cudaMallocHost memory is device-accessible under the same pointer) - a few KB over PCIe on the
+            // side stream, and one driver call less on the host
+            VO_TRY(launch_cand_add(c, p->h_add[f] + 16, n_add, p->h_add[f], nullptr, true));
             c->side_writes_counts = true;
         }
         if (p->profiling) cudaEventRecord(p->ev_side[0], c->stream2);

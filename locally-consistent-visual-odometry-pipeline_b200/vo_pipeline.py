@@ -721,19 +721,17 @@ class LandmarkTriangulator():
         elif method == 'feed':   # pre-generated candidate feed (benchmarks / tests)
             new_candidates_list = _candidate_feed.pop(0) if _candidate_feed else []
         if len(new_candidates_list) > 0:
-            # appended on the device when the next frame has been uploaded (or when someone looks)
+            # appended on the device with the next tracking step (or when someone looks); the rows are
+            # copied when that happens, so the caller's feed array is snapshotted here
             rt.pending_add = (np.array(new_candidates_list, np.float64), new_pose.copy())   # T = eye(4) @ new_pose (vo:582)
 
         rt.state_version += 1
         rt.ext_version += 1
         if isinstance(state, DeviceState):
-            state._rebind(rt.state_version)
+            dict.clear(state)            # (_rebind, inlined: this sits between the pose and the next launch)
+            state._version, state._dirty, state._limit = rt.state_version, False, None
         else:
             state = DeviceState(rt, rt.state_version)
-        if isinstance(extended_state, DeviceExtendedState):
-            extended_state._rebind(rt.ext_version)
-        else:
-            extended_state = DeviceExtendedState(rt, rt.ext_version)
         # The next frame is already on the ingest stream (prefetch_frame / FrameIngest): enqueue its
         # tracking now, right behind the promotion step, instead of leaving the GPU idle until main.py
         # comes round to associateKeypointsToLandmarks - which then finds the work done, or takes it back
@@ -744,6 +742,10 @@ class LandmarkTriangulator():
             add, rt.pending_add = rt.pending_add, None
             rt.ctx.klt_track_landmarks(rt.pair[3], pre[0], rt.klt, add=add)
             rt.spec_track = {'old': new_frame, 'fp': pre[2], 'k_old': rt.pair[3], 'k_new': pre[0], 'state': state}
+        if isinstance(extended_state, DeviceExtendedState):
+            extended_state._rebind(rt.ext_version)
+        else:
+            extended_state = DeviceExtendedState(rt, rt.ext_version)
         return (state, extended_state, cur_des)
 
 
