@@ -574,3 +574,25 @@ def test_pipelined_frames_equal_the_synchronous_call(pkg, scene_mod):
             assert np.array_equal(u, v)
     finally:
         a.close(); b.close()
+
+
+def test_frame_ingest_from_files(dropin, scene_mod, tmp_path):
+    """FrameIngest over file paths (cv2.imread on the worker thread, as main.py:217-223 reads them): frames
+    arrive bit-identical, in order, in pinned buffers, and a missing file surfaces in the consumer."""
+    cv2 = pytest.importorskip("cv2")
+    sq = get_sequence(scene_mod, "kitti_half")
+    paths = []
+    for k in range(6):
+        p = str(tmp_path / ("%06d.png" % k))
+        cv2.imwrite(p, sq.frames[k])
+        paths.append(p)
+    got = []
+    for img in dropin.FrameIngest(paths, depth=3):
+        assert img.dtype == np.uint8 and img.flags["C_CONTIGUOUS"]
+        got.append(img.copy())
+    assert len(got) == 6 and all(np.array_equal(a, b) for a, b in zip(got, sq.frames))
+    with pytest.raises(FileNotFoundError):
+        for _ in dropin.FrameIngest(paths[:2] + [str(tmp_path / "missing.png")]):
+            pass
+    with pytest.raises(ValueError):
+        dropin.FrameIngest(paths, depth=2)
