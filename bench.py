@@ -199,7 +199,7 @@ def run_gpu(args, rank, world, local_rank):
         if step_fn is lib.vo_process_frame_pipelined:
             # counts as of the pose read-back (before this frame's promotion and append): the same
             # bookkeeping as the e2e loop uses
-            return cnt.n_landmarks, cnt.n_candidates + want
+            return cnt.n_landmarks + cnt.n_promoted, cnt.n_candidates + want
         return cnt.n_landmarks, cnt.n_candidates
 
     # ---- value: device-resident inputs, per-step CUDA events, L2 flush between steps -------------------
@@ -354,7 +354,7 @@ def run_e2e(pkg, sq, steps, warmup, local_rank, world, prefetch=True):
         # sizes for the next feed from the scalars the PnP sync already brought back (no extra sync):
         # inliers now, candidates as they were after the previous frame's append
         c = vo._runtime().ctx.counters(sync=False)
-        n_land, n_cand = c["n_landmarks"], c["n_candidates"] + len(feed)
+        n_land, n_cand = c["n_landmarks"] + c["n_promoted"], c["n_candidates"] + len(feed)
         h2d += w * h + feed.nbytes + 128
         d2h += 256
     vo._runtime().ctx.synchronize()

@@ -168,6 +168,16 @@ int vo_klt_track_landmarks(vo_ctx* ctx, int64_t prev_key, int64_t next_key, cons
  * kernel sits between the caller and the landmark launch (the head of the chain the pose waits for). */
 int vo_klt_track_landmarks_add(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
                                const double* new_candidates, int n_new, const double T44[16], int* n_kept);
+/* The same, plus the pose-independent half of the coming promotion step on the side stream behind the
+ * candidates' KLT: lost rows out and positions updated (vo_pipeline.py:503-545), bearing test with
+ * threshold early_alpha_deg (:621-642, raw pixels only), compaction of C/F/T.  The promotion call that
+ * follows (vo_pnp_ransac_promote / vo_track_triangulate_promote) with the same alpha then only
+ * triangulates and appends the promoted rows; with another alpha, without a pose, or if something looks
+ * at the candidates first, the early half is taken back and redone the long way.  Results are identical.
+ * early_alpha_deg < 0: none (= vo_klt_track_landmarks_add). */
+int vo_klt_track_landmarks_ex(vo_ctx* ctx, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
+                              const double* new_candidates, int n_new, const double T44[16], double early_alpha_deg,
+                              int* n_kept);
 /* Undo the last vo_klt_track_landmarks[_add], provided nothing but that tracking step has run since:
  * the drop-in enqueues the tracking of a frame it was handed early (vo_prefetch_frame) right behind the
  * previous frame's promotion, BEFORE associateKeypointsToLandmarks is called for it, and takes it back
@@ -190,7 +200,10 @@ int vo_pnp_ransac(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, d
  * ok=0 is rolled back internally.  Until then the promoted rows sit behind the n_inliers rows of P/X.
  * n_promoted == NULL: the host waits only for the pose (the scalar block is read back between the PnP
  * and the promotion kernels), so the promotion step keeps the GPU busy while the host walks on to
- * triangulate_landmark; vo_peek_counters then shows the counts as they were BEFORE the promotion. */
+ * triangulate_landmark; vo_peek_counters then shows the landmarks as they were BEFORE the promoted rows
+ * are appended (n_landmarks = n_inliers), and the candidates before the promotion step too - unless the
+ * tracking call already classified them (vo_klt_track_landmarks_ex), then n_candidates / n_promoted /
+ * n_candidates_lost are the final ones. */
 int vo_pnp_ransac_promote(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, double alpha_deg,
                           double T44[16], int* n_inliers, int* ok, int* n_promoted);
 int vo_promote_commit(vo_ctx* ctx);
@@ -273,7 +286,8 @@ int vo_process_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, i
                      const double* new_candidates, int n_new, double T44[16], vo_counters* counters);
 
 /* The same with the frames overlapped: the host waits for the pose only, so `counters` holds the counts
- * as they were BEFORE this frame's promotion and append (n_promoted = 0), and if a frame has been handed
+ * as of the PnP: n_landmarks = n_inliers (the n_promoted rows are appended behind the host's back) and the
+ * candidates after the classification but before the append of new_candidates.  If a frame has been handed
  * over with vo_prefetch_frame since the last call, the tracking step (next_key -> that frame) is enqueued
  * right behind the append.  The next call for that frame pair finds it done; any other call takes it
  * back (vo_track_rollback).  With the stage timers on it behaves like vo_process_frame. */

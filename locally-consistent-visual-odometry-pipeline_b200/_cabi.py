@@ -88,6 +88,7 @@ SIGNATURES = {
     "vo_klt_track_landmarks": (c_int, [c_void_p, c_i64, c_i64, _PK, _PI]),
     "vo_pnp_ransac": (c_int, [c_void_p, c_void_p, _PP, c_void_p, _PI, _PI]),
     "vo_klt_track_landmarks_add": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, _PI]),
+    "vo_klt_track_landmarks_ex": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, c_double, _PI]),
     "vo_track_rollback": (c_int, [c_void_p]),
     "vo_map_reset": (c_int, [c_void_p]),
     "vo_map_accumulate": (c_int, [c_void_p, c_void_p, c_double, c_double, c_int, _PI]),
@@ -339,18 +340,23 @@ class Context:
         return cnt.as_dict()
 
     # ---- per-frame stages ------------------------------------------------------------------------
-    def klt_track_landmarks(self, prev_key, next_key, params=None, sync=False, add=None):
+    def klt_track_landmarks(self, prev_key, next_key, params=None, sync=False, add=None, early_alpha=None):
         """a1.  add=(pts n x 2 float64, T 4x4): the previous frame's new candidates, appended on the side
-        stream in front of the candidates' KLT (vo_klt_track_landmarks_add)."""
+        stream in front of the candidates' KLT (vo_klt_track_landmarks_add).  early_alpha (degrees): the
+        pose-independent half of the coming promotion step runs behind that KLT (vo_klt_track_landmarks_ex)."""
         n = c_int()
         pk = ctypes.byref(params) if params is not None else None
-        if add is not None and len(add[0]) > 0:
-            pts = np.ascontiguousarray(add[0], np.float64).reshape(-1, 2)
-            T = np.ascontiguousarray(add[1], np.float64)
-            self._check(self.lib.vo_klt_track_landmarks_add(self.h, prev_key, next_key, pk, _ptr(pts), len(pts), _ptr(T),
-                                                            ctypes.byref(n) if sync else None))
+        pn = ctypes.byref(n) if sync else None
+        have_add = add is not None and len(add[0]) > 0
+        if have_add or early_alpha is not None:
+            pts = T = None
+            if have_add:
+                pts = np.ascontiguousarray(add[0], np.float64).reshape(-1, 2)
+                T = np.ascontiguousarray(add[1], np.float64)
+            self._check(self.lib.vo_klt_track_landmarks_ex(self.h, prev_key, next_key, pk, _ptr(pts), 0 if pts is None else len(pts),
+                                                           _ptr(T), -1.0 if early_alpha is None else float(early_alpha), pn))
         else:
-            self._check(self.lib.vo_klt_track_landmarks(self.h, prev_key, next_key, pk, ctypes.byref(n) if sync else None))
+            self._check(self.lib.vo_klt_track_landmarks(self.h, prev_key, next_key, pk, pn))
         return n.value if sync else None
 
     def pnp_ransac(self, K, params=None):

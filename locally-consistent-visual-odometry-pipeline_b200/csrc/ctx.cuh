@@ -230,6 +230,8 @@ struct DevScalars {
     int32_t finalized;     // the refit of the current RANSAC run has been done
     int32_t klt_iters_cand; // sum of LK iterations over the candidates (roofline accounting)
     int32_t ticket2;       // same for kernels enqueued on the side stream (they overlap main-stream kernels)
+    int32_t klt_iters_cand2; // side-stream accumulator of klt_iters_cand (early classification), moved over by the finish kernel
+    int32_t pad2_;
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -284,6 +286,11 @@ struct Pipeline {
     // the last promotion step consumed a candidate KLT: C[ccur ^ 1] holds the candidates' previous
     // positions, klt_status + mask_src_off their status, d_sc->spec_n_cand their number (detector mask)
     bool mask_src_valid = false; int mask_src_off = 0;
+    // early classification (tri.cu): the candidate side of the promotion step - lost rows, bearing test,
+    // compaction of C/F/T - already ran on the side stream behind the candidates' KLT with this alpha;
+    // the promoted rows wait in prom_rows / prom_ti for the pose (promote_finish_kernel)
+    bool early_valid = false; double early_alpha = 0.; int early_ncand_upper = 0;
+    DevBuf<double> prom_rows; DevBuf<int32_t> prom_ti;
     // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
     bool spec_pending = false;
     // host-side values before the last tracking step (vo_track_rollback)
@@ -347,6 +354,10 @@ int launch_landmark_compact(Ctx* c, int n_upper);   // after KLT: keep status==1
 // Tnew == nullptr: take the pose the last PnP left on the device (fused per-frame call)
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper,
                    bool use_klt, int b_off);
+// the pose-independent half of the promotion step on the side stream, right behind the candidates' KLT
+int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off);
+// take an early classification back (the candidates are again as the KLT found them); no-op if there is none
+int early_undo(Ctx* c);
 // d_pts: n_new x 2 doubles on the device; d_Thost: 16 doubles on the device or nullptr (= device pose)
 // d_n_new: optional device count (the rows actually appended are min(*d_n_new, n_new))
 int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new = nullptr,

@@ -92,13 +92,14 @@ struct DeferredAdd { const double* pts; int n; const double* T44; };
 // (usually most of the tracks, and with them the slowest stragglers) follow on the side stream, behind
 // the optional deferred append, and are joined by the promotion step.
 static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& prm, bool with_candidates,
-                      const DeferredAdd* add = nullptr)
+                      const DeferredAdd* add = nullptr, double early_alpha = -1.)
 {
     Pipeline* p = c->pipe;
     const int nA = p->n_land_upper;
     const int n_add = (add && with_candidates && add->n > 0) ? add->n : 0;
     const int nB = with_candidates ? p->n_cand_upper + n_add : 0;
     const size_t tot = (size_t)nA + nB > 0 ? (size_t)nA + nB : 1;
+    VO_TRY(early_undo(c));          // (a classification nobody finished: its tracking is being replaced)
     VO_TRY(join_side_stream(c));
     VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
     VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
@@ -136,6 +137,8 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
         VO_TRY(launch_klt2(c, a->pyr, b->pyr, nullptr, nullptr, 0, p->C[p->ccur].p, &p->d_sc->n_cand, nB, nA, p->klt_out.p,
                            p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, c->stream2));
         if (p->profiling) cudaEventRecord(p->ev_side[1], c->stream2);
+        // the pose-independent half of the promotion step follows the candidates' KLT on the side stream
+        if (early_alpha >= 0.) VO_TRY(launch_promote_early(c, early_alpha, nB, nA));
         VO_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
         c->side_inflight = true;
     }
@@ -281,6 +284,7 @@ int vo_get_snapshot(vo_ctx* c, float* P, double* X, int cap, int* n)
 int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* T, int n, int cf_alias)
 {
     VO_NEED(c);
+    VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     if (n < 0 || (n > 0 && (!C || !F || !T))) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
@@ -308,6 +312,7 @@ int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* 
 int vo_get_candidates(vo_ctx* c, float* C, double* F, double* T, int cap, int* n)
 {
     VO_NEED(c);
+    VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     Pipeline* p = c->pipe;
     VO_TRY(read_scalars(c));
@@ -359,7 +364,7 @@ int vo_peek_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out,
 
 // ---- a1: KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227)
 static int track_landmarks_impl(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
-                                const DeferredAdd* add, int* n_kept)
+                                const DeferredAdd* add, int* n_kept, double early_alpha = -1.)
 {
     VO_NEED(c);
     Pipeline* p = c->pipe;
@@ -370,7 +375,7 @@ static int track_landmarks_impl(vo_ctx* c, int64_t prev_key, int64_t next_key, c
     if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
     // candidates ride along: triangulate_landmark (vo:501) tracks them over the same frame pair, and
     // their tracking does not depend on the pose
-    VO_TRY(track_both(c, a, b, prm, true, add));
+    VO_TRY(track_both(c, a, b, prm, true, add, early_alpha));
     p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
     p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
     VO_TRY(launch_landmark_compact(c, p->n_land_upper));
@@ -401,6 +406,20 @@ __global__ void track_rollback_kernel(DevScalars* sc)
     sc->n_land = sc->prev_n_land; sc->n_tracked = 0; sc->n_lost = 0;
 }
 
+// The same, and the pose-independent half of the coming promotion step (vo_pipeline.py:503-545: lost rows
+// out, positions updated; :621-642: bearing test with threshold early_alpha_deg; compaction of C/F/T) goes
+// to the side stream behind the candidates' KLT.  The promotion call that follows with the same alpha
+// only triangulates and appends the promoted rows; with another alpha, or if something looks at the
+// candidates first, the early half is taken back.  early_alpha_deg < 0: none.
+int vo_klt_track_landmarks_ex(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_klt_params* params,
+                              const double* new_candidates, int n_new, const double T44[16], double early_alpha_deg,
+                              int* n_kept)
+{
+    if (n_new < 0 || (n_new > 0 && (!new_candidates || !T44))) return VO_ERR_INVALID;
+    DeferredAdd add{ new_candidates, n_new, T44 };
+    return track_landmarks_impl(c, prev_key, next_key, params, n_new > 0 ? &add : nullptr, n_kept, early_alpha_deg);
+}
+
 // Undo the last vo_klt_track_landmarks[_add] (nothing but the tracking step may have run since): the
 // landmarks are again the ones it started from - the compaction wrote into another buffer of the
 // rotation - and the candidates' pending KLT result is dropped.  A folded append stays (it is not part
@@ -410,6 +429,7 @@ int vo_track_rollback(vo_ctx* c)
     VO_NEED(c);
     Pipeline* p = c->pipe;
     if (!p->rb_valid || !p->packed_valid) return set_error(c, VO_ERR_STATE, "no tracking step to undo");
+    VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     track_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
     c->launches++;
@@ -504,6 +524,10 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     // (and whatever is enqueued next) runs while the host walks on to triangulate_landmark.
     const bool early = n_promoted == nullptr;
     const int ncand_before = p->n_cand_upper;
+    // (Classifying the candidates here, on the side stream under the PnP, was measured: the pose comes
+    // back 5.6 us later on the same box - A/B with tools/e2e_phases.py - so the class-surface path leaves
+    // the early half to callers of vo_klt_track_landmarks_ex / vo_process_frame[_pipelined].)
+    const bool cls_done = p->early_valid && alpha_deg == p->early_alpha;   // candidate side already classified
     if (early) {
         VO_TRY(join_side_stream(c));   // a deferred append on the side stream writes n_cand (long done by now)
         if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
@@ -530,11 +554,17 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
                         p->trace_ready, p->trace_n);
         }
         VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
-        DevScalars* s = p->h_sc;   // values BEFORE the promotion step: bounds stay upper bounds
-        p->n_land_upper = s->n_land + ncand_before;
-        p->n_cand_upper = s->n_cand;
-        s->spec_n_land = s->n_land; s->spec_n_cand = s->n_cand;   // what a rollback restores on the host side
-        s->n_promoted = 0; s->n_cand_lost = 0;
+        DevScalars* s = p->h_sc;   // as of the PnP: the promoted rows are not appended yet
+        s->spec_n_land = s->n_land;   // what a rollback restores on the host side
+        if (cls_done) {   // the side stream has classified the candidates: their counts are final already
+            p->n_land_upper = s->n_land + s->n_promoted;
+            p->n_cand_upper = s->n_cand;
+        } else {          // values BEFORE the promotion step: bounds stay upper bounds
+            p->n_land_upper = s->n_land + ncand_before;
+            p->n_cand_upper = s->n_cand;
+            s->spec_n_cand = s->n_cand;
+            s->n_promoted = 0; s->n_cand_lost = 0;
+        }
     } else {
         VO_TRY(read_scalars(c));
     }
@@ -575,6 +605,7 @@ int vo_candidates_tracked(vo_ctx* c, int64_t prev_key, int64_t next_key)
 int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
 {
     VO_NEED(c);
+    VO_TRY(early_undo(c));
     if (n < 0 || (n > 0 && !pts) || !T44) return VO_ERR_INVALID;
     if (n == 0) return VO_OK;   // the reference appends nothing (vo:574)
     Pipeline* p = c->pipe;
@@ -593,6 +624,7 @@ int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
 int vo_detect_add_candidates_shi(vo_ctx* c, int64_t frame_key, const vo_gftt_params* params, const double T44[16])
 {
     VO_NEED(c);
+    VO_TRY(early_undo(c));
     Pipeline* p = c->pipe;
     vo_gftt_params prm;
     if (params) prm = *params; else vo_gftt_params_default(&prm);
@@ -646,6 +678,7 @@ int vo_track_candidates(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_
 int vo_get_candidate_tracks(vo_ctx* c, float* prev_pts, float* next_pts, uint8_t* status, int cap, int* n)
 {
     VO_NEED(c);
+    VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     Pipeline* p = c->pipe;
     if (!p->cand_tracked_valid) return set_error(c, VO_ERR_STATE, "no pending candidate tracking");
@@ -726,7 +759,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     }
     const bool prof = p->profiling;
     if (prof) cudaEventRecord(p->ev[1], c->stream);
-    if (!tracked) VO_TRY(track_both(c, a, b, kp, true));
+    if (!tracked) VO_TRY(track_both(c, a, b, kp, true, nullptr, alpha_deg));
     if (prof) cudaEventRecord(p->ev[2], c->stream);
     if (!tracked) VO_TRY(launch_landmark_compact(c, p->n_land_upper));
     p->packed_valid = true;
@@ -739,6 +772,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     VO_TRY(launch_pnp(c, L));
     if (prof) cudaEventRecord(p->ev[4], c->stream);
     const int ncand_before = p->n_cand_upper;
+    const bool early_used = p->early_valid;   // the promotion below only finishes an early classification
     if (pipelined) {
         VO_TRY(join_side_stream(c));
         if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
@@ -759,7 +793,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
             FrameSlot* a2 = get_frame(c, next_key);
             FrameSlot* b2 = get_frame(c, nk);
             if (a2 && b2) {
-                VO_TRY(track_both(c, a2, b2, kp, true));
+                VO_TRY(track_both(c, a2, b2, kp, true, nullptr, alpha_deg));
                 p->cand_tracked_prev = next_key; p->cand_tracked_next = nk; p->cand_tracked_valid = true;
                 p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
                 VO_TRY(launch_landmark_compact(c, p->n_land_upper));
@@ -769,12 +803,25 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         }
         VO_TRY(flush_frame_hint(c, true));
         VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
-        DevScalars* s = p->h_sc;   // as of the PnP: before the promotion and the append
+        DevScalars* s = p->h_sc;   // as of the PnP: before the append of the promoted rows and of the new candidates
         // (still upper bounds for what the promotion, the append and a tracking step enqueued above leave)
-        p->n_land_upper = s->n_land + ncand_before; p->n_cand_upper = s->n_cand + n_new;
-        s->n_promoted = 0; s->n_cand_lost = 0;
+        if (early_used) { p->n_land_upper = s->n_land + s->n_promoted; p->n_cand_upper = s->n_cand + n_new; }
+        else {
+            p->n_land_upper = s->n_land + ncand_before; p->n_cand_upper = s->n_cand + n_new;
+            s->n_promoted = 0; s->n_cand_lost = 0;
+        }
         if (!s->ok && p->ahead_valid) { VO_TRY(vo_track_rollback(c)); p->ahead_valid = false; }
     } else {
+        VO_TRY(read_scalars(c));
+    }
+    if (!p->h_sc->ok && early_used) {
+        // no pose, but the early classification assumed one and took the would-be promoted rows out of the
+        // candidates: back to the tracked candidates, then the step as it goes without a pose (lost rows out,
+        // positions updated, nothing promoted)
+        VO_TRY(read_scalars(c));
+        VO_TRY(promote_rollback(c));
+        VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+        p->cand_tracked_valid = false;
         VO_TRY(read_scalars(c));
     }
     VO_TRY(check_rng(c));

@@ -241,12 +241,13 @@ __global__ void __launch_bounds__(kCandThreads)
 cand_classify_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out,
                      const uint8_t* __restrict__ status, const float2* __restrict__ C_in,
                      const double2* __restrict__ F_in, uint8_t* __restrict__ flag, int32_t* __restrict__ blk_counts,
-                     const int32_t* __restrict__ klt_iters)
+                     const int32_t* __restrict__ klt_iters, int early)
 {
     pdl_prologue();
     const int n = min(sc->n_cand, a.ncand_upper);
     const bool alias = sc->cf_alias != 0;
-    const bool have_pose = a.use_dev_T ? sc->ok != 0 : true;
+    // early (side stream, before the PnP): a pose is assumed; the host takes the step back if none comes
+    const bool have_pose = early ? true : (a.use_dev_T ? sc->ok != 0 : true);
     const int i = blockIdx.x * kCandThreads + threadIdx.x;
     uint8_t f = kCandNone;
     if (i < n) {
@@ -261,7 +262,7 @@ cand_classify_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ k
     if (a.use_klt && klt_iters) {   // roofline accounting: iterations spent on the candidates
         int it = i < n ? klt_iters[a.b_off + i] : 0;
         it = __reduce_add_sync(0xffffffffu, it);
-        if ((threadIdx.x & 31) == 0 && it) atomicAdd(&sc->klt_iters_cand, it);
+        if ((threadIdx.x & 31) == 0 && it) atomicAdd(early ? &sc->klt_iters_cand2 : &sc->klt_iters_cand, it);
     }
     const int n_stay = __syncthreads_count(f == kCandStay);
     const int n_prom = __syncthreads_count(f == kCandPromote);
@@ -273,7 +274,8 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
                   const float2* __restrict__ C_in, const double2* __restrict__ F_in, const int32_t* __restrict__ Ti_in,
                   const uint8_t* __restrict__ flag, const int32_t* __restrict__ blk_counts,
                   float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
-                  const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap)
+                  const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap,
+                  int early, double* __restrict__ prom_rows, int32_t* __restrict__ prom_ti)
 {
     __shared__ int sWarpStay[kCandThreads / 32], sWarpProm[kCandThreads / 32];
     __shared__ int sBaseStay, sBaseProm, sLast;
@@ -289,7 +291,7 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
         st = __reduce_add_sync(0xffffffffu, st);
         pr = __reduce_add_sync(0xffffffffu, pr);
         if (lane == 0) { sBaseStay = st; sBaseProm = pr; }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1 && lane == 0 && !early) {
         k_times_pose(a.K, a.use_dev_T ? sc->T : a.Tnew, sM2);
     }
     const int i = blockIdx.x * kCandThreads + tid;
@@ -305,6 +307,11 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
     if (f == kCandStay || f == kCandPromote) {
         const CandRow r = load_cand(a, alias, i, klt_out, status, C_in, F_in);
         if (f == kCandStay) { C_out[os] = r.c; F_out[os] = r.f; Ti_out[os] = Ti_in[i]; }
+        else if (early) {   // the row waits for the pose: promote_finish_kernel triangulates and appends it
+            prom_rows[4 * (size_t)op] = r.f.x; prom_rows[4 * (size_t)op + 1] = r.f.y;
+            prom_rows[4 * (size_t)op + 2] = (double)r.c.x; prom_rows[4 * (size_t)op + 3] = (double)r.c.y;
+            prom_ti[op] = Ti_in[i];
+        }
         else if (n_land + op < land_cap) {
             double M1[12], Xh[4];
             k_times_pose(a.K, poses + 16 * (size_t)Ti_in[i], M1);
@@ -316,9 +323,10 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
     }
     // the last CTA to get here publishes the sizes: every CTA has read the old ones by then
     __syncthreads();
+    int32_t* ticket = early ? &sc->ticket2 : &sc->ticket;   // early: on the side stream, under main-stream kernels
     if (tid == 0) {
         __threadfence();
-        sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
+        sLast = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
     }
     __syncthreads();
     if (!sLast) return;
@@ -329,17 +337,61 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
         pr = __reduce_add_sync(0xffffffffu, pr);
         if (lane == 0) {
             const int kept = st + pr, n_lost = n - kept;
-            sc->spec_n_land = n_land; sc->spec_n_cand = sc->n_cand; sc->spec_cf_alias = sc->cf_alias;
+            // (early: the landmark side - spec_n_land, n_land - belongs to the main stream's chain, which is
+            // pruning the landmarks right now; promote_finish_kernel sets it)
+            if (!early) sc->spec_n_land = n_land;
+            sc->spec_n_cand = sc->n_cand; sc->spec_cf_alias = sc->cf_alias;
             sc->spec_cand_was_empty = sc->cand_was_empty;
             sc->n_cand = st;
             sc->n_promoted = pr;
             sc->n_cand_lost = n_lost;
-            sc->n_land = min(n_land + pr, land_cap);
+            if (!early) sc->n_land = min(n_land + pr, land_cap);
             sc->cand_was_empty = kept == 0;                    // C empty after tracking/removal (vo:579)
             sc->cf_alias = alias && n_lost == 0 && pr == 0;    // np.delete re-allocates: aliasing ends
-            sc->ticket = 0;
+            *ticket = 0;
         }
     }
+}
+
+// The pose-dependent rest of an early classification: DLT of the promoted rows with (T_first, T_new),
+// appended behind the live landmarks.  One CTA; ~20 rows per frame, each a serial FP64 Jacobi SVD.
+__global__ void __launch_bounds__(128)
+promote_finish_kernel(DevScalars* sc, PromoteArgs a, const double* __restrict__ prom_rows,
+                      const int32_t* __restrict__ prom_ti, const double* __restrict__ poses, float2* __restrict__ P,
+                      double* __restrict__ X, int land_cap)
+{
+    __shared__ double sM2[12];
+    pdl_prologue();
+    const int tid = threadIdx.x;
+    const int n_land = sc->n_land;
+    const int n_prom = sc->n_promoted;
+    if (tid == 0) k_times_pose(a.K, a.use_dev_T ? sc->T : a.Tnew, sM2);
+    __syncthreads();
+    for (int i = tid; i < n_prom; i += blockDim.x) {
+        const int o = n_land + i;
+        if (o >= land_cap) break;
+        double M1[12], Xh[4];
+        k_times_pose(a.K, poses + 16 * (size_t)prom_ti[i], M1);
+        const double fx = prom_rows[4 * (size_t)i], fy = prom_rows[4 * (size_t)i + 1];
+        const double cx = prom_rows[4 * (size_t)i + 2], cy = prom_rows[4 * (size_t)i + 3];
+        dlt_point(M1, sM2, fx, fy, cx, cy, Xh);
+        P[o] = make_float2((float)cx, (float)cy);
+        X[3 * (size_t)o] = Xh[0] / Xh[3]; X[3 * (size_t)o + 1] = Xh[1] / Xh[3]; X[3 * (size_t)o + 2] = Xh[2] / Xh[3];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        sc->spec_n_land = n_land;
+        sc->n_land = min(n_land + n_prom, land_cap);
+        sc->klt_iters_cand = sc->klt_iters_cand2;
+        sc->klt_iters_cand2 = 0;
+    }
+}
+
+// take an early classification back: the candidate-side scalars as the KLT left them
+__global__ void early_undo_kernel(DevScalars* sc)
+{
+    sc->n_cand = sc->spec_n_cand; sc->cf_alias = sc->spec_cf_alias; sc->cand_was_empty = sc->spec_cand_was_empty;
+    sc->n_promoted = 0; sc->n_cand_lost = 0; sc->klt_iters_cand2 = 0;
 }
 
 // append n_new candidates: C := F := pts, T := pose (vo_pipeline.py:574-591); the last CTA to
@@ -423,11 +475,89 @@ int launch_landmark_compact(Ctx* c, int n_upper)
     return VO_OK;
 }
 
+int early_undo(Ctx* c)
+{
+    Pipeline* p = c->pipe;
+    if (!p->early_valid) return VO_OK;
+    p->early_valid = false;
+    VO_TRY(join_side_stream(c));
+    early_undo_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
+    c->launches++;
+    VO_CUDA(c, cudaGetLastError());
+    p->ccur ^= 1;                 // the buffers the classification read from are intact
+    p->mask_src_valid = false;
+    // a scalar read-back in between may have tightened the bound to the classified count
+    if (p->n_cand_upper < p->early_ncand_upper) p->n_cand_upper = p->early_ncand_upper;
+    return VO_OK;
+}
+
+// Candidate side of the promotion step on the side stream, behind the candidates' KLT that track_both
+// has just enqueued there (vo_pipeline.py:503-545 and the bearing test :621-642 need no pose): runs
+// under the landmark chain and the PnP.  launch_promote finishes it when it is called with the same
+// alpha, or takes it back.
+int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off)
+{
+    Pipeline* p = c->pipe;
+    if (ncand_upper <= 0) return VO_OK;
+    PromoteArgs a;
+    memset(&a, 0, sizeof(a));
+    a.alpha_deg = alpha_deg; a.use_dev_T = 1; a.use_klt = 1; a.b_off = b_off; a.ncand_upper = ncand_upper;
+    const size_t nc = ncand_upper;
+    VO_TRY(ensure(c, p->C[p->ccur ^ 1], nc * 2));
+    VO_TRY(ensure(c, p->F[p->ccur ^ 1], nc * 2));
+    VO_TRY(ensure(c, p->Ti[p->ccur ^ 1], nc));
+    VO_TRY(ensure(c, p->prom_rows, nc * 4));
+    VO_TRY(ensure(c, p->prom_ti, nc));
+    const int nb = (ncand_upper + kCandThreads - 1) / kCandThreads;
+    VO_TRY(ensure(c, p->cand_flag, nc));
+    VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
+    VO_CUDA(c, launch_pdl(cand_classify_kernel, dim3(nb), dim3(kCandThreads), c->stream2,
+        p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p, 1));
+    VO_CUDA(c, launch_pdl(cand_apply_kernel, dim3(nb), dim3(kCandThreads), c->stream2,
+        p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
+        (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
+        (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
+        p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)nullptr, (double*)nullptr, 0, 1, p->prom_rows.p,
+        p->prom_ti.p));
+    c->launches += 2;
+    VO_CUDA(c, cudaGetLastError());
+    p->ccur ^= 1;
+    p->mask_src_valid = true; p->mask_src_off = b_off;
+    p->early_valid = true; p->early_alpha = alpha_deg; p->early_ncand_upper = ncand_upper;
+    c->side_writes_counts = true;   // n_cand is being rewritten over there
+    return VO_OK;
+}
+
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper, bool use_klt,
                    int b_off)
 {
     Pipeline* p = c->pipe;
     VO_TRY(join_side_stream(c));   // the candidates' KLT results come from the side stream
+    if (p->early_valid) {
+        if (use_klt && alpha_deg == p->early_alpha) {
+            // the candidate side is done: triangulate the promoted rows with the pose and append them
+            p->early_valid = false;
+            PromoteArgs a;
+            memcpy(a.K, K, sizeof(a.K));
+            if (Tnew) memcpy(a.Tnew, Tnew, sizeof(a.Tnew)); else memset(a.Tnew, 0, sizeof(a.Tnew));
+            a.alpha_deg = alpha_deg; a.use_dev_T = Tnew == nullptr; a.use_klt = 1; a.b_off = b_off;
+            a.ncand_upper = p->early_ncand_upper;
+            const size_t need = (size_t)p->n_land_upper + (size_t)p->early_ncand_upper + 1;
+            VO_TRY(ensure(c, p->P[p->cur], need * 2, true));
+            VO_TRY(ensure(c, p->X[p->cur], need * 3, true));
+            const int land_cap = (int)(p->P[p->cur].cap / 2);
+            VO_CUDA(c, launch_pdl(promote_finish_kernel, dim3(1), dim3(128), c->stream, p->d_sc, a,
+                                  (const double*)p->prom_rows.p, (const int32_t*)p->prom_ti.p, (const double*)p->poses.p,
+                                  (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap));
+            c->launches++;
+            p->n_land_upper += p->early_ncand_upper;
+            VO_CUDA(c, cudaGetLastError());
+            return VO_OK;
+        }
+        VO_TRY(early_undo(c));   // other arguments than assumed: back to the tracked candidates
+        if (ncand_upper < p->n_cand_upper) ncand_upper = p->n_cand_upper;   // (the caller's bound may be the classified count)
+    }
     PromoteArgs a;
     memcpy(a.K, K, sizeof(a.K));
     if (Tnew) memcpy(a.Tnew, Tnew, sizeof(a.Tnew)); else memset(a.Tnew, 0, sizeof(a.Tnew));
@@ -450,12 +580,13 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
     VO_CUDA(c, launch_pdl(cand_classify_kernel, dim3(nb), dim3(kCandThreads), c->stream,
         p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p));
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p, 0));
     VO_CUDA(c, launch_pdl(cand_apply_kernel, dim3(nb), dim3(kCandThreads), c->stream,
         p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
         (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
         (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
-        p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap));
+        p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap, 0,
+        (double*)nullptr, (int32_t*)nullptr));
     c->launches++;
     c->launches++;
     p->ccur ^= 1;

@@ -194,7 +194,10 @@ def test_speculative_promotion_commit_and_rollback(pkg, scene_mod, early):
             if early:
                 assert nprom is None
                 pk = b.counters(sync=False)              # as of the pose read-back: before the promotion
-                assert pk["n_landmarks"] == ninl and pk["n_candidates"] == len(Ca0[0]) and pk["n_promoted"] == 0
+                # landmarks pruned, promoted rows not appended yet; candidates untouched (plain tracking call) or,
+                # had the tracking call classified them early, final counts
+                assert pk["n_landmarks"] == ninl
+                assert pk["n_candidates"] + pk["n_promoted"] + pk["n_candidates_lost"] == len(Ca0[0])
                 nprom = None
             if k % 2 == 0:
                 b.promote_rollback()
@@ -560,8 +563,11 @@ def test_pipelined_frames_equal_the_synchronous_call(pkg, scene_mod):
                 b.prefetch_frame(sq.frames[k + 1], k + 2)          # the next frame, one step ahead
             Tb, cb = b.process_frame(sq.frames[k], k, k + 1, K, 1.0, sq.feeds[k], pnp=pnp, pipelined=True)
             assert ca["pnp_ok"] == 1 and cb["pnp_ok"] == 1 and np.array_equal(Ta, Tb), k
-            assert ca["n_inliers"] == cb["n_inliers"] and cb["n_promoted"] == 0
-            assert cb["n_landmarks"] == cb["n_inliers"]            # as of the pose: pruned, nothing promoted yet
+            assert ca["n_inliers"] == cb["n_inliers"]
+            assert cb["n_landmarks"] == cb["n_inliers"]            # as of the pose: pruned, promoted rows not appended yet
+            if k > 1:   # the candidates were classified on the side stream during the tracking: final counts
+                assert cb["n_promoted"] == ca["n_promoted"] and cb["n_candidates_lost"] == ca["n_candidates_lost"]
+                assert cb["n_candidates"] + len(sq.feeds[k]) == ca["n_candidates"]
         # leave the pipelined mode: one synchronous call on both, then compare everything
         Ta, ca = a.process_frame(sq.frames[n], n, n + 1, K, 1.0, sq.feeds[n], pnp=pnp)
         Tb, cb = b.process_frame(sq.frames[n], n, n + 1, K, 1.0, sq.feeds[n], pnp=pnp)
@@ -596,3 +602,65 @@ def test_frame_ingest_from_files(dropin, scene_mod, tmp_path):
             pass
     with pytest.raises(ValueError):
         dropin.FrameIngest(paths, depth=2)
+
+
+def test_early_classification_paths(pkg, scene_mod):
+    """vo_klt_track_landmarks_ex: the candidate side of the promotion classified on the side stream during
+    the tracking.  Finished by a promotion with the same alpha, redone with another alpha, taken back by a
+    look at the candidates, and without a pose (fewer than 4 landmarks): always the state the plain
+    path reaches, bit for bit."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    K = sq.K
+    pnp = pkg.pnp_defaults()
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)   # plain
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)   # early classification
+    try:
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        pend = None
+        for k in range(1, 13):
+            for c in (a, b):
+                c.upload_frame(sq.frames[k], k + 1)
+            a.klt_track_landmarks(k, k + 1, add=pend)
+            b.klt_track_landmarks(k, k + 1, add=pend, early_alpha=1.0)
+            alpha = 1.0 if k % 3 else 0.4                         # every third frame: another threshold
+            if k % 4 == 2:
+                Ca, Cb = a.get_candidates(), b.get_candidates()   # looks at the candidates: taken back
+                assert all(np.array_equal(u, v) for u, v in zip(Ca, Cb))
+            oka, Ta, na = a.pnp_ransac(K, pnp)
+            a.track_triangulate_promote(k, k + 1, K, Ta, alpha)
+            if k % 2:
+                okb, Tb, nb, _ = b.pnp_ransac_promote(K, pnp, alpha, early=True)
+                b.promote_commit()
+            else:
+                okb, Tb, nb = b.pnp_ransac(K, pnp)
+                b.track_triangulate_promote(k, k + 1, K, Tb, alpha)
+            assert oka and okb and na == nb and np.array_equal(Ta, Tb), k
+            pend = (sq.feeds[k].copy(), Ta.copy()) if len(sq.feeds[k]) else None
+            ca, cb = a.counters(), b.counters()
+            for key in ("n_landmarks", "n_candidates", "n_promoted", "n_candidates_lost", "cf_alias"):
+                assert ca[key] == cb[key], (k, key)
+            Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+            assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb), k
+            for u, v in zip(a.get_candidates(), b.get_candidates()):
+                assert np.array_equal(u, v)
+        # no pose: three landmarks only
+        for c in (a, b):
+            P, X = c.get_state()
+            c.set_state(P[:3], X[:3])
+        k = 13
+        Ta, ca = None, None
+        a.upload_frame(sq.frames[k], k + 1)
+        a.klt_track_landmarks(k, k + 1, add=pend)
+        oka, _, _ = a.pnp_ransac(K, pnp)
+        assert not oka
+        Tb, cb = b.process_frame(sq.frames[k], k, k + 1, K, 1.0, None, pnp=pnp)   # (tracks with the early half)
+        assert cb["pnp_ok"] == 0 and cb["n_promoted"] == 0
+        ca = a.counters()
+        assert ca["n_landmarks"] == cb["n_landmarks"]
+        Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+        assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+    finally:
+        a.close(); b.close()
