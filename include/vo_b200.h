@@ -155,6 +155,10 @@ int vo_get_candidates(vo_ctx* ctx, float* C, double* F, double* T, int cap, int*
 int vo_get_lost(vo_ctx* ctx, float* lost, int cap, int* n);
 int vo_get_counters(vo_ctx* ctx, vo_counters* out);   /* synchronises */
 int vo_peek_counters(vo_ctx* ctx, vo_counters* out);  /* as of the last synchronising call; no sync */
+/* Diagnostics: %globaltimer stamps (ns) taken by the CTA that finished the last RANSAC run - {kernel entry,
+ * its P3P done, its hypotheses scored, chunk bookkeeping done, inlier mask done, LM refit done, pruning
+ * done, 0}.  Synchronises. */
+int vo_debug_pnp_stamps(vo_ctx* ctx, uint64_t out[8]);
 
 /* a1  KeypointsToLandmarksAssociator.associateKeypointsToLandmarks (vo_pipeline.py:188-227):
  * KLT of P from prev to next frame, keep status==1 rows of P and X.  The candidates C are tracked

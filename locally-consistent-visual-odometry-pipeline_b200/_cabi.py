@@ -90,6 +90,7 @@ SIGNATURES = {
     "vo_klt_track_landmarks_add": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, _PI]),
     "vo_klt_track_landmarks_ex": (c_int, [c_void_p, c_i64, c_i64, _PK, c_void_p, c_int, c_void_p, c_double, _PI]),
     "vo_track_rollback": (c_int, [c_void_p]),
+    "vo_debug_pnp_stamps": (c_int, [c_void_p, c_void_p]),
     "vo_map_reset": (c_int, [c_void_p]),
     "vo_map_accumulate": (c_int, [c_void_p, c_void_p, c_double, c_double, c_int, _PI]),
     "vo_map_get": (c_int, [c_void_p, c_void_p, c_int, _PI, c_void_p, c_int, _PI, c_void_p]),
@@ -378,6 +379,12 @@ class Context:
                                                    float(alpha_deg), _ptr(T), ctypes.byref(ninl), ctypes.byref(ok),
                                                    None if early else ctypes.byref(nprom)))
         return bool(ok.value), T, ninl.value, (None if early else nprom.value)
+
+    def pnp_stamps(self):
+        """ns between the stamps of the last RANSAC run: P3P, scoring, bookkeeping, mask, LM, pruning."""
+        t = np.zeros(8, np.uint64)
+        self._check(self.lib.vo_debug_pnp_stamps(self.h, _ptr(t)))
+        return np.diff(t[:7].astype(np.int64))
 
     def track_rollback(self):
         self._check(self.lib.vo_track_rollback(self.h))

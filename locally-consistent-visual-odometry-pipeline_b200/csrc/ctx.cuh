@@ -235,6 +235,9 @@ struct DevScalars {
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
+    // %globaltimer (ns) stamps of the CTA that finished the last RANSAC run (vo_debug_pnp_stamps):
+    // entry, P3P done, hypotheses scored, chunk bookkeeping done, inlier mask done, LM done, pruning done
+    unsigned long long stamps[8];
 };
 
 struct Pipeline {

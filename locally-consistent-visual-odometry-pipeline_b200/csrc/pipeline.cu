@@ -359,6 +359,15 @@ static int fill_counters(vo_ctx* c, vo_counters* out, bool sync)
 }
 
 int vo_get_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, true); }
+// diagnostics: %globaltimer stamps (ns) of the last RANSAC run, see DevScalars::stamps.  Synchronises.
+int vo_debug_pnp_stamps(vo_ctx* c, uint64_t out[8])
+{
+    VO_NEED(c);
+    if (!out) return VO_ERR_INVALID;
+    VO_TRY(read_scalars(c));
+    for (int k = 0; k < 8; k++) out[k] = c->pipe->h_sc->stamps[k];
+    return VO_OK;
+}
 // values as of the last synchronising call (no device access)
 int vo_peek_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, false); }
 

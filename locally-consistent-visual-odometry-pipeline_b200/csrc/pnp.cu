@@ -457,6 +457,13 @@ __device__ void lm_accumulate(const double* Rt, const double* K, const float4* _
     __syncthreads();
 }
 
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __restrict__ q4,
                              const float* __restrict__ qv, uint8_t* mask, const PnpArgs& a, const FinalizeBufs& fb, int n)
 {
@@ -494,6 +501,7 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
 #pragma unroll
         for (int w = 0; w < kFinThreads / 32; w++) ninl += sWarpTot[w];
 
+        if (tid == 0) sc->stamps[4] = gtime();
         // ---- LM: evaluate at the current pose, then trial steps ------------------------------------
         lm_accumulate(sRt, a.K, q4, qv, mask, n, sPart, sAcc);
         if (tid == 0) {
@@ -564,6 +572,7 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
             }
             sc->T[12] = 0.; sc->T[13] = 0.; sc->T[14] = 0.; sc->T[15] = 1.;
             sc->cost = sCost; sc->lm_iters = sIters;
+            sc->stamps[5] = gtime();
         }
     } else {
         for (int i = tid; i < n; i += kFinThreads) mask[i] = 0;
@@ -623,6 +632,8 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
     __shared__ int sCount[kHypThreads / 32];
     pdl_prologue();
     const int tid = threadIdx.x;
+    const unsigned long long t_in = gtime();
+    unsigned long long t_p3p = t_in;
     const int n = min(sc->n_tracked, a.n_upper);
     // the first chunk lies inside the initial budget by construction (one CTA per hypothesis); later
     // chunks run on a fixed small grid that strides over whatever budget the previous chunk's
@@ -653,6 +664,7 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
             }
         }
         __syncthreads();
+        t_p3p = gtime();
         if (sValid) {
             double R[9], t[3];
 #pragma unroll
@@ -678,6 +690,7 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
     }
     // ---- chunk bookkeeping by the last CTA to get here --------------------------------------------
     __syncthreads();
+    const unsigned long long t_scored = gtime();
     if (tid == 0) {
         __threadfence();
         sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
@@ -691,8 +704,12 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
     // the run is over (budget reached, or this was the last chunk) and not refitted yet: refit here
     if (!sc->done || sc->finalized) return;
     __syncthreads();
-    if (tid == 0) sc->finalized = 1;
+    if (tid == 0) {
+        sc->finalized = 1;
+        sc->stamps[0] = t_in; sc->stamps[1] = t_p3p; sc->stamps[2] = t_scored; sc->stamps[3] = gtime();
+    }
     pnp_finalize(sc, hyp, q4, qv, mask, a, fb, n);
+    if (tid == 0) sc->stamps[6] = gtime();
 }
 
 }  // namespace
