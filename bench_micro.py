@@ -73,7 +73,7 @@ def main():
     sm_mhz = pk.get("sm_max_mhz", 1965.0)
     fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12      # TFLOP/s, CUDA-core FMA
     ptr = lambda t: ctypes.c_void_p(t.data_ptr())
-    want = set(args.only.split(",")) if args.only else {"klt", "pyramid", "ransac", "dlt", "gftt"}
+    want = set(args.only.split(",")) if args.only else {"klt", "pyramid", "ransac", "dlt", "gftt", "map"}
 
     def check(r):
         if r != 0:
@@ -214,6 +214,46 @@ def main():
         except ImportError:
             pass
         print(json.dumps(line))
+    if "map" in want:
+        # trajectory / map bookkeeping: main.py:239-255 per frame on the device, and the
+        # headless plot; numpy (the reference's own calls, oracle/map_ref.py) on the host beside it
+        import time
+        from oracle import map_ref
+        rng = np.random.default_rng(9)
+        nl = 2000
+        X = rng.uniform(-40, 40, size=(nl, 3))
+        P = rng.uniform(0, 1000, size=(nl, 2)).astype(np.float32)
+        ctx.set_state(P, X)
+        T = np.eye(4); T[:3, 3] = (0.3, -0.1, 2.0)
+        d_T = torch.from_numpy(T).to(dev)
+        check(lib.vo_map_reset(h))
+
+        def run():
+            check(lib.vo_map_accumulate(h, ptr(d_T), 3.0, 50.0, 0, None))
+        med, best = timed(torch, stream, run, 200)
+        ref = map_ref.MapRef()
+        ts = []
+        for _ in range(200):
+            t0 = time.perf_counter()
+            ref.update(T, X)
+            ts.append((time.perf_counter() - t0) * 1e3)
+        traj, pts, _ = ctx.map_get()
+        line = {"kernel": "map_accumulate_kernel", "regime": "2000 landmarks per frame, %d rows accumulated" % len(pts),
+                "ms": med, "ms_min": best, "algorithmic_bytes": nl * 24 + int(len(pts) / 202) * 24,
+                "numpy_ms": float(np.median(ts)), "note": "one launch per frame, no D2H; the reference reads all landmarks back and filters with numpy"}
+        print(json.dumps(line))
+        img = torch.empty((600, 1200, 3), dtype=torch.uint8, device=dev)
+        bounds = np.zeros(4)
+
+        def run2():
+            check(lib.vo_map_render(h, ptr(img), 1200, 600, 40, 3, bounds.ctypes.data))
+        med, best = timed(torch, stream, run2, 20)
+        t0 = time.perf_counter()
+        oimg, ob = map_ref.render(traj, pts, 1200, 600, 40, 3)
+        t_np = (time.perf_counter() - t0) * 1e3
+        print(json.dumps({"kernel": "map_bounds + map_clear + map_points + map_path", "regime": "1200x600 plot of %d landmarks, %d poses" % (len(pts), len(traj)),
+                          "ms": med, "ms_min": best, "algorithmic_bytes": 1200 * 600 * 3 + len(pts) * 24,
+                          "numpy_ms": t_np, "same_pixels_as_oracle": bool(np.array_equal(oimg, img.cpu().numpy()))}))
     ctx.close()
 
 
