@@ -302,6 +302,10 @@ struct Pipeline {
     bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0;
     double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
     cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion
+    // read-back right behind the FIRST RANSAC chunk (the run usually ends there; the second chunk kernel then only
+    // drains): pinned copies of the scalar block taken there and behind the last chunk
+    cudaEvent_t ev_pose_first = nullptr; DevScalars* h_sc_first = nullptr; DevScalars* h_sc_late = nullptr;
+    bool first_rb_enqueued = false;
     int64_t spec_prev_key = -1, spec_next_key = -1;
     DevScalars* d_sc = nullptr;
     DevScalars* h_sc = nullptr;  // pinned mirror
@@ -348,6 +352,7 @@ struct PnpLaunch {
     double K[9];
     vo_pnp_params prm;
     bool compact;                       // prune landmark buffers to the inliers (estimatePose)
+    bool readback_after_first = false;  // copy the scalar block to Pipeline::h_sc_first behind the first chunk (if more follow)
 };
 int launch_pnp(Ctx* c, const PnpLaunch& L);
 // raw cv::RNG output table on the device, large enough for H iterations (grows, never shrinks)

@@ -52,6 +52,8 @@ void pipeline_free(Ctx* c)
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
     if (p->ev_pose) cudaEventDestroy(p->ev_pose);
+    if (p->ev_pose_first) cudaEventDestroy(p->ev_pose_first);
+    cudaFreeHost(p->h_sc_first); cudaFreeHost(p->h_sc_late);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
     delete p;
     c->pipe = nullptr;
@@ -524,6 +526,9 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
     L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
     L.d_sets_in = nullptr; L.compact = true;
+    static const bool no_first_rb = getenv("VO_NO_FIRST_RB") != nullptr;   // A/B switch (tools/e2e_phases.py)
+    L.readback_after_first = n_promoted == nullptr && !no_first_rb;
+    p->first_rb_enqueued = false;
     memcpy(L.K, K, sizeof(L.K));
     VO_TRY(launch_pnp(c, L));
     p->packed_valid = false;
@@ -540,7 +545,10 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     if (early) {
         VO_TRY(join_side_stream(c));   // a deferred append on the side stream writes n_cand (long done by now)
         if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
-        VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+        // (with a read-back behind the first chunk in flight, this one goes to its own buffer: the host may be
+        // working on h_sc already when it lands)
+        VO_CUDA(c, cudaMemcpyAsync(p->first_rb_enqueued ? p->h_sc_late : p->h_sc, p->d_sc, sizeof(DevScalars),
+                                   cudaMemcpyDeviceToHost, c->stream));
         VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));
     }
     VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
@@ -553,8 +561,9 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
         if (trace) {   // host time blocked on the pose (tools/profile_e2e.py)
             timespec t0, t1;
             clock_gettime(CLOCK_MONOTONIC, &t0);
-            const bool ready = cudaEventQuery(p->ev_pose) == cudaSuccess;
-            cudaEventSynchronize(p->ev_pose);
+            cudaEvent_t ev_w = p->first_rb_enqueued ? p->ev_pose_first : p->ev_pose;
+            const bool ready = cudaEventQuery(ev_w) == cudaSuccess;
+            cudaEventSynchronize(ev_w);
             clock_gettime(CLOCK_MONOTONIC, &t1);
             p->trace_wait_us += (t1.tv_sec - t0.tv_sec) * 1e6 + (t1.tv_nsec - t0.tv_nsec) * 1e-3;
             p->trace_ready += ready; p->trace_n++;
@@ -562,7 +571,18 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
                 fprintf(stderr, "[vo trace] pose wait %.1f us/frame, pose already there %d/%d\n", p->trace_wait_us / p->trace_n,
                         p->trace_ready, p->trace_n);
         }
-        VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
+        if (p->first_rb_enqueued) {
+            p->first_rb_enqueued = false;
+            VO_CUDA(c, cudaEventSynchronize(p->ev_pose_first));
+            if (p->h_sc_first->finalized) {
+                *p->h_sc = *p->h_sc_first;          // the run ended in its first chunk: this is the final block
+            } else {
+                VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
+                *p->h_sc = *p->h_sc_late;
+            }
+        } else {
+            VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
+        }
         DevScalars* s = p->h_sc;   // as of the PnP: the promoted rows are not appended yet
         s->spec_n_land = s->n_land;   // what a rollback restores on the host side
         if (cls_done) {   // the side stream has classified the candidates: their counts are final already

@@ -783,6 +783,19 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         c->launches++;
         h0 = h1;
         if (last) break;
+        if (k == 0 && L.readback_after_first) {
+            // the run usually ends inside the first chunk (finalized = 1 then, pose and counts final): let the
+            // host have the scalar block from here instead of from behind the draining later chunks
+            VO_TRY(join_side_stream(c));   // (a deferred append on the side stream writes n_cand)
+            if (!p->h_sc_first) {
+                VO_CUDA(c, cudaMallocHost((void**)&p->h_sc_first, sizeof(DevScalars)));
+                VO_CUDA(c, cudaMallocHost((void**)&p->h_sc_late, sizeof(DevScalars)));
+                VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose_first, cudaEventDisableTiming));
+            }
+            VO_CUDA(c, cudaMemcpyAsync(p->h_sc_first, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+            VO_CUDA(c, cudaEventRecord(p->ev_pose_first, c->stream));
+            p->first_rb_enqueued = true;
+        }
     }
     if (L.compact) {
         const int nxt = (p->cur + 1) % 3;
