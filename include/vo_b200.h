@@ -210,7 +210,7 @@ int vo_pnp_ransac(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, d
  * n_candidates_lost are the final ones. */
 int vo_pnp_ransac_promote(vo_ctx* ctx, const double K[9], const vo_pnp_params* params, double alpha_deg,
                           double T44[16], int* n_inliers, int* ok, int* n_promoted);
-int vo_promote_commit(vo_ctx* ctx);
+int vo_promote_commit(vo_ctx* ctx);   /* (a vo_klt_track_landmarks* call behind the speculation confirms it too) */
 int vo_promote_rollback(vo_ctx* ctx);
 int vo_promote_pending(vo_ctx* ctx);
 /* 1 if the candidates were tracked over (prev, next) together with the landmarks and not consumed yet */

@@ -384,6 +384,7 @@ static int track_landmarks_impl(vo_ctx* c, int64_t prev_key, int64_t next_key, c
     FrameSlot* a = get_frame(c, prev_key);
     FrameSlot* b = get_frame(c, next_key);
     if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
+    p->spec_pending = false;   // a tracking step behind a speculative promotion confirms it (= vo_promote_commit)
     // candidates ride along: triangulate_landmark (vo:501) tracks them over the same frame pair, and
     // their tracking does not depend on the pose
     VO_TRY(track_both(c, a, b, prm, true, add, early_alpha));

@@ -680,10 +680,11 @@ class LandmarkTriangulator():
                      and rt.pair[0] is old_frame and rt.pair[1] is new_frame
                      and float(threshold) == sp['alpha'] and new_pose.tobytes() == sp['T']
                      and np.asarray(self.K, np.float64).tobytes() == sp['K'])
+        committed = True
         if confirmed:
             # the promotion ran ahead of estimatePose's sync with exactly these arguments
             rt.spec = None
-            rt.ctx.promote_commit()
+            committed = False     # (left to the tracking call below when there is one: one ctypes call less)
         else:
             rt.drop_speculation()
             k_old, k_new = rt.pair_keys(old_frame, new_frame)
@@ -738,10 +739,19 @@ class LandmarkTriangulator():
         # (vo_track_rollback) if it is called with anything else than (new_frame, that frame, this state).
         pre = rt.last_prefetch
         if (confirmed and pre is not None and bool(_cfg('speculative_tracking'))
-                and (method == 'feed' or device_shi) and rt.ctx.has_frame(pre[0])):
-            add, rt.pending_add = rt.pending_add, None
-            rt.ctx.klt_track_landmarks(rt.pair[3], pre[0], rt.klt, add=add)
-            rt.spec_track = {'old': new_frame, 'fp': pre[2], 'k_old': rt.pair[3], 'k_new': pre[0], 'state': state}
+                and (method == 'feed' or device_shi)):
+            add = rt.pending_add
+            try:    # (confirms the promotion as well; fails only if the frame ahead has left the slot cache)
+                rt.ctx.klt_track_landmarks(rt.pair[3], pre[0], rt.klt, add=add)
+                rt.pending_add = None
+                committed = True
+                rt.spec_track = {'old': new_frame, 'fp': pre[2], 'k_old': rt.pair[3], 'k_new': pre[0], 'state': state}
+            except _cabi.VoError as e:
+                if e.code != -4:      # anything but VO_ERR_NOFRAME is a real failure
+                    raise
+                rt.last_prefetch = None
+        if not committed:
+            rt.ctx.promote_commit()
         if isinstance(extended_state, DeviceExtendedState):
             extended_state._rebind(rt.ext_version)
         else:
