@@ -100,6 +100,46 @@ __device__ __forceinline__ void sample_run(const uint8_t* __restrict__ p, int st
     for (int x = 0; x < kRun; x++) v[x] >>= 9;
 }
 
+// ---- the moving window's neighbourhood in shared memory ------------------------------------------
+// A Gauss-Newton step reads 12 words per lane from 22 different rows of the next image: one warp-wide
+// request touches >= 21 L1 lines, so the L1 tag stage (one line per cycle, shared by every warp of the
+// SM), not the arithmetic, paces the step (ncu set g: long-scoreboard 39 % of the stall samples, 20
+// sectors per request).  Per level the warp copies the (WIN+11) x 48 B neighbourhood of the starting
+// position into its own shared-memory tile once (12 requests of ~4 lines) and samples from there while
+// the window stays inside it (+-5 rows, -12..+10 columns); outside - or at the very edge of the padded
+// level - the step reads global memory as before.  Same bytes either way: results do not change.
+template <int WIN> struct Tile {
+    static constexpr int kWords = (WIN + 18) / 4 + 3;           // 12 words (48 B) per row
+    static constexpr int kPitch = kWords | 1;                    // odd: rows spread over the banks
+    static constexpr int kRows = WIN + 1 + 10;                   // 32
+    static constexpr int kOyMax = kRows - (WIN + 1);             // 10
+    static constexpr int kOxMax = 4 * (kWords - 3) + 3 - (WIN - kRun);   // 25: last run's third word is in the row
+    static constexpr int kOx0 = (kOxMax / 2) | 3;                // start offset 12..15 after the alignment
+    static constexpr int kOy0 = kOyMax / 2;
+};
+
+__device__ __forceinline__ void load8_s(const unsigned* __restrict__ row, int xb, unsigned& W0, unsigned& W1)
+{
+    const unsigned* a = row + (xb >> 2);
+    const unsigned sh = ((unsigned)xb & 3u) * 8u;
+    const unsigned a0 = a[0], a1 = a[1], a2 = a[2];
+    W0 = __funnelshift_r(a0, a1, sh);
+    W1 = __funnelshift_r(a1, a2, sh);
+}
+
+__device__ __forceinline__ void sample_run_s(const unsigned* __restrict__ row, int pitch, int xb, int wtop, int wbot, int* v)
+{
+    unsigned T0, T1, B0, B1;
+    load8_s(row, xb, T0, T1);
+    load8_s(row + pitch, xb, B0, B1);
+#pragma unroll
+    for (int x = 0; x < kRun; x++) v[x] = 1 << 8;
+    row7(T0, T1, wtop, v);
+    row7(B0, B1, wbot, v);
+#pragma unroll
+    for (int x = 0; x < kRun; x++) v[x] >>= 9;
+}
+
 template <int WIN>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
 klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const float2* __restrict__ ptsA,
@@ -107,14 +147,17 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
                  const int32_t* __restrict__ nB_dev, const int nB_upper, const int b_off,
                  float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
                  int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
-                 const double min_eig_thr)
+                 const double min_eig_thr, const int use_tile)
 {
     static_assert(WIN % kRun == 0, "window side must be a multiple of the run length");
     constexpr int RPR = WIN / kRun;            // runs per row
     constexpr int NRUNS = WIN * RPR;           // 63
     constexpr int NR = (NRUNS + 31) / 32;      // runs per lane
+    using TL = Tile<WIN>;
+    __shared__ unsigned s_tile[kWarpsPerBlock][TL::kRows * TL::kPitch];
     pdl_prologue();
     const int lane = threadIdx.x & 31;
+    unsigned* const tile = s_tile[threadIdx.x >> 5];
     int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     // two track lists share one launch: landmarks (A) then candidates (B, written at b_off)
     float2 pt;
@@ -206,6 +249,23 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
         int joff[NR];
 #pragma unroll
         for (int r = 0; r < NR; r++) joff[r] = rrow[r] * jstride + rcol[r];
+        // stage the neighbourhood of the starting position (padded coordinates, x origin word aligned)
+        const int X0 = __float2int_rd(qx) + kPad, Y0 = __float2int_rd(qy) + kPad;
+        const int tx0 = (X0 - TL::kOx0 + 3) & ~3, ty0 = Y0 - TL::kOy0;
+        const bool tile_ok = use_tile && max_iters > 0 && X0 >= 0 && X0 < jstride && tx0 >= 0 && tx0 + 4 * TL::kWords <= jstride &&
+                             ty0 >= 0 && ty0 + TL::kRows <= LJ.h + 2 * kPad;
+        if (tile_ok) {
+            const unsigned* src = reinterpret_cast<const unsigned*>(LJ.img + (size_t)ty0 * jstride + tx0);
+            const int wstride = jstride >> 2;
+            __syncwarp();   // the previous level's readers are done
+#pragma unroll
+            for (int i = 0; i < (TL::kRows * TL::kWords + 31) / 32; i++) {
+                const int idx = i * 32 + lane;
+                const int row = idx / TL::kWords, col = idx - row * TL::kWords;
+                if (idx < TL::kRows * TL::kWords) tile[row * TL::kPitch + col] = __ldg(src + (size_t)row * wstride + col);
+            }
+            __syncwarp();
+        }
         for (int j = 0; j < max_iters; j++) {
             const int jx = __float2int_rd(qx), jy = __float2int_rd(qy);
             if (jx < -WIN || jx >= LJ.w || jy < -WIN || jy >= LJ.h) {
@@ -215,17 +275,32 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
             iters++;
             w = make_weights(__fsub_rn(qx, (float)jx), __fsub_rn(qy, (float)jy));
             const int wtop = pack_w(w.w00, w.w01), wbot = pack_w(w.w10, w.w11);
-            const uint8_t* jb = LJ.img + (size_t)(jy + kPad) * jstride + (jx + kPad);
             int b1 = 0, b2 = 0;
+            const int ox = jx + kPad - tx0, oy = jy + kPad - ty0;
+            if (tile_ok && (unsigned)ox <= (unsigned)TL::kOxMax && (unsigned)oy <= (unsigned)TL::kOyMax) {
 #pragma unroll
-            for (int r = 0; r < NR; r++) {
-                int v[kRun];
-                sample_run(jb + joff[r], jstride, wtop, wbot, v);
+                for (int r = 0; r < NR; r++) {
+                    int v[kRun];
+                    sample_run_s(tile + (oy + rrow[r]) * TL::kPitch, TL::kPitch, ox + rcol[r], wtop, wbot, v);
 #pragma unroll
-                for (int x = 0; x < kRun; x++) {
-                    const int diff = v[x] - Iw[r][x];
-                    b1 += diff * dIx[r][x];
-                    b2 += diff * dIy[r][x];
+                    for (int x = 0; x < kRun; x++) {
+                        const int diff = v[x] - Iw[r][x];
+                        b1 += diff * dIx[r][x];
+                        b2 += diff * dIy[r][x];
+                    }
+                }
+            } else {
+                const uint8_t* jb = LJ.img + (size_t)(jy + kPad) * jstride + (jx + kPad);
+#pragma unroll
+                for (int r = 0; r < NR; r++) {
+                    int v[kRun];
+                    sample_run(jb + joff[r], jstride, wtop, wbot, v);
+#pragma unroll
+                    for (int x = 0; x < kRun; x++) {
+                        const int diff = v[x] - Iw[r][x];
+                        b1 += diff * dIx[r][x];
+                        b2 += diff * dIy[r][x];
+                    }
                 }
             }
             const float fb1 = __fmul_rn(__ll2float_rn(warp_sum_i64(b1)), FLT_SCALE);
@@ -332,10 +407,11 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
     int max_iters = prm.max_iters < 0 ? 0 : (prm.max_iters > 100 ? 100 : prm.max_iters);
     const double eps = prm.epsilon < 0. ? 0. : (prm.epsilon > 10. ? 10. : prm.epsilon);
     const double eps2 = eps * eps;
+    static const bool no_tile = getenv("VO_KLT_NO_TILE") != nullptr;   // A/B switch (same results either way)
     const int blocks = (n_upper + nB_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
     klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
         prev, next, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
-        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr);
+        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : 1);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
