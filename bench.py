@@ -27,6 +27,7 @@ k's stages.  Every step still copies and builds exactly one frame inside the tim
 N > 1 (torchrun): one independent stream per GPU, no collective on the data path (weak scaling).
 """
 import argparse
+import gc
 import importlib
 import json
 import os
@@ -332,10 +333,15 @@ def run_e2e(pkg, sq, steps, warmup, local_rank, world, prefetch=True):
     h2d = d2h = 0
     t0 = None
     img2 = None
+    trace = [] if os.environ.get("VO_BENCH_TRACE") else None   # per-step host times to stderr (diagnostic)
     for s in range(steps + warmup):
         if s == warmup:
             vo._runtime().ctx.synchronize()
             barrier(world)
+            # as timeit does: no cyclic-GC pass inside the timed region (38 ms; one full collection of an
+            # interpreter with torch and cv2 loaded costs several ms and made this leg bimodal)
+            gc.collect()
+            gc.disable()
             t0 = time.perf_counter()
             h2d = d2h = 0
         a, b = order[s], order[s + 1]
@@ -357,9 +363,17 @@ def run_e2e(pkg, sq, steps, warmup, local_rank, world, prefetch=True):
         n_land, n_cand = c["n_landmarks"] + c["n_promoted"], c["n_candidates"] + len(feed)
         h2d += w * h + feed.nbytes + 128
         d2h += 256
+        if trace is not None:
+            trace.append(time.perf_counter())
     vo._runtime().ctx.synchronize()
     barrier(world)
     dt = time.perf_counter() - t0
+    gc.enable()
+    if trace:
+        d = np.diff(np.array(trace[warmup:])) * 1e6
+        print("e2e step us: median %.1f p90 %.1f p99 %.1f max %.1f, steps > 2x median: %d (%.2f ms over the median)"
+              % (np.median(d), np.percentile(d, 90), np.percentile(d, 99), d.max(), int((d > 2 * np.median(d)).sum()),
+                 float((d - np.median(d))[d > 2 * np.median(d)].sum()) * 1e-3), file=sys.stderr)
     vo._reset_runtime()
     sys.modules.pop("vo_pipeline", None)
     sys.path.remove(os.path.join(ROOT, PKG))
