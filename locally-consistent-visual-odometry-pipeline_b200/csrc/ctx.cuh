@@ -301,6 +301,7 @@ struct Pipeline {
     bool ahead_valid = false; int64_t ahead_prev = 0, ahead_next = 0;
     bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0;
     double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
+    cudaEvent_t ev_land = nullptr;   // behind the landmark KLT launch (candidates' KLT ordered after it, see track_both)
     cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion
     // read-back right behind the FIRST RANSAC chunk (the run usually ends there; the second chunk kernel then only
     // drains): pinned copies of the scalar block taken there and behind the last chunk

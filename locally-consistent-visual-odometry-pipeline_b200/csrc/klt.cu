@@ -116,6 +116,14 @@ template <int WIN> struct Tile {
     static constexpr int kOxMax = 4 * (kWords - 3) + 3 - (WIN - kRun);   // 25: last run's third word is in the row
     static constexpr int kOx0 = (kOxMax / 2) | 3;                // start offset 12..15 after the alignment
     static constexpr int kOy0 = kOyMax / 2;
+    // the template window of a level: (WIN+1) rows of the image (word aligned, <= 7 words) and of the
+    // derivative plane ((WIN+1) short2 per row), staged the same way for the per-level set-up
+    static constexpr int kIWords = (3 + WIN + 1 + 3) / 4 + 1;     // 8 (7 used + the over-read word of load8_s)
+    static constexpr int kIPitch = kIWords | 1;                   // 9
+    static constexpr int kDPitch = (WIN + 1) | 1;                 // 23
+    static constexpr int kSetupWords = (WIN + 1) * (kIPitch + kDPitch);
+    static constexpr int kTileWords = kRows * kPitch;
+    static constexpr int kSmemWords = kSetupWords > kTileWords ? kSetupWords : kTileWords;
 };
 
 __device__ __forceinline__ void load8_s(const unsigned* __restrict__ row, int xb, unsigned& W0, unsigned& W1)
@@ -154,7 +162,7 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
     constexpr int NRUNS = WIN * RPR;           // 63
     constexpr int NR = (NRUNS + 31) / 32;      // runs per lane
     using TL = Tile<WIN>;
-    __shared__ unsigned s_tile[kWarpsPerBlock][TL::kRows * TL::kPitch];
+    __shared__ unsigned s_tile[kWarpsPerBlock][TL::kSmemWords];
     pdl_prologue();
     const int lane = threadIdx.x & 31;
     unsigned* const tile = s_tile[threadIdx.x >> 5];
@@ -212,21 +220,56 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
         const int stride = LI.stride;
         const size_t base = (size_t)(iy + kPad) * stride + (ix + kPad);
         int a11 = 0, a12 = 0, a22 = 0;
+        // stage the (WIN+1)^2 neighbourhood of image and derivative plane (always inside the padded level:
+        // ix + kPad >= kPad - WIN and the row has kPad + slack behind the image)
+        unsigned* const sI = tile;
+        short2* const sD = reinterpret_cast<short2*>(tile + (WIN + 1) * TL::kIPitch);
+        const int xal = (ix + kPad) & 3;
+        if (use_tile) {
+            const unsigned* srcI = reinterpret_cast<const unsigned*>(LI.img + base - xal);
+            const short2* srcD = LI.deriv + base;
+            const int wstride = stride >> 2;
+            __syncwarp();   // the previous level's iteration tile is no longer read
 #pragma unroll
-        for (int r = 0; r < NR; r++) {
-            const int off = rrow[r] * stride + rcol[r];
-            sample_run(LI.img + base + off, stride, pack_w(w.w00, w.w01), pack_w(w.w10, w.w11), Iw[r]);
-            const short2* d = LI.deriv + base + off;
-            short2 t = d[0], b = d[stride];
+            for (int i = 0; i < ((WIN + 1) * TL::kIWords + 31) / 32; i++) {
+                const int idx = i * 32 + lane;
+                const int row = idx / TL::kIWords, col = idx - row * TL::kIWords;
+                if (idx < (WIN + 1) * TL::kIWords) sI[row * TL::kIPitch + col] = __ldg(srcI + (size_t)row * wstride + col);
+            }
+#pragma unroll
+            for (int i = 0; i < ((WIN + 1) * (WIN + 1) + 31) / 32; i++) {
+                const int idx = i * 32 + lane;
+                const int row = idx / (WIN + 1), col = idx - row * (WIN + 1);
+                if (idx < (WIN + 1) * (WIN + 1)) sD[row * TL::kDPitch + col] = srcD[(size_t)row * stride + col];
+            }
+            __syncwarp();
+        }
+        // one run's derivatives: bilinear blend of the Scharr plane, structure-tensor sums
+        auto deriv_run = [&](const short2* d, const int dstride, const int r) {
+            short2 t = d[0], b = d[dstride];
 #pragma unroll
             for (int x = 0; x < kRun; x++) {
-                const short2 tn = d[x + 1], bn = d[stride + x + 1];
+                const short2 tn = d[x + 1], bn = d[dstride + x + 1];
                 int ixv = (t.x * w.w00 + tn.x * w.w01 + b.x * w.w10 + bn.x * w.w11 + (1 << 13)) >> 14;
                 int iyv = (t.y * w.w00 + tn.y * w.w01 + b.y * w.w10 + bn.y * w.w11 + (1 << 13)) >> 14;
                 if (!rvalid[r]) { ixv = 0; iyv = 0; }
                 dIx[r][x] = ixv; dIy[r][x] = iyv;
                 a11 += ixv * ixv; a12 += ixv * iyv; a22 += iyv * iyv;
                 t = tn; b = bn;
+            }
+        };
+        if (use_tile) {
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                sample_run_s(sI + rrow[r] * TL::kIPitch, TL::kIPitch, xal + rcol[r], pack_w(w.w00, w.w01), pack_w(w.w10, w.w11), Iw[r]);
+                deriv_run(sD + rrow[r] * TL::kDPitch + rcol[r], TL::kDPitch, r);
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const int off = rrow[r] * stride + rcol[r];
+                sample_run(LI.img + base + off, stride, pack_w(w.w00, w.w01), pack_w(w.w10, w.w11), Iw[r]);
+                deriv_run(LI.deriv + base + off, stride, r);
             }
         }
         const float FLT_SCALE = 1.f / (1 << 20);

@@ -52,6 +52,7 @@ void pipeline_free(Ctx* c)
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
     for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
     if (p->ev_pose) cudaEventDestroy(p->ev_pose);
+    if (p->ev_land) cudaEventDestroy(p->ev_land);
     if (p->ev_pose_first) cudaEventDestroy(p->ev_pose_first);
     cudaFreeHost(p->h_sc_first); cudaFreeHost(p->h_sc_late);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
@@ -134,6 +135,12 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
             // side stream, and one driver call less on the host
             VO_TRY(launch_cand_add(c, p->h_add[f] + 16, n_add, p->h_add[f], nullptr, true));
             c->side_writes_counts = true;
+        }
+        static const int cand_order = getenv("VO_CAND_AFTER_LAND") ? atoi(getenv("VO_CAND_AFTER_LAND")) : 0;
+        if (cand_order && nA > 0) {
+            if (!p->ev_land) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_land, cudaEventDisableTiming));
+            VO_CUDA(c, cudaEventRecord(p->ev_land, c->stream));
+            VO_CUDA(c, cudaStreamWaitEvent(c->stream2, p->ev_land, 0));
         }
         if (p->profiling) cudaEventRecord(p->ev_side[0], c->stream2);
         VO_TRY(launch_klt2(c, a->pyr, b->pyr, nullptr, nullptr, 0, p->C[p->ccur].p, &p->d_sc->n_cand, nB, nA, p->klt_out.p,
