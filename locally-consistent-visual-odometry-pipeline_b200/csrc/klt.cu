@@ -12,7 +12,8 @@
 // aligned 32-bit words and re-aligned with funnel shifts, and its 7 bilinear values cost 14
 // DP2A (two 14-bit weights x two u8 taps per instruction) instead of 28 byte loads + 28 IMAD.
 // The template window I and its derivatives stay in registers for the whole level; only the
-// moving window of the next image is gathered each Gauss-Newton step (L1/L2 resident).  The
+// moving window of the next image is gathered each Gauss-Newton step - from a per-warp shared-memory
+// tile holding its neighbourhood (see Tile below), from global memory when it leaves the tile.  The
 // per-step sums are exact: products fit int32 per lane and the cross-lane sum is two REDUX.SUM
 // instructions (16-bit split), so results do not depend on the lane mapping or summation order.
 #include "ctx.cuh"
