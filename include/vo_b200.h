@@ -132,6 +132,8 @@ typedef struct vo_counters {
     int32_t klt_iters;                   /* sum of LK iterations over the last landmark KLT */
     int32_t klt_iters_candidates;        /* same over the last candidate KLT (set by the promotion step) */
     double reproj_cost;                  /* sum of squared reprojection errors of the refit */
+    int32_t n_appended;                  /* rows the last vo_append_landmarks / queued batch added */
+    int32_t reserved_;
 } vo_counters;
 
 /* Upload landmarks after bootstrap (main.py:198-200 vision.state = state).  Synchronises. */
@@ -232,6 +234,22 @@ int vo_get_candidate_tracks(vo_ctx* ctx, float* prev_pts, float* next_pts, uint8
  * Call after vo_track_triangulate_promote (new rows have alpha = 0 and are never promoted in the
  * frame they arrive, so the order does not change results). */
 int vo_add_candidates(vo_ctx* ctx, const double* pts, int n, const double T44[16]);
+
+/* Landmarks from outside the tracking loop, appended behind P/X: what the reference does with the fresh
+ * landmarks of its re-bootstrap (vo_pipeline.py:318-320, np.vstack onto associations['P'] / ['X']) and with
+ * the bootstrap result (main.py:198-200).  P: n x 2 float32 pixel positions in the frame tracked INTO last,
+ * X: n x 3 float64; host or device.  target_total > 0: top-up - only the first
+ * min(n, max(0, target_total - |P|)) rows are appended; the count is decided on the device (|P| is not known
+ * to the host without a round trip) and reported in vo_counters.n_appended.  Enqueued on the ctx stream, no
+ * synchronisation; pageable rows are copied before the call returns, device / pinned rows must stay valid
+ * until the next synchronising call.  Valid between frames (after the promotion step of one frame, before the
+ * tracking step of the next); a tracking step enqueued ahead (vo_process_frame_pipelined) is taken back. */
+int vo_append_landmarks(vo_ctx* ctx, const float* P, const double* X, int n, int target_total);
+/* The same, deferred: the batch is appended by the next vo_process_frame[_pipelined] right behind that
+ * frame's promotion step and candidate append - in front of a tracking step it enqueues ahead, so the frames
+ * stay overlapped.  Up to 4 batches per frame, appended in call order.  Rows must stay valid until the call
+ * AFTER that one returns (pageable rows: until that call returns). */
+int vo_queue_landmarks(vo_ctx* ctx, const float* P, const double* X, int n, int target_total);
 
 /* ---- SURVEY.md 8f-1 (first "next" row): the Shi-Tomasi candidate detector on the device.
  * Replaces cv2.goodFeaturesToTrack(new_frame, maxCorners=500, qualityLevel=0.03, minDistance=10,

@@ -43,7 +43,7 @@ class Counters(ctypes.Structure):
         "n_landmarks", "n_candidates", "n_tracked", "n_lost", "n_inliers", "pnp_ok", "ransac_iters",
         "best_hypothesis", "lm_iters", "n_promoted", "n_candidates_lost", "cf_alias", "klt_iters",
         "klt_iters_candidates")] + [
-        ("reproj_cost", c_double)]
+        ("reproj_cost", c_double), ("n_appended", ctypes.c_int32), ("reserved_", ctypes.c_int32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -103,6 +103,8 @@ SIGNATURES = {
     "vo_get_prev_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
     "vo_add_candidates": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vo_append_landmarks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
+    "vo_queue_landmarks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "vo_track_candidates": (c_int, [c_void_p, c_i64, c_i64, _PK]),
     "vo_get_candidate_tracks": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_process_frame": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_i64, c_i64, c_void_p, _PK, _PP,
@@ -435,6 +437,19 @@ class Context:
         pts = np.ascontiguousarray(pts, np.float64).reshape(-1, 2)
         T44 = np.ascontiguousarray(T44, np.float64)
         self._check(self.lib.vo_add_candidates(self.h, _ptr(pts), len(pts), _ptr(T44)))
+
+    def append_landmarks(self, P, X, target_total=0, queue=False):
+        """Append landmarks behind P/X (reference vo_pipeline.py:318-320); target_total > 0: top-up to that
+        many rows, decided on the device.  queue=True: with the next process_frame call.  Host arrays are
+        copied before the call returns (pageable) - keep pinned / device rows alive yourself."""
+        P = np.ascontiguousarray(P, np.float32).reshape(-1, 2)
+        X = np.ascontiguousarray(X, np.float64).reshape(-1, 3)
+        if len(P) != len(X):
+            raise ValueError("P and X must have the same number of rows")
+        if queue:
+            self._queued_rows = getattr(self, "_queued_rows", [])[-6:] + [(P, X)]   # keep the arrays alive
+        fn = self.lib.vo_queue_landmarks if queue else self.lib.vo_append_landmarks
+        self._check(fn(self.h, _ptr(P), _ptr(X), len(P), int(target_total)))
 
     def process_frame(self, img, prev_key, next_key, K, alpha_deg, new_candidates=None, klt=None, pnp=None,
                       want_counters=True, pipelined=False):

@@ -138,6 +138,7 @@ int vo_destroy(vo_ctx* c)
     for (auto& s : c->slots) { cudaFree(s.raw); cudaFree(s.img_pool); cudaFree(s.deriv_pool); if (s.ready) cudaEventDestroy(s.ready); }
     cudaFree(c->u_pts.p); cudaFree(c->u_out.p); cudaFree(c->u_err.p); cudaFree(c->u_status.p);
     cudaFree(c->u_iters.p); cudaFree(c->u_n.p);
+    cudaFree(c->fb_pts.p); cudaFree(c->fb_pts2.p); cudaFree(c->fb_status.p); cudaFree(c->fb_status2.p);
     cudaFreeHost(c->pinned_stage);
     cudaFreeHost(c->pinned_stage2);
     if (c->stream3) cudaStreamDestroy(c->stream3);

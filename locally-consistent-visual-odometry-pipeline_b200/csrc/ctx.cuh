@@ -118,8 +118,8 @@ struct Ctx {
     DevBuf<int32_t> u_iters;
     DevBuf<int32_t> u_n;
     // forward-backward check scratch
-    DevBuf<float> fb_pts;
-    DevBuf<uint8_t> fb_status;
+    DevBuf<float> fb_pts, fb_pts2;
+    DevBuf<uint8_t> fb_status, fb_status2;
 
     Detector det;
 
@@ -231,7 +231,7 @@ struct DevScalars {
     int32_t klt_iters_cand; // sum of LK iterations over the candidates (roofline accounting)
     int32_t ticket2;       // same for kernels enqueued on the side stream (they overlap main-stream kernels)
     int32_t klt_iters_cand2; // side-stream accumulator of klt_iters_cand (early classification), moved over by the finish kernel
-    int32_t pad2_;
+    int32_t n_appended;    // rows the last landmark append added (top-up decided on the device)
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -284,6 +284,12 @@ struct Pipeline {
     // deferred append riding on the side stream (vo_klt_track_landmarks_add): double-buffered staging
     double* h_add[2] = { nullptr, nullptr }; size_t h_add_cap = 0; int add_flip = 0;
     DevBuf<double> d_add[2];
+    // landmark rows waiting for the next vo_process_frame (vo_queue_landmarks), and the pinned staging ring
+    // pageable rows are copied into (the append kernel reads it over the unified address space)
+    struct LandSeg { const float* P; const double* X; int n; int target; };
+    LandSeg land_q[4]; int n_land_q = 0;
+    double* h_land[4] = { nullptr, nullptr, nullptr, nullptr }; size_t h_land_cap[4] = { 0, 0, 0, 0 }; int land_flip = 0;
+    cudaEvent_t ev_land_slot[4] = {}; int land_slot_used = -1;
     int klt_b_off = 0;      // offset of the candidate results inside the klt_* buffers
     bool packed_valid = false;  // q4/qv hold the current landmarks (set by the post-KLT compaction)
     // the last promotion step consumed a candidate KLT: C[ccur ^ 1] holds the candidates' previous
@@ -327,7 +333,7 @@ int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const f
 int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_ptsA,
                 const int32_t* d_nA, int nA_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
-                const vo_klt_params& prm, cudaStream_t st = nullptr);
+                const vo_klt_params& prm, cudaStream_t st = nullptr, const int32_t* gate = nullptr);
 // make `stream` wait for the work in flight on the side stream (no-op if there is none)
 int join_side_stream(Ctx* c);
 // put a deferred frame hint on the ingest stream now (no-op if there is none)
@@ -339,7 +345,7 @@ int close_step(Ctx* c);
 // round trip misses the start point by more than prm.fb_thresh
 int klt_fb_check(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
                  const int32_t* d_n, int n_upper, const float* d_out, uint8_t* d_status,
-                 const vo_klt_params& prm);
+                 const vo_klt_params& prm, cudaStream_t st = nullptr, int which = 0, const int32_t* gate = nullptr);
 FrameSlot* get_frame(Ctx* c, int64_t key);
 int pipeline_init(Ctx* c, int track_capacity, int hyp_capacity);
 void pipeline_free(Ctx* c);
@@ -359,12 +365,14 @@ int launch_pnp(Ctx* c, const PnpLaunch& L);
 // raw cv::RNG output table on the device, large enough for H iterations (grows, never shrinks)
 int ensure_rng_table(Ctx* c, int H);
 // tri.cu
-int launch_landmark_compact(Ctx* c, int n_upper);   // after KLT: keep status==1, pack q4/qv
+// after KLT: keep status==1, pack q4/qv.  gate (device flag, may be NULL): the kernel does nothing when it is 0
+// - for work enqueued ahead of a pose that may not come (vo_process_frame_pipelined)
+int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate = nullptr);
 // Tnew == nullptr: take the pose the last PnP left on the device (fused per-frame call)
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper,
                    bool use_klt, int b_off);
 // the pose-independent half of the promotion step on the side stream, right behind the candidates' KLT
-int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off);
+int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, const int32_t* gate = nullptr);
 // take an early classification back (the candidates are again as the KLT found them); no-op if there is none
 int early_undo(Ctx* c);
 // d_pts: n_new x 2 doubles on the device; d_Thost: 16 doubles on the device or nullptr (= device pose)
@@ -379,6 +387,7 @@ int detector_free(Ctx* c);
 int launch_gftt(Ctx* c, const FrameSlot& f, const uint8_t* d_mask, const vo_gftt_params& prm);
 int build_point_mask(Ctx* c, int w, int h, const float* d_pts, const uint8_t* d_status, const int32_t* d_n, int n_upper);
 int corners_to_stage(Ctx* c, double* d_stage);
+int launch_land_append(Ctx* c, const float* d_P, const double* d_X, int n_rows, int target, const int32_t* gate = nullptr);
 int launch_triangulate(Ctx* c, const double* d_M1, const double* d_M2, int per_point, const double* d_p1,
                        const double* d_p2, int n, double* d_X4);
 

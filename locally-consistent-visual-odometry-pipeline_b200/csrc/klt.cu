@@ -156,7 +156,7 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
                  const int32_t* __restrict__ nB_dev, const int nB_upper, const int b_off,
                  float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
                  int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
-                 const double min_eig_thr, const int use_tile)
+                 const double min_eig_thr, const int use_tile, const int32_t* __restrict__ gate)
 {
     static_assert(WIN % kRun == 0, "window side must be a multiple of the run length");
     constexpr int RPR = WIN / kRun;            // runs per row
@@ -165,6 +165,7 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
     using TL = Tile<WIN>;
     __shared__ unsigned s_tile[kWarpsPerBlock][TL::kSmemWords];
     pdl_prologue();
+    if (gate && !*gate) return;   // enqueued ahead of a pose that did not come: leave every buffer as it is
     const int lane = threadIdx.x & 31;
     unsigned* const tile = s_tile[threadIdx.x >> 5];
     int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
@@ -395,8 +396,9 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
 
 __global__ void fb_compare_kernel(const float2* __restrict__ pts, const float2* __restrict__ back,
                                   const uint8_t* __restrict__ back_status, const int32_t* __restrict__ n_dev,
-                                  int n_upper, float thr2, uint8_t* __restrict__ status)
+                                  int n_upper, float thr2, uint8_t* __restrict__ status, const int32_t* __restrict__ gate)
 {
+    if (gate && !*gate) return;
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int n = n_dev ? min(*n_dev, n_upper) : n_upper;
     if (i >= n) return;
@@ -406,17 +408,24 @@ __global__ void fb_compare_kernel(const float2* __restrict__ pts, const float2* 
 
 }  // namespace
 
+// Forward-backward check (BASELINE.json north_star; the reference has none, so it is off by default): the
+// tracked positions are tracked back into the previous frame and a track keeps its status only if the way
+// back succeeds and ends within fb_thresh px of where it started.  `which` selects the scratch (0: main
+// stream / landmarks, 1: side stream / candidates).
 int klt_fb_check(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
                  const int32_t* d_n, int n_upper, const float* d_out, uint8_t* d_status,
-                 const vo_klt_params& prm)
+                 const vo_klt_params& prm, cudaStream_t st, int which, const int32_t* gate)
 {
     if (n_upper <= 0) return VO_OK;
-    VO_TRY(ensure(c, c->fb_pts, (size_t)n_upper * 2));
-    VO_TRY(ensure(c, c->fb_status, (size_t)n_upper));
-    VO_TRY(launch_klt(c, next, prev, d_out, d_n, n_upper, c->fb_pts.p, c->fb_status.p, nullptr, nullptr, prm));
-    fb_compare_kernel<<<(n_upper + 255) / 256, 256, 0, c->stream>>>(
-        (const float2*)d_pts, (const float2*)c->fb_pts.p, c->fb_status.p, d_n, n_upper,
-        (float)(prm.fb_thresh * prm.fb_thresh), d_status);
+    if (!st) st = c->stream;
+    DevBuf<float>& bp = which ? c->fb_pts2 : c->fb_pts;
+    DevBuf<uint8_t>& bs = which ? c->fb_status2 : c->fb_status;
+    VO_TRY(ensure(c, bp, (size_t)n_upper * 2));
+    VO_TRY(ensure(c, bs, (size_t)n_upper));
+    VO_TRY(launch_klt2(c, next, prev, d_out, d_n, n_upper, nullptr, nullptr, 0, 0, bp.p, bs.p, nullptr, nullptr, prm, st, gate));
+    fb_compare_kernel<<<(n_upper + 255) / 256, 256, 0, st>>>(
+        (const float2*)d_pts, (const float2*)bp.p, bs.p, d_n, n_upper,
+        (float)(prm.fb_thresh * prm.fb_thresh), d_status, gate);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
@@ -433,7 +442,7 @@ int launch_klt(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const f
 int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const float* d_pts,
                 const int32_t* d_n, int n_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
-                const vo_klt_params& prm, cudaStream_t st)
+                const vo_klt_params& prm, cudaStream_t st, const int32_t* gate)
 {
     if (!st) st = c->stream;
     if (n_upper < 0) n_upper = 0;
@@ -455,7 +464,7 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
     const int blocks = (n_upper + nB_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
     klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
         prev, next, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
-        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : 1);
+        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : 1, gate);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;

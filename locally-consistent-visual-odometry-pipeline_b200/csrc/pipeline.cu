@@ -47,6 +47,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
     cudaFree(p->rng_tab.p); cudaFree(p->blk_counts.p); cudaFree(p->cand_flag.p);
     for (int k = 0; k < 2; k++) { cudaFree(p->d_add[k].p); if (p->h_add[k]) cudaFreeHost(p->h_add[k]); }
+    for (int k = 0; k < 4; k++) { if (p->h_land[k]) cudaFreeHost(p->h_land[k]); if (p->ev_land_slot[k]) cudaEventDestroy(p->ev_land_slot[k]); }
     cudaFree(p->d_sc);
     cudaFreeHost(p->h_sc);
     for (int k = 0; k < 6; k++) if (p->ev[k]) cudaEventDestroy(p->ev[k]);
@@ -95,7 +96,7 @@ struct DeferredAdd { const double* pts; int n; const double* T44; };
 // (usually most of the tracks, and with them the slowest stragglers) follow on the side stream, behind
 // the optional deferred append, and are joined by the promotion step.
 static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& prm, bool with_candidates,
-                      const DeferredAdd* add = nullptr, double early_alpha = -1.)
+                      const DeferredAdd* add = nullptr, double early_alpha = -1., const int32_t* gate = nullptr)
 {
     Pipeline* p = c->pipe;
     const int nA = p->n_land_upper;
@@ -108,7 +109,9 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
     VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
     if (nB > 0) VO_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));   // the side stream forks BEFORE the landmark launch
     VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, nullptr, nullptr, 0, 0, p->klt_out.p,
-                       p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm));
+                       p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, nullptr, gate));
+    if (prm.fb_check)
+        VO_TRY(klt_fb_check(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, p->klt_out.p, p->klt_status.p, prm, c->stream, 0, gate));
     p->klt_b_off = nA;
     if (nB > 0) {
         VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
@@ -144,10 +147,13 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
         }
         if (p->profiling) cudaEventRecord(p->ev_side[0], c->stream2);
         VO_TRY(launch_klt2(c, a->pyr, b->pyr, nullptr, nullptr, 0, p->C[p->ccur].p, &p->d_sc->n_cand, nB, nA, p->klt_out.p,
-                           p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, c->stream2));
+                           p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, c->stream2, gate));
+        if (prm.fb_check)
+            VO_TRY(klt_fb_check(c, a->pyr, b->pyr, p->C[p->ccur].p, &p->d_sc->n_cand, nB, p->klt_out.p + 2 * (size_t)nA,
+                                p->klt_status.p + nA, prm, c->stream2, 1, gate));
         if (p->profiling) cudaEventRecord(p->ev_side[1], c->stream2);
         // the pose-independent half of the promotion step follows the candidates' KLT on the side stream
-        if (early_alpha >= 0.) VO_TRY(launch_promote_early(c, early_alpha, nB, nA));
+        if (early_alpha >= 0.) VO_TRY(launch_promote_early(c, early_alpha, nB, nA, gate));
         VO_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
         c->side_inflight = true;
     }
@@ -186,16 +192,73 @@ __global__ void pack_points_kernel(DevScalars* sc, const double* __restrict__ X,
     }
 }
 
+// ---- landmark append (reference vo_pipeline.py:318-320, main.py:198-200) ---------------------------------
+// Rows the kernel can read in place (device memory, pinned or registered host memory) are used where they
+// are; pageable rows are copied into a slot of the pinned staging ring first, so the caller's arrays may
+// go away as soon as the call returns.
+static int land_rows_device_view(Ctx* c, const float* P, const double* X, int n, const float** dP, const double** dX)
+{
+    Pipeline* p = c->pipe;
+    cudaPointerAttributes aP{}, aX{};
+    const bool okP = cudaPointerGetAttributes(&aP, P) == cudaSuccess && aP.type != cudaMemoryTypeUnregistered;
+    const bool okX = cudaPointerGetAttributes(&aX, X) == cudaSuccess && aX.type != cudaMemoryTypeUnregistered;
+    cudaGetLastError();   // (older drivers report unregistered host pointers as an error)
+    if (okP && okX) { *dP = P; *dX = X; return VO_OK; }
+    const int slot = p->land_flip = (p->land_flip + 1) & 3;
+    const size_t need = (size_t)n * 4;   // doubles: 3 per X row + 1 (= 2 floats) per P row
+    if (p->ev_land_slot[slot]) VO_CUDA(c, cudaEventSynchronize(p->ev_land_slot[slot]));   // its last reader is done
+    else VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_land_slot[slot], cudaEventDisableTiming));
+    if (need > p->h_land_cap[slot]) {
+        size_t cap = 4096;
+        while (cap < need) cap *= 2;
+        if (p->h_land[slot]) cudaFreeHost(p->h_land[slot]);
+        p->h_land[slot] = nullptr; p->h_land_cap[slot] = 0;
+        VO_CUDA(c, cudaMallocHost((void**)&p->h_land[slot], cap * sizeof(double)));
+        p->h_land_cap[slot] = cap;
+    }
+    double* hx = p->h_land[slot];
+    float* hp = reinterpret_cast<float*>(hx + 3 * (size_t)n);
+    memcpy(hx, X, sizeof(double) * 3 * n);
+    memcpy(hp, P, sizeof(float) * 2 * n);
+    *dP = hp; *dX = hx;
+    p->land_slot_used = slot;
+    return VO_OK;
+}
+
+static int append_landmarks_now(Ctx* c, const float* P, const double* X, int n, int target)
+{
+    Pipeline* p = c->pipe;
+    const float* dP; const double* dX;
+    p->land_slot_used = -1;
+    VO_TRY(land_rows_device_view(c, P, X, n, &dP, &dX));
+    VO_TRY(launch_land_append(c, dP, dX, n, target));
+    if (p->land_slot_used >= 0) VO_CUDA(c, cudaEventRecord(p->ev_land_slot[p->land_slot_used], c->stream));
+    return VO_OK;
+}
+
 #define VO_NEED(c) do { if (!(c) || !(c)->pipe) return VO_ERR_INVALID; } while (0)
 
 extern "C" {
 
 // ---- state I/O --------------------------------------------------------------------------------
+int vo_track_rollback(vo_ctx* c);
+
+// A tracking step that vo_process_frame_pipelined enqueued ahead belongs to the NEXT frame: whoever looks at
+// the state or replaces it in between gets (and leaves) the state as the last frame left it.
+static int drop_ahead(vo_ctx* c)
+{
+    Pipeline* p = c->pipe;
+    if (p->ahead_valid && p->rb_valid && p->packed_valid) VO_TRY(vo_track_rollback(c));
+    p->ahead_valid = false;
+    return VO_OK;
+}
+
 int vo_set_state(vo_ctx* c, const float* P, const double* X, int n)
 {
     VO_NEED(c);
     if (n < 0 || (n > 0 && (!P || !X))) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
+    VO_TRY(drop_ahead(c));
     const size_t m = n > 0 ? n : 1;
     VO_TRY(ensure(c, p->P[p->cur], m * 2)); VO_TRY(ensure(c, p->X[p->cur], m * 3));
     if (n > 0) {
@@ -217,6 +280,7 @@ int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
 {
     VO_NEED(c);
     Pipeline* p = c->pipe;
+    VO_TRY(drop_ahead(c));
     VO_TRY(read_scalars(c));
     const int m = p->h_sc->n_land;
     if (n) *n = m;
@@ -293,6 +357,7 @@ int vo_get_snapshot(vo_ctx* c, float* P, double* X, int cap, int* n)
 int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* T, int n, int cf_alias)
 {
     VO_NEED(c);
+    VO_TRY(drop_ahead(c));
     VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     if (n < 0 || (n > 0 && (!C || !F || !T))) return VO_ERR_INVALID;
@@ -321,6 +386,7 @@ int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* 
 int vo_get_candidates(vo_ctx* c, float* C, double* F, double* T, int cap, int* n)
 {
     VO_NEED(c);
+    VO_TRY(drop_ahead(c));
     VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     Pipeline* p = c->pipe;
@@ -363,11 +429,16 @@ static int fill_counters(vo_ctx* c, vo_counters* out, bool sync)
     out->n_inliers = s->n_inliers; out->pnp_ok = s->ok; out->ransac_iters = s->iters_run; out->best_hypothesis = s->best_hyp;
     out->lm_iters = s->lm_iters; out->n_promoted = s->n_promoted; out->n_candidates_lost = s->n_cand_lost;
     out->cf_alias = s->cf_alias; out->klt_iters = s->klt_iters; out->klt_iters_candidates = s->klt_iters_cand;
-    out->reproj_cost = s->cost;
+    out->reproj_cost = s->cost; out->n_appended = s->n_appended; out->reserved_ = 0;
     return VO_OK;
 }
 
-int vo_get_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, true); }
+int vo_get_counters(vo_ctx* c, vo_counters* out)
+{
+    VO_NEED(c);
+    VO_TRY(drop_ahead(c));
+    return fill_counters(c, out, true);
+}
 // diagnostics: %globaltimer stamps (ns) of the last RANSAC run, see DevScalars::stamps.  Synchronises.
 int vo_debug_pnp_stamps(vo_ctx* c, uint64_t out[8])
 {
@@ -638,6 +709,35 @@ int vo_candidates_tracked(vo_ctx* c, int64_t prev_key, int64_t next_key)
     return p->cand_tracked_valid && p->packed_valid && p->cand_tracked_prev == prev_key && p->cand_tracked_next == next_key;
 }
 
+// ---- externally supplied landmarks (vo_pipeline.py:318-320: np.vstack of the re-bootstrap's fresh landmarks
+// onto associations['P'], ['X']; main.py:198-200) ---------------------------------------------------------------
+int vo_append_landmarks(vo_ctx* c, const float* P, const double* X, int n, int target_total)
+{
+    VO_NEED(c);
+    if (n < 0 || (n > 0 && (!P || !X))) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    if (p->ahead_valid && p->rb_valid && p->packed_valid) {   // a tracking step enqueued ahead did not see these rows
+        VO_TRY(vo_track_rollback(c));
+        p->ahead_valid = false;
+    }
+    if (p->packed_valid)
+        return set_error(c, VO_ERR_STATE, "landmarks are appended between frames, not between a tracking step and its PnP");
+    p->spec_pending = false;   // (an append behind a speculative promotion confirms it, as a tracking step does)
+    if (n == 0) return VO_OK;
+    return append_landmarks_now(c, P, X, n, target_total);
+}
+
+int vo_queue_landmarks(vo_ctx* c, const float* P, const double* X, int n, int target_total)
+{
+    VO_NEED(c);
+    if (n < 0 || (n > 0 && (!P || !X))) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    if (n == 0) return VO_OK;
+    if (p->n_land_q >= 4) return set_error(c, VO_ERR_CAPACITY, "at most 4 landmark batches can wait for a frame");
+    p->land_q[p->n_land_q++] = Pipeline::LandSeg{ P, X, n, target_total };
+    return VO_OK;
+}
+
 // ---- a6 (second half): append new candidates, F := C, T := pose (vo_pipeline.py:574-591)
 int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
 {
@@ -704,6 +804,8 @@ int vo_track_candidates(vo_ctx* c, int64_t prev_key, int64_t next_key, const vo_
     VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
     VO_TRY(launch_klt(c, a->pyr, b->pyr, p->C[p->ccur].p, &p->d_sc->n_cand, nB, p->klt_out.p, p->klt_status.p,
                       p->klt_err.p, p->klt_iters.p, prm));
+    if (prm.fb_check)
+        VO_TRY(klt_fb_check(c, a->pyr, b->pyr, p->C[p->ccur].p, &p->d_sc->n_cand, nB, p->klt_out.p, p->klt_status.p, prm));
     p->klt_b_off = 0;
     p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
     return VO_OK;
@@ -765,6 +867,7 @@ static void fill_counters_from(const DevScalars* s, vo_counters* counters)
     counters->ransac_iters = s->iters_run; counters->best_hypothesis = s->best_hyp; counters->lm_iters = s->lm_iters;
     counters->n_promoted = s->n_promoted; counters->n_candidates_lost = s->n_cand_lost; counters->cf_alias = s->cf_alias;
     counters->klt_iters = s->klt_iters; counters->klt_iters_candidates = s->klt_iters_cand; counters->reproj_cost = s->cost;
+    counters->n_appended = s->n_appended; counters->reserved_ = 0;
 }
 
 static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t prev_key, int64_t next_key,
@@ -819,10 +922,18 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
     VO_TRY(close_step(c));
     if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
+    // landmark batches waiting for this frame (vo_queue_landmarks): behind the promoted rows, in call order
+    Pipeline::LandSeg segs[4];
+    const int n_segs = p->n_land_q;
+    for (int k = 0; k < n_segs; k++) segs[k] = p->land_q[k];
+    p->n_land_q = 0;
+    for (int k = 0; k < n_segs; k++) VO_TRY(append_landmarks_now(c, segs[k].P, segs[k].X, segs[k].n, segs[k].target));
     if (prof) cudaEventRecord(p->ev[5], c->stream);
     p->cand_tracked_valid = false;
     p->packed_valid = false;
     p->rb_valid = false;
+    const int b_off_k = p->klt_b_off, mask_off_k = p->mask_src_off;   // this frame's, should the step ahead be taken back
+    const bool mask_valid_k = p->mask_src_valid;
     if (pipelined) {
         // the next frame is on the ingest stream already: its tracking goes right behind the append
         if (c->last_ingest_valid && c->last_ingest_key != next_key && vo_has_frame(c, c->last_ingest_key)) {
@@ -830,10 +941,14 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
             FrameSlot* a2 = get_frame(c, next_key);
             FrameSlot* b2 = get_frame(c, nk);
             if (a2 && b2) {
-                VO_TRY(track_both(c, a2, b2, kp, true, nullptr, alpha_deg));
+                // every kernel of the step ahead looks at this frame's `ok` first and leaves all buffers alone
+                // when no pose came: the failure path below then finds this frame's tracking results, candidate
+                // buffers and scalars exactly as they were
+                const int32_t* gate = &p->d_sc->ok;
+                VO_TRY(track_both(c, a2, b2, kp, true, nullptr, alpha_deg, gate));
                 p->cand_tracked_prev = next_key; p->cand_tracked_next = nk; p->cand_tracked_valid = true;
                 p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
-                VO_TRY(launch_landmark_compact(c, p->n_land_upper));
+                VO_TRY(launch_landmark_compact(c, p->n_land_upper, gate));
                 p->rb_valid = true; p->packed_valid = true;
                 p->ahead_valid = true; p->ahead_prev = next_key; p->ahead_next = nk;
             }
@@ -847,7 +962,22 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
             p->n_land_upper = s->n_land + ncand_before; p->n_cand_upper = s->n_cand + n_new;
             s->n_promoted = 0; s->n_cand_lost = 0;
         }
-        if (!s->ok && p->ahead_valid) { VO_TRY(vo_track_rollback(c)); p->ahead_valid = false; }
+        for (int k = 0; k < n_segs; k++) {   // the appended batches: same rule as the kernel, on the bounds
+            int up = p->n_land_upper + segs[k].n;
+            if (segs[k].target > 0 && up > segs[k].target) up = segs[k].target > p->n_land_upper ? segs[k].target : p->n_land_upper;
+            p->n_land_upper = up;
+        }
+        if (!s->ok && p->ahead_valid) {
+            // the step ahead did nothing on the device (gated): take back its host-side bookkeeping only
+            VO_TRY(join_side_stream(c));
+            p->cur = p->rb_cur; p->prev = p->rb_prev; p->prev_n_upper = p->rb_prev_n_upper; p->n_land_upper = p->rb_n_land_upper;
+            if (p->early_valid) {
+                p->early_valid = false; p->ccur ^= 1;
+                if (p->n_cand_upper < p->early_ncand_upper) p->n_cand_upper = p->early_ncand_upper;
+            }
+            p->klt_b_off = b_off_k; p->mask_src_valid = mask_valid_k; p->mask_src_off = mask_off_k;
+            p->rb_valid = false; p->packed_valid = false; p->cand_tracked_valid = false; p->ahead_valid = false;
+        }
     } else {
         VO_TRY(read_scalars(c));
     }
@@ -859,6 +989,8 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         VO_TRY(promote_rollback(c));
         VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
         p->cand_tracked_valid = false;
+        // (the rollback also dropped the batches appended behind the would-be promoted rows: once more)
+        for (int k = 0; k < n_segs; k++) VO_TRY(append_landmarks_now(c, segs[k].P, segs[k].X, segs[k].n, segs[k].target));
         VO_TRY(read_scalars(c));
     }
     VO_TRY(check_rng(c));

@@ -51,11 +51,12 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
                         const uint8_t* __restrict__ status, const int32_t* __restrict__ iters,
                         const double* __restrict__ X_in, float2* __restrict__ P_out, double* __restrict__ X_out,
                         float4* __restrict__ q4, float* __restrict__ qv, float2* __restrict__ lost,
-                        int32_t* __restrict__ sets, RngTab rt)
+                        int32_t* __restrict__ sets, RngTab rt, const int32_t* __restrict__ gate)
 {
     constexpr int NW = kScanThreads / 32 - 1;   // data warps
     __shared__ int sKeepW[32], sLostW[32], sIterW[32];
     pdl_prologue();
+    if (gate && !*gate) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(sc->n_land, n_upper);
     const int seg = ((n + NW - 1) / NW + 31) & ~31;   // rows per data warp, a multiple of the warp width
@@ -241,9 +242,10 @@ __global__ void __launch_bounds__(kCandThreads)
 cand_classify_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_out,
                      const uint8_t* __restrict__ status, const float2* __restrict__ C_in,
                      const double2* __restrict__ F_in, uint8_t* __restrict__ flag, int32_t* __restrict__ blk_counts,
-                     const int32_t* __restrict__ klt_iters, int early)
+                     const int32_t* __restrict__ klt_iters, int early, const int32_t* __restrict__ gate)
 {
     pdl_prologue();
+    if (gate && !*gate) return;
     const int n = min(sc->n_cand, a.ncand_upper);
     const bool alias = sc->cf_alias != 0;
     // early (side stream, before the PnP): a pose is assumed; the host takes the step back if none comes
@@ -275,12 +277,14 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
                   const uint8_t* __restrict__ flag, const int32_t* __restrict__ blk_counts,
                   float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
                   const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap,
-                  int early, double* __restrict__ prom_rows, int32_t* __restrict__ prom_ti)
+                  int early, double* __restrict__ prom_rows, int32_t* __restrict__ prom_ti,
+                  const int32_t* __restrict__ gate)
 {
     __shared__ int sWarpStay[kCandThreads / 32], sWarpProm[kCandThreads / 32];
     __shared__ int sBaseStay, sBaseProm, sLast;
     __shared__ double sM2[12];
     pdl_prologue();
+    if (gate && !*gate) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int n = min(sc->n_cand, a.ncand_upper);
     const int n_land = sc->n_land;
@@ -435,6 +439,28 @@ __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts,
     }
 }
 
+// Append externally supplied landmarks behind P/X (reference vo_pipeline.py:318-320: the re-bootstrap
+// stacks its fresh landmarks onto associations['P'] / ['X']; main.py:198-200 sets the first ones).
+// target > 0: top-up - only as many of the offered rows as bring |P| to `target` (decided here, on the
+// device: the host does not know |P| without a round trip).  One CTA.
+__global__ void __launch_bounds__(1024)
+land_append_kernel(DevScalars* sc, const float2* __restrict__ srcP, const double* __restrict__ srcX, int n_rows,
+                   int target, float2* __restrict__ P, double* __restrict__ X, int cap, const int32_t* gate)
+{
+    pdl_prologue();
+    if (gate && !*gate) return;
+    const int n0 = sc->n_land;
+    int n_add = target > 0 ? min(n_rows, max(target - n0, 0)) : n_rows;
+    n_add = max(min(n_add, cap - n0), 0);
+    for (int i = threadIdx.x; i < n_add; i += blockDim.x) {
+        P[n0 + i] = srcP[i];
+        const size_t o = 3 * (size_t)(n0 + i), s = 3 * (size_t)i;
+        X[o] = srcX[s]; X[o + 1] = srcX[s + 1]; X[o + 2] = srcX[s + 2];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) { sc->n_land = n0 + n_add; sc->n_appended = n_add; }
+}
+
 __global__ void triangulate_kernel(const double* __restrict__ M1, const double* __restrict__ M2, int per_point,
                                    const double2* __restrict__ p1, const double2* __restrict__ p2, int n,
                                    double* __restrict__ X4)
@@ -452,7 +478,7 @@ __global__ void triangulate_kernel(const double* __restrict__ M1, const double* 
 
 }  // namespace
 
-int launch_landmark_compact(Ctx* c, int n_upper)
+int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
 {
     Pipeline* p = c->pipe;
     const size_t n = n_upper > 0 ? n_upper : 1;
@@ -466,7 +492,7 @@ int launch_landmark_compact(Ctx* c, int n_upper)
     VO_CUDA(c, launch_pdl(landmark_compact_kernel, dim3(1), dim3(kScanThreads), c->stream,
         p->d_sc, n_upper, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const int32_t*)p->klt_iters.p,
         (const double*)p->X[p->cur].p, (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p,
-        p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }));
+        p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }, gate));
     c->launches++;
     p->prev = p->cur;
     p->prev_n_upper = n_upper;
@@ -495,7 +521,7 @@ int early_undo(Ctx* c)
 // has just enqueued there (vo_pipeline.py:503-545 and the bearing test :621-642 need no pose): runs
 // under the landmark chain and the PnP.  launch_promote finishes it when it is called with the same
 // alpha, or takes it back.
-int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off)
+int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, const int32_t* gate)
 {
     Pipeline* p = c->pipe;
     if (ncand_upper <= 0) return VO_OK;
@@ -513,13 +539,13 @@ int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off)
     VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
     VO_CUDA(c, launch_pdl(cand_classify_kernel, dim3(nb), dim3(kCandThreads), c->stream2,
         p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p, 1));
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p, 1, gate));
     VO_CUDA(c, launch_pdl(cand_apply_kernel, dim3(nb), dim3(kCandThreads), c->stream2,
         p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
         (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
         (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
         p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)nullptr, (double*)nullptr, 0, 1, p->prom_rows.p,
-        p->prom_ti.p));
+        p->prom_ti.p, gate));
     c->launches += 2;
     VO_CUDA(c, cudaGetLastError());
     p->ccur ^= 1;
@@ -580,13 +606,14 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
     VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
     VO_CUDA(c, launch_pdl(cand_classify_kernel, dim3(nb), dim3(kCandThreads), c->stream,
         p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
-        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p, 0));
+        (const double2*)p->F[p->ccur].p, p->cand_flag.p, p->blk_counts.p, (const int32_t*)p->klt_iters.p, 0,
+        (const int32_t*)nullptr));
     VO_CUDA(c, launch_pdl(cand_apply_kernel, dim3(nb), dim3(kCandThreads), c->stream,
         p->d_sc, a, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const float2*)p->C[p->ccur].p,
         (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
         (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
         p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap, 0,
-        (double*)nullptr, (int32_t*)nullptr));
+        (double*)nullptr, (int32_t*)nullptr, (const int32_t*)nullptr));
     c->launches++;
     c->launches++;
     p->ccur ^= 1;
@@ -614,6 +641,25 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
     c->launches++;
     p->n_poses++;
     p->n_cand_upper += n_new > 0 ? n_new : 0;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+// d_P / d_X must be device-accessible (device memory or pinned host memory, read over the unified
+// address space).  The host-side bound of |P| follows the same rule as the kernel.
+int launch_land_append(Ctx* c, const float* d_P, const double* d_X, int n_rows, int target, const int32_t* gate)
+{
+    Pipeline* p = c->pipe;
+    if (n_rows <= 0) return VO_OK;
+    int upper = p->n_land_upper + n_rows;
+    if (target > 0 && upper > target) upper = target > p->n_land_upper ? target : p->n_land_upper;
+    VO_TRY(ensure(c, p->P[p->cur], (size_t)upper * 2 + 2, true));
+    VO_TRY(ensure(c, p->X[p->cur], (size_t)upper * 3 + 3, true));
+    const int cap = (int)(p->P[p->cur].cap / 2);
+    VO_CUDA(c, launch_pdl(land_append_kernel, dim3(1), dim3(1024), c->stream, p->d_sc, (const float2*)d_P, d_X, n_rows,
+                          target, (float2*)p->P[p->cur].p, p->X[p->cur].p, cap, gate));
+    c->launches++;
+    p->n_land_upper = upper;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
 }

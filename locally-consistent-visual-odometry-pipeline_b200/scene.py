@@ -62,13 +62,15 @@ class CorridorScene:
     """Ground plane y=cam_h, walls x=-half_w / x=+half_w, far wall z=length."""
 
     def __init__(self, shape="kitti", seed=0, length=260.0, half_w=7.0, cam_h=1.65, texels_per_m=24.0,
-                 step=0.8, yaw_amp=0.04, yaw_period=90.0, scale=1.0):
+                 step=0.8, yaw_amp=0.04, yaw_period=90.0, scale=1.0, heading=0.0, z0=2.0):
         w, h, K = SHAPES[shape]
         self.w, self.h = int(round(w * scale)), int(round(h * scale))
         self.K = K.copy()
         self.K[:2] *= scale
         self.length, self.half_w, self.cam_h, self.tpm = length, half_w, cam_h, texels_per_m
         self.step, self.yaw_amp, self.yaw_period = step, yaw_amp, yaw_period
+        self.z0 = z0
+        self.heading = heading     # pi/2: the camera looks at the right wall and moves sideways (parking-shaped)
         self.wall_h = 12.0
         L = int(length * texels_per_m) + 8
         self.tex = {
@@ -81,8 +83,8 @@ class CorridorScene:
     # ---- trajectory -------------------------------------------------------------------------------
     def pose(self, k):
         """World->camera 4x4 of frame k: forward motion `step` m/frame with a sinusoidal yaw/sway."""
-        z = 2.0 + self.step * k
-        yaw = self.yaw_amp * np.sin(2 * np.pi * k / self.yaw_period)
+        z = self.z0 + self.step * k
+        yaw = self.heading + self.yaw_amp * np.sin(2 * np.pi * k / self.yaw_period)
         x = 0.8 * np.sin(2 * np.pi * k / (1.7 * self.yaw_period))
         c, s = np.cos(yaw), np.sin(yaw)
         Rwc = np.array([[c, 0, s], [0, 1, 0], [-s, 0, c]])   # camera->world
@@ -215,3 +217,83 @@ def ate(est_T, gt_T):
     s = np.trace(np.diag(S) @ D) / max((A ** 2).sum() / len(a), 1e-300)
     al = (s * (R @ A.T)).T + mb
     return float(np.sqrt(((al - b) ** 2).sum(1).mean()))
+
+
+# ---- steady-state streams for bench.py (SURVEY.md 8a sizing: |P| ~ n_tracks held stationary) ---------------
+def bearing_deg(c, f):
+    """The reference's bearing angle between two raw-pixel observations (vo_pipeline.py:621-642)."""
+    a = np.concatenate([c, np.ones((len(c), 1))], 1)
+    b = np.concatenate([f, np.ones((len(f), 1))], 1)
+    a /= np.linalg.norm(a, axis=1, keepdims=True)
+    b /= np.linalg.norm(b, axis=1, keepdims=True)
+    return np.degrees(np.arccos(np.clip((a * b).sum(1), -1.0, 1.0)))
+
+
+_POOL_SCENE = None
+
+
+def _pool_frame(args):
+    k, n_feed, seed, md, rate_lo, rate_hi, horizon, n_burst = args
+    sc = _POOL_SCENE
+    img = sc.render(k)
+    out = {"k": k, "img": img}
+    if n_feed > 0:
+        # a detector that only offers what will be promotable: corners whose bearing (as the reference
+        # measures it, on raw pixels) grows by >= alpha / horizon per frame and that stay inside the image
+        # for `horizon` more frames; the rest of the corners (far wall, image centre) would sit in C forever
+        pts = corner_points(img, 4 * n_feed, seed + 200 + k, min_dist=md)
+        Xw = sc.backproject(k, pts)
+        p1, z1 = sc.project(k + 1, Xw)
+        ph, zh = sc.project(k + horizon, Xw)
+        rate = bearing_deg(pts.astype(np.float64), p1)
+        ok = (rate >= rate_lo) & (rate <= rate_hi) & (z1 > 0.5) & (zh > 0.5)
+        ok &= (ph[:, 0] > 8) & (ph[:, 0] < sc.w - 8) & (ph[:, 1] > 8) & (ph[:, 1] < sc.h - 8)
+        out["feed"] = pts[ok][:n_feed].astype(np.float64)
+    if n_burst > 0:
+        # a stale external map: well-textured pixels of this frame paired with the 3-D points of OTHER
+        # pixels, so KLT keeps them and PnP has to reject them
+        pts = corner_points(img, n_burst, seed + 7000 + k, min_dist=md)
+        Xw = sc.backproject(k, pts)
+        out["burst_P"] = pts
+        out["burst_X"] = np.roll(Xw, len(Xw) // 2 + 1, axis=0)
+    return out
+
+
+class SteadyStream:
+    """Forward drive down a long corridor, one rendered frame per step (no ping-pong inside `n_frames`),
+    with what bench.py needs to hold the landmark count stationary:
+
+      feeds[k]            promotable corner pixels of frame k (candidate feed)
+      burst_P/burst_X[k]  an outlier landmark batch for frame k (relocalisation against a stale map): appended
+                          to P/X after frame k on the frames bench.py chooses, so that PnP-RANSAC really iterates
+
+    Frames are rendered by a fork pool (numpy ray casting, ~0.2 s per KITTI frame on one core)."""
+
+    def __init__(self, shape="kitti", n_frames=64, n_tracks=2000, n_feed=600, n_burst=0, seed=0, rate_lo=0.08,
+                 rate_hi=0.6, horizon=12, workers=None, scale=1.0, step=0.8, **scene_kw):
+        import multiprocessing as mp
+        import os
+        global _POOL_SCENE
+        self.scene = CorridorScene(shape, seed=seed, scale=scale, step=step,
+                                   length=scene_kw.get("z0", 2.0) + step * (n_frames + horizon + 2) + 90.0, **scene_kw)
+        self.K = self.scene.K
+        md = 6 if scale >= 0.75 else 4
+        jobs = [(k, n_feed if k > 0 else 0, seed, md, rate_lo, rate_hi, horizon, n_burst) for k in range(n_frames)]
+        workers = workers or min(os.cpu_count() or 1, 16)
+        _POOL_SCENE = self.scene
+        if workers > 1 and n_frames > 4:
+            with mp.get_context("fork").Pool(workers) as pool:
+                res = pool.map(_pool_frame, jobs, chunksize=max(1, n_frames // (4 * workers)))
+        else:
+            res = [_pool_frame(j) for j in jobs]
+        _POOL_SCENE = None
+        self.frames = [r["img"] for r in res]
+        self.poses = [self.scene.pose(k) for k in range(n_frames)]
+        self.feeds = [r.get("feed", np.zeros((0, 2))) for r in res]
+        self.burst_P = [r.get("burst_P", np.zeros((0, 2), np.float32)) for r in res]
+        self.burst_X = [r.get("burst_X", np.zeros((0, 3))) for r in res]
+        self.P0 = corner_points(self.frames[0], n_tracks, seed + 100, min_dist=md)
+        self.X0 = self.scene.backproject(0, self.P0)
+
+    def checksum(self):
+        return int(sum(int(f.astype(np.int64).sum()) * (i + 1) for i, f in enumerate(self.frames)))

@@ -726,6 +726,14 @@ class LandmarkTriangulator():
             # copied when that happens, so the caller's feed array is snapshotted here
             rt.pending_add = (np.array(new_candidates_list, np.float64), new_pose.copy())   # T = eye(4) @ new_pose (vo:582)
 
+        # landmark batches from outside the tracking loop (set_landmark_feed): behind the promoted rows, in
+        # front of the next tracking step
+        if _landmark_feed:
+            batches = _landmark_feed.pop(0)
+            for bP, bX, target in batches:
+                if len(bP):
+                    rt.ctx.append_landmarks(bP, bX, target)
+                    committed = True      # (an append behind a speculative promotion confirms it)
         rt.state_version += 1
         rt.ext_version += 1
         if isinstance(state, DeviceState):
@@ -780,6 +788,36 @@ _candidate_feed = []
 def set_candidate_feed(feed):
     """Per-frame candidate positions used when config['find_new_candidates_method'] == 'feed'."""
     _candidate_feed[:] = list(feed)
+
+
+# landmark feed: per frame a list of (P n x 2, X n x 3, target_total) batches appended behind state P/X at the
+# end of triangulate_landmark - what the reference does with the fresh landmarks of its re-bootstrap
+# (vo_pipeline.py:318-320), offered here as a hook for map-based relocalisation and for benchmarks
+_landmark_feed = []
+
+
+def set_landmark_feed(feed):
+    """feed: one entry per coming frame, each a list of (P, X, target_total) batches; target_total > 0 appends
+    only as many rows as bring |P| up to it (decided on the device), 0 appends all rows."""
+    _landmark_feed[:] = list(feed)
+
+
+def append_landmarks(state, P, X, target_total=0):
+    """state['P'], state['X'] := vstack with (P, X) (reference vo_pipeline.py:318-320) without a round trip
+    through the host when `state` mirrors the device; returns the state to use from here on."""
+    rt = _runtime()
+    if isinstance(state, DeviceState) and state._current():
+        rt.drop_speculation()
+        rt.drop_spec_track()
+        rt.ctx.append_landmarks(P, X, target_total)
+        rt.state_version += 1
+        state._rebind(rt.state_version)
+        return state
+    P0 = np.asarray(state['P'], np.float64).reshape(-1, 2)
+    X0 = np.asarray(state['X'], np.float64).reshape(-1, 3)
+    n = len(P) if target_total <= 0 else int(np.clip(target_total - len(P0), 0, len(P)))
+    return {'P': np.vstack((P0, np.asarray(P, np.float64).reshape(-1, 2)[:n])),
+            'X': np.vstack((X0, np.asarray(X, np.float64).reshape(-1, 3)[:n]))}
 
 
 # ---- frame ingest (SURVEY.md 8f-2; the reference reads frame k+1 from disk only after frame k is done,

@@ -139,5 +139,15 @@ class RefPipeline:
         return new_state, ext, T
 
 
+def append_landmarks(state, P, X, target_total=0):
+    """np.vstack of externally supplied landmarks onto state P/X (vo_pipeline.py:318-320); target_total > 0:
+    only as many rows as bring |P| up to it - the rule of vo_append_landmarks, restated."""
+    P0 = np.asarray(state['P'], np.float64).reshape(-1, 2)
+    X0 = np.asarray(state['X'], np.float64).reshape(-1, 3)
+    n = len(P) if target_total <= 0 else int(np.clip(target_total - len(P0), 0, len(P)))
+    return {'P': np.vstack((P0, np.asarray(P, np.float64).reshape(-1, 2)[:n])),
+            'X': np.vstack((X0, np.asarray(X, np.float64).reshape(-1, 3)[:n]))}
+
+
 def empty_ext():
     return {'C': np.zeros((0, 2)), 'F': np.zeros((0, 2)), 'T': np.zeros((0, 4, 4))}
