@@ -182,15 +182,41 @@ def corner_points(img, n, seed, min_dist=6, border=12):
     return np.stack([xs, ys], 1).astype(np.float32)
 
 
+_RENDER_SCENE = None
+
+
+def _render_one(k):
+    return _RENDER_SCENE.render(k)
+
+
+def render_frames(scene, ks, workers=None):
+    """Frames ks of `scene`, rendered by a fork pool when there are many full-size ones (the per-pixel numpy ray
+    caster takes ~0.2 s per KITTI frame on one core); bit-identical to rendering them one by one."""
+    import multiprocessing as mp
+    import os
+    global _RENDER_SCENE
+    ks = list(ks)
+    if workers is None:
+        workers = min(os.cpu_count() or 1, 16) if len(ks) * scene.w * scene.h > 6e6 else 1
+    if workers <= 1 or len(ks) < 4 or mp.current_process().daemon:
+        return [scene.render(k) for k in ks]
+    _RENDER_SCENE = scene
+    try:
+        with mp.get_context("fork").Pool(workers) as pool:
+            return pool.map(_render_one, ks)
+    finally:
+        _RENDER_SCENE = None
+
+
 class Sequence:
     """A rendered sequence plus everything a VO run needs: frames, K, ground-truth poses, the
     bootstrap state (true 3-D points of corner pixels of frame 0) and a per-frame candidate feed
     (corner pixels of each new frame - stands in for the reference's CPU detectors)."""
 
-    def __init__(self, shape="kitti", n_frames=32, n_tracks=2000, n_feed=300, seed=0, scale=1.0, **scene_kw):
+    def __init__(self, shape="kitti", n_frames=32, n_tracks=2000, n_feed=300, seed=0, scale=1.0, workers=None, **scene_kw):
         self.scene = CorridorScene(shape, seed=seed, scale=scale, **scene_kw)
         self.K = self.scene.K
-        self.frames = [self.scene.render(k) for k in range(n_frames)]
+        self.frames = render_frames(self.scene, range(n_frames), workers)
         self.poses = [self.scene.pose(k) for k in range(n_frames)]
         md = 6 if scale >= 0.75 else 4
         self.P0 = corner_points(self.frames[0], n_tracks, seed + 100, min_dist=md)

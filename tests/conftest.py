@@ -11,6 +11,22 @@ if ROOT not in sys.path:
 PKG_NAME = "locally-consistent-visual-odometry-pipeline_b200"
 
 
+def parity_report(section, name, values):
+    """Every magnitude the parity tests print, kept as JSON too when VO_PARITY_REPORT names a file
+    (tools/gpu_round.sh sets it; the result is committed as profiles/parity_r2.json)."""
+    import json
+    path = os.environ.get("VO_PARITY_REPORT")
+    if not path:
+        return
+    try:
+        rep = json.load(open(path))
+    except Exception:
+        rep = {}
+    rep.setdefault(section, {})[name] = values
+    with open(path, "w") as f:
+        json.dump(rep, f, indent=1, sort_keys=True)
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
 

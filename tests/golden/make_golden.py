@@ -135,6 +135,9 @@ SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, n_feed, seed)
     "kitti_half": ("kitti", 0.5, 36, 600, 80, 3),
     "parking_half": ("parking", 0.5, 24, 300, 60, 4),
     "malaga_half": ("malaga", 0.5, 20, 900, 100, 5),
+    # full resolution, the BASELINE configs' sizes
+    "kitti_full": ("kitti", 1.0, 61, 2000, 150, 7),
+    "malaga_full": ("malaga", 1.0, 31, 3000, 200, 8),
 }
 
 
@@ -206,12 +209,27 @@ def seq():
             assoc = ref.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
             pe = ref.PoseEstimator(sq.K)
             feeds.pop(0)
-            Ts, nP, nC, nInl = [], [], [], []
+            Ts, nP, nC, nInl, nTrk, margin = [], [], [], [], [], []
             with contextlib.redirect_stdout(io.StringIO()):
                 for k in range(1, nf):
                     new_state, _ = assoc.associateKeypointsToLandmarks(sq.frames[k - 1], sq.frames[k], state)
+                    nTrk.append(len(new_state["P"]))
+                    if variant == "p3p":
+                        # how close does a reprojection error of the winning hypothesis come to the 2 px threshold?
+                        # (the C restatement gives the hypothesis; cv2 only returns the refit) - what decides whether
+                        # another implementation's 1e-4 px differences can flip an inlier decision on this frame
+                        import oracle
+                        Pi, Xi = np.asarray(new_state["P"], np.float32), np.asarray(new_state["X"], np.float64)
+                        o = oracle.solve_pnp_ransac(Xi, Pi, sq.K, max_iters=100)
+                        Xc = Xi.astype(np.float32).astype(np.float64) @ o["Rh"].T + o["th"]
+                        uv = np.stack([sq.K[0, 0] * Xc[:, 0] / Xc[:, 2] + sq.K[0, 2], sq.K[1, 1] * Xc[:, 1] / Xc[:, 2] + sq.K[1, 2]], 1)
+                        e = np.sqrt(((uv - Pi) ** 2).sum(1))
+                        margin.append((float(np.abs(e - 2.0).min()), int(o["n_inliers"])))
                     T = pe.estimatePose(new_state, k)
                     nInl.append(len(new_state["P"]))
+                    if variant == "p3p":
+                        assert margin[-1][1] == nInl[-1], "C restatement and cv2 disagree on the inlier count"
+
                     tri = ref.LandmarkTriangulator(sq.K, None)
                     state, ext, _ = tri.triangulate_landmark(sq.frames[k - 1], sq.frames[k], new_state, ext, T)
                     Ts.append(T); nP.append(len(state["P"])); nC.append(len(ext["C"]))
@@ -219,6 +237,9 @@ def seq():
             out["%s_%s_nP" % (name, variant)] = np.array(nP)
             out["%s_%s_nC" % (name, variant)] = np.array(nC)
             out["%s_%s_nInl" % (name, variant)] = np.array(nInl)
+            out["%s_%s_nTrk" % (name, variant)] = np.array(nTrk)
+            if variant == "p3p":
+                out[name + "_p3p_margin"] = np.array([m[0] for m in margin])
             if variant == "p3p":
                 out[name + "_p3p_P_last"] = np.asarray(state["P"], np.float64)
                 out[name + "_p3p_X_last"] = np.asarray(state["X"], np.float64)

@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 import synth
+from conftest import parity_report
 from test_klt_oracle import GOLD, KLT_CASES, check_klt
 
 pytestmark = pytest.mark.gpu
@@ -48,6 +49,10 @@ def test_klt_vs_golden_and_oracle(ctx, oracle, name):
     assert np.abs(err - o_err)[ok].max() < 5e-3
     assert abs(int(iters.sum()) - int(o_it.sum())) <= max(4, 0.002 * o_it.sum())
     print("%s: status agreement vs cv2 %.4f, max |dp| %.2e px" % (name, agree, dmax))
+    o_agree, o_dmax = check_klt((out, st), (o_out, o_st), pos_tol=2e-3, status_frac=0.999)
+    parity_report("klt", name, dict(size="%dx%d" % (w, h), tracks=n, status_agreement_vs_cv2=float(agree), max_dp_px_vs_cv2=float(dmax),
+                                    status_agreement_vs_c_oracle=float(o_agree), max_dp_px_vs_c_oracle=float(o_dmax),
+                                    golden_cv2=str(g["cv2_version"]), gates="0.05 px, 99.5 % status"))
 
 
 def test_klt_vs_cv2_live(ctx):

@@ -10,12 +10,13 @@ import numpy as np
 import pytest
 
 from test_pipeline_oracle import GOLD, SEQ_CASES, SHI_SEQ_CASES, get_sequence, get_shi_sequence, run_port, run_port_shi
+from conftest import parity_report
 from test_pnp_oracle import rot_angle
 
 pytestmark = pytest.mark.gpu
 
 
-def drive_dropin(vo, sq, read_prev_state=True):
+def drive_dropin(vo, sq, read_prev_state=True, want_counts=False):
     """main.py's loop body with the candidate feed in place of the detector."""
     vo.set_candidate_feed([f.copy() for f in sq.feeds[1:]])
     vision = vo.BestVision(sq.K)
@@ -23,12 +24,14 @@ def drive_dropin(vo, sq, read_prev_state=True):
     vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
     associate = vo.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
     pose_estimator = vo.PoseEstimator(sq.K)
-    Ts, nP, nC = [], [], []
+    Ts, nP, nC, nTrk, nInl = [], [], [], [], []
     img1 = sq.frames[0]
     for k in range(1, len(sq.frames)):
         img2 = sq.frames[k]
         new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
         new_pose = pose_estimator.estimatePose(new_state, k)
+        c = vo._runtime().ctx.counters(sync=False)                  # as of the pose read-back
+        nTrk.append(c["n_tracked"]); nInl.append(c["n_inliers"])
         pos = np.linalg.inv(new_pose)[0:3, 3]                       # main.py:239
         if read_prev_state:
             X = vision.state["X"]                                   # main.py:248: the PREVIOUS state
@@ -42,6 +45,8 @@ def drive_dropin(vo, sq, read_prev_state=True):
         vo._runtime().flush_pending_add()      # the append is deferred to the next frame's upload
         cnt = vo._runtime().ctx.counters()
         nP.append(cnt["n_landmarks"]); nC.append(cnt["n_candidates"])
+    if want_counts:
+        return np.array(Ts), np.array(nP), np.array(nC), vision, np.array(nTrk), np.array(nInl)
     return np.array(Ts), np.array(nP), np.array(nC), vision
 
 
@@ -50,16 +55,19 @@ def test_dropin_sequence_vs_reference_classes(dropin, scene_mod, name):
     g = np.load(os.path.join(GOLD, "seq.npz"))
     sq = get_sequence(scene_mod, name)
     same_frames = sq.checksum() == int(g[name + "_checksum"])
-    Ts, nP, nC, vision = drive_dropin(dropin, sq)
+    Ts, nP, nC, vision, nTrk, nInl = drive_dropin(dropin, sq, want_counts=True)
     gt = sq.poses[1:]
     ate_ours = scene_mod.ate(Ts, gt)
+    margin = None
     if same_frames:
         Tg, nPg, nCg = g[name + "_p3p_T"], g[name + "_p3p_nP"], g[name + "_p3p_nC"]
+        nTrkg, nInlg, margin = g[name + "_p3p_nTrk"], g[name + "_p3p_nInl"], g[name + "_p3p_margin"]
         Tl = g[name + "_literal_T"]
     else:   # frames rendered differently here: compare with the port run live instead
         pytest.importorskip("cv2")
         Tg, nPg, nCg, _, _ = run_port(sq, "p3p")
         Tl = run_port(sq, "literal")[0]
+        nTrkg = nInlg = None
     ate_p3p, ate_lit = scene_mod.ate(Tg, gt), scene_mod.ate(Tl, gt)
     path_len = sq.scene.step * (len(sq.frames) - 1)
     dR = max(rot_angle(a[:3, :3], b[:3, :3]) for a, b in zip(Ts, Tg))
@@ -67,12 +75,27 @@ def test_dropin_sequence_vs_reference_classes(dropin, scene_mod, name):
     print("%s: ATE ours %.4f, reference P3P-variant %.4f, literal %.4f (m over %.1f m); max dR %.2e rad, max dt %.2e m; "
           "max |dnP| %d, max |dnC| %d" % (name, ate_ours, ate_p3p, ate_lit, path_len, dR, dt,
                                           np.abs(nP - nPg).max(), np.abs(nC - nCg).max()))
-    # state sizes: identical until the first threshold-straddling track flips (the minimal sets are
-    # drawn as rng % n, so one row more or less re-deals every later RANSAC), close afterwards
+    # State sizes are identical until the first track that sits on a decision threshold flips (the minimal sets
+    # are drawn as rng % n, so one row more or less re-deals every later RANSAC).  The split must have such a cause:
     same = (nP == nPg) & (nC == nCg)
+    if nTrkg is not None:
+        same &= (nTrk == nTrkg) & (nInl == nInlg)
     first_diff = int(np.argmin(same)) if not same.all() else len(same)
-    print("   state sizes identical for the first %d of %d frames" % (first_diff, len(same)))
-    assert first_diff >= len(same) // 2
+    cause = None
+    if first_diff < len(same) and nTrkg is not None:
+        f = first_diff
+        if nTrk[f] != nTrkg[f]:       # a KLT status flag (north_star allows 0.5 % of them to differ from cv2)
+            cause = "KLT status flag: %d vs %d tracked" % (nTrk[f], nTrkg[f])
+            assert abs(int(nTrk[f]) - int(nTrkg[f])) <= max(1, int(0.005 * nTrkg[f]))
+        elif nInl[f] != nInlg[f]:     # an inlier decision: some reprojection error must sit at the 2 px threshold
+            cause = "inlier decision, closest reprojection error %.2e px from the threshold" % margin[f]
+            assert margin[f] <= 2e-3, "inlier counts split at frame %d without an error near the threshold" % f
+            assert abs(int(nInl[f]) - int(nInlg[f])) <= 3
+        else:                         # the candidate side: a candidate's status flag or a bearing angle at alpha
+            cause = "candidate status flag / bearing angle at the threshold: |dnC| %d, |dnP| %d" % (
+                abs(int(nC[f]) - int(nCg[f])), abs(int(nP[f]) - int(nPg[f])))
+            assert abs(int(nC[f]) - int(nCg[f])) <= max(2, int(0.005 * nCg[f])) and abs(int(nP[f]) - int(nPg[f])) <= 2
+    print("   state sizes identical for the first %d of %d frames; split caused by: %s" % (first_diff, len(same), cause))
     assert np.abs(nP - nPg).max() <= 0.15 * nPg.max()
     assert np.abs(nC - nCg).max() <= 0.05 * nCg.max()
     # while the two runs see identical inputs their poses agree to the north_star PnP tolerance
@@ -83,8 +106,22 @@ def test_dropin_sequence_vs_reference_classes(dropin, scene_mod, name):
     dt0 = max(np.linalg.norm(a[:3, 3] - b[:3, 3]) / np.linalg.norm(b[:3, 3]) for a, b in zip(Ts[:m], Tg[:m]))
     print("   over the identical-input prefix: max dR %.2e rad, max dt_rel %.2e" % (dR0, dt0))
     assert dR0 <= 1e-4 and dt0 <= 1e-4
-    # north_star: ATE within 1 % of the reference's (not worse than the literal reference by > 1 %)
-    assert ate_ours <= 1.01 * max(ate_lit, ate_p3p) + 1e-3
+    # north_star: trajectory ATE within 1 % of the reference's.  Against the same-solver oracle as long as the run IS
+    # that oracle's run (identical masks throughout, or over the identical prefix); once a threshold flip has re-dealt
+    # the minimal sets the run is another RANSAC realisation, and the reference's two realisations (P3P-variant and
+    # literal, e.g. 0.095 m vs 0.246 m on malaga_full) bound what 1 % can mean
+    if m >= 3:
+        ate_pre_ours, ate_pre_ref = scene_mod.ate(Ts[:m], gt[:m]), scene_mod.ate(Tg[:m], gt[:m])
+        assert ate_pre_ours <= 1.01 * ate_pre_ref + 1e-4
+    if first_diff == len(same):
+        assert ate_ours <= 1.01 * ate_p3p + 1e-4
+    else:
+        assert ate_ours <= 1.01 * max(ate_lit, ate_p3p) + 1e-3
+    parity_report("sequence", name, dict(frames=len(same), ate_ours_m=ate_ours, ate_reference_p3p_m=ate_p3p, ate_reference_literal_m=ate_lit,
+                                         path_m=path_len, identical_prefix_frames=first_diff, split_cause=cause,
+                                         prefix_max_dR_rad=dR0, prefix_max_dt_rel=dt0, all_max_dR_rad=dR, all_max_dt_m=dt,
+                                         max_abs_dnP=int(np.abs(nP - nPg).max()), max_abs_dnC=int(np.abs(nC - nCg).max()),
+                                         golden_cv2=str(g["cv2_version"]), same_frames_as_golden=bool(same_frames)))
     # the lazily mirrored state is consistent
     P, X = vision.state["P"], vision.state["X"]
     assert len(P) == len(X) == nP[-1] and P.dtype == np.float32 and X.dtype == np.float64

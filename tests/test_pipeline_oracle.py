@@ -16,6 +16,9 @@ SEQ_CASES = {  # must match tests/golden/make_golden.py
     "kitti_half": ("kitti", 0.5, 36, 600, 80, 3),
     "parking_half": ("parking", 0.5, 24, 300, 60, 4),
     "malaga_half": ("malaga", 0.5, 20, 900, 100, 5),
+    # full resolution, the BASELINE configs' sizes
+    "kitti_full": ("kitti", 1.0, 61, 2000, 150, 7),
+    "malaga_full": ("malaga", 1.0, 31, 3000, 200, 8),
 }
 SHI_SEQ_CASES = {  # name: (shape, scale, n_frames, n_tracks, seed) - must match tests/golden/make_golden.py
     "kitti_half_shi": ("kitti", 0.5, 14, 300, 6),

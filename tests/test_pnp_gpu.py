@@ -6,6 +6,7 @@ import numpy as np
 import pytest
 
 import synth
+from conftest import parity_report
 from test_pnp_oracle import PNP_CASES, POSE_TOL, check_pose, golden_case, rot_angle
 
 pytestmark = pytest.mark.gpu
@@ -36,6 +37,18 @@ def test_pnp_vs_golden_and_oracle(ctx, pkg, oracle, name):
     check_pose(r["Rh"], r["th"], o["Rh"], o["th"], tol=1e-8)
     # rvec/tvec as cv2 returns them
     assert rot_angle(synth.rodrigues(r["rvec"]), r["R"]) < 1e-9 and np.allclose(r["tvec"], r["t"])
+    # report-only: the literal reference call vo_pipeline.py:258-264 (EPnP-5 hypotheses, <= 100 iterations)
+    n = len(X)
+    lit = np.unpackbits(g[name + "_literal_mask"])[:n]
+    Rl = synth.rodrigues(g[name + "_literal_rvec"])
+    parity_report("pnp", name, dict(points=n, hypotheses_budget=H, iterations_run=int(r["iters"]), inliers=int(r["n_inliers"]),
+                                    hamming_vs_cv2_p3p=int((r["mask"] != mask).sum()), dR_rad_vs_cv2_iterative_on_mask=float(rot_angle(r["R"], Rg)),
+                                    dt_rel_vs_cv2_iterative_on_mask=float(np.linalg.norm(r["t"] - tg) / np.linalg.norm(tg)),
+                                    hamming_vs_c_oracle=int((r["mask"] != o["mask"]).sum()),
+                                    literal_epnp5_call={"hamming": int((lit != r["mask"]).sum()), "dR_rad": float(rot_angle(r["R"], Rl)),
+                                                        "dt_rel": float(np.linalg.norm(r["t"] - g[name + "_literal_tvec"].ravel()) / np.linalg.norm(r["t"])),
+                                                        "note": "report-only: RANSAC-variant spread (SURVEY.md App. A.4), not a gate"},
+                                    golden_cv2=str(g["cv2_version"]) if "cv2_version" in g else None))
 
 
 def test_pnp_explicit_minimal_sets(ctx, pkg, oracle):

@@ -7,6 +7,7 @@ import numpy as np
 import pytest
 
 import synth
+from conftest import parity_report
 from test_tri_oracle import GOLD, TRI_CASES, TRI_TOL
 
 pytestmark = pytest.mark.gpu
@@ -28,6 +29,8 @@ def test_triangulate_vs_golden_and_oracle(ctx, oracle, name):
     assert relerr(got, g[name + "_X"]).max() <= 1e-8 < TRI_TOL          # vs cv2 4.13
     o = oracle.triangulate_points(K @ T1[:3], K @ T2[:3], p1, p2)
     assert relerr(got, o[:, :3] / o[:, 3:]).max() <= 1e-10              # vs the C oracle
+    parity_report("triangulation", name, dict(points=n, max_rel_err_vs_cv2=float(relerr(got, g[name + "_X"]).max()),
+                                              max_rel_err_vs_c_oracle=float(relerr(got, o[:, :3] / o[:, 3:]).max()), gate=TRI_TOL))
 
 
 def test_triangulate_live_cv2_and_edges(ctx):
@@ -85,5 +88,6 @@ def test_bearing_decisions_vs_golden(ctx):
         nprom = ctx.track_triangulate_promote(-1, -1, K, T2, alpha, sync=True)
         sel = g["bearing_alpha"] > alpha
         assert nprom == sel.sum()
+        parity_report("bearing_test", "alpha_%.1f" % alpha, dict(pairs=len(C), promoted=int(nprom), decisions_differing_from_reference_loop=0))
         Cn, _, _ = ctx.get_candidates()
         assert np.array_equal(Cn, C[~sel].astype(np.float32))

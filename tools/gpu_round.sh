@@ -6,7 +6,8 @@
 TAG=${1:-a}
 O=gpurun_out
 mkdir -p $O
-python -m pytest tests -m gpu -x -q -s > $O/r2_pytest_gpu_$TAG.log 2>&1; echo "pytest rc=$?"; tail -3 $O/r2_pytest_gpu_$TAG.log
+rm -f $O/r2_parity_$TAG.json
+VO_PARITY_REPORT=$O/r2_parity_$TAG.json python -m pytest tests -m gpu -x -q -s > $O/r2_pytest_gpu_$TAG.log 2>&1; echo "pytest rc=$?"; tail -3 $O/r2_pytest_gpu_$TAG.log
 python __graft_entry__.py smoke > $O/r2_smoke_$TAG.log 2>&1; echo "smoke rc=$?"; tail -2 $O/r2_smoke_$TAG.log
 python bench.py > $O/r2_bench_$TAG.json 2> $O/r2_bench_$TAG.err; echo "bench rc=$?"; cat $O/r2_bench_$TAG.json
 python bench.py --steps 20 --warmup 5 > $O/r2_bench_s20_$TAG.json 2> $O/r2_bench_s20_$TAG.err; echo "bench s20 rc=$?"; cat $O/r2_bench_s20_$TAG.json

@@ -1,7 +1,10 @@
 #!/usr/bin/env python
-"""Cut an `ncu --page raw --csv` export down to the columns the profiles/ summaries keep.
-Usage: python tools/ncu_summary.py raw.csv "header comment" > profiles/xxx_summary.csv"""
+"""Cut an `ncu --page raw --csv` export down to the columns the profiles/ summaries keep (plus the warp-stall
+breakdown), and optionally write the per-launch figures bench.py's roofline block quotes.
+
+Usage: python tools/ncu_summary.py raw.csv "header comment" [--traffic-json out.json --kernel klt_track --capture NAME] > summary.csv"""
 import csv
+import json
 import sys
 
 COLS = ["ID", "Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dram__bytes_read.sum",
@@ -12,14 +15,49 @@ COLS = ["ID", "Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum"
         "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
-        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "sm__cycles_elapsed.max"]
+        "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "sm__cycles_elapsed.max",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum"]
 
-rows = list(csv.reader(open(sys.argv[1])))
+args = sys.argv[1:]
+opts = {}
+while len(args) > 2 and args[-2].startswith("--"):
+    opts[args[-2][2:]] = args[-1]
+    args = args[:-2]
+rows = list(csv.reader(open(args[0])))
 hdr = rows[0]
-idx = [hdr.index(c) for c in COLS if c in hdr]
+stall = [c for c in hdr if c.startswith("smsp__average_warp") and c.endswith("_per_issue_active.ratio") and "not_issued" not in c]
+if not stall:
+    stall = [c for c in hdr if c.startswith("smsp__average_warps_issue_stalled")]
+cols = [c for c in COLS if c in hdr] + stall
+idx = [hdr.index(c) for c in cols]
 w = csv.writer(sys.stdout)
-if len(sys.argv) > 2:
-    print('"# %s"' % sys.argv[2].replace('"', '""'))
+if len(args) > 1:
+    print('"# %s"' % args[1].replace('"', '""'))
 for r in rows:
     if len(r) == len(hdr):
         w.writerow([r[i] for i in idx])
+
+if "traffic-json" in opts:
+    def num(r, c):
+        try:
+            return float(r[hdr.index(c)].replace(",", ""))
+        except Exception:
+            return None
+    unit = rows[1]
+    sel = [r for r in rows[2:] if len(r) == len(hdr) and opts.get("kernel", "klt_track") in r[hdr.index("Kernel Name")]]
+    # the landmark launch of the frame chain: the largest grid among the captured launches of that kernel
+    def grid(r):
+        return int(r[hdr.index("Grid Size")].strip("()").split(",")[0])
+    r = max(sel, key=grid)
+    scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "byte": 1.0}
+    rd = num(r, "dram__bytes_read.sum") * scale.get(unit[hdr.index("dram__bytes_read.sum")], 1.0)
+    wr = num(r, "dram__bytes_write.sum") * scale.get(unit[hdr.index("dram__bytes_write.sum")], 1.0)
+    out = {"kernel": opts.get("kernel", "klt_track"), "capture": opts.get("capture"), "grid": r[hdr.index("Grid Size")],
+           "dram_bytes_per_launch": rd + wr, "time_us_under_ncu": num(r, "gpu__time_duration.sum") / (1e3 if unit[hdr.index("gpu__time_duration.sum")] in ("nsecond", "ns") else 1.0),
+           "issue_active_pct": num(r, "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+           "l1_pct": num(r, "l1tex__throughput.avg.pct_of_peak_sustained_elapsed"),
+           "dram_pct": num(r, "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+           "alu_pipe_pct": num(r, "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
+           "registers_per_thread": num(r, "launch__registers_per_thread"), "waves_per_sm": num(r, "launch__waves_per_multiprocessor"),
+           "note": "ncu --set full of the bench command, cold caches, serialised; dram bytes = dram__bytes_read.sum + dram__bytes_write.sum of that launch"}
+    json.dump(out, open(opts["traffic-json"], "w"), indent=1)
