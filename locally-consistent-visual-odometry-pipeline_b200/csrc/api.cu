@@ -46,6 +46,14 @@ int join_side_stream(Ctx* c)
     return VO_OK;
 }
 
+int join_pose_stream(Ctx* c)
+{
+    if (!c->pose_inflight) return VO_OK;
+    c->pose_inflight = false;
+    VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_pose_done, 0));
+    return VO_OK;
+}
+
 int close_step(Ctx* c)
 {
     VO_CUDA(c, cudaEventRecord(c->ev_step_end[c->step_id & 3], c->stream));
@@ -105,6 +113,11 @@ int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity
     }
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream4, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_ransac, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_pose_side, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_snap, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_pose_done, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_ingest_fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_step_end[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_step_end[1], cudaEventDisableTiming) != cudaSuccess ||
@@ -132,6 +145,7 @@ int vo_destroy(vo_ctx* c)
     cudaStreamSynchronize(c->stream);
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->stream3) cudaStreamSynchronize(c->stream3);
+    if (c->stream4) cudaStreamSynchronize(c->stream4);
     map_free(c);
     pipeline_free(c);
     detector_free(c);
@@ -142,6 +156,11 @@ int vo_destroy(vo_ctx* c)
     cudaFreeHost(c->pinned_stage);
     cudaFreeHost(c->pinned_stage2);
     if (c->stream3) cudaStreamDestroy(c->stream3);
+    if (c->stream4) cudaStreamDestroy(c->stream4);
+    if (c->ev_ransac) cudaEventDestroy(c->ev_ransac);
+    if (c->ev_pose_side) cudaEventDestroy(c->ev_pose_side);
+    if (c->ev_snap) cudaEventDestroy(c->ev_snap);
+    if (c->ev_pose_done) cudaEventDestroy(c->ev_pose_done);
     if (c->ev_ingest_fork) cudaEventDestroy(c->ev_ingest_fork);
     for (auto& e : c->ev_step_end) if (e) cudaEventDestroy(e);
     if (c->own_stream) cudaStreamDestroy(c->stream);

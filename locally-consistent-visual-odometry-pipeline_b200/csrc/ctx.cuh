@@ -91,6 +91,12 @@ struct Ctx {
     bool side_writes_counts = false;   // a deferred candidate append is part of the side stream's work
     // ingest stream: upload + pyramid of the NEXT frame while the current one is tracked
     cudaStream_t stream3 = nullptr;
+    // pose stream: LM refit, pose read-back and the pose-dependent rest of the promotion, while the main stream
+    // already tracks the next frame (vo_process_frame_pipelined)
+    cudaStream_t stream4 = nullptr;
+    cudaEvent_t ev_ransac = nullptr, ev_pose_side = nullptr;
+    cudaEvent_t ev_snap = nullptr, ev_pose_done = nullptr;   // counters snapshot taken (main) / pose-side work of the frame done
+    bool pose_inflight = false;   // work of the last pipelined frame may still be running on stream4
     cudaEvent_t ev_ingest_fork = nullptr;
     uint64_t ingest_seq = 0;
     int64_t last_ingest_key = 0; bool last_ingest_valid = false;   // newest frame on the ingest stream, not used yet
@@ -188,6 +194,7 @@ int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
         }
         // stream-ordered w.r.t. earlier kernels still reading the old buffer
         cudaStreamSynchronize(c->stream);
+        if (c->stream4) cudaStreamSynchronize(c->stream4);
         cudaFree(b.p);
     }
     b.p = np_;
@@ -232,6 +239,11 @@ struct DevScalars {
     int32_t ticket2;       // same for kernels enqueued on the side stream (they overlap main-stream kernels)
     int32_t klt_iters_cand2; // side-stream accumulator of klt_iters_cand (early classification), moved over by the finish kernel
     int32_t n_appended;    // rows the last landmark append added (top-up decided on the device)
+    int32_t epoch;         // round flag of the persistent RANSAC kernel (run id << 12 | round)
+    int32_t prom_base;     // row of P/X where the promoted rows of the frame start (split promotion)
+    // counters as of the pose (vo_process_frame_pipelined reads the block back while the main stream goes on)
+    int32_t snap_n_land, snap_n_cand, snap_cf_alias, snap_n_appended;
+    int32_t pad3_;
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -277,6 +289,8 @@ struct Pipeline {
     DevBuf<double> hyp;     // H x 12 [R|t]
     DevBuf<int32_t> counts; // H (-1 = no model)
     DevBuf<uint8_t> mask;   // n
+    DevBuf<float> q4i, qvi; // the inliers of the last RANSAC, packed for the refit kernel
+    unsigned pnp_run = 0;   // RANSAC launches so far (epoch base of the persistent kernel)
     DevBuf<uint8_t> promote;// n_cand
     DevBuf<double> stage_d; // host->device staging (unit-level calls, candidate feed)
     DevBuf<float> stage_f;
@@ -336,6 +350,8 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
                 const vo_klt_params& prm, cudaStream_t st = nullptr, const int32_t* gate = nullptr);
 // make `stream` wait for the work in flight on the side stream (no-op if there is none)
 int join_side_stream(Ctx* c);
+// make `stream` wait for the pose-side work of the last pipelined frame (LM refit, X of the promoted rows)
+int join_pose_stream(Ctx* c);
 // put a deferred frame hint on the ingest stream now (no-op if there is none)
 int flush_frame_hint(Ctx* c, bool under_current_stages = false);
 // the promotion stage of a frame has been enqueued: close the step (see Ctx::ev_step_end)
@@ -359,7 +375,8 @@ struct PnpLaunch {
     double K[9];
     vo_pnp_params prm;
     bool compact;                       // prune landmark buffers to the inliers (estimatePose)
-    bool readback_after_first = false;  // copy the scalar block to Pipeline::h_sc_first behind the first chunk (if more follow)
+    bool readback_after_first = false;  // (unused since the RANSAC is one launch)
+    bool refit_on_pose_stream = false;  // LM refit on Ctx::stream4: the landmark side of the frame goes on without it
 };
 int launch_pnp(Ctx* c, const PnpLaunch& L);
 // raw cv::RNG output table on the device, large enough for H iterations (grows, never shrinks)
@@ -369,8 +386,11 @@ int ensure_rng_table(Ctx* c, int H);
 // - for work enqueued ahead of a pose that may not come (vo_process_frame_pipelined)
 int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate = nullptr);
 // Tnew == nullptr: take the pose the last PnP left on the device (fused per-frame call)
+// split (pipelined frames, early classification done): the promoted rows' positions are appended on the main
+// stream at once, their 3-D points (DLT with the refined pose) and the pose-table row `pose_idx` (-1: none)
+// follow on the pose stream
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper,
-                   bool use_klt, int b_off);
+                   bool use_klt, int b_off, bool split = false, int pose_idx = -1);
 // the pose-independent half of the promotion step on the side stream, right behind the candidates' KLT
 int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, const int32_t* gate = nullptr);
 // take an early classification back (the candidates are again as the KLT found them); no-op if there is none
@@ -378,7 +398,7 @@ int early_undo(Ctx* c);
 // d_pts: n_new x 2 doubles on the device; d_Thost: 16 doubles on the device or nullptr (= device pose)
 // d_n_new: optional device count (the rows actually appended are min(*d_n_new, n_new))
 int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new = nullptr,
-                    bool on_side_stream = false);
+                    bool on_side_stream = false, bool write_pose = true);
 // map.cu
 void map_free(Ctx* c);
 // det.cu

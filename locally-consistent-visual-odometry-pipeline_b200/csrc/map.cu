@@ -257,6 +257,7 @@ int vo_map_accumulate(vo_ctx* c, const double T44[16], double r_min, double r_ma
     Pipeline* p = c->pipe;
     MapState* m;
     VO_TRY(map_get(c, &m));
+    VO_TRY(join_pose_stream(c));   // the refined pose / promoted rows' 3-D points of a pipelined frame
     int src = p->cur;
     if (use_prev_state) {
         if (p->prev < 0) return set_error(c, VO_ERR_STATE, "no previous state is held");

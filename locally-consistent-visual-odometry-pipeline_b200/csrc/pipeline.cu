@@ -44,6 +44,7 @@ void pipeline_free(Ctx* c)
     cudaFree(p->poses.p); cudaFree(p->klt_in.p); cudaFree(p->klt_out.p); cudaFree(p->klt_err.p);
     cudaFree(p->klt_status.p); cudaFree(p->klt_iters.p); cudaFree(p->lost.p); cudaFree(p->q4.p); cudaFree(p->qv.p);
     cudaFree(p->sets.p); cudaFree(p->hyp.p); cudaFree(p->counts.p); cudaFree(p->mask.p); cudaFree(p->promote.p);
+    cudaFree(p->q4i.p); cudaFree(p->qvi.p);
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
     cudaFree(p->rng_tab.p); cudaFree(p->blk_counts.p); cudaFree(p->cand_flag.p);
     for (int k = 0; k < 2; k++) { cudaFree(p->d_add[k].p); if (p->h_add[k]) cudaFreeHost(p->h_add[k]); }
@@ -65,6 +66,7 @@ void pipeline_free(Ctx* c)
 static int read_scalars(Ctx* c)
 {
     Pipeline* p = c->pipe;
+    VO_TRY(join_pose_stream(c));                               // the refined pose comes from there
     if (c->side_writes_counts) VO_TRY(join_side_stream(c));   // n_cand is being updated over there
     VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -153,7 +155,11 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
                                 p->klt_status.p + nA, prm, c->stream2, 1, gate));
         if (p->profiling) cudaEventRecord(p->ev_side[1], c->stream2);
         // the pose-independent half of the promotion step follows the candidates' KLT on the side stream
-        if (early_alpha >= 0.) VO_TRY(launch_promote_early(c, early_alpha, nB, nA, gate));
+        if (early_alpha >= 0.) {
+            // (a pose read-back still in flight on the pose stream copies the scalar block: let it go first)
+            if (c->pose_inflight && p->ev_pose) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, p->ev_pose, 0));
+            VO_TRY(launch_promote_early(c, early_alpha, nB, nA, gate));
+        }
         VO_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
         c->side_inflight = true;
     }
@@ -259,6 +265,7 @@ int vo_set_state(vo_ctx* c, const float* P, const double* X, int n)
     if (n < 0 || (n > 0 && (!P || !X))) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
     VO_TRY(drop_ahead(c));
+    VO_TRY(join_pose_stream(c));
     const size_t m = n > 0 ? n : 1;
     VO_TRY(ensure(c, p->P[p->cur], m * 2)); VO_TRY(ensure(c, p->X[p->cur], m * 3));
     if (n > 0) {
@@ -281,7 +288,7 @@ int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
     VO_NEED(c);
     Pipeline* p = c->pipe;
     VO_TRY(drop_ahead(c));
-    VO_TRY(read_scalars(c));
+    VO_TRY(read_scalars(c));   // (joins the pose stream: X of rows promoted by a pipelined frame)
     const int m = p->h_sc->n_land;
     if (n) *n = m;
     if (m > cap) return (P || X) ? set_error(c, VO_ERR_CAPACITY, "state has %d rows, buffer %d", m, cap) : VO_OK;
@@ -317,6 +324,7 @@ int vo_snapshot_state(vo_ctx* c)
 {
     VO_NEED(c);
     Pipeline* p = c->pipe;
+    VO_TRY(join_pose_stream(c));
     const size_t n = p->n_land_upper > 0 ? p->n_land_upper : 1;
     if (n > p->snap_cap) {
         VO_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -358,6 +366,7 @@ int vo_set_candidates(vo_ctx* c, const float* C, const double* F, const double* 
 {
     VO_NEED(c);
     VO_TRY(drop_ahead(c));
+    VO_TRY(join_pose_stream(c));
     VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     if (n < 0 || (n > 0 && (!C || !F || !T))) return VO_ERR_INVALID;
@@ -605,8 +614,6 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
     L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
     L.d_sets_in = nullptr; L.compact = true;
-    static const bool no_first_rb = getenv("VO_NO_FIRST_RB") != nullptr;   // A/B switch (tools/e2e_phases.py)
-    L.readback_after_first = n_promoted == nullptr && !no_first_rb;
     p->first_rb_enqueued = false;
     memcpy(L.K, K, sizeof(L.K));
     VO_TRY(launch_pnp(c, L));
@@ -761,6 +768,7 @@ int vo_add_candidates(vo_ctx* c, const double* pts, int n, const double T44[16])
 int vo_detect_add_candidates_shi(vo_ctx* c, int64_t frame_key, const vo_gftt_params* params, const double T44[16])
 {
     VO_NEED(c);
+    VO_TRY(join_pose_stream(c));
     VO_TRY(early_undo(c));
     Pipeline* p = c->pipe;
     vo_gftt_params prm;
@@ -909,19 +917,26 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     L.d_sets_in = nullptr; L.compact = true;
     memcpy(L.K, K, sizeof(L.K));
     if (prof) cudaEventRecord(p->ev[3], c->stream);
+    // Pipelined frames with the candidates already classified (the steady state): the landmark side of the frame is
+    // final when the RANSAC kernel ends (pruned P/X, promoted rows' positions, appended batches), so the main stream goes
+    // straight on to the next frame's tracking, while the pose stream runs the LM refit, hands the pose to the host and
+    // triangulates the promoted rows - needed again only by the next frame's compaction, which waits for it.
+    const bool split = pipelined && p->early_valid && alpha_deg == p->early_alpha;
+    L.refit_on_pose_stream = split;
+    if (pipelined && !p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
     VO_TRY(launch_pnp(c, L));
     if (prof) cudaEventRecord(p->ev[4], c->stream);
     const int ncand_before = p->n_cand_upper;
     const bool early_used = p->early_valid;   // the promotion below only finishes an early classification
-    if (pipelined) {
+    if (pipelined && !split) {
         VO_TRY(join_side_stream(c));
-        if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
         VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
         VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));
     }
-    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+    if (n_new > 0) VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));   // (before a kernel gets the pointer)
+    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off, split, n_new > 0 ? p->n_poses : -1));
     VO_TRY(close_step(c));
-    if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
+    if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr, nullptr, false, !split));
     // landmark batches waiting for this frame (vo_queue_landmarks): behind the promoted rows, in call order
     Pipeline::LandSeg segs[4];
     const int n_segs = p->n_land_q;
@@ -956,6 +971,9 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         VO_TRY(flush_frame_hint(c, true));
         VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
         DevScalars* s = p->h_sc;   // as of the PnP: before the append of the promoted rows and of the new candidates
+        if (split) {   // (read back while the main stream went on: the counters come from the snapshot taken at the pose)
+            s->n_land = s->snap_n_land; s->n_cand = s->snap_n_cand; s->cf_alias = s->snap_cf_alias; s->n_appended = s->snap_n_appended;
+        }
         // (still upper bounds for what the promotion, the append and a tracking step enqueued above leave)
         if (early_used) { p->n_land_upper = s->n_land + s->n_promoted; p->n_cand_upper = s->n_cand + n_new; }
         else {

@@ -25,7 +25,7 @@ namespace vo {
 namespace {
 
 constexpr int kHypThreads = 256;      // threads of a RANSAC CTA (hypothesis scoring, and the refit by the last CTA)
-constexpr int kFinThreads = kHypThreads;
+constexpr int kFinThreads = 512;            // threads of the refit kernel
 
 struct PnpArgs {
     double K[9];
@@ -333,13 +333,14 @@ __device__ void ransac_select(DevScalars* sc, int32_t* sets, const int32_t* coun
         sc->iters_run = h >= niters ? max(niters, best_hyp + 1) : h1;
     }
     __syncwarp();
+    next_end = min(next_end, niters);
     if (!done && !a.explicit_sets && next_end > sc->sets_ready && n > kMinimal) gen_sets_warp(sc, sets, rt, n, next_end);
 }
 
-// Single CTA: inlier mask of the winner, LM refit on SE(3), pose output, optional pruning of the
-// landmark buffers to the inliers (vo_pipeline.py:327-331).
+// landmark buffers the pruning reads and writes (vo_pipeline.py:327-331)
 struct FinalizeBufs {
-    const float* P_in; const double* X_in; float* P_out; double* X_out;   // landmark ping-pong
+    const float* P_in; const double* X_in; float* P_out; double* X_out;   // landmark rotation
+    float4* q4i; float* qvi;                                              // the inliers, packed for the refit
 };
 
 __device__ __forceinline__ void so3_exp(const double* w, double* R)
@@ -398,17 +399,15 @@ __device__ __forceinline__ bool chol6_solve(double* A, double* b)
 
 constexpr int kAcc = 28;  // 21 (lower triangle of JtJ) + 6 (Jt r) + 1 (cost)
 
-// accumulate JtJ, Jt r and the cost at pose Rt over the masked points; result in sAcc (all threads
+// accumulate JtJ, Jt r and the cost at pose Rt over the n packed inliers; result in sAcc (all threads
 // see it after the trailing __syncthreads)
 __device__ void lm_accumulate(const double* Rt, const double* K, const float4* __restrict__ q4,
-                              const float* __restrict__ qv, const uint8_t* mask, int n,
-                              double (*sPart)[kAcc], double* sAcc)
+                              const float* __restrict__ qv, int n, double (*sPart)[kAcc], double* sAcc)
 {
     double acc[32];   // kAcc used, padded to the warp width for the halving reduction
 #pragma unroll
     for (int i = 0; i < 32; i++) acc[i] = 0.;
     for (int i = threadIdx.x; i < n; i += kFinThreads) {
-        if (!mask[i]) continue;
         const float4 q = q4[i];
         const double X = q.x, Y = q.y, Z = q.z;
         const double rx = Rt[0] * X + Rt[1] * Y + Rt[2] * Z;
@@ -464,8 +463,13 @@ __device__ __forceinline__ unsigned long long gtime()
     return t;
 }
 
-__device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __restrict__ q4,
-                             const float* __restrict__ qv, uint8_t* mask, const PnpArgs& a, const FinalizeBufs& fb, int n)
+// ---- the refit kernel ------------------------------------------------------------------------------
+// LM on SE(3) over the winner's inlier set, from the winning hypothesis to the converged optimum (what
+// cv2.solvePnP(SOLVEPNP_ITERATIVE) returns on that set).  One CTA; separate from the RANSAC kernel because
+// nothing on the landmark side waits for it: the pruned landmarks are final when the RANSAC kernel ends,
+// only the pose (host read-back, DLT of the promoted candidates) comes from here.
+__global__ void __launch_bounds__(kFinThreads)
+pnp_refit_kernel(DevScalars* sc, const float4* __restrict__ q4i, const float* __restrict__ qvi, PnpArgs a)
 {
     __shared__ double sPart[kFinThreads / 32][kAcc];
     __shared__ double sAcc[kAcc];
@@ -473,175 +477,203 @@ __device__ void pnp_finalize(DevScalars* sc, const double* hyp, const float4* __
     __shared__ double sCost, sLambda, sStep;
     __shared__ int sFails, sIters;
     __shared__ int sState;   // 0 = continue with trial, 1 = stop
-    __shared__ int sWarpTot[kFinThreads / 32];
+    pdl_prologue();
+    const int tid = threadIdx.x;
+    if (tid == 0) sc->stamps[4] = gtime();
+    if (!sc->ok) {
+        if (tid < 16) sc->T[tid] = 0.;
+        if (tid == 0) { sc->lm_iters = 0; sc->cost = 0.; sc->stamps[5] = gtime(); }
+        return;
+    }
+    const int n = sc->n_inliers;
+    if (tid < 12) sRt[tid] = sc->Th[tid];
+    __syncthreads();
+    // ---- evaluate at the current pose, then trial steps ---------------------------------------------
+    lm_accumulate(sRt, a.K, q4i, qvi, n, sPart, sAcc);
+    if (tid == 0) {
+        for (int i = 0; i < 21; i++) sH[i] = sAcc[i];
+        for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
+        sCost = sAcc[27]; sLambda = 1e-6; sState = 0; sFails = 0; sIters = 0;
+    }
+    __syncthreads();
+    while (sIters < a.refine_iters) {
+        if (tid == 0) {
+            double A[36], d[6];
+            bool solved = false;
+            while (!solved && sFails < 12) {
+                int k = 0;
+                for (int r = 0; r < 6; r++)
+                    for (int c = 0; c <= r; c++) A[6 * r + c] = sH[k++];
+                for (int r = 0; r < 6; r++) { A[6 * r + r] *= 1. + sLambda; d[r] = -sG[r]; }
+                solved = chol6_solve(A, d);
+                if (!solved) { sLambda *= 10.; sFails++; }
+            }
+            if (!solved) sState = 1;
+            else {
+                double dR[9];
+                so3_exp(d, dR);
+                for (int r = 0; r < 3; r++)
+                    for (int c = 0; c < 3; c++)
+                        sTrial[3 * r + c] = dR[3 * r] * sRt[c] + dR[3 * r + 1] * sRt[3 + c] + dR[3 * r + 2] * sRt[6 + c];
+                for (int r = 0; r < 3; r++) sTrial[9 + r] = sRt[9 + r] + d[3 + r];
+                double step = 0.;
+                for (int r = 0; r < 6; r++) step += d[r] * d[r];
+                sStep = step;
+                // a step below 1e-9 (rad / scene units) cannot move the pose at the level any gate
+                // looks at: converged, no trial evaluation needed
+                sState = step < 1e-18 ? 1 : 0;
+            }
+        }
+        __syncthreads();
+        if (sState) break;
+        lm_accumulate(sTrial, a.K, q4i, qvi, n, sPart, sAcc);
+        if (tid == 0) {
+            const double cn = sAcc[27];
+            if (cn <= sCost) {
+                const double dec = sCost - cn;
+                for (int i = 0; i < 12; i++) sRt[i] = sTrial[i];
+                for (int i = 0; i < 21; i++) sH[i] = sAcc[i];
+                for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
+                sCost = cn; sLambda = fmax(sLambda * 0.1, 1e-12);
+                sFails = 0; sIters++;
+                // Gauss-Newton contracts the error by orders of magnitude per step: after an accepted
+                // step below 1e-7 the next one would be far below 1e-9
+                sState = (sStep < 1e-14 || dec <= 1e-13 * cn) ? 1 : 0;   // 1 = converged
+            } else if (sStep < 1e-14) {
+                sState = 1;   // a rejected step this small: the cost is at its rounding floor
+            } else {
+                sLambda *= 10.;
+                if (++sFails >= 12) sState = 1;
+            }
+        }
+        __syncthreads();
+        const int st = sState;
+        __syncthreads();
+        if (st) break;
+    }
+    if (tid == 0) {
+        for (int r = 0; r < 3; r++) {
+            for (int cc = 0; cc < 3; cc++) { sc->T[4 * r + cc] = sRt[3 * r + cc]; }
+            sc->T[4 * r + 3] = sRt[9 + r];
+        }
+        sc->T[12] = 0.; sc->T[13] = 0.; sc->T[14] = 0.; sc->T[15] = 1.;
+        sc->cost = sCost; sc->lm_iters = sIters;
+        sc->stamps[5] = gtime();
+    }
+}
+
+// Last CTA of the RANSAC kernel: inlier mask of the winner, pruning of the landmark buffers to the inliers
+// (vo_pipeline.py:327-331; order preserved; no model: all rows kept) and the float32 inlier pack the refit
+// reads - one pass over the points.
+__device__ void pnp_mask_prune(DevScalars* sc, const double* hyp, const float4* __restrict__ q4,
+                               const float* __restrict__ qv, uint8_t* mask, const PnpArgs& a, const FinalizeBufs& fb, int n)
+{
+    __shared__ double sRtF[12];
+    __shared__ int sWarpKeep[kHypThreads / 32], sWarpInl[kHypThreads / 32];
     const int tid = threadIdx.x;
     const int best = sc->best_hyp;
     const bool ok = best >= 0;
-
-    int ninl = 0;
-    if (ok) {
-        if (tid < 12) sRt[tid] = __ldcg(hyp + (size_t)best * 12 + tid);
-        __syncthreads();
-        double R[9], t[3];
+    if (ok && tid < 12) { const double v = __ldcg(hyp + (size_t)best * 12 + tid); sRtF[tid] = v; sc->Th[tid] = v; }
+    __syncthreads();
+    double R[9], t[3];
 #pragma unroll
-        for (int i = 0; i < 9; i++) R[i] = sRt[i];
+    for (int i = 0; i < 9; i++) R[i] = ok ? sRtF[i] : 0.;
 #pragma unroll
-        for (int i = 0; i < 3; i++) t[i] = sRt[9 + i];
-        int c = 0;
-        for (int i = tid; i < n; i += kFinThreads) {
-            const float4 q = q4[i];
-            const uint8_t f = n == kMinimal ? 1 : (reproj_err2(R, t, a.K, q.x, q.y, q.z, q.w, qv[i]) <= a.thr2);
-            mask[i] = f;
-            c += f;
-        }
-        c = __reduce_add_sync(0xffffffffu, c);
-        if ((tid & 31) == 0) sWarpTot[tid >> 5] = c;
-        if (tid < 12) sc->Th[tid] = sRt[tid];   // the winning unrefined hypothesis
-        __syncthreads();
-#pragma unroll
-        for (int w = 0; w < kFinThreads / 32; w++) ninl += sWarpTot[w];
-
-        if (tid == 0) sc->stamps[4] = gtime();
-        // ---- LM: evaluate at the current pose, then trial steps ------------------------------------
-        lm_accumulate(sRt, a.K, q4, qv, mask, n, sPart, sAcc);
-        if (tid == 0) {
-            for (int i = 0; i < 21; i++) sH[i] = sAcc[i];
-            for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
-            sCost = sAcc[27]; sLambda = 1e-6; sState = 0; sFails = 0; sIters = 0;
-        }
-        __syncthreads();
-        while (sIters < a.refine_iters) {
-            if (tid == 0) {
-                double A[36], d[6];
-                bool solved = false;
-                while (!solved && sFails < 12) {
-                    int k = 0;
-                    for (int r = 0; r < 6; r++)
-                        for (int c = 0; c <= r; c++) A[6 * r + c] = sH[k++];
-                    for (int r = 0; r < 6; r++) { A[6 * r + r] *= 1. + sLambda; d[r] = -sG[r]; }
-                    solved = chol6_solve(A, d);
-                    if (!solved) { sLambda *= 10.; sFails++; }
-                }
-                if (!solved) sState = 1;
-                else {
-                    double dR[9];
-                    so3_exp(d, dR);
-                    for (int r = 0; r < 3; r++)
-                        for (int c = 0; c < 3; c++)
-                            sTrial[3 * r + c] = dR[3 * r] * sRt[c] + dR[3 * r + 1] * sRt[3 + c] + dR[3 * r + 2] * sRt[6 + c];
-                    for (int r = 0; r < 3; r++) sTrial[9 + r] = sRt[9 + r] + d[3 + r];
-                    double step = 0.;
-                    for (int r = 0; r < 6; r++) step += d[r] * d[r];
-                    sStep = step;
-                    // a step below 1e-9 (rad / scene units) cannot move the pose at the level any gate
-                    // looks at: converged, no trial evaluation needed
-                    sState = step < 1e-18 ? 1 : 0;
-                }
-            }
-            __syncthreads();
-            if (sState) break;
-            lm_accumulate(sTrial, a.K, q4, qv, mask, n, sPart, sAcc);
-            if (tid == 0) {
-                const double cn = sAcc[27];
-                if (cn <= sCost) {
-                    const double dec = sCost - cn;
-                    for (int i = 0; i < 12; i++) sRt[i] = sTrial[i];
-                    for (int i = 0; i < 21; i++) sH[i] = sAcc[i];
-                    for (int i = 0; i < 6; i++) sG[i] = sAcc[21 + i];
-                    sCost = cn; sLambda = fmax(sLambda * 0.1, 1e-12);
-                    sFails = 0; sIters++;
-                    // Gauss-Newton contracts the error by orders of magnitude per step: after an accepted
-                    // step below 1e-7 the next one would be far below 1e-9
-                    sState = (sStep < 1e-14 || dec <= 1e-13 * cn) ? 1 : 0;   // 1 = converged
-                } else if (sStep < 1e-14) {
-                    sState = 1;   // a rejected step this small: the cost is at its rounding floor
-                } else {
-                    sLambda *= 10.;
-                    if (++sFails >= 12) sState = 1;
-                }
-            }
-            __syncthreads();
-            const int st = sState;
-            __syncthreads();
-            if (st) break;
-        }
-        if (tid == 0) {
-            for (int r = 0; r < 3; r++) {
-                for (int cc = 0; cc < 3; cc++) { sc->T[4 * r + cc] = sRt[3 * r + cc]; }
-                sc->T[4 * r + 3] = sRt[9 + r];
-            }
-            sc->T[12] = 0.; sc->T[13] = 0.; sc->T[14] = 0.; sc->T[15] = 1.;
-            sc->cost = sCost; sc->lm_iters = sIters;
-            sc->stamps[5] = gtime();
-        }
-    } else {
-        for (int i = tid; i < n; i += kFinThreads) mask[i] = 0;
-        if (tid < 16) sc->T[tid] = 0.;
-        if (tid == 0) sc->lm_iters = 0;
-        __syncthreads();
-    }
-    if (tid == 0) { sc->ok = ok; sc->n_inliers = ninl; }
-
-    if (!a.compact) return;
-    // ---- prune landmarks to the inliers, order preserved (no model: state left as it is) -------
-    int base = 0;
-    for (int i0 = 0; i0 < n; i0 += kFinThreads) {
+    for (int i = 0; i < 3; i++) t[i] = ok ? sRtF[9 + i] : 0.;
+    int base_keep = 0, base_inl = 0;
+    for (int i0 = 0; i0 < n; i0 += kHypThreads) {
         const int i = i0 + tid;
-        const bool keep = i < n && (!ok || mask[i]);
-        float2 pp = make_float2(0.f, 0.f);
+        const bool in = i < n;
+        float4 q = make_float4(0.f, 0.f, 0.f, 0.f);
+        float v = 0.f;
+        if (in) { q = q4[i]; v = qv[i]; }
+        const bool inl = in && ok && (n == kMinimal || reproj_err2(R, t, a.K, q.x, q.y, q.z, q.w, v) <= a.thr2);
+        const bool keep = in && (!ok || inl);
+        if (in) mask[i] = inl;
         double x0 = 0., x1 = 0., x2 = 0.;
-        if (keep) {   // issued before the barrier: the load latency overlaps the rank computation
-            pp = reinterpret_cast<const float2*>(fb.P_in)[i];
+        if (keep && a.compact) {   // issued before the barrier: the load latency overlaps the rank computation
             x0 = fb.X_in[3 * (size_t)i]; x1 = fb.X_in[3 * (size_t)i + 1]; x2 = fb.X_in[3 * (size_t)i + 2];
         }
-        const unsigned bal = __ballot_sync(0xffffffffu, keep);
-        const int wpre = __popc(bal & ((1u << (tid & 31)) - 1));
-        if ((tid & 31) == 0) sWarpTot[tid >> 5] = __popc(bal);
+        const unsigned bk = __ballot_sync(0xffffffffu, keep), bi = __ballot_sync(0xffffffffu, inl);
+        const unsigned below = (1u << (tid & 31)) - 1;
+        if ((tid & 31) == 0) { sWarpKeep[tid >> 5] = __popc(bk); sWarpInl[tid >> 5] = __popc(bi); }
         __syncthreads();
-        int off = base, tot = 0;
+        int ok_ = base_keep, oi_ = base_inl, tk = 0, ti = 0;
 #pragma unroll
-        for (int w = 0; w < kFinThreads / 32; w++) {
-            const int cw = sWarpTot[w];
-            if (w < (tid >> 5)) off += cw;
-            tot += cw;
+        for (int w = 0; w < kHypThreads / 32; w++) {
+            const int ck = sWarpKeep[w], ci = sWarpInl[w];
+            if (w < (tid >> 5)) { ok_ += ck; oi_ += ci; }
+            tk += ck; ti += ci;
         }
-        if (keep) {
-            const int o = off + wpre;
-            reinterpret_cast<float2*>(fb.P_out)[o] = pp;
+        if (keep && a.compact) {
+            const int o = ok_ + __popc(bk & below);
+            reinterpret_cast<float2*>(fb.P_out)[o] = make_float2(q.w, v);   // (u, v) as the tracking step left them
             fb.X_out[3 * (size_t)o] = x0; fb.X_out[3 * (size_t)o + 1] = x1; fb.X_out[3 * (size_t)o + 2] = x2;
         }
-        base += tot;
+        if (inl) {
+            const int o = oi_ + __popc(bi & below);
+            fb.q4i[o] = q; fb.qvi[o] = v;
+        }
+        base_keep += tk; base_inl += ti;
         __syncthreads();
     }
-    if (tid == 0) sc->n_land = base;
+    if (tid == 0) {
+        sc->ok = ok; sc->n_inliers = base_inl;
+        if (a.compact) sc->n_land = base_keep;
+    }
+}
+
+__device__ __forceinline__ int ld_acquire(const int* p)
+{
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(int* p, int v)
+{
+    asm volatile("st.release.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
 // ---- the RANSAC kernel -----------------------------------------------------------------------------
-// One CTA per hypothesis of the chunk [h0, h0 + gridDim.x): lanes 0-3 solve P3P, the CTA scores all
-// points.  The last CTA to finish (ticket) replays the sequential bookkeeping over the chunk's
-// counts and, for the final chunk, goes on to the refit and the pruning - so a RANSAC that ends
-// inside its first chunk (the usual case) is ONE launch, with no set-up, selection or refit
-// launches around it.
+// ONE persistent launch for the whole run (all CTAs resident: grid <= kPnpChunk0 <= number of SMs, one
+// CTA per SM by registers).  The run proceeds in rounds; in a round every CTA takes B consecutive hypotheses:
+// quads of lanes solve their P3Ps side by side, then the whole CTA scores the points against them, up to
+// kScoreTile hypotheses per pass over the points.  The last CTA to finish a round (ticket) replays the
+// sequential bookkeeping of the reference loop (first strictly-better model wins, the budget shrinks) over
+// the round's counts and opens the next round (epoch flag the others spin on) or ends the run: then it writes
+// the inlier mask, prunes the landmarks and packs the inliers for the refit kernel.
+//   round 0: one hypothesis per CTA (the adaptive stop usually ends the run inside it);
+//   later rounds: B = ceil(remaining budget / CTAs), at most kBatch - a run with a pinned budget of 4096 is two rounds.
+constexpr int kBatch = 32;       // hypotheses per CTA per round (P3P quads side by side: 128 threads)
+constexpr int kScoreTile = 4;    // hypotheses scored per pass over the points
+
 __global__ void __launch_bounds__(kHypThreads)
-pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, const float* __restrict__ qv,
-                 double* hyp, int32_t* counts, uint8_t* mask, PnpArgs a, RngTab rt, FinalizeBufs fb,
-                 int h0, int h1, int next_end, int first, int last)
+pnp_ransac_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, const float* __restrict__ qv,
+                  double* hyp, int32_t* counts, uint8_t* mask, PnpArgs a, RngTab rt, FinalizeBufs fb, int H, int epoch0)
 {
-    __shared__ double sRt[12];
-    __shared__ int sValid, sLast;
-    __shared__ int sCount[kHypThreads / 32];
+    __shared__ double sRt[kBatch][12];
+    __shared__ int sValid[kBatch];
+    __shared__ int sCount[kHypThreads / 32][kScoreTile];
+    __shared__ int sLast;
     pdl_prologue();
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int G = gridDim.x;
     const unsigned long long t_in = gtime();
-    unsigned long long t_p3p = t_in;
+    unsigned long long t_p3p = t_in, t_scored = t_in;
     const int n = min(sc->n_tracked, a.n_upper);
-    // the first chunk lies inside the initial budget by construction (one CTA per hypothesis); later
-    // chunks run on a fixed small grid that strides over whatever budget the previous chunk's
-    // bookkeeping left (hypotheses beyond it are never looked at; usually there are none)
-    const int lim = first ? ((n >= kMinimal && a.max_iters > 0) ? (n == kMinimal ? 1 : h1) : 0)
-                          : (sc->done ? 0 : min(h1, sc->niters));
-    for (int h = h0 + blockIdx.x; h < lim; h += gridDim.x) {
-        if (tid < 4) {   // a quad of lanes solves the minimal problem
+    const int niters0 = (n < kMinimal || a.max_iters <= 0) ? 0 : (n == kMinimal ? 1 : a.max_iters);
+    int h0 = 0;
+    for (int round = 0;; round++) {
+        const int budget = round == 0 ? niters0 : sc->niters;
+        const int remaining = budget - h0;
+        int B = round == 0 ? 1 : (remaining + G - 1) / G;
+        B = max(1, min(B, kBatch));
+        const int h1 = min(budget, h0 + G * B);
+        const int hb = h0 + (int)blockIdx.x * B;         // this CTA's hypotheses: [hb, hb + nb)
+        const int nb = max(0, min(B, h1 - hb));
+        // ---- P3P: quad q of the CTA solves hypothesis hb + q ---------------------------------------
+        if (tid < 4 * nb) {
+            const int b = tid >> 2, h = hb + b;
             int4 s = n == kMinimal ? make_int4(0, 1, 2, 3) : reinterpret_cast<const int4*>(sets)[h];
             const int idx[4] = { s.x, s.y, s.z, s.w };
             double X[12], p[8];
@@ -656,60 +688,68 @@ pnp_chunk_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, c
             }
             double Rt[12];
             bool found = false;
-            const bool winner = ok && p3p4_quad(X, p, a.K, Rt, tid, 0xFu, &found);
-            if (tid == 0) sValid = ok && found;
+            const unsigned qmask = 0xFu << (lane & 28);
+            const bool winner = ok && p3p4_quad(X, p, a.K, Rt, tid & 3, qmask, &found);
+            if ((tid & 3) == 0) sValid[b] = ok && found;
             if (winner) {
 #pragma unroll
-                for (int i = 0; i < 12; i++) { sRt[i] = Rt[i]; hyp[(size_t)h * 12 + i] = Rt[i]; }
+                for (int i = 0; i < 12; i++) { sRt[b][i] = Rt[i]; hyp[(size_t)h * 12 + i] = Rt[i]; }
             }
         }
         __syncthreads();
-        t_p3p = gtime();
-        if (sValid) {
-            double R[9], t[3];
+        if (round == 0) t_p3p = gtime();
+        // ---- scoring: up to kScoreTile hypotheses per pass over the points ------------------------
+        for (int b0 = 0; b0 < nb; b0 += kScoreTile) {
+            int good[kScoreTile];
+            bool valid[kScoreTile];
 #pragma unroll
-            for (int i = 0; i < 9; i++) R[i] = sRt[i];
-#pragma unroll
-            for (int i = 0; i < 3; i++) t[i] = sRt[9 + i];
-            int good = 0;
+            for (int j = 0; j < kScoreTile; j++) { good[j] = 0; valid[j] = b0 + j < nb && sValid[b0 + j]; }
             for (int i = tid; i < n; i += kHypThreads) {
                 const float4 q = q4[i];
-                good += reproj_err2(R, t, a.K, q.x, q.y, q.z, q.w, qv[i]) <= a.thr2;
-            }
-            good = __reduce_add_sync(0xffffffffu, good);
-            if ((tid & 31) == 0) sCount[tid >> 5] = good;
-            __syncthreads();
-            if (tid == 0) {
-                int s = 0;
+                const float v = qv[i];
 #pragma unroll
-                for (int w = 0; w < kHypThreads / 32; w++) s += sCount[w];
-                counts[h] = s;
+                for (int j = 0; j < kScoreTile; j++)
+                    if (valid[j]) good[j] += reproj_err2(sRt[b0 + j], sRt[b0 + j] + 9, a.K, q.x, q.y, q.z, q.w, v) <= a.thr2;
             }
-        } else if (tid == 0) counts[h] = -1;
-        __syncthreads();   // sRt / sValid / sCount are reused by the next hypothesis of this CTA
+#pragma unroll
+            for (int j = 0; j < kScoreTile; j++) {
+                const int g = __reduce_add_sync(0xffffffffu, good[j]);
+                if (lane == 0) sCount[warp][j] = g;
+            }
+            __syncthreads();
+            if (tid < kScoreTile && b0 + tid < nb) {
+                int sum = 0;
+#pragma unroll
+                for (int w = 0; w < kHypThreads / 32; w++) sum += sCount[w][tid];
+                counts[hb + b0 + tid] = sValid[b0 + tid] ? sum : -1;
+            }
+            __syncthreads();
+        }
+        if (round == 0) t_scored = gtime();
+        // ---- round barrier: the last CTA to arrive does the bookkeeping and opens the next round ----
+        if (tid == 0) {
+            __threadfence();
+            sLast = atomicAdd(&sc->ticket, 1) == G - 1;
+        }
+        __syncthreads();
+        if (sLast) {
+            __threadfence();
+            // (the minimal sets of the next round are drawn here, for what is left of the budget only)
+            if (tid < 32) ransac_select(sc, sets, counts, a, rt, n, round == 0, h0, h1, h1 + G * kBatch, h1 >= H);
+            __syncthreads();
+            if (tid == 0) { sc->ticket = 0; __threadfence(); st_release(&sc->epoch, epoch0 + round + 1); }
+        } else {
+            if (tid == 0) while (ld_acquire(&sc->epoch) != epoch0 + round + 1) __nanosleep(40);
+        }
+        __syncthreads();
+        if (*(volatile int32_t*)&sc->done) break;
+        h0 = h1;
     }
-    // ---- chunk bookkeeping by the last CTA to get here --------------------------------------------
-    __syncthreads();
-    const unsigned long long t_scored = gtime();
-    if (tid == 0) {
-        __threadfence();
-        sLast = atomicAdd(&sc->ticket, 1) == (int)gridDim.x - 1;
-    }
-    __syncthreads();
     if (!sLast) return;
-    __threadfence();
-    if (tid < 32) ransac_select(sc, sets, counts, a, rt, n, first, h0, h1, next_end, last);
-    __syncthreads();
-    if (tid == 0) sc->ticket = 0;
-    // the run is over (budget reached, or this was the last chunk) and not refitted yet: refit here
-    if (!sc->done || sc->finalized) return;
-    __syncthreads();
-    if (tid == 0) {
-        sc->finalized = 1;
-        sc->stamps[0] = t_in; sc->stamps[1] = t_p3p; sc->stamps[2] = t_scored; sc->stamps[3] = gtime();
-    }
-    pnp_finalize(sc, hyp, q4, qv, mask, a, fb, n);
-    if (tid == 0) sc->stamps[6] = gtime();
+    // the run is over: this CTA finishes it
+    if (tid == 0) { sc->stamps[0] = t_in; sc->stamps[1] = t_p3p; sc->stamps[2] = t_scored; sc->stamps[3] = gtime(); }
+    pnp_mask_prune(sc, hyp, q4, qv, mask, a, fb, n);
+    if (tid == 0) { sc->finalized = 1; sc->stamps[6] = gtime(); }
 }
 
 }  // namespace
@@ -740,6 +780,7 @@ int ensure_rng_table(Ctx* c, int H)
 int launch_pnp(Ctx* c, const PnpLaunch& L)
 {
     Pipeline* p = c->pipe;
+    VO_TRY(join_pose_stream(c));   // (a refit still running there reads the inlier pack this run overwrites)
     PnpArgs a;
     memcpy(a.K, L.K, sizeof(a.K));
     a.confidence = L.prm.confidence;
@@ -750,9 +791,11 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
     a.explicit_sets = L.d_sets_in != nullptr;
     a.compact = L.compact;
     const int H = a.max_iters;
+    const size_t npts = (size_t)(L.n_upper > 0 ? L.n_upper : 1);
     VO_TRY(ensure(c, p->hyp, (size_t)(H > 0 ? H : 1) * 12));
     VO_TRY(ensure(c, p->counts, (size_t)(H > 0 ? H : 1)));
-    VO_TRY(ensure(c, p->mask, (size_t)(L.n_upper > 0 ? L.n_upper : 1)));
+    VO_TRY(ensure(c, p->mask, npts));
+    VO_TRY(ensure(c, p->q4i, npts * 4)); VO_TRY(ensure(c, p->qvi, npts));
     int32_t* sets = const_cast<int32_t*>(L.d_sets_in);
     RngTab rt{ nullptr, 0 };
     if (!sets) {
@@ -763,40 +806,31 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         rt.tab = p->rng_tab.p; rt.len = p->rng_tab_len;
     }
     FinalizeBufs fb{};
+    fb.q4i = (float4*)p->q4i.p; fb.qvi = p->qvi.p;
     if (L.compact) {
         fb.P_in = p->P[p->cur].p; fb.X_in = p->X[p->cur].p;
         const int nxt = (p->cur + 1) % 3;
-        VO_TRY(ensure(c, p->P[nxt], (size_t)(L.n_upper > 0 ? L.n_upper : 1) * 2));
-        VO_TRY(ensure(c, p->X[nxt], (size_t)(L.n_upper > 0 ? L.n_upper : 1) * 3));
+        VO_TRY(ensure(c, p->P[nxt], npts * 2));
+        VO_TRY(ensure(c, p->X[nxt], npts * 3));
         fb.P_out = p->P[nxt].p; fb.X_out = p->X[nxt].p;
     }
-    // chunks: the first is small (the adaptive stop usually ends inside it: one launch for the whole
-    // RANSAC), the others take up to 2048 hypotheses each
-    for (int h0 = 0, k = 0; k == 0 || h0 < H; k++) {
-        const int h1 = k == 0 ? (H < kPnpChunk0 ? H : kPnpChunk0) : (H - h0 < 2048 ? H : h0 + 2048);
-        const int next_end = H - h1 < 2048 ? H : h1 + 2048;
-        const int last = h1 >= H;
-        int grid = h1 - h0 > 0 ? h1 - h0 : 1;
-        if (k > 0 && grid > 2 * c->sm_count) grid = 2 * c->sm_count;   // later chunks: fixed grid, strided
-        VO_CUDA(c, launch_pdl(pnp_chunk_kernel, dim3(grid), dim3(kHypThreads), c->stream, p->d_sc, sets, (const float4*)L.q4,
-                              L.qv, p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, h0, h1, next_end, k == 0 ? 1 : 0, last));
-        c->launches++;
-        h0 = h1;
-        if (last) break;
-        if (k == 0 && L.readback_after_first) {
-            // the run usually ends inside the first chunk (finalized = 1 then, pose and counts final): let the
-            // host have the scalar block from here instead of from behind the draining later chunks
-            VO_TRY(join_side_stream(c));   // (a deferred append on the side stream writes n_cand)
-            if (!p->h_sc_first) {
-                VO_CUDA(c, cudaMallocHost((void**)&p->h_sc_first, sizeof(DevScalars)));
-                VO_CUDA(c, cudaMallocHost((void**)&p->h_sc_late, sizeof(DevScalars)));
-                VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose_first, cudaEventDisableTiming));
-            }
-            VO_CUDA(c, cudaMemcpyAsync(p->h_sc_first, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
-            VO_CUDA(c, cudaEventRecord(p->ev_pose_first, c->stream));
-            p->first_rb_enqueued = true;
-        }
+    // one persistent launch: every CTA must be resident (they meet at a flag between rounds)
+    int grid = H < kPnpChunk0 ? (H > 0 ? H : 1) : kPnpChunk0;
+    if (grid > c->sm_count) grid = c->sm_count;
+    const int epoch0 = (int)((unsigned)(++p->pnp_run) << 12);
+    VO_CUDA(c, launch_pdl(pnp_ransac_kernel, dim3(grid), dim3(kHypThreads), c->stream, p->d_sc, sets, (const float4*)L.q4, L.qv,
+                          p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, H, epoch0));
+    c->launches++;
+    // the refit: on the caller's stream, or on the pose stream when the landmark side goes on without it
+    cudaStream_t rs = c->stream;
+    if (L.refit_on_pose_stream) {
+        VO_CUDA(c, cudaEventRecord(c->ev_ransac, c->stream));
+        VO_CUDA(c, cudaStreamWaitEvent(c->stream4, c->ev_ransac, 0));
+        rs = c->stream4;
     }
+    VO_CUDA(c, launch_pdl(pnp_refit_kernel, dim3(1), dim3(kFinThreads), rs, p->d_sc, (const float4*)p->q4i.p,
+                          (const float*)p->qvi.p, a));
+    c->launches++;
     if (L.compact) {
         const int nxt = (p->cur + 1) % 3;
         if (nxt == p->prev) p->prev = -1;   // pruning without a preceding tracking step reuses that buffer

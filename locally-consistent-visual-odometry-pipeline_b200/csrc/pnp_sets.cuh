@@ -24,22 +24,38 @@ __device__ inline void gen_sets_warp(DevScalars* sc, int32_t* sets, RngTab rt, i
     int h = sc->sets_ready;
     long long pos = (long long)sc->rng;
     int exhausted = 0;
+    // the raw draws of the NEXT step are requested before this step's are looked at (as if no set of this step
+    // needed a re-draw, which is the rule): the table is cold in L1 and a step is otherwise one L2 round trip long
+    auto fetch = [&](long long p0, uint32_t* d) {
+        const bool in = p0 + 3 < rt.len;
+#pragma unroll
+        for (int k = 0; k < 4; k++) d[k] = in ? __ldg(rt.tab + p0 + k) : 0u;
+        return in;
+    };
+    uint32_t cur[4], nxt[4];
+    bool cur_in = fetch(pos + 4 * lane, cur);
     while (h < to && !exhausted) {
         const int cnt = min(32, to - h);
+        const bool nxt_in = fetch(pos + 128 + 4 * lane, nxt);
         bool ok = false;
         int4 v = make_int4(0, 0, 0, 0);
-        const long long p0 = pos + 4 * lane;
-        if (lane < cnt && p0 + 3 < rt.len) {
-            v.x = (int)(rt.tab[p0] % (unsigned)n);
-            v.y = (int)(rt.tab[p0 + 1] % (unsigned)n);
-            v.z = (int)(rt.tab[p0 + 2] % (unsigned)n);
-            v.w = (int)(rt.tab[p0 + 3] % (unsigned)n);
+        if (lane < cnt && cur_in) {
+            v.x = (int)(cur[0] % (unsigned)n);
+            v.y = (int)(cur[1] % (unsigned)n);
+            v.z = (int)(cur[2] % (unsigned)n);
+            v.w = (int)(cur[3] % (unsigned)n);
             ok = v.y != v.x && v.z != v.x && v.z != v.y && v.w != v.x && v.w != v.y && v.w != v.z;
         }
         const unsigned bad = __ballot_sync(0xffffffffu, lane < cnt && !ok);
         const int good = bad ? __ffs(bad) - 1 : cnt;
         if (lane < good) reinterpret_cast<int4*>(sets)[h + lane] = v;
         h += good; pos += 4 * good;
+        if (good == 32) {   // the usual case: the prefetched draws are the next step's
+#pragma unroll
+            for (int k = 0; k < 4; k++) cur[k] = nxt[k];
+            cur_in = nxt_in;
+            continue;
+        }
         if (good < cnt) {   // set h: serial draw with re-draws (or the table ran out)
             long long np = pos;
             int fail = 0;
@@ -63,6 +79,7 @@ __device__ inline void gen_sets_warp(DevScalars* sc, int32_t* sets, RngTab rt, i
             pos = __shfl_sync(0xffffffffu, np, 0);
             if (!exhausted) h++;
         }
+        if (h < to && !exhausted) cur_in = fetch(pos + 4 * lane, cur);   // the draw position moved: fetch again
     }
     __syncwarp();
     if (lane == 0) {

@@ -358,18 +358,46 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
 }
 
 // The pose-dependent rest of an early classification: DLT of the promoted rows with (T_first, T_new),
-// appended behind the live landmarks.  One CTA; ~20 rows per frame, each a serial FP64 Jacobi SVD.
+// appended behind the live landmarks.  One CTA; each row a serial FP64 Jacobi SVD.
+//   mode 0  positions, 3-D points and counters in one go (synchronous paths);
+//   mode 1  positions and counters only - all the next tracking step needs (main stream, pipelined frames);
+//   mode 2  the 3-D points of the rows mode 1 appended, once the refined pose is there (pose stream), and the
+//           pose-table row of the frame's new candidates.
 __global__ void __launch_bounds__(128)
 promote_finish_kernel(DevScalars* sc, PromoteArgs a, const double* __restrict__ prom_rows,
-                      const int32_t* __restrict__ prom_ti, const double* __restrict__ poses, float2* __restrict__ P,
-                      double* __restrict__ X, int land_cap)
+                      const int32_t* __restrict__ prom_ti, double* __restrict__ poses, float2* __restrict__ P,
+                      double* __restrict__ X, int land_cap, int mode, int pose_idx)
 {
     __shared__ double sM2[12];
     pdl_prologue();
     const int tid = threadIdx.x;
-    const int n_land = sc->n_land;
+    const bool ok = a.use_dev_T ? sc->ok != 0 : true;
+    if (mode == 1) {
+        // counters as of the pose, for the host (the block is read back while this stream goes on)
+        const int n_land = sc->n_land;
+        const int n_prom = ok ? sc->n_promoted : 0;
+        __syncthreads();
+        if (tid == 0) {
+            sc->snap_n_land = n_land; sc->snap_n_cand = sc->n_cand; sc->snap_cf_alias = sc->cf_alias;
+            sc->snap_n_appended = sc->n_appended;
+            sc->prom_base = n_land;
+            sc->spec_n_land = n_land;
+            sc->n_land = min(n_land + n_prom, land_cap);
+            sc->klt_iters_cand = sc->klt_iters_cand2;
+            sc->klt_iters_cand2 = 0;
+        }
+        for (int i = tid; i < n_prom; i += blockDim.x) {
+            const int o = n_land + i;
+            if (o >= land_cap) break;
+            P[o] = make_float2((float)prom_rows[4 * (size_t)i + 2], (float)prom_rows[4 * (size_t)i + 3]);
+        }
+        return;
+    }
+    if (mode == 2 && !ok) return;
+    const int n_land = mode == 2 ? sc->prom_base : sc->n_land;
     const int n_prom = sc->n_promoted;
     if (tid == 0) k_times_pose(a.K, a.use_dev_T ? sc->T : a.Tnew, sM2);
+    if (mode == 2 && pose_idx >= 0 && tid >= 32 && tid < 48) poses[16 * (size_t)pose_idx + (tid - 32)] = sc->T[tid - 32];
     __syncthreads();
     for (int i = tid; i < n_prom; i += blockDim.x) {
         const int o = n_land + i;
@@ -379,9 +407,10 @@ promote_finish_kernel(DevScalars* sc, PromoteArgs a, const double* __restrict__ 
         const double fx = prom_rows[4 * (size_t)i], fy = prom_rows[4 * (size_t)i + 1];
         const double cx = prom_rows[4 * (size_t)i + 2], cy = prom_rows[4 * (size_t)i + 3];
         dlt_point(M1, sM2, fx, fy, cx, cy, Xh);
-        P[o] = make_float2((float)cx, (float)cy);
+        if (mode == 0) P[o] = make_float2((float)cx, (float)cy);
         X[3 * (size_t)o] = Xh[0] / Xh[3]; X[3 * (size_t)o + 1] = Xh[1] / Xh[3]; X[3 * (size_t)o + 2] = Xh[2] / Xh[3];
     }
+    if (mode != 0) return;
     __syncthreads();
     if (tid == 0) {
         sc->spec_n_land = n_land;
@@ -404,7 +433,7 @@ __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts,
                                 const int32_t* __restrict__ n_new_dev, int use_dev_T,
                                 const double* __restrict__ Thost, float2* __restrict__ C, double2* __restrict__ F,
                                 int32_t* __restrict__ Ti, double* __restrict__ poses, int pose_idx, int cand_cap,
-                                int side)
+                                int side, int write_pose)
 {
     __shared__ int sLast;
     pdl_prologue();
@@ -414,7 +443,8 @@ __global__ void cand_add_kernel(DevScalars* sc, const double2* __restrict__ pts,
     const int n_new = n_new_dev ? min(*n_new_dev, n_new_upper) : n_new_upper;
     const bool skip = use_dev_T && !sc->ok;   // no pose this frame: nothing is added
     if (!skip) {
-        if (i < 16) poses[16 * (size_t)pose_idx + i] = use_dev_T ? sc->T[i] : Thost[i];
+        // (write_pose = 0: the refined pose is still being computed on the pose stream, which writes the row itself)
+        if (i < 16 && write_pose) poses[16 * (size_t)pose_idx + i] = use_dev_T ? sc->T[i] : Thost[i];
         if (i < n_new && n0 + i < cand_cap) {
             const double2 p = pts[i];
             C[n0 + i] = make_float2((float)p.x, (float)p.y);
@@ -481,6 +511,7 @@ __global__ void triangulate_kernel(const double* __restrict__ M1, const double* 
 int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
 {
     Pipeline* p = c->pipe;
+    VO_TRY(join_pose_stream(c));   // the 3-D points of rows promoted by a pipelined frame come from the pose stream
     const size_t n = n_upper > 0 ? n_upper : 1;
     const int nxt = (p->cur + 1) % 3;
     VO_TRY(ensure(c, p->P[nxt], n * 2));
@@ -556,10 +587,19 @@ int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, c
 }
 
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper, bool use_klt,
-                   int b_off)
+                   int b_off, bool split, int pose_idx)
 {
     Pipeline* p = c->pipe;
-    VO_TRY(join_side_stream(c));   // the candidates' KLT results come from the side stream
+    if (!(split && p->early_valid && use_klt && alpha_deg == p->early_alpha)) split = false;
+    if (split) {   // (the pose stream is in order: no need to wait for its previous frame here)
+        if (c->side_inflight) {
+            c->side_inflight = false; c->side_writes_counts = false;
+            VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+        }
+    } else {
+        VO_TRY(join_pose_stream(c));   // pose table rows / 3-D points a pipelined frame left to the pose stream
+        VO_TRY(join_side_stream(c));   // the candidates' KLT results come from the side stream
+    }
     if (p->early_valid) {
         if (use_klt && alpha_deg == p->early_alpha) {
             // the candidate side is done: triangulate the promoted rows with the pose and append them
@@ -573,10 +613,28 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
             VO_TRY(ensure(c, p->P[p->cur], need * 2, true));
             VO_TRY(ensure(c, p->X[p->cur], need * 3, true));
             const int land_cap = (int)(p->P[p->cur].cap / 2);
-            VO_CUDA(c, launch_pdl(promote_finish_kernel, dim3(1), dim3(128), c->stream, p->d_sc, a,
-                                  (const double*)p->prom_rows.p, (const int32_t*)p->prom_ti.p, (const double*)p->poses.p,
-                                  (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap));
-            c->launches++;
+            if (!split) {
+                VO_CUDA(c, launch_pdl(promote_finish_kernel, dim3(1), dim3(128), c->stream, p->d_sc, a,
+                                      (const double*)p->prom_rows.p, (const int32_t*)p->prom_ti.p, p->poses.p,
+                                      (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap, 0, -1));
+                c->launches++;
+            } else {
+                // main stream: positions + counters (and the snapshot the host reads with the pose)
+                VO_CUDA(c, launch_pdl(promote_finish_kernel, dim3(1), dim3(128), c->stream, p->d_sc, a,
+                                      (const double*)p->prom_rows.p, (const int32_t*)p->prom_ti.p, p->poses.p,
+                                      (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap, 1, -1));
+                VO_CUDA(c, cudaEventRecord(c->ev_snap, c->stream));
+                // pose stream, behind the refit: scalar block back to the host, then the 3-D points
+                VO_CUDA(c, cudaStreamWaitEvent(c->stream4, c->ev_snap, 0));
+                VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream4));
+                VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream4));
+                VO_CUDA(c, launch_pdl(promote_finish_kernel, dim3(1), dim3(128), c->stream4, p->d_sc, a,
+                                      (const double*)p->prom_rows.p, (const int32_t*)p->prom_ti.p, p->poses.p,
+                                      (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap, 2, pose_idx));
+                VO_CUDA(c, cudaEventRecord(c->ev_pose_done, c->stream4));
+                c->pose_inflight = true;
+                c->launches += 2;
+            }
             p->n_land_upper += p->early_ncand_upper;
             VO_CUDA(c, cudaGetLastError());
             return VO_OK;
@@ -624,7 +682,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
 }
 
 int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new,
-                    bool on_side_stream)
+                    bool on_side_stream, bool write_pose)
 {
     Pipeline* p = c->pipe;
     if (!on_side_stream) VO_TRY(join_side_stream(c));
@@ -637,7 +695,8 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
     const int threads = 256, blocks = ((n_new > 16 ? n_new : 16) + threads - 1) / threads;
     VO_CUDA(c, launch_pdl(cand_add_kernel, dim3(blocks), dim3(threads), on_side_stream ? c->stream2 : c->stream, p->d_sc,
                           (const double2*)d_pts, n_new, d_n_new, (int)(d_Thost == nullptr), d_Thost, (float2*)p->C[p->ccur].p,
-                          (double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap, (int)on_side_stream));
+                          (double2*)p->F[p->ccur].p, p->Ti[p->ccur].p, p->poses.p, p->n_poses, cap, (int)on_side_stream,
+                          (int)write_pose));
     c->launches++;
     p->n_poses++;
     p->n_cand_upper += n_new > 0 ? n_new : 0;
