@@ -409,7 +409,8 @@ def run_e2e(pkg, cfg, sq, steps, warmup, local_rank, world, prefetch=True):
     with open(os.path.join(tmp, "config.yaml"), "w") as f:
         f.write("dataset: 'kitti'\nfind_new_candidates_method: 'feed'\ninit_detector: 'sift'\ninit_descriptor: 'sift'\n"
                 "debug: False\nvisualization: False\nanimation: False\nsift_alpha: 1\nsift_ransac_confidence: 0.99999\n"
-                "shi_alpha: 1.5\nshi_ransac_confidence: 0.999993\npnp_max_iters: %d\ndevice: %d\n" % (cfg["pnp_iters"], local_rank))
+                "shi_alpha: 1.5\nshi_ransac_confidence: 0.999993\npnp_max_iters: %d\ndevice: %d\nframe_ahead: %s\n"
+                % (cfg["pnp_iters"], local_rank, "True" if prefetch else "False"))
     cwd = os.getcwd()
     os.chdir(tmp)
     sys.path.insert(0, os.path.join(ROOT, PKG))

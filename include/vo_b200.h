@@ -133,7 +133,7 @@ typedef struct vo_counters {
     int32_t klt_iters_candidates;        /* same over the last candidate KLT (set by the promotion step) */
     double reproj_cost;                  /* sum of squared reprojection errors of the refit */
     int32_t n_appended;                  /* rows the last vo_append_landmarks / queued batch added */
-    int32_t reserved_;
+    int32_t reserved_;                   /* vo_process_frame_pipelined: bit 0 = the next frame's tracking step is enqueued ahead */
 } vo_counters;
 
 /* Upload landmarks after bootstrap (main.py:198-200 vision.state = state).  Synchronises. */
@@ -145,6 +145,10 @@ int vo_get_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
  * landmark buffer keeps them on the device until the next tracking step (main.py:248 reads the
  * previous frame's state['X'] after the current frame's associate + estimatePose).  Synchronises. */
 int vo_get_prev_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
+/* ... and as they were before the tracking step before that one (a fourth buffer of the rotation): what main.py:248
+ * reads when the next frame's tracking step has already been enqueued inside the pose call
+ * (vo_process_frame_pipelined).  Synchronises. */
+int vo_get_prev2_state(vo_ctx* ctx, float* P, double* X, int cap, int* n);
 /* Asynchronous pinned-host snapshot of P/X as they are now, readable after later calls have
  * replaced them on the device (main.py:248 reads the previous frame's state['X'] after the next
  * frame's associate/estimatePose).  vo_get_snapshot synchronises. */
@@ -215,6 +219,10 @@ int vo_pnp_ransac_promote(vo_ctx* ctx, const double K[9], const vo_pnp_params* p
 int vo_promote_commit(vo_ctx* ctx);   /* (a vo_klt_track_landmarks* call behind the speculation confirms it too) */
 int vo_promote_rollback(vo_ctx* ctx);
 int vo_promote_pending(vo_ctx* ctx);
+/* The caller adopts the tracking step vo_process_frame_pipelined enqueued ahead as the next frame's tracking
+ * step (the class surface does, when associateKeypointsToLandmarks is called with the arguments assumed):
+ * state queries then no longer take it back. */
+int vo_ahead_adopt(vo_ctx* ctx);
 /* 1 if the candidates were tracked over (prev, next) together with the landmarks and not consumed yet */
 int vo_candidates_tracked(vo_ctx* ctx, int64_t prev_key, int64_t next_key);
 /* a6  LandmarkTriangulator.triangulate_landmark, steps 1 and 3 (vo_pipeline.py:489-545, 608-721):

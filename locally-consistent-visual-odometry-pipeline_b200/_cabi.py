@@ -99,8 +99,10 @@ SIGNATURES = {
     "vo_promote_commit": (c_int, [c_void_p]),
     "vo_promote_rollback": (c_int, [c_void_p]),
     "vo_promote_pending": (c_int, [c_void_p]),
+    "vo_ahead_adopt": (c_int, [c_void_p]),
     "vo_candidates_tracked": (c_int, [c_void_p, c_i64, c_i64]),
     "vo_get_prev_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
+    "vo_get_prev2_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
     "vo_add_candidates": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
     "vo_append_landmarks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
@@ -400,8 +402,21 @@ class Context:
     def candidates_tracked(self, prev_key, next_key):
         return bool(self.lib.vo_candidates_tracked(self.h, prev_key, next_key))
 
+    def ahead_adopt(self):
+        self._check(self.lib.vo_ahead_adopt(self.h))
+
     def promote_pending(self):
         return bool(self.lib.vo_promote_pending(self.h))
+
+    def get_prev2_state(self):
+        """The landmarks as they were two tracking steps back (see vo_get_prev2_state)."""
+        n = c_int()
+        self._check(self.lib.vo_get_prev2_state(self.h, None, None, 0, ctypes.byref(n)))
+        P = np.empty((n.value, 2), np.float32)
+        X = np.empty((n.value, 3), np.float64)
+        if n.value:
+            self._check(self.lib.vo_get_prev2_state(self.h, _ptr(P), _ptr(X), n.value, ctypes.byref(n)))
+        return P, X
 
     def get_prev_state(self):
         n = c_int()

@@ -205,6 +205,7 @@ int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
 // ---- device-resident Markov state (reference: BestVision.state / .extended_state,
 // /root/reference/src/vo_pipeline.py:36-37) and PnP / promotion scratch ------------------------
 constexpr int kMinimal = 4;          // P3P on 3 points + 1 disambiguation point
+constexpr int kLandBufs = 4;         // landmark buffers in rotation
 constexpr int kPnpChunks = 3;        // hypotheses are evaluated in <=3 chunks (adaptive stop between)
 
 // small block of scalars living in device memory; mirrored to pinned host memory on demand
@@ -232,6 +233,7 @@ struct DevScalars {
     int32_t rng_exhausted; // the RNG draw table ran out (host reports VO_ERR_CAPACITY)
     int32_t ticket;        // multi-CTA kernels: last-block-done counter (always 0 between kernels)
     int32_t prev_n_land;   // |P| before the last tracking step (rows of the `prev` landmark buffer)
+    int32_t prev2_n_land;  // ... and before the tracking step before that (`prev2` buffer)
     // values before the last promotion step (rollback of a speculative promotion)
     int32_t spec_n_land, spec_n_cand, spec_cf_alias, spec_cand_was_empty;
     int32_t finalized;     // the refit of the current RANSAC run has been done
@@ -243,7 +245,6 @@ struct DevScalars {
     int32_t prom_base;     // row of P/X where the promoted rows of the frame start (split promotion)
     // counters as of the pose (vo_process_frame_pipelined reads the block back while the main stream goes on)
     int32_t snap_n_land, snap_n_cand, snap_cf_alias, snap_n_appended;
-    int32_t pad3_;
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -259,10 +260,13 @@ struct Pipeline {
     // until the next frame's compaction - main.py:248 reads it after estimatePose
     int cur = 0;
     int prev = -1;          // buffer holding the state before the last tracking step (-1: none)
-    DevBuf<float> P[3];     // n x 2
-    DevBuf<double> X[3];    // n x 3
+    DevBuf<float> P[kLandBufs];     // n x 2
+    DevBuf<double> X[kLandBufs];    // n x 3
     int n_land_upper = 0;   // host-known upper bound of n_land
     int prev_n_upper = 0;   // same for the rows of the `prev` buffer
+    // the state before the tracking step before that: with a tracking step enqueued one frame ahead (inside the pose
+    // call) this is the buffer main.py:248 reads - the fourth buffer of the rotation keeps it intact
+    int prev2 = -1, prev2_n_upper = 0;
     // candidates, ping-pong
     int ccur = 0;
     DevBuf<float> C[2];     // n x 2 (current observation; float32-exact)
@@ -319,7 +323,7 @@ struct Pipeline {
     // host-side values before the last tracking step (vo_track_rollback)
     // vo_process_frame_pipelined: the tracking step (ahead_prev -> ahead_next) is already enqueued
     bool ahead_valid = false; int64_t ahead_prev = 0, ahead_next = 0;
-    bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0;
+    bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0, rb_prev2 = -1, rb_prev2_n_upper = 0;
     double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
     cudaEvent_t ev_land = nullptr;   // behind the landmark KLT launch (candidates' KLT ordered after it, see track_both)
     cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion

@@ -21,7 +21,7 @@ int pipeline_init(Ctx* c, int track_capacity, int hyp_capacity)
     VO_CUDA(c, cudaMallocHost((void**)&p->h_sc, sizeof(DevScalars)));
     memset(p->h_sc, 0, sizeof(DevScalars));
     const size_t n = p->track_capacity;
-    for (int k = 0; k < 3; k++) { VO_TRY(ensure(c, p->P[k], n * 2)); VO_TRY(ensure(c, p->X[k], n * 3)); }
+    for (int k = 0; k < kLandBufs; k++) { VO_TRY(ensure(c, p->P[k], n * 2)); VO_TRY(ensure(c, p->X[k], n * 3)); }
     for (int k = 0; k < 2; k++) {
         VO_TRY(ensure(c, p->C[k], n * 2)); VO_TRY(ensure(c, p->F[k], n * 2)); VO_TRY(ensure(c, p->Ti[k], n));
     }
@@ -39,7 +39,7 @@ void pipeline_free(Ctx* c)
 {
     Pipeline* p = c->pipe;
     if (!p) return;
-    for (int k = 0; k < 3; k++) { cudaFree(p->P[k].p); cudaFree(p->X[k].p); }
+    for (int k = 0; k < kLandBufs; k++) { cudaFree(p->P[k].p); cudaFree(p->X[k].p); }
     for (int k = 0; k < 2; k++) { cudaFree(p->C[k].p); cudaFree(p->F[k].p); cudaFree(p->Ti[k].p); }
     cudaFree(p->poses.p); cudaFree(p->klt_in.p); cudaFree(p->klt_out.p); cudaFree(p->klt_err.p);
     cudaFree(p->klt_status.p); cudaFree(p->klt_iters.p); cudaFree(p->lost.p); cudaFree(p->q4.p); cudaFree(p->qv.p);
@@ -302,20 +302,26 @@ int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
 // The landmarks as they were before the last vo_klt_track_landmarks / vo_process_frame: the third
 // landmark buffer keeps them until the next tracking step (main.py:248 reads the previous frame's
 // state['X'] after the current frame's associate + estimatePose).  Synchronises.
-int vo_get_prev_state(vo_ctx* c, float* P, double* X, int cap, int* n)
+static int get_state_before(vo_ctx* c, int steps_back, float* P, double* X, int cap, int* n)
 {
     VO_NEED(c);
     Pipeline* p = c->pipe;
-    if (p->prev < 0) return set_error(c, VO_ERR_STATE, "no previous state is held");
+    const int buf = steps_back == 2 ? p->prev2 : p->prev;
+    if (buf < 0) return set_error(c, VO_ERR_STATE, "no state from %d tracking step(s) back is held", steps_back);
     VO_TRY(read_scalars(c));
-    const int m = p->h_sc->prev_n_land;
+    const int m = steps_back == 2 ? p->h_sc->prev2_n_land : p->h_sc->prev_n_land;
     if (n) *n = m;
     if (m > cap) return (P || X) ? set_error(c, VO_ERR_CAPACITY, "previous state has %d rows, buffer %d", m, cap) : VO_OK;
-    if (m > 0 && P) VO_CUDA(c, cudaMemcpyAsync(P, p->P[p->prev].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
-    if (m > 0 && X) VO_CUDA(c, cudaMemcpyAsync(X, p->X[p->prev].p, sizeof(double) * 3 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && P) VO_CUDA(c, cudaMemcpyAsync(P, p->P[buf].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && X) VO_CUDA(c, cudaMemcpyAsync(X, p->X[buf].p, sizeof(double) * 3 * m, cudaMemcpyDefault, c->stream));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     return VO_OK;
 }
+
+int vo_get_prev_state(vo_ctx* c, float* P, double* X, int cap, int* n) { return get_state_before(c, 1, P, X, cap, n); }
+// ... and the state before the tracking step before that one: what main.py:248 reads when the tracking of the next
+// frame has been enqueued one frame ahead (inside the pose call, see vo_process_frame_pipelined)
+int vo_get_prev2_state(vo_ctx* c, float* P, double* X, int cap, int* n) { return get_state_before(c, 2, P, X, cap, n); }
 
 // main.py:248 reads the PREVIOUS frame's state['X'] after the next frame's associate/estimatePose
 // have already replaced it on the device: keep an asynchronous pinned-host snapshot (64 KB at 2k
@@ -442,12 +448,8 @@ static int fill_counters(vo_ctx* c, vo_counters* out, bool sync)
     return VO_OK;
 }
 
-int vo_get_counters(vo_ctx* c, vo_counters* out)
-{
-    VO_NEED(c);
-    VO_TRY(drop_ahead(c));
-    return fill_counters(c, out, true);
-}
+// (counters are read as they are: with a tracking step enqueued ahead they already show its effect)
+int vo_get_counters(vo_ctx* c, vo_counters* out) { return fill_counters(c, out, true); }
 // diagnostics: %globaltimer stamps (ns) of the last RANSAC run, see DevScalars::stamps.  Synchronises.
 int vo_debug_pnp_stamps(vo_ctx* c, uint64_t out[8])
 {
@@ -477,6 +479,7 @@ static int track_landmarks_impl(vo_ctx* c, int64_t prev_key, int64_t next_key, c
     VO_TRY(track_both(c, a, b, prm, true, add, early_alpha));
     p->cand_tracked_prev = prev_key; p->cand_tracked_next = next_key; p->cand_tracked_valid = true;
     p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
+    p->rb_prev2 = p->prev2; p->rb_prev2_n_upper = p->prev2_n_upper;
     VO_TRY(launch_landmark_compact(c, p->n_land_upper));
     p->rb_valid = true;
     p->packed_valid = true;
@@ -502,7 +505,7 @@ int vo_klt_track_landmarks_add(vo_ctx* c, int64_t prev_key, int64_t next_key, co
 
 __global__ void track_rollback_kernel(DevScalars* sc)
 {
-    sc->n_land = sc->prev_n_land; sc->n_tracked = 0; sc->n_lost = 0;
+    sc->n_land = sc->prev_n_land; sc->prev_n_land = sc->prev2_n_land; sc->n_tracked = 0; sc->n_lost = 0;
 }
 
 // The same, and the pose-independent half of the coming promotion step (vo_pipeline.py:503-545: lost rows
@@ -533,7 +536,9 @@ int vo_track_rollback(vo_ctx* c)
     track_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
-    p->cur = p->rb_cur; p->prev = -1; p->prev_n_upper = 0; p->n_land_upper = p->rb_n_land_upper;
+    // (the fourth buffer of the rotation: the state before the tracking step before this one is still there)
+    p->cur = p->rb_cur; p->prev = p->rb_prev; p->prev_n_upper = p->rb_prev_n_upper; p->prev2 = -1; p->prev2_n_upper = 0;
+    p->n_land_upper = p->rb_n_land_upper;
     p->rb_valid = false; p->packed_valid = false; p->cand_tracked_valid = false;
     return VO_OK;
 }
@@ -614,30 +619,26 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
     L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
     L.d_sets_in = nullptr; L.compact = true;
-    p->first_rb_enqueued = false;
     memcpy(L.K, K, sizeof(L.K));
+    // n_promoted == NULL: the caller only needs the pose now; the host waits for the scalar block only, so the
+    // promotion step (and whatever is enqueued next) runs while the host walks on to triangulate_landmark.
+    const bool early = n_promoted == nullptr;
+    const int ncand_before = p->n_cand_upper;
+    const bool cls_done = p->early_valid && alpha_deg == p->early_alpha;   // candidate side already classified
+    // ... and with the candidates classified by the tracking call (vo_klt_track_landmarks_ex) the landmark side is
+    // final when the RANSAC kernel ends: refit, read-back and the promoted rows' DLT go to the pose stream
+    const bool split = early && cls_done;
+    L.refit_on_pose_stream = split;
     VO_TRY(launch_pnp(c, L));
     p->packed_valid = false;
     p->spec_prev_key = p->cand_tracked_prev; p->spec_next_key = p->cand_tracked_next;
-    // n_promoted == NULL: the caller only needs the pose now.  The scalar block is read back between
-    // the PnP and the promotion kernels and the host waits for THAT copy only, so the promotion step
-    // (and whatever is enqueued next) runs while the host walks on to triangulate_landmark.
-    const bool early = n_promoted == nullptr;
-    const int ncand_before = p->n_cand_upper;
-    // (Classifying the candidates here, on the side stream under the PnP, was measured: the pose comes
-    // back 5.6 us later on the same box - A/B with tools/e2e_phases.py - so the class-surface path leaves
-    // the early half to callers of vo_klt_track_landmarks_ex / vo_process_frame[_pipelined].)
-    const bool cls_done = p->early_valid && alpha_deg == p->early_alpha;   // candidate side already classified
-    if (early) {
+    if (early && !p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
+    if (early && !split) {
         VO_TRY(join_side_stream(c));   // a deferred append on the side stream writes n_cand (long done by now)
-        if (!p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
-        // (with a read-back behind the first chunk in flight, this one goes to its own buffer: the host may be
-        // working on h_sc already when it lands)
-        VO_CUDA(c, cudaMemcpyAsync(p->first_rb_enqueued ? p->h_sc_late : p->h_sc, p->d_sc, sizeof(DevScalars),
-                                   cudaMemcpyDeviceToHost, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
         VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));
     }
-    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off));
+    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off, split, -1));
     VO_TRY(close_step(c));
     p->cand_tracked_valid = false;
     p->spec_pending = true;
@@ -647,9 +648,8 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
         if (trace) {   // host time blocked on the pose (tools/profile_e2e.py)
             timespec t0, t1;
             clock_gettime(CLOCK_MONOTONIC, &t0);
-            cudaEvent_t ev_w = p->first_rb_enqueued ? p->ev_pose_first : p->ev_pose;
-            const bool ready = cudaEventQuery(ev_w) == cudaSuccess;
-            cudaEventSynchronize(ev_w);
+            const bool ready = cudaEventQuery(p->ev_pose) == cudaSuccess;
+            cudaEventSynchronize(p->ev_pose);
             clock_gettime(CLOCK_MONOTONIC, &t1);
             p->trace_wait_us += (t1.tv_sec - t0.tv_sec) * 1e6 + (t1.tv_nsec - t0.tv_nsec) * 1e-3;
             p->trace_ready += ready; p->trace_n++;
@@ -657,19 +657,11 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
                 fprintf(stderr, "[vo trace] pose wait %.1f us/frame, pose already there %d/%d\n", p->trace_wait_us / p->trace_n,
                         p->trace_ready, p->trace_n);
         }
-        if (p->first_rb_enqueued) {
-            p->first_rb_enqueued = false;
-            VO_CUDA(c, cudaEventSynchronize(p->ev_pose_first));
-            if (p->h_sc_first->finalized) {
-                *p->h_sc = *p->h_sc_first;          // the run ended in its first chunk: this is the final block
-            } else {
-                VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
-                *p->h_sc = *p->h_sc_late;
-            }
-        } else {
-            VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
-        }
+        VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
         DevScalars* s = p->h_sc;   // as of the PnP: the promoted rows are not appended yet
+        if (split) {   // (read back while the main stream went on: the counters come from the snapshot taken at the pose)
+            s->n_land = s->snap_n_land; s->n_cand = s->snap_n_cand; s->cf_alias = s->snap_cf_alias; s->n_appended = s->snap_n_appended;
+        }
         s->spec_n_land = s->n_land;   // what a rollback restores on the host side
         if (cls_done) {   // the side stream has classified the candidates: their counts are final already
             p->n_land_upper = s->n_land + s->n_promoted;
@@ -708,6 +700,15 @@ int vo_promote_rollback(vo_ctx* c)
 }
 
 int vo_promote_pending(vo_ctx* c) { return c && c->pipe && c->pipe->spec_pending ? 1 : 0; }
+
+// The caller takes over a tracking step vo_process_frame_pipelined enqueued ahead (it is about to use it as the
+// tracking step of the next frame): state queries no longer take it back.
+int vo_ahead_adopt(vo_ctx* c)
+{
+    VO_NEED(c);
+    c->pipe->ahead_valid = false;
+    return VO_OK;
+}
 
 int vo_candidates_tracked(vo_ctx* c, int64_t prev_key, int64_t next_key)
 {
@@ -890,8 +891,9 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     if (p->profiling) pipelined = false;   // the stage timers bracket the stages of ONE frame
     if (p->profiling) cudaEventRecord(p->ev[0], c->stream);
     // a tracking step enqueued ahead by the previous pipelined call: ours, or to be taken back
-    const bool tracked = p->ahead_valid && p->ahead_prev == prev_key && p->ahead_next == next_key && p->packed_valid &&
-                         p->cand_tracked_valid;
+    // ... or one the caller made itself (vo_klt_track_landmarks* for this frame pair, the class surface's associate call)
+    const bool tracked = p->packed_valid && p->cand_tracked_valid && p->cand_tracked_prev == prev_key &&
+                         p->cand_tracked_next == next_key;
     if (p->ahead_valid && !tracked && p->rb_valid && p->packed_valid) VO_TRY(vo_track_rollback(c));
     p->ahead_valid = false;
     if (img) VO_TRY(vo_upload_frame(c, img, w, h, pitch, next_key));
@@ -950,6 +952,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     const int b_off_k = p->klt_b_off, mask_off_k = p->mask_src_off;   // this frame's, should the step ahead be taken back
     const bool mask_valid_k = p->mask_src_valid;
     if (pipelined) {
+        VO_TRY(flush_frame_hint(c, true));   // a frame announced for later goes to the ingest stream now: it may be the next one
         // the next frame is on the ingest stream already: its tracking goes right behind the append
         if (c->last_ingest_valid && c->last_ingest_key != next_key && vo_has_frame(c, c->last_ingest_key)) {
             const int64_t nk = c->last_ingest_key;
@@ -963,6 +966,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
                 VO_TRY(track_both(c, a2, b2, kp, true, nullptr, alpha_deg, gate));
                 p->cand_tracked_prev = next_key; p->cand_tracked_next = nk; p->cand_tracked_valid = true;
                 p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
+    p->rb_prev2 = p->prev2; p->rb_prev2_n_upper = p->prev2_n_upper;
                 VO_TRY(launch_landmark_compact(c, p->n_land_upper, gate));
                 p->rb_valid = true; p->packed_valid = true;
                 p->ahead_valid = true; p->ahead_prev = next_key; p->ahead_next = nk;
@@ -989,6 +993,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
             // the step ahead did nothing on the device (gated): take back its host-side bookkeeping only
             VO_TRY(join_side_stream(c));
             p->cur = p->rb_cur; p->prev = p->rb_prev; p->prev_n_upper = p->rb_prev_n_upper; p->n_land_upper = p->rb_n_land_upper;
+            p->prev2 = p->rb_prev2; p->prev2_n_upper = p->rb_prev2_n_upper;
             if (p->early_valid) {
                 p->early_valid = false; p->ccur ^= 1;
                 if (p->n_cand_upper < p->early_ncand_upper) p->n_cand_upper = p->early_ncand_upper;
@@ -1022,7 +1027,10 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         p->stage_frames++;
     }
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
-    if (counters) fill_counters_from(p->h_sc, counters);
+    if (counters) {
+        fill_counters_from(p->h_sc, counters);
+        counters->reserved_ = p->ahead_valid ? 1 : 0;   // bit 0: the next frame's tracking step has been enqueued ahead
+    }
     return VO_OK;
 }
 

@@ -809,7 +809,7 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
     fb.q4i = (float4*)p->q4i.p; fb.qvi = p->qvi.p;
     if (L.compact) {
         fb.P_in = p->P[p->cur].p; fb.X_in = p->X[p->cur].p;
-        const int nxt = (p->cur + 1) % 3;
+        const int nxt = (p->cur + 1) % kLandBufs;
         VO_TRY(ensure(c, p->P[nxt], npts * 2));
         VO_TRY(ensure(c, p->X[nxt], npts * 3));
         fb.P_out = p->P[nxt].p; fb.X_out = p->X[nxt].p;
@@ -832,8 +832,9 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
                           (const float*)p->qvi.p, a));
     c->launches++;
     if (L.compact) {
-        const int nxt = (p->cur + 1) % 3;
+        const int nxt = (p->cur + 1) % kLandBufs;
         if (nxt == p->prev) p->prev = -1;   // pruning without a preceding tracking step reuses that buffer
+        if (nxt == p->prev2) p->prev2 = -1;
         p->cur = nxt;
     }
     VO_CUDA(c, cudaGetLastError());

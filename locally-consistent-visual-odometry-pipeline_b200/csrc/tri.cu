@@ -117,7 +117,7 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
         int its = sIterW[lane];
         its = __reduce_add_sync(0xffffffffu, its);
         if (lane == 0) {
-            sc->klt_iters_cand = 0; sc->prev_n_land = n; sc->n_land = n_keep; sc->n_tracked = n_keep; sc->n_lost = n_lost;
+            sc->klt_iters_cand = 0; sc->prev2_n_land = sc->prev_n_land; sc->prev_n_land = n; sc->n_land = n_keep; sc->n_tracked = n_keep; sc->n_lost = n_lost;
             sc->klt_iters = its;
         }
     }
@@ -513,7 +513,7 @@ int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
     Pipeline* p = c->pipe;
     VO_TRY(join_pose_stream(c));   // the 3-D points of rows promoted by a pipelined frame come from the pose stream
     const size_t n = n_upper > 0 ? n_upper : 1;
-    const int nxt = (p->cur + 1) % 3;
+    const int nxt = (p->cur + 1) % kLandBufs;
     VO_TRY(ensure(c, p->P[nxt], n * 2));
     VO_TRY(ensure(c, p->X[nxt], n * 3));
     VO_TRY(ensure(c, p->q4, n * 4));
@@ -525,6 +525,7 @@ int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
         (const double*)p->X[p->cur].p, (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p,
         p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }, gate));
     c->launches++;
+    p->prev2 = p->prev == nxt ? -1 : p->prev; p->prev2_n_upper = p->prev_n_upper;
     p->prev = p->cur;
     p->prev_n_upper = n_upper;
     p->cur = nxt;

@@ -71,6 +71,11 @@ _DEFAULTS = {
     'klt_fb_thresh': 1.0,
     'speculative_promotion': True,   # enqueue the promotion step ahead of estimatePose's sync
     'speculative_tracking': True,    # track into a frame handed over early right behind the promotion step
+    # 'feed' mode only: estimatePose enqueues the WHOLE rest of the frame (promotion, candidate feed, landmark batches) and
+    # the next frame's tracking step before it waits for the pose, so the GPU never waits for the host between frames.
+    # triangulate_landmark must then be called as main.py:280-284 calls it (the state, frames and pose just returned);
+    # anything else raises instead of silently diverging.
+    'frame_ahead': False,
     'emulate_cf_alias': True,    # reference quirk App. B-5 (first candidate batch: F follows C)
     'device': 0,
     'gpu_detector': True,        # find_new_candidates_shi on the device (csrc/det.cu); False: cv2 on the CPU
@@ -101,6 +106,9 @@ class _Runtime:
         self.spec = None          # assumptions of a pending speculative promotion
         self.spec_track = None    # assumptions of a tracking step enqueued ahead of its associate call
         self.last_prefetch = None # (key, frame, fingerprint) of the newest frame on the ingest stream
+        self.ahead = None         # frame_ahead: what estimatePose assumed about the coming triangulate_landmark call
+        self.tracks_ahead = 0     # tracking steps the device has taken beyond the last associate call (0 or 1)
+        self.need_adopt = False   # an adopted step ahead the C side has not been told about yet
 
     # frames arrive as host uint8 arrays; the same object is passed to several stages and then
     # becomes the "old" frame of the next iteration (main.py:293), so upload + pyramid happen once
@@ -157,6 +165,7 @@ class _Runtime:
         """Take back a tracking step that was enqueued ahead of an associate call that never came."""
         if self.spec_track is not None:
             self.spec_track = None
+            self.tracks_ahead = 0
             self.ctx.track_rollback()
 
     def pair_keys(self, old_frame, new_frame):
@@ -215,16 +224,27 @@ class DeviceState(dict):
 
     def _load(self):
         if not dict.__contains__(self, 'P'):
-            st = self._rt.spec_track
-            if st is not None and st['state'] is self and self._current():
+            rt = self._rt
+            st = rt.spec_track
+            ah = rt.ahead
+            if ah is not None and ah['state'] is self and self._current():
+                # frame_ahead, between estimatePose and triangulate_landmark: the inlier rows of this frame; the device may
+                # already have tracked them into the next frame (they are then the head of the buffer it tracked FROM)
+                P, X = rt.ctx.get_prev_state() if rt.tracks_ahead else rt.ctx.get_state()
+                P, X = P[:ah['n_inl']], X[:ah['n_inl']]
+            elif st is not None and st['state'] is self and self._current():
                 P, X = self._rt.ctx.get_prev_state()   # the device is one tracking step ahead of this dict
             elif self._current():
+                if rt.need_adopt:     # the step ahead is this frame's tracking step now: do not let the query take it back
+                    rt.ctx.ahead_adopt()
+                    rt.need_adopt = False
                 P, X = self._rt.ctx.get_state()
                 lim = getattr(self, '_limit', None)
                 if lim is not None and self._rt.spec is not None:   # speculatively promoted rows are not visible yet
                     P, X = P[:lim], X[:lim]
             elif self._rt is _rt and getattr(self, '_prev', None) == self._rt.prev_token:
-                P, X = self._rt.ctx.get_prev_state()   # previous frame's state (main.py:248)
+                # previous frame's state (main.py:248); two tracking steps back when the pose call already enqueued the next one
+                P, X = self._rt.ctx.get_prev2_state() if self._rt.tracks_ahead else self._rt.ctx.get_prev_state()
             else:
                 raise RuntimeError("stale DeviceState: the device landmarks have moved on to a later frame")
             dict.__setitem__(self, 'P', P)
@@ -287,6 +307,9 @@ class DeviceExtendedState(dict):
             if not self._current():
                 raise RuntimeError("stale DeviceExtendedState: the device candidates have moved on")
             self._rt.drop_speculation()
+            st = self._rt.spec_track
+            if st is not None and st.get('ahead'):   # (the query would take the step ahead back behind our back)
+                self._rt.drop_spec_track()
             self._rt.flush_pending_add()
             C, F, T = self._rt.ctx.get_candidates()
             dict.__setitem__(self, 'C', C.astype(np.float64))
@@ -428,6 +451,17 @@ class KeypointsToLandmarksAssociator():
         with new_state = rows of P (new positions, float32) and X whose status is 1."""
         rt = _runtime(new_frame)
         rt.drop_speculation()      # estimatePose without a matching triangulate_landmark
+        if rt.ahead is not None:   # frame_ahead: that frame's stage is on the device already; its inputs are consumed
+            rt.ahead = None
+            if _candidate_feed:
+                _candidate_feed.pop(0)
+            if _landmark_feed:
+                _landmark_feed.pop(0)
+            rt.state_version += 1
+            rt.ext_version += 1
+            if rt.tracks_ahead:
+                rt.tracks_ahead = 0
+                rt.ctx.track_rollback()
         st = rt.spec_track
         if st is not None:
             # triangulate_landmark already enqueued this very tracking step behind its promotion (the frame
@@ -444,6 +478,8 @@ class KeypointsToLandmarksAssociator():
                     fr = rt.frames
                     del fr[min(fr, key=lambda i: fr[i][0])]
                 rt.pair = (old_frame, new_frame, st['k_old'], st['k_new'])
+                rt.tracks_ahead = 0
+                rt.need_adopt = bool(st.get('ahead'))
                 rt.prev_token += 1
                 if not dict.__contains__(state, 'P'):
                     state._prev = rt.prev_token
@@ -451,6 +487,7 @@ class KeypointsToLandmarksAssociator():
                 rt.state_version += 1
                 return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
             rt.ctx.track_rollback()
+            rt.tracks_ahead = 0
         pr = rt.pair
         if pr is not None and pr[1] is old_frame and rt.ctx.has_frame(pr[3]):
             k_old = pr[3]          # main.py:293 (img1 = img2): the frame tracked INTO last time, as uploaded then
@@ -469,7 +506,7 @@ class KeypointsToLandmarksAssociator():
             # the caller may still read this (now previous) state after the device has moved on:
             # the third landmark buffer keeps it until the next tracking step
             state._prev = rt.prev_token
-        rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt, add=add)
+        rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt, add=add, early_alpha=_early_alpha())
         rt.issue_hint(deferred=True)   # next frame's ingest: enqueued by the pose call, under the GPU's PnP
         rt.state_version += 1
         return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
@@ -545,6 +582,9 @@ class PoseEstimator():
         # sync this method ends in, with the pose taken from the device, and let triangulate_landmark
         # confirm it when its arguments are the ones assumed (main.py always passes them).
         method = config['find_new_candidates_method']
+        if (bool(_cfg('frame_ahead')) and method == 'feed' and bool(_cfg('speculative_promotion')) and not uploaded
+                and rt.pair is not None and rt.ctx.candidates_tracked(rt.pair[2], rt.pair[3])):
+            return self._estimate_frame_ahead(rt, associations, img_idx)
         speculate = (bool(_cfg('speculative_promotion')) and not uploaded
                      and (method in ('feed', 'sift-sift') or (method == 'shi-mask' and _device_shi()))
                      and rt.pair is not None and rt.ctx.candidates_tracked(rt.pair[2], rt.pair[3]))
@@ -570,6 +610,38 @@ class PoseEstimator():
                        'state_version': rt.state_version, 'ext_version': rt.ext_version}
             if isinstance(associations, DeviceState):
                 associations._limit = n_inl
+        return T
+
+    def _estimate_frame_ahead(self, rt, associations, img_idx):
+        """config frame_ahead: PnP, then - before the pose is waited for - the promotion step, the append of this
+        frame's candidate feed and landmark batches and the tracking step into the frame handed over early
+        (vo_process_frame_pipelined on the tracking step associate made).  triangulate_landmark only confirms."""
+        alpha = float(_alpha_threshold())
+        feed = _candidate_feed[0] if _candidate_feed else None
+        batches = _landmark_feed[0] if _landmark_feed else None
+        for bP, bX, target in (batches or ()):
+            if len(bP):
+                rt.ctx.append_landmarks(bP, bX, target, queue=True)
+        T, cnt = rt.ctx.process_frame(None, rt.pair[2], rt.pair[3], self.K, alpha, feed if feed is not None and len(feed) else None,
+                                      klt=rt.klt, pnp=self._params(), pipelined=True)
+        ok, n_inl = bool(cnt['pnp_ok']), cnt['n_inliers']
+        self.last = {'ok': ok, 'n_inliers': n_inl}
+        rt.need_adopt = False
+        rt.tracks_ahead = 1 if (cnt['reserved_'] & 1) else 0
+        if not ok or n_inl < 4:
+            rt.tracks_ahead = 0
+            if _candidate_feed:
+                _candidate_feed.pop(0)
+            if _landmark_feed:
+                _landmark_feed.pop(0)
+            rt.state_version += 1
+            rt.ext_version += 1
+            return self._rebootstrap(associations, img_idx)
+        rt.state_version += 1
+        associations._rebind(rt.state_version)
+        rt.ahead = {'T': T.tobytes(), 'alpha': alpha, 'K': np.asarray(self.K, np.float64).tobytes(), 'pair': rt.pair,
+                    'state': associations, 'n_inl': n_inl, 'feed': feed, 'batches': batches, 'ext_version': rt.ext_version,
+                    'pre': rt.last_prefetch if rt.tracks_ahead else None}
         return T
 
     def _rebootstrap(self, associations, img_idx):
@@ -657,6 +729,36 @@ class LandmarkTriangulator():
         keep = np.isin(keypoints, old_keypoints, invert=True).all(axis=1)   # element-wise, as the reference
         return (keypoints[keep], cur_des)
 
+    def _confirm_frame_ahead(self, rt, old_frame, new_frame, state, extended_state, new_pose):
+        """config frame_ahead: estimatePose has enqueued this whole stage already; check that it is being asked for
+        what it assumed (main.py:280-284 always does) and hand the state objects on."""
+        ah, rt.ahead = rt.ahead, None
+        new_pose = np.ascontiguousarray(new_pose, np.float64)
+        if isinstance(extended_state, DeviceExtendedState):
+            ext_ok = extended_state._current()
+        else:
+            ext_ok = rt.ext_version == 0 and len(np.asarray(extended_state['C'])) == 0
+        feed = _candidate_feed.pop(0) if _candidate_feed else None
+        batches = _landmark_feed.pop(0) if _landmark_feed else None
+        if not (ext_ok and ah['ext_version'] == rt.ext_version and state is ah['state'] and state._current()
+                and ah['pair'] is rt.pair and rt.pair[0] is old_frame and rt.pair[1] is new_frame
+                and float(_alpha_threshold()) == ah['alpha'] and new_pose.tobytes() == ah['T']
+                and np.asarray(self.K, np.float64).tobytes() == ah['K'] and feed is ah['feed'] and batches is ah['batches']):
+            raise RuntimeError("frame_ahead: triangulate_landmark was not called with the frames, state and pose of the "
+                               "estimatePose call before it (set frame_ahead: False for arbitrary call sequences)")
+        rt.state_version += 1
+        rt.ext_version += 1
+        dict.clear(state)
+        state._version, state._dirty, state._limit = rt.state_version, False, None
+        pre = ah['pre']
+        if pre is not None:    # the tracking step into the frame handed over early is on the stream already
+            rt.spec_track = {'old': new_frame, 'fp': pre[2], 'k_old': rt.pair[3], 'k_new': pre[0], 'state': state, 'ahead': True}
+        if isinstance(extended_state, DeviceExtendedState):
+            extended_state._rebind(rt.ext_version)
+        else:
+            extended_state = DeviceExtendedState(rt, rt.ext_version)
+        return (state, extended_state, [])
+
     # ---- the per-frame stage ---------------------------------------------------------------------------
     def triangulate_landmark(self, old_frame: np.ndarray, new_frame: np.ndarray, state: dict, extended_state: dict,
                              new_pose):
@@ -665,6 +767,8 @@ class LandmarkTriangulator():
         with (T, new_pose), append it to state P/X and remove it from C/F/T.
         Returns (state, extended_state, cur_des)."""
         rt = _runtime(new_frame)
+        if rt.ahead is not None:
+            return self._confirm_frame_ahead(rt, old_frame, new_frame, state, extended_state, new_pose)
         rt.drop_spec_track()
         method = config['find_new_candidates_method']
         threshold = _alpha_threshold()
@@ -750,7 +854,7 @@ class LandmarkTriangulator():
                 and (method == 'feed' or device_shi)):
             add = rt.pending_add
             try:    # (confirms the promotion as well; fails only if the frame ahead has left the slot cache)
-                rt.ctx.klt_track_landmarks(rt.pair[3], pre[0], rt.klt, add=add)
+                rt.ctx.klt_track_landmarks(rt.pair[3], pre[0], rt.klt, add=add, early_alpha=_early_alpha())
                 rt.pending_add = None
                 committed = True
                 rt.spec_track = {'old': new_frame, 'fp': pre[2], 'k_old': rt.pair[3], 'k_new': pre[0], 'state': state}
@@ -765,6 +869,15 @@ class LandmarkTriangulator():
         else:
             extended_state = DeviceExtendedState(rt, rt.ext_version)
         return (state, extended_state, cur_des)
+
+
+def _early_alpha():
+    """Threshold for classifying the candidates on the side stream during the tracking step (the pose-independent
+    half of the promotion): only when estimatePose will enqueue the promotion itself, with this very alpha."""
+    method = config['find_new_candidates_method']
+    if bool(_cfg('speculative_promotion')) and (method in ('feed', 'sift-sift') or (method == 'shi-mask' and _device_shi())):
+        return float(_alpha_threshold())
+    return None
 
 
 def _device_shi():

@@ -252,3 +252,96 @@ def test_fb_check_inside_the_tracking_step(pkg, scene_mod, oracle):
             c2.close()
     finally:
         c.close()
+
+
+# ---- the class surface one frame ahead (config frame_ahead) ---------------------------------------------------------
+def _drive(vo, sq, n, frame_ahead, read_states, pinned=None):
+    """main.py's loop with candidate feed, landmark batches, a frame handed over early, and the reads main.py does."""
+    vo.config['frame_ahead'] = frame_ahead
+    vo._reset_runtime()
+    rng = np.random.default_rng(9)
+    feeds = [f.copy() for f in sq.feeds]
+    batches = [[(rng.uniform(20, 300, (40, 2)).astype(np.float32), rng.normal(size=(40, 3)) + [0, 0, 20], len(sq.P0) + 3)]
+               + ([(rng.uniform(20, 300, (15, 2)).astype(np.float32), rng.normal(size=(15, 3)) + [0, 0, 9], 0)] if k % 4 == 2 else [])
+               for k in range(n + 2)]
+    vision = vo.BestVision(sq.K)
+    vision.state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+    vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+    associate = vo.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+    pose_estimator = vo.PoseEstimator(sq.K)
+    out = dict(T=[], prevX=[], midX=[], endX=[], nP=[])
+    frames = sq.frames if pinned is None else pinned
+    img1 = frames[0]
+    for k in range(1, n):
+        img2 = frames[k]
+        vo.set_candidate_feed([feeds[k]])
+        vo.set_landmark_feed([batches[k]])
+        if k + 1 < len(frames):
+            vo.prefetch_frame(frames[k + 1])
+        new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
+        if read_states and k % 3 == 1:
+            out["nP"].append(len(new_state["P"]))                     # tracked rows, before the pose (debug print of main.py:232)
+        new_pose = pose_estimator.estimatePose(new_state, k)
+        out["T"].append(new_pose.copy())
+        if read_states:
+            out["prevX"].append(np.array(vision.state["X"]))           # main.py:248: the PREVIOUS frame's final state
+            if k % 2 == 0:
+                out["midX"].append(np.array(new_state["X"]))           # the inlier rows of this frame
+        tri = vo.LandmarkTriangulator(sq.K, None)
+        vision.state, vision.extended_state, _ = tri.triangulate_landmark(img1, img2, new_state, vision.extended_state, new_pose)
+        if read_states and k % 5 == 0:
+            out["endX"].append(np.array(vision.state["X"]))            # this frame's final state, read before the next associate
+        img1 = img2
+    out["final"] = (np.array(vision.state["P"]), np.array(vision.state["X"]))
+    out["ext"] = tuple(np.array(vision.extended_state[k]) for k in "CFT")
+    return out
+
+
+@pytest.mark.parametrize("read_states", [False, True])
+def test_dropin_frame_ahead_equals_the_transparent_path(dropin, pkg, scene_mod, read_states):
+    """config frame_ahead: estimatePose enqueues the rest of the frame and the next frame's tracking step before it
+    waits for the pose.  Same poses, same states (also the ones read late, main.py:248, and in between), bit for bit."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    n = 14
+    h, w = sq.frames[0].shape
+    pinned = []
+    for f in sq.frames[:n + 1]:
+        pa = pkg.PinnedArray((h, w), np.uint8)
+        pa.array[...] = f
+        pinned.append(pa)
+    views = [p.array for p in pinned]
+    a = _drive(dropin, sq, n, False, read_states, views)
+    b = _drive(dropin, sq, n, True, read_states, views)
+    assert len(a["T"]) == len(b["T"]) == n - 1
+    for k, (x, y) in enumerate(zip(a["T"], b["T"])):
+        assert np.array_equal(x, y), k
+    for key in ("prevX", "midX", "endX"):
+        assert len(a[key]) == len(b[key])
+        for k, (x, y) in enumerate(zip(a[key], b[key])):
+            assert np.array_equal(x, y), (key, k)
+    assert a["nP"] == b["nP"]
+    assert np.array_equal(a["final"][0], b["final"][0]) and np.array_equal(a["final"][1], b["final"][1])
+    for u, v in zip(a["ext"], b["ext"]):
+        assert np.array_equal(u, v)
+    dropin.config['frame_ahead'] = False
+
+
+def test_dropin_frame_ahead_refuses_other_arguments(dropin, scene_mod):
+    sq = get_sequence(scene_mod, "kitti_half")
+    dropin.config['frame_ahead'] = True
+    dropin._reset_runtime()
+    try:
+        vision = dropin.BestVision(sq.K)
+        state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+        ext = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+        associate = dropin.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+        pe = dropin.PoseEstimator(sq.K)
+        dropin.set_candidate_feed([sq.feeds[1], sq.feeds[2]])
+        ns, _ = associate.associateKeypointsToLandmarks(sq.frames[0], sq.frames[1], state)
+        T = pe.estimatePose(ns, 1)
+        T2 = T.copy()
+        T2[0, 3] += 0.5
+        with pytest.raises(RuntimeError):
+            dropin.LandmarkTriangulator(sq.K, None).triangulate_landmark(sq.frames[0], sq.frames[1], ns, ext, T2)
+    finally:
+        dropin.config['frame_ahead'] = False
