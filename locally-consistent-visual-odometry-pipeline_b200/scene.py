@@ -323,3 +323,52 @@ class SteadyStream:
 
     def checksum(self):
         return int(sum(int(f.astype(np.int64).sum()) * (i + 1) for i, f in enumerate(self.frames)))
+
+
+# ---- datasets on disk in the reference's layouts (main.py:14-68) -------------------------------------------------------
+def write_dataset(seq, root, layout="parking", n_frames=None):
+    """Write the frames and ground-truth poses of `seq` (Sequence / SteadyStream) under `root` the way the
+    reference's main.py reads them: parking/images/img_%05d.png + parking/poses.txt (12 columns, row-major 3x4
+    camera->world, main.py:48-64), kitti-dataset/05/image_0/%06d.png + kitti-dataset/poses/05.txt (main.py:14-31; main.py
+    counts files ending in 'left.png' there, so as many placeholders are written), or the Malaga folder with
+    *left.jpg frames and the GPS table whose columns 8, 9 it plots (main.py:33-46).  Returns the frame paths."""
+    import os
+    import cv2
+    n = len(seq.frames) if n_frames is None else min(n_frames, len(seq.frames))
+    rows = []
+    for k in range(n):
+        Twc = np.linalg.inv(seq.poses[k])
+        rows.append(Twc[:3].ravel())
+    rows = np.array(rows)
+    paths = []
+    if layout == "parking":
+        d = os.path.join(root, "parking", "images")
+        os.makedirs(d, exist_ok=True)
+        for k in range(n):
+            paths.append(os.path.join(d, "img_%05d.png" % k))
+            cv2.imwrite(paths[-1], seq.frames[k])
+        np.savetxt(os.path.join(root, "parking", "poses.txt"), rows)
+    elif layout == "kitti":
+        d = os.path.join(root, "kitti-dataset", "05", "image_0")
+        os.makedirs(d, exist_ok=True)
+        os.makedirs(os.path.join(root, "kitti-dataset", "poses"), exist_ok=True)
+        for k in range(n):
+            paths.append(os.path.join(d, "%06d.png" % k))
+            cv2.imwrite(paths[-1], seq.frames[k])
+            open(os.path.join(d, "%06d_left.png" % k), "wb").close()
+        np.savetxt(os.path.join(root, "kitti-dataset", "poses", "05.txt"), rows)
+    elif layout == "malaga":
+        base = os.path.join(root, "malaga-urban-dataset-extract-07")
+        d = os.path.join(base, "malaga-urban-dataset-extract-07_rectified_800x600_Images")
+        os.makedirs(d, exist_ok=True)
+        for k in range(n):
+            paths.append(os.path.join(d, "img_CAMERA1_%010d_left.jpg" % k))
+            cv2.imwrite(paths[-1], seq.frames[k], [cv2.IMWRITE_JPEG_QUALITY, 98])
+        gps = np.zeros((n, 10))
+        gps[:, 8], gps[:, 9] = rows[:, 3], rows[:, 11]
+        np.savetxt(os.path.join(base, "malaga-urban-dataset-extract-07_all-sensors_GPS.txt"), gps)
+    else:
+        raise ValueError("layout must be parking, kitti or malaga")
+    for sub in ("result-trajectory-plots", "initialization-plots-and-figures", "ground-truth-trajectories"):
+        os.makedirs(os.path.join(root, sub), exist_ok=True)
+    return paths

@@ -945,20 +945,25 @@ def prefetch_frame(img):
 
 
 class FrameIngest:
-    """Pre-decoded frames in a ring of pinned host buffers, decoded one frame ahead by a worker
-    thread (cv2.imread releases the GIL) and handed to the device one frame ahead of their use:
+    """Pre-decoded frames in a ring of pinned host buffers, decoded ahead of their use by a pool of worker
+    threads (cv2.imread releases the GIL; main.py:216-223 decodes one frame per iteration, 3-4 ms each) and handed
+    to the device one frame ahead:
 
-        for img2 in FrameIngest(paths):          # instead of cv2.imread(...) per iteration
+        for img2 in FrameIngest(paths, workers=8):          # instead of cv2.imread(...) per iteration
             new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
 
     `source` is a sequence of file paths (read with cv2.IMREAD_GRAYSCALE, as main.py:217-223 does) or of
-    2-D uint8 arrays.  Yields numpy views over pinned memory; a view stays valid for `depth - 2` more
-    iterations (main.py keeps the previous frame as img1)."""
+    2-D uint8 arrays.  Frames come out in order whatever order the workers finish in.  Yields numpy views over
+    pinned memory; a view stays valid for two more iterations (main.py keeps the previous frame as img1).
+    depth: ring slots (default workers + 3: previous, current and next frame are live, the rest is decode-ahead)."""
 
-    def __init__(self, source, depth=4, prefetch=True):
+    def __init__(self, source, depth=None, prefetch=True, workers=1):
+        workers = max(int(workers), 1)
+        if depth is None:
+            depth = workers + 3
         if depth < 3:
             raise ValueError("FrameIngest needs depth >= 3 (previous, current and next frame are live)")
-        self.source, self.depth, self.do_prefetch = source, depth, prefetch
+        self.source, self.depth, self.do_prefetch, self.workers = source, depth, prefetch, workers
         self.ring, self.shape = [], None
 
     def _decode(self, item):
@@ -985,33 +990,77 @@ class FrameIngest:
 
     def __iter__(self):
         import threading
-        import queue
-        q = queue.Queue(maxsize=1)   # one decoded frame ahead; its ring slot is not live yet
+        n = len(self.source)
+        # frame i may be written into its ring slot once frame i - depth is dead.  `consumed` = the last frame whose
+        # iteration the caller has finished: it still holds that one (img1), the generator holds the next two, every
+        # older frame is dead - so frame i is free to decode while i <= consumed + depth - 1
+        cond = threading.Condition()
+        done = {}                    # index -> pinned view, or the exception its decode raised
+        state = {"next": 0, "consumed": -1, "stop": False}
 
         def worker():
-            try:
-                for i, item in enumerate(self.source):
-                    q.put((i, self._decode(item)))
-                q.put(None)
-            except BaseException as e:   # surface decode errors in the consumer
-                q.put(e)
+            while True:
+                with cond:
+                    while not state["stop"] and (state["next"] >= n or state["next"] > state["consumed"] + self.depth - 1):
+                        if state["next"] >= n:
+                            return
+                        cond.wait()
+                    if state["stop"]:
+                        return
+                    i = state["next"]
+                    state["next"] += 1
+                try:
+                    img = self._decode(self.source[i])
+                    with cond:       # (ring allocation and the copy into the slot; slots of different frames differ)
+                        if self.shape != img.shape:
+                            self._slot(i, img)
+                            res = self.ring[i % self.depth].array
+                        else:
+                            res = None
+                    if res is None:
+                        res = self.ring[i % self.depth].array
+                        res[...] = img
+                except BaseException as e:   # surface decode errors in the consumer, at the frame's position
+                    res = e
+                with cond:
+                    done[i] = res
+                    cond.notify_all()
 
-        t = threading.Thread(target=worker, daemon=True)
-        t.start()
+        threads = [threading.Thread(target=worker, daemon=True) for _ in range(min(self.workers, max(n, 1)))]
+        for t in threads:
+            t.start()
 
-        def take():
-            r = q.get()
+        def take(i):
+            if i >= n:
+                return None
+            with cond:
+                while i not in done:
+                    cond.wait()
+                r = done.pop(i)
             if isinstance(r, BaseException):
+                with cond:
+                    state["stop"] = True
+                    cond.notify_all()
                 raise r
-            return None if r is None else self._slot(*r)
+            return r
 
-        cur = take()
-        while cur is not None:
-            nxt = take()
-            if nxt is not None and self.do_prefetch:
-                prefetch_frame(nxt)
-            yield cur
-            cur = nxt
+        try:
+            cur = take(0)
+            j = 0
+            while cur is not None:
+                nxt = take(j + 1)
+                if nxt is not None and self.do_prefetch:
+                    prefetch_frame(nxt)
+                yield cur
+                with cond:
+                    state["consumed"] = j
+                    cond.notify_all()
+                cur = nxt
+                j += 1
+        finally:
+            with cond:
+                state["stop"] = True
+                cond.notify_all()
 
 
 # ---- trajectory / map bookkeeping on the device (main.py:239-255, :262-271, :296-305) ----
