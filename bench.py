@@ -482,6 +482,75 @@ def run_e2e(pkg, cfg, sq, steps, warmup, local_rank, world, prefetch=True):
     return dict(fps=float(np.median(win)), windows=[float(x) for x in win], h2d=h2d / n, d2h=d2h / n)
 
 
+def run_files_leg(pkg, cfg, sq, local_rank, n_frames=160, workers=None):
+    """PNG files on disk -> poses, through the drop-in classes with FrameIngest(workers=k) decoding ahead
+    (cv2.imread on k threads, in-order hand-off into a pinned ring).  Reported beside the headline, not as it: the
+    decode, not the VO core, sets this number."""
+    import shutil
+    import tempfile
+    import cv2
+    scene = importlib.import_module(PKG + ".scene")
+    workers = workers or max(min((os.cpu_count() or 2) - 2, 16), 1)
+    tmp = tempfile.mkdtemp(prefix="vo_files_")
+    n = min(n_frames, len(sq.frames))
+    paths = scene.write_dataset(sq, tmp, "kitti", n)
+    with open(os.path.join(tmp, "config.yaml"), "w") as f:
+        f.write("dataset: 'kitti'\nfind_new_candidates_method: 'feed'\ninit_detector: 'sift'\ninit_descriptor: 'sift'\n"
+                "debug: False\nvisualization: False\nanimation: False\nsift_alpha: 1\nsift_ransac_confidence: 0.99999\n"
+                "shi_alpha: 1.5\nshi_ransac_confidence: 0.999993\npnp_max_iters: %d\ndevice: %d\nframe_ahead: True\n" % (cfg["pnp_iters"], local_rank))
+    cwd = os.getcwd()
+    os.chdir(tmp)
+    sys.path.insert(0, os.path.join(ROOT, PKG))
+    try:
+        sys.modules.pop("vo_pipeline", None)
+        vo = importlib.import_module("vo_pipeline")
+    finally:
+        os.chdir(cwd)
+    cv2.setNumThreads(1)
+    try:
+        t0 = time.perf_counter()
+        for _ in vo.FrameIngest(paths, prefetch=False, workers=workers):
+            pass
+        decode_fps = n / (time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        for p in paths[:24]:
+            cv2.imread(p, cv2.IMREAD_GRAYSCALE)
+        one_thread_fps = 24 / (time.perf_counter() - t0)
+        vision = vo.BestVision(sq.K)
+        vision.state = {"P": sq.P0.astype(np.float64), "X": sq.X0.copy()}
+        vision.extended_state = {"C": np.array([]), "F": np.array([]), "T": np.array([])}
+        associate = vo.KeypointsToLandmarksAssociator(sq.K, np.eye(4))
+        pose_estimator = vo.PoseEstimator(sq.K)
+        img1 = None
+        t0 = None
+        for b, img2 in enumerate(vo.FrameIngest(paths, workers=workers)):
+            if b == 0:
+                img1 = img2
+                continue
+            if b == 9:     # the first frames fill the decode pipeline and warm the kernels up
+                vo._runtime().ctx.synchronize()
+                t0 = time.perf_counter()
+            vo.set_candidate_feed([sq.feeds[b]])
+            vo.set_landmark_feed([batches_for(cfg, sq, b - 1, b)])
+            new_state, lost = associate.associateKeypointsToLandmarks(img1, img2, vision.state)
+            new_pose = pose_estimator.estimatePose(new_state, b)
+            pos = np.linalg.inv(new_pose)[0:3, 3]
+            tri = vo.LandmarkTriangulator(sq.K, None)
+            vision.state, vision.extended_state, _ = tri.triangulate_landmark(img1, img2, new_state, vision.extended_state, new_pose)
+            img1 = img2
+        vo._runtime().ctx.synchronize()
+        fps = (n - 9) / (time.perf_counter() - t0)
+    finally:
+        vo._reset_runtime()
+        sys.modules.pop("vo_pipeline", None)
+        sys.path.remove(os.path.join(ROOT, PKG))
+        shutil.rmtree(tmp, ignore_errors=True)
+    return {"frames_per_s": fps, "decode_only_frames_per_s": decode_fps, "cv2_imread_one_thread_frames_per_s": one_thread_fps,
+            "decode_workers": workers, "frames": n, "format": "PNG %dx%d gray" % (sq.frames[0].shape[1], sq.frames[0].shape[0]),
+            "note": "FrameIngest(paths, workers=%d) -> associate / estimatePose / triangulate_landmark; main.py:216-223 decodes one frame per "
+                    "iteration on one thread" % workers}
+
+
 def parity_block(cfg, sq, gpu_trace, port_trace):
     """GPU path (synchronous leg) against the CPU port on the same frames, same process."""
     scene = importlib.import_module(PKG + ".scene")
@@ -819,6 +888,11 @@ def main():
                   "host": "rank pinned to cores %s, torch/cv2 thread pools at 1 in the GPU arm" % (
                       "%d-%d" % (my_cores[0], my_cores[-1]) if my_cores else "?")},
     })
+    if world == 1 and args.config == "kitti":
+        try:
+            line["files_to_poses"] = run_files_leg(importlib.import_module(PKG), cfg, sq, local_rank)
+        except Exception as ex:   # (an extra leg: never let it take the headline line down)
+            line["files_to_poses"] = {"error": repr(ex)}
     if world == 1 and not args.no_cpu_baseline:
         n = 60
         n_par = PREROLL + min(args.warmup, 5) + n

@@ -221,6 +221,7 @@ int vo_drop_frames(vo_ctx* c)
 // Upload + pyramid of one frame on `st` (the main stream, or the ingest stream for a prefetch).
 static int upload_impl(vo_ctx* c, const uint8_t* img, int w, int h, int pitch, int64_t key, bool ingest, bool overlap = false)
 {
+    VO_NVTX(ingest ? "vo:frame_ingest(H2D+pyramid)" : "vo:frame_upload(H2D+pyramid)");
     if (!c || !img) return VO_ERR_INVALID;
     if (w <= 0 || h <= 0 || w > c->max_w || h > c->max_h || pitch < w)
         return set_error(c, VO_ERR_INVALID, "frame %dx%d (pitch %d) outside ctx limits %dx%d", w, h, pitch, c->max_w, c->max_h);

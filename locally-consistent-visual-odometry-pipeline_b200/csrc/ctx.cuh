@@ -8,7 +8,17 @@
 #include <vector>
 #include "../../include/vo_b200.h"
 
+#include <nvtx3/nvToolsExt.h>
+
 namespace vo {
+
+// NVTX range over the host-side enqueue of a stage (header-only NVTX v3: a no-op costing a few ns unless a tool
+// such as ncu / nsys injects itself); the stage names are the rows of DESIGN.md's kernel table
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+};
+#define VO_NVTX(name) ::vo::NvtxRange _nvtx_range_##__LINE__(name)
 
 constexpr int kPad = 32;        // border (px) around every pyramid level, REFLECT_101 filled
 constexpr int kMaxLevels = 8;   // hard cap on pyramid levels

@@ -648,6 +648,7 @@ int detector_free(Ctx* c)
 // device: d.out (float2 corners in cv2's order), d.d_sc->n_out.
 int launch_gftt(Ctx* c, const FrameSlot& f, const uint8_t* d_mask, const vo_gftt_params& prm)
 {
+    VO_NVTX("vo:shi_tomasi");
     Detector& d = c->det;
     const int w = f.w, h = f.h;
     if (prm.block_size < 1 || prm.block_size > kMaxBlock)

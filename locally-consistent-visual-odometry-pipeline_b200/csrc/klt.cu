@@ -444,6 +444,7 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
                 const vo_klt_params& prm, cudaStream_t st, const int32_t* gate)
 {
+    VO_NVTX("vo:klt_track");
     if (!st) st = c->stream;
     if (n_upper < 0) n_upper = 0;
     if (nB_upper < 0) nB_upper = 0;

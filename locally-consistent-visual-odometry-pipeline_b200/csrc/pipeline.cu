@@ -883,6 +883,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
                               const double K[9], const vo_klt_params* kparams, const vo_pnp_params* pparams, double alpha_deg,
                               const double* new_candidates, int n_new, double T44[16], vo_counters* counters, bool pipelined)
 {
+    VO_NVTX(pipelined ? "vo:process_frame_pipelined" : "vo:process_frame");
     VO_NEED(c);
     if (!K || n_new < 0 || (n_new > 0 && !new_candidates)) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;

@@ -779,6 +779,7 @@ int ensure_rng_table(Ctx* c, int H)
 
 int launch_pnp(Ctx* c, const PnpLaunch& L)
 {
+    VO_NVTX("vo:pnp_ransac+refit");
     Pipeline* p = c->pipe;
     VO_TRY(join_pose_stream(c));   // (a refit still running there reads the inlier pack this run overwrites)
     PnpArgs a;

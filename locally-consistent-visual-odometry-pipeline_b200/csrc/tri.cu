@@ -510,6 +510,7 @@ __global__ void triangulate_kernel(const double* __restrict__ M1, const double* 
 
 int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
 {
+    VO_NVTX("vo:landmark_compact");
     Pipeline* p = c->pipe;
     VO_TRY(join_pose_stream(c));   // the 3-D points of rows promoted by a pipelined frame come from the pose stream
     const size_t n = n_upper > 0 ? n_upper : 1;
@@ -555,6 +556,7 @@ int early_undo(Ctx* c)
 // alpha, or takes it back.
 int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, const int32_t* gate)
 {
+    VO_NVTX("vo:promote_early(classify)");
     Pipeline* p = c->pipe;
     if (ncand_upper <= 0) return VO_OK;
     PromoteArgs a;
@@ -590,6 +592,7 @@ int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, c
 int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_deg, int ncand_upper, bool use_klt,
                    int b_off, bool split, int pose_idx)
 {
+    VO_NVTX("vo:promote");
     Pipeline* p = c->pipe;
     if (!(split && p->early_valid && use_klt && alpha_deg == p->early_alpha)) split = false;
     if (split) {   // (the pose stream is in order: no need to wait for its previous frame here)
@@ -685,6 +688,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
 int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thost, const int32_t* d_n_new,
                     bool on_side_stream, bool write_pose)
 {
+    VO_NVTX("vo:cand_add");
     Pipeline* p = c->pipe;
     if (!on_side_stream) VO_TRY(join_side_stream(c));
     const size_t need = (size_t)p->n_cand_upper + (n_new > 0 ? n_new : 0) + 1;
@@ -709,6 +713,7 @@ int launch_cand_add(Ctx* c, const double* d_pts, int n_new, const double* d_Thos
 // address space).  The host-side bound of |P| follows the same rule as the kernel.
 int launch_land_append(Ctx* c, const float* d_P, const double* d_X, int n_rows, int target, const int32_t* gate)
 {
+    VO_NVTX("vo:land_append");
     Pipeline* p = c->pipe;
     if (n_rows <= 0) return VO_OK;
     int upper = p->n_land_upper + n_rows;

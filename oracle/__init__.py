@@ -247,3 +247,39 @@ def good_features_to_track(img, max_corners=500, quality=0.03, min_distance=10.0
     if want_eig:
         return corners[:n].copy(), eig, nc.value
     return corners[:n].copy()
+
+
+# ---- bootstrap: five-point essential-matrix RANSAC + recoverPose (oracle/fivept.c) -----------------------------------
+def five_point(q1, q2):
+    """Essential matrices (m x 3 x 3, m <= 10, unit Frobenius norm) through 5 normalised correspondences."""
+    q1 = np.ascontiguousarray(q1, np.float64).reshape(5, 2)
+    q2 = np.ascontiguousarray(q2, np.float64).reshape(5, 2)
+    Es = np.zeros((10, 9))
+    m = _f("vo_oracle_five_point", _I, [_VP, _VP, _VP])(_p(q1), _p(q2), _p(Es))
+    return Es[:m].reshape(m, 3, 3)
+
+
+def find_essential_mat(p1, p2, K, prob=0.999, thr=1.0, max_iters=1000):
+    """cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, prob, thr) restated -> dict(ok, E, mask, iters, best_iter, best_model, n_inliers)."""
+    p1 = np.ascontiguousarray(p1, np.float64).reshape(-1, 2)
+    p2 = np.ascontiguousarray(p2, np.float64).reshape(-1, 2)
+    K = np.ascontiguousarray(K, np.float64)
+    n = len(p1)
+    E = np.zeros((3, 3)); mask = np.zeros(max(n, 1), np.uint8); info = np.zeros(4, np.int32)
+    ok = _f("vo_oracle_find_essential_mat", _I, [_VP, _VP, _I, _VP, _D, _D, _I, _VP, _VP, _VP])(
+        _p(p1), _p(p2), n, _p(K), prob, thr, max_iters, _p(E), _p(mask), _p(info))
+    return dict(ok=bool(ok), E=E, mask=mask[:n], iters=int(info[0]), best_iter=int(info[1]), best_model=int(info[2]), n_inliers=int(info[3]))
+
+
+def recover_pose(E, p1, p2, K, mask=None):
+    """cv2.recoverPose(E, p1, p2, K, mask=mask) restated -> (count, R, t, mask ANDed with the winner's cheirality test, which)."""
+    E = np.ascontiguousarray(E, np.float64)
+    p1 = np.ascontiguousarray(p1, np.float64).reshape(-1, 2)
+    p2 = np.ascontiguousarray(p2, np.float64).reshape(-1, 2)
+    K = np.ascontiguousarray(K, np.float64)
+    n = len(p1)
+    m = np.ones(max(n, 1), np.uint8) if mask is None else np.ascontiguousarray(np.asarray(mask).ravel() != 0, np.uint8).copy()
+    R = np.zeros((3, 3)); t = np.zeros(3); which = np.zeros(1, np.int32)
+    g = _f("vo_oracle_recover_pose", _I, [_VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _VP])(
+        _p(E), _p(p1), _p(p2), n, _p(K), _p(m), _p(R), _p(t), _p(which))
+    return g, R, t, m[:n], int(which[0])

@@ -280,8 +280,41 @@ def seq():
     np.savez_compressed(os.path.join(HERE, "seq.npz"), **out)
 
 
+BOOT_CASES = {  # name: (n, outlier_frac, seed, K name) - SURVEY.md 8f-3
+    "n300_o20": (300, 0.2, 2, "kitti"), "n800_o30": (800, 0.3, 3, "kitti"), "n1500_o45": (1500, 0.45, 4, "kitti"),
+    "n200_o0": (200, 0.0, 5, "kitti"), "n60_o10": (60, 0.1, 6, "parking"), "n2000_o20": (2000, 0.2, 7, "malaga"),
+    "n500_o50": (500, 0.5, 8, "kitti"), "n5_exact": (5, 0.0, 9, "kitti"),
+}
+
+
+def bootstrap():
+    """The bootstrap's two cv2 calls exactly as the reference makes them (vo_pipeline.py:139-162):
+    findEssentialMat(k1, k2, K, RANSAC, 0.999, 1.0, None) and recoverPose(E, k1, k2, K, mask=mask), whose
+    mask argument is ANDed with the cheirality test in place."""
+    Ks = {"kitti": synth.K_KITTI, "parking": synth.K_PARKING, "malaga": synth.K_MALAGA}
+    out = {"cv2_version": cv2.__version__}
+    for name, (n, of, seed, kn) in BOOT_CASES.items():
+        K = Ks[kn]
+        p1, p2, R, t, _ = synth.bootstrap_scene(n, of, seed, K=K, noise=0.0 if n == 5 else 0.3)
+        E, mask = cv2.findEssentialMat(p1, p2, K, cv2.RANSAC, 0.999, 1.0, None)
+        out[name + "_psum"] = float(p1.sum() + p2.sum())
+        out[name + "_E_all"] = E                          # n == 5: every model cv2 found, stacked
+        E0 = E[:3]
+        out[name + "_E"] = E0
+        out[name + "_mask_E"] = np.packbits(mask.ravel() != 0)
+        m2 = mask.copy()
+        good, Rc, tc, m2o = cv2.recoverPose(E0, p1, p2, K, mask=m2)
+        assert np.array_equal(m2, m2o)                    # modified in place, as the reference relies on
+        out[name + "_good"] = good
+        out[name + "_R"] = Rc
+        out[name + "_t"] = tc.ravel()
+        out[name + "_mask_pose"] = np.packbits(m2o.ravel() != 0)
+        print(name, "inliers", int((mask != 0).sum()), "after recoverPose", good)
+    np.savez_compressed(os.path.join(HERE, "bootstrap.npz"), **out)
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["klt", "pnp", "tri", "gftt", "seq"]
+    which = sys.argv[1:] or ["klt", "pnp", "tri", "gftt", "seq", "bootstrap"]
     for w in which:
         globals()[w]()
     print("golden vectors written with cv2", cv2.__version__)

@@ -133,3 +133,24 @@ def bearing_pairs(n, seed, w=1241, h=376, sigma=15.0):
     C = np.stack([rng.uniform(0, w, n), rng.uniform(0, h, n)], 1).astype(np.float32).astype(np.float64)
     F = (C + rng.normal(0, sigma, C.shape)).astype(np.float32).astype(np.float64)
     return C, F
+
+
+# ---- two-view bootstrap scenes: matched pixel pairs with outliers ---------------------------------------
+def bootstrap_scene(n, outlier_frac, seed, K=K_KITTI, w=1241, h=376, noise=0.3, t=(0.9, -0.05, 0.3), rvec=(0.01, -0.03, 0.005)):
+    """n matches between two views ~1 m apart; outliers are uniform random pixels in the second view.
+    Returns p1, p2 (n x 2 float64), R, t (the true relative pose, |t| not normalised), outlier flags."""
+    rng = np.random.default_rng(seed)
+    X = np.stack([rng.uniform(-15, 15, n), rng.uniform(-3, 3, n), rng.uniform(5, 50, n)], 1)
+    R = rodrigues(rvec)
+    t = np.asarray(t, np.float64)
+
+    def proj(Xc):
+        return np.stack([K[0, 0] * Xc[:, 0] / Xc[:, 2] + K[0, 2], K[1, 1] * Xc[:, 1] / Xc[:, 2] + K[1, 2]], 1)
+    p1 = proj(X) + rng.normal(0, noise, (n, 2))
+    p2 = proj(X @ R.T + t) + rng.normal(0, noise, (n, 2))
+    no = int(outlier_frac * n)
+    idx = rng.choice(n, no, replace=False)
+    p2[idx] = np.stack([rng.uniform(0, w, no), rng.uniform(0, h, no)], 1)
+    is_out = np.zeros(n, bool)
+    is_out[idx] = True
+    return p1, p2, R, t, is_out
