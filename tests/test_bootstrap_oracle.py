@@ -75,7 +75,7 @@ def test_oracle_bootstrap_vs_cv2_live(oracle):
         p1, p2, R, t, _ = synth.bootstrap_scene(n, of, seed, K=synth.K_MALAGA, w=1024, h=768)
         E, mask = cv2.findEssentialMat(p1, p2, synth.K_MALAGA, cv2.RANSAC, 0.999, 1.0, None)
         o = oracle.find_essential_mat(p1, p2, synth.K_MALAGA)
-        assert np.array_equal(o["mask"], (mask.ravel() != 0).astype(np.uint8)) and e_dist(o["E"], E) < 1e-9
+        assert np.array_equal(o["mask"], (mask.ravel() != 0).astype(np.uint8)) and e_dist(o["E"], E) < 1e-7   # (roots from two different polynomial solvers)
         m2 = mask.copy()
         good, Rc, tc, _ = cv2.recoverPose(E, p1, p2, synth.K_MALAGA, mask=m2)
         g2, Ro, to, mo, _ = oracle.recover_pose(E, p1, p2, synth.K_MALAGA, mask=mask)
