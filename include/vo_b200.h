@@ -259,6 +259,27 @@ int vo_append_landmarks(vo_ctx* ctx, const float* P, const double* X, int n, int
  * AFTER that one returns (pageable rows: until that call returns). */
 int vo_queue_landmarks(vo_ctx* ctx, const float* P, const double* X, int n, int target_total);
 
+/* ---- the bootstrap on the device.  Replaces, in VOInitializer.getPoseEstimate
+ * (vo_pipeline.py:139-162) and in the "< 4 inliers" re-bootstrap of estimatePose (vo_pipeline.py:274-324),
+ *     E, mask = cv2.findEssentialMat(kps1, kps2, K, cv2.RANSAC, 0.999, 1.0, None)
+ *     _, R, t, _ = cv2.recoverPose(E, kps1, kps2, K, mask=mask)
+ * five-point essential-matrix RANSAC (cv::RNG(2^64-1) subsets, Sampson error in float32, first strictly better
+ * model wins, adaptive budget, no refit), then the cheirality vote over the four (R, t) decompositions with
+ * OpenCV's distance threshold 50, whose mask is ANDed into the RANSAC mask - as the in-place `mask=mask` of the
+ * reference's call does. */
+typedef struct vo_boot_params {
+    double prob;        /* RANSAC confidence (reference: 0.999) */
+    double threshold;   /* Sampson threshold in pixels (reference: 1.0) */
+    int max_iters;      /* OpenCV's default maxIters: 1000 */
+} vo_boot_params;
+void vo_boot_params_default(vo_boot_params* p);
+/* kps1, kps2: n x 2 float64 pixel positions (host or device).  Outputs (all optional): T34 = [R | t] 3x4 row-major
+ * (|t| = 1), mask n bytes (host or device; 1 = RANSAC inlier that passes the winner's cheirality test), E 3x3 (unit
+ * Frobenius norm), info = {ok, iterations run, winning iteration, winning model of it, RANSAC inliers, inliers after the
+ * cheirality test}.  ok = 0 (fewer than 5 matches, no model): everything zero.  Synchronises. */
+int vo_bootstrap_pose(vo_ctx* ctx, const double* kps1, const double* kps2, int n, const double K[9],
+                      const vo_boot_params* params, double T34[12], uint8_t* mask, double E[9], int32_t info[6]);
+
 /* ---- SURVEY.md 8f-1 (first "next" row): the Shi-Tomasi candidate detector on the device.
  * Replaces cv2.goodFeaturesToTrack(new_frame, maxCorners=500, qualityLevel=0.03, minDistance=10,
  * mask=mask, blockSize=4, gradientSize=3, useHarrisDetector=False) at vo_pipeline.py:381

@@ -38,6 +38,10 @@ class GfttParams(ctypes.Structure):
                 ("block_size", c_int), ("vec_cols", c_int), ("use_cluster", c_int)]
 
 
+class BootParams(ctypes.Structure):
+    _fields_ = [("prob", c_double), ("threshold", c_double), ("max_iters", c_int)]
+
+
 class Counters(ctypes.Structure):
     _fields_ = [(n, ctypes.c_int32) for n in (
         "n_landmarks", "n_candidates", "n_tracked", "n_lost", "n_inliers", "pnp_ok", "ransac_iters",
@@ -105,6 +109,9 @@ SIGNATURES = {
     "vo_get_prev2_state": (c_int, [c_void_p, c_void_p, c_void_p, c_int, _PI]),
     "vo_track_triangulate_promote": (c_int, [c_void_p, c_i64, c_i64, c_void_p, c_void_p, c_double, _PK, _PI]),
     "vo_add_candidates": (c_int, [c_void_p, c_void_p, c_int, c_void_p]),
+    "vo_boot_params_default": (None, [ctypes.POINTER(BootParams)]),
+    "vo_bootstrap_pose": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, ctypes.POINTER(BootParams), c_void_p, c_void_p,
+                                  c_void_p, c_void_p]),
     "vo_append_landmarks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "vo_queue_landmarks": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int]),
     "vo_track_candidates": (c_int, [c_void_p, c_i64, c_i64, _PK]),
@@ -465,6 +472,20 @@ class Context:
             self._queued_rows = getattr(self, "_queued_rows", [])[-6:] + [(P, X)]   # keep the arrays alive
         fn = self.lib.vo_queue_landmarks if queue else self.lib.vo_append_landmarks
         self._check(fn(self.h, _ptr(P), _ptr(X), len(P), int(target_total)))
+
+    def bootstrap_pose(self, kps1, kps2, K, prob=0.999, threshold=1.0, max_iters=1000):
+        """cv2.findEssentialMat(kps1, kps2, K, cv2.RANSAC, prob, threshold) + cv2.recoverPose(E, kps1, kps2, K, mask=mask)
+        on the device (reference vo_pipeline.py:139-162) -> dict(ok, T34, mask, E, iters, best_iter, best_model, n_inliers, n_good)."""
+        kps1 = np.ascontiguousarray(kps1, np.float64).reshape(-1, 2)
+        kps2 = np.ascontiguousarray(kps2, np.float64).reshape(-1, 2)
+        K = np.ascontiguousarray(K, np.float64)
+        n = len(kps1)
+        prm = BootParams(float(prob), float(threshold), int(max_iters))
+        T = np.zeros((3, 4)); E = np.zeros((3, 3)); mask = np.zeros(max(n, 1), np.uint8); info = np.zeros(6, np.int32)
+        self._check(self.lib.vo_bootstrap_pose(self.h, _ptr(kps1), _ptr(kps2), n, _ptr(K), ctypes.byref(prm), _ptr(T), _ptr(mask),
+                                               _ptr(E), _ptr(info)))
+        return dict(ok=bool(info[0]), T34=T, mask=mask[:n], E=E, iters=int(info[1]), best_iter=int(info[2]), best_model=int(info[3]),
+                    n_inliers=int(info[4]), n_good=int(info[5]))
 
     def process_frame(self, img, prev_key, next_key, K, alpha_deg, new_candidates=None, klt=None, pnp=None,
                       want_counters=True, pipelined=False):

@@ -79,6 +79,7 @@ _DEFAULTS = {
     'emulate_cf_alias': True,    # reference quirk App. B-5 (first candidate batch: F follows C)
     'device': 0,
     'gpu_detector': True,        # find_new_candidates_shi on the device (csrc/det.cu); False: cv2 on the CPU
+    'gpu_bootstrap': True,       # five-point RANSAC + recoverPose on the device (csrc/boot.cu); False: cv2 on the CPU
 }
 
 
@@ -422,7 +423,18 @@ class VOInitializer():
         return (np.array([kps1[m.queryIdx].pt for m in good]), np.array([kps2[m.trainIdx].pt for m in good]))
 
     def getPoseEstimate(self, kps_f1, kps_f2):
-        """5-point essential-matrix RANSAC + cheirality: 3x4 [R|t] of frame2 w.r.t. frame1, inlier mask."""
+        """5-point essential-matrix RANSAC + cheirality: 3x4 [R|t] of frame2 w.r.t. frame1, inlier mask (n x 1 uint8, as
+        cv2 returns it and as recoverPose leaves it: RANSAC inliers that pass the cheirality test).  On the device
+        (csrc/boot.cu); config gpu_bootstrap: False keeps the cv2 calls of the reference."""
+        if _cfg('gpu_bootstrap'):
+            try:
+                r = _runtime().ctx.bootstrap_pose(kps_f1, kps_f2, self.K, 0.999, 1.0)
+            except _cabi.VoError:
+                r = None
+            if r is not None:
+                if not r['ok']:    # cv2 hands back E = None here and recoverPose raises on it: same loud failure
+                    raise ValueError("bootstrap: no essential matrix found for %d matches" % len(kps_f1))
+                return r['T34'], r['mask'].reshape(-1, 1)
         self._need_cv2()
         E, mask = cv2.findEssentialMat(kps_f1, kps_f2, self.K, cv2.RANSAC, 0.999, 1.0, None)
         _, R, t, _ = cv2.recoverPose(E, kps_f1, kps_f2, self.K, mask=mask)

@@ -43,12 +43,21 @@ def reference_src():
 
 
 def stub_matplotlib():
+    """matplotlib is not installed here; main.py and visual.py import it.  Returns the names to remove again."""
+    def getter(k):
+        if k.startswith("__"):
+            raise AttributeError(k)
+        return lambda *a, **kw: None
+    added = []
     for name in ("matplotlib", "matplotlib.pyplot"):
         if name not in sys.modules:
             m = types.ModuleType(name)
-            m.__getattr__ = lambda k: (lambda *a, **kw: None)
+            m.__getattr__ = getter
             sys.modules[name] = m
-    sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+            added.append(name)
+    if added:
+        sys.modules["matplotlib"].pyplot = sys.modules["matplotlib.pyplot"]
+    return added
 
 
 def run_main(src, first_on_path, workdir):
@@ -80,7 +89,15 @@ def test_reference_main_py_runs_unchanged_over_the_dropin(tmp_path, scene_mod):
     if src is None:
         pytest.skip("the reference's main.py is on neither /root/reference/src nor baseline/_ref/src on this machine")
     cv2 = pytest.importorskip("cv2")
-    stub_matplotlib()
+    stubs = stub_matplotlib()
+    try:
+        _run_and_compare(src, tmp_path, scene_mod)
+    finally:
+        for name in stubs:
+            sys.modules.pop(name, None)
+
+
+def _run_and_compare(src, tmp_path, scene_mod):
     n = 44
     sq = scene_mod.Sequence("parking", n_frames=n, n_tracks=10, n_feed=1, seed=21, step=0.08, heading=float(np.pi / 2), z0=25.0)
     scene_mod.write_dataset(sq, str(tmp_path), "parking")
