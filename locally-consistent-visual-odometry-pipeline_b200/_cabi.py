@@ -144,7 +144,16 @@ def load(build_if_missing=True):
     if _lib is not None:
         return _lib
     if build_if_missing and _build.needs_build():
-        _build.build()
+        # N ranks of one job may get here together on a fresh checkout: one of them builds, the others wait
+        import fcntl
+        os.makedirs(_build.OBJ, exist_ok=True)
+        with open(os.path.join(_build.OBJ, ".build.lock"), "w") as lock:
+            fcntl.flock(lock, fcntl.LOCK_EX)
+            try:
+                if _build.needs_build():
+                    _build.build()
+            finally:
+                fcntl.flock(lock, fcntl.LOCK_UN)
     if not os.path.exists(_build.LIB):
         raise ImportError("libvo_b200.so is missing (%s) and there is no CPU fallback" % _build.LIB)
     lib = ctypes.CDLL(_build.LIB)

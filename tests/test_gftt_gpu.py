@@ -63,7 +63,11 @@ def test_gftt_vs_cv2_live(ctx):
         c = c.reshape(-1, 2)
         o = ctx.good_features_to_track(k, params=ctx_params(ctx, mc, q, md, bs), shape=img.shape)
         agree.append(len(c) == len(o) and np.array_equal(c, o))
-    # the SIMD dispatch of the cv2 build on this host decides a few rounding details (oracle/gftt.c);
+        if not agree[-1]:
+            # another cv2 build than the goldens': its SIMD dispatch decides a few rounding details of the min-eigenvalue
+            # map (oracle/gftt.c), which can swap near-ties in the greedy selection - but not move corners about
+            d = np.abs(c[:, None, :] - o[None, :, :]).max(-1).min(1) if len(c) and len(o) else np.ones(1)
+            assert abs(len(c) - len(o)) <= max(2, len(c) // 50) and (d <= 1.0).mean() >= 0.9, (md, mc, q, bs)
     # on the build the goldens were recorded with every case is identical
     assert np.mean(agree) >= 0.5
     if cv2.__version__ == str(np.load(os.path.join(GOLD, "gftt.npz"))["cv2_version"]):
