@@ -11,11 +11,15 @@ if ROOT not in sys.path:
 PKG_NAME = "locally-consistent-visual-odometry-pipeline_b200"
 
 
+# (resolved at import: fixtures change the working directory later)
+_PARITY_PATH = os.path.abspath(os.environ["VO_PARITY_REPORT"]) if os.environ.get("VO_PARITY_REPORT") else None
+
+
 def parity_report(section, name, values):
     """Every magnitude the parity tests print, kept as JSON too when VO_PARITY_REPORT names a file
     (tools/gpu_round.sh sets it; the result is committed as profiles/parity_r2.json)."""
     import json
-    path = os.environ.get("VO_PARITY_REPORT")
+    path = _PARITY_PATH
     if not path:
         return
     try:

@@ -116,3 +116,35 @@ def test_pnp_stress_properties(ctx, pkg):
     c = ctx.solve_pnp_ransac(X[perm], P[perm], K, p, sets=inv[sets].astype(np.int32))
     assert np.array_equal(c["mask"], a["mask"][perm])
     assert rot_angle(a["R"], R) < 2e-3 and np.linalg.norm(a["t"] - t) < 0.05
+
+
+def test_pnp_f32_filter_changes_nothing(pkg, monkeypatch):
+    """The scoring kernel decides pairs far from the threshold in float32 and only the rest in cv2's float64
+    arithmetic (VO_PNP_F32_FILTER=1; off by default, it measured slower): counts, winner, mask and pose must be those of the
+    all-float64 scoring, also
+    far from the origin, where float32 has little to offer, and with points near the camera plane."""
+    rng = np.random.default_rng(12)
+    cases = []
+    X, P, R, t, _ = synth.pnp_scene(10000, 0.5, 77)
+    cases.append((X, P, 4096, 1.0))
+    X2, P2, _, _, _ = synth.pnp_scene(3000, 0.3, 78)
+    cases.append((X2, P2, 500, 0.99999))
+    # the same scene 20 km from the origin (world coordinates of a long trajectory): X and t are huge, x_c is not
+    shift = np.array([20000.0, -3000.0, 15000.0])
+    cases.append((X2 + shift, P2, 500, 0.99999))
+    # points all around (and inside 0.5 m of) the camera plane of most hypotheses
+    X3 = rng.uniform(-2, 2, (2000, 3)) + [0, 0, 1.0]
+    P3 = np.stack([rng.uniform(0, 1241, 2000), rng.uniform(0, 376, 2000)], 1).astype(np.float32)
+    cases.append((X3, P3, 300, 0.99999))
+    for X, P, H, conf in cases:
+        out = []
+        for on in ("0", "1"):
+            monkeypatch.setenv("VO_PNP_F32_FILTER", on)
+            c = pkg.Context(device=0, max_w=64, max_h=64, hyp_capacity=4096)
+            try:
+                out.append(c.solve_pnp_ransac(X, P, K, params(pkg, H, conf=conf)))
+            finally:
+                c.close()
+        a, b = out
+        assert a["ok"] == b["ok"] and a["iters"] == b["iters"] and a["best_iter"] == b["best_iter"] and a["n_inliers"] == b["n_inliers"]
+        assert np.array_equal(a["mask"], b["mask"]) and np.array_equal(a["T"], b["T"])
