@@ -421,6 +421,8 @@ int detector_free(Ctx* c);
 int launch_gftt(Ctx* c, const FrameSlot& f, const uint8_t* d_mask, const vo_gftt_params& prm);
 int build_point_mask(Ctx* c, int w, int h, const float* d_pts, const uint8_t* d_status, const int32_t* d_n, int n_upper);
 int corners_to_stage(Ctx* c, double* d_stage);
+int launch_frame_tail(Ctx* c, const double K[9], double alpha_deg, int b_off, const double* d_feed, int n_new,
+                      const Pipeline::LandSeg* segs, int n_segs);
 int launch_land_append(Ctx* c, const float* d_P, const double* d_X, int n_rows, int target, const int32_t* gate = nullptr);
 int launch_triangulate(Ctx* c, const double* d_M1, const double* d_M2, int per_point, const double* d_p1,
                        const double* d_p2, int n, double* d_X4);

@@ -936,16 +936,32 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
         VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream));
     }
-    if (n_new > 0) VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));   // (before a kernel gets the pointer)
-    VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off, split, n_new > 0 ? p->n_poses : -1));
-    VO_TRY(close_step(c));
-    if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr, nullptr, false, !split));
     // landmark batches waiting for this frame (vo_queue_landmarks): behind the promoted rows, in call order
     Pipeline::LandSeg segs[4];
     const int n_segs = p->n_land_q;
     for (int k = 0; k < n_segs; k++) segs[k] = p->land_q[k];
     p->n_land_q = 0;
-    for (int k = 0; k < n_segs; k++) VO_TRY(append_landmarks_now(c, segs[k].P, segs[k].X, segs[k].n, segs[k].target));
+    if (split) {
+        // one launch for the promoted rows' positions, the new candidates and the batches
+        Pipeline::LandSeg dsegs[4];
+        int slots[4];
+        for (int k = 0; k < n_segs; k++) {
+            const float* dP; const double* dX;
+            p->land_slot_used = -1;
+            VO_TRY(land_rows_device_view(c, segs[k].P, segs[k].X, segs[k].n, &dP, &dX));
+            slots[k] = p->land_slot_used;
+            dsegs[k] = Pipeline::LandSeg{ dP, dX, segs[k].n, segs[k].target };
+        }
+        VO_TRY(launch_frame_tail(c, K, alpha_deg, p->klt_b_off, n_new > 0 ? p->stage_d.p + 16 : nullptr, n_new, dsegs, n_segs));
+        for (int k = 0; k < n_segs; k++) if (slots[k] >= 0) VO_CUDA(c, cudaEventRecord(p->ev_land_slot[slots[k]], c->stream));
+        VO_TRY(close_step(c));
+    } else {
+        if (n_new > 0) VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));   // (before a kernel gets the pointer)
+        VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off, false, -1));
+        VO_TRY(close_step(c));
+        if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
+        for (int k = 0; k < n_segs; k++) VO_TRY(append_landmarks_now(c, segs[k].P, segs[k].X, segs[k].n, segs[k].target));
+    }
     if (prof) cudaEventRecord(p->ev[5], c->stream);
     p->cand_tracked_valid = false;
     p->packed_valid = false;

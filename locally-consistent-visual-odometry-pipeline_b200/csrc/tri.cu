@@ -432,6 +432,60 @@ land_append_kernel(DevScalars* sc, const float2* __restrict__ srcP, const double
     if (threadIdx.x == 0) { sc->n_land = n0 + n_add; sc->n_appended = n_add; }
 }
 
+// Pipelined frames: everything the main stream still owes the frame once the RANSAC kernel has ended, in ONE launch
+// (one CTA) instead of four - the promoted rows' positions and the counters snapshot (promote_finish_kernel mode 1),
+// the append of the frame's new candidates (cand_add_kernel; their pose-table row is written on the pose stream) and
+// the landmark batches (land_append_kernel), in that order.  Same results as the separate kernels.
+struct TailArgs {
+    const double* prom_rows; float2* P; double* X; int land_cap;
+    const double2* feed; int n_new; float2* C; double2* F; int32_t* Ti; int pose_idx; int cand_cap;
+    int n_segs; const float2* segP[4]; const double* segX[4]; int segN[4]; int segTarget[4];
+};
+
+__global__ void __launch_bounds__(1024) frame_tail_kernel(DevScalars* sc, TailArgs a)
+{
+    pdl_prologue();
+    const int tid = threadIdx.x;
+    const bool ok = sc->ok != 0;
+    const int n_land0 = sc->n_land, n_cand0 = sc->n_cand;
+    const int n_prom = ok ? sc->n_promoted : 0;
+    const int cf_alias0 = sc->cf_alias, was_empty0 = sc->cand_was_empty, n_app0 = sc->n_appended, iters2 = sc->klt_iters_cand2;
+    __syncthreads();   // every thread has read the scalars thread 0 is about to rewrite
+    // promoted rows: positions now, 3-D points when the refined pose is there (pose stream)
+    int n_land = min(n_land0 + n_prom, a.land_cap);
+    for (int i = tid; i < n_prom && n_land0 + i < a.land_cap; i += blockDim.x)
+        a.P[n_land0 + i] = make_float2((float)a.prom_rows[4 * (size_t)i + 2], (float)a.prom_rows[4 * (size_t)i + 3]);
+    // new candidates (no pose this frame: none)
+    const bool add = ok && a.n_new > 0;
+    if (add)
+        for (int i = tid; i < a.n_new && n_cand0 + i < a.cand_cap; i += blockDim.x) {
+            const double2 p = a.feed[i];
+            a.C[n_cand0 + i] = make_float2((float)p.x, (float)p.y);
+            a.F[n_cand0 + i] = p;
+            a.Ti[n_cand0 + i] = a.pose_idx;
+        }
+    // landmark batches, in call order
+    int n_app = n_app0;
+    for (int k = 0; k < a.n_segs; k++) {
+        int n_add = a.segTarget[k] > 0 ? min(a.segN[k], max(a.segTarget[k] - n_land, 0)) : a.segN[k];
+        n_add = max(min(n_add, a.land_cap - n_land), 0);
+        for (int i = tid; i < n_add; i += blockDim.x) {
+            a.P[n_land + i] = a.segP[k][i];
+            const size_t o = 3 * (size_t)(n_land + i), s = 3 * (size_t)i;
+            a.X[o] = a.segX[k][s]; a.X[o + 1] = a.segX[k][s + 1]; a.X[o + 2] = a.segX[k][s + 2];
+        }
+        n_land += n_add;
+        n_app = n_add;
+    }
+    if (tid == 0) {
+        sc->snap_n_land = n_land0; sc->snap_n_cand = n_cand0; sc->snap_cf_alias = cf_alias0; sc->snap_n_appended = n_app0;
+        sc->prom_base = n_land0; sc->spec_n_land = n_land0;
+        sc->klt_iters_cand = iters2; sc->klt_iters_cand2 = 0;
+        sc->n_land = n_land; sc->n_appended = n_app;
+        if (add) { sc->cf_alias = was_empty0 ? 1 : 0; sc->n_cand = min(n_cand0 + a.n_new, a.cand_cap); sc->cand_was_empty = 0; }
+    }
+}
+
 __global__ void triangulate_kernel(const double* __restrict__ M1, const double* __restrict__ M2, int per_point,
                                    const double2* __restrict__ p1, const double2* __restrict__ p2, int n,
                                    double* __restrict__ X4)
@@ -665,6 +719,62 @@ int launch_land_append(Ctx* c, const float* d_P, const double* d_X, int n_rows, 
     VO_CUDA(c, launch_pdl(land_append_kernel, dim3(1), dim3(1024), c->stream, p->d_sc, (const float2*)d_P, d_X, n_rows,
                           target, (float2*)p->P[p->cur].p, p->X[p->cur].p, cap, gate));
     c->launches++;
+    p->n_land_upper = upper;
+    VO_CUDA(c, cudaGetLastError());
+    return VO_OK;
+}
+
+// See frame_tail_kernel.  The early classification of this frame must be pending with this alpha (the caller checked);
+// segments: device-accessible rows.  Afterwards: scalar block read-back and the promoted rows' DLT on the pose stream.
+int launch_frame_tail(Ctx* c, const double K[9], double alpha_deg, int b_off, const double* d_feed, int n_new,
+                      const Pipeline::LandSeg* segs, int n_segs)
+{
+    VO_NVTX("vo:frame_tail");
+    Pipeline* p = c->pipe;
+    if (c->side_inflight) {   // the candidates' classification comes from the side stream
+        c->side_inflight = false; c->side_writes_counts = false;
+        VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_join, 0));
+    }
+    p->early_valid = false;
+    PromoteArgs pa;
+    memcpy(pa.K, K, sizeof(pa.K));
+    memset(pa.Tnew, 0, sizeof(pa.Tnew));
+    pa.alpha_deg = alpha_deg; pa.use_dev_T = 1; pa.use_klt = 1; pa.b_off = b_off; pa.ncand_upper = p->early_ncand_upper;
+    // capacities: promoted rows + every batch behind the landmarks; the new candidates behind the candidates
+    int upper = p->n_land_upper + p->early_ncand_upper;
+    for (int k = 0; k < n_segs; k++) {
+        int up = upper + segs[k].n;
+        if (segs[k].target > 0 && up > segs[k].target) up = segs[k].target > upper ? segs[k].target : upper;
+        upper = up;
+    }
+    VO_TRY(ensure(c, p->P[p->cur], (size_t)upper * 2 + 2, true));
+    VO_TRY(ensure(c, p->X[p->cur], (size_t)upper * 3 + 3, true));
+    const size_t cneed = (size_t)p->n_cand_upper + (n_new > 0 ? n_new : 0) + 1;
+    VO_TRY(ensure(c, p->C[p->ccur], cneed * 2, true));
+    VO_TRY(ensure(c, p->F[p->ccur], cneed * 2, true));
+    VO_TRY(ensure(c, p->Ti[p->ccur], cneed, true));
+    VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));
+    TailArgs a;
+    memset(&a, 0, sizeof(a));
+    a.prom_rows = p->prom_rows.p; a.P = (float2*)p->P[p->cur].p; a.X = p->X[p->cur].p; a.land_cap = (int)(p->P[p->cur].cap / 2);
+    a.feed = (const double2*)d_feed; a.n_new = n_new > 0 ? n_new : 0;
+    a.C = (float2*)p->C[p->ccur].p; a.F = (double2*)p->F[p->ccur].p; a.Ti = p->Ti[p->ccur].p;
+    a.pose_idx = p->n_poses; a.cand_cap = (int)(p->C[p->ccur].cap / 2);
+    a.n_segs = n_segs;
+    for (int k = 0; k < n_segs; k++) { a.segP[k] = (const float2*)segs[k].P; a.segX[k] = segs[k].X; a.segN[k] = segs[k].n; a.segTarget[k] = segs[k].target; }
+    VO_CUDA(c, launch_pdl(frame_tail_kernel, dim3(1), dim3(1024), c->stream, p->d_sc, a));
+    VO_CUDA(c, cudaEventRecord(c->ev_snap, c->stream));
+    // pose stream, behind the refit: scalar block back to the host, then the 3-D points and the pose-table row
+    VO_CUDA(c, cudaStreamWaitEvent(c->stream4, c->ev_snap, 0));
+    VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream4));
+    VO_CUDA(c, cudaEventRecord(p->ev_pose, c->stream4));
+    VO_CUDA(c, launch_pdl(promote_finish_kernel, dim3(1), dim3(128), c->stream4, p->d_sc, pa, (const double*)p->prom_rows.p,
+                          (const int32_t*)p->prom_ti.p, p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p, a.land_cap, 2,
+                          n_new > 0 ? p->n_poses : -1));
+    VO_CUDA(c, cudaEventRecord(c->ev_pose_done, c->stream4));
+    c->pose_inflight = true;
+    c->launches += 2;
+    if (n_new > 0) { p->n_poses++; p->n_cand_upper += n_new; }
     p->n_land_upper = upper;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
