@@ -482,6 +482,23 @@ class Context:
         fn = self.lib.vo_queue_landmarks if queue else self.lib.vo_append_landmarks
         self._check(fn(self.h, _ptr(P), _ptr(X), len(P), int(target_total)))
 
+    def process_frame_tracked(self, prev_key, next_key, K, alpha_deg, feed, klt, pnp, T_out, cnt):
+        """vo_process_frame_pipelined on a tracking step that is already on the stream (the class surface's hot path):
+        no conversions - K float64 C-contiguous 3x3, feed float64 C-contiguous n x 2 or None, T_out 4x4 float64, cnt a
+        Counters instance, both filled in place."""
+        r = self.lib.vo_process_frame_pipelined(
+            self.h, None, 0, 0, 0, prev_key, next_key, K.ctypes.data, ctypes.byref(klt), ctypes.byref(pnp), alpha_deg,
+            feed.ctypes.data if feed is not None else None, 0 if feed is None else len(feed), T_out.ctypes.data, ctypes.byref(cnt))
+        if r != 0:
+            self._check(r)
+
+    def queue_landmarks_raw(self, P, X, target_total):
+        """vo_queue_landmarks without conversions (P float32 n x 2, X float64 n x 3, both C-contiguous; the caller keeps
+        them alive until the call after the next process_frame returns)."""
+        r = self.lib.vo_queue_landmarks(self.h, P.ctypes.data, X.ctypes.data, len(P), target_total)
+        if r != 0:
+            self._check(r)
+
     def bootstrap_pose(self, kps1, kps2, K, prob=0.999, threshold=1.0, max_iters=1000):
         """cv2.findEssentialMat(kps1, kps2, K, cv2.RANSAC, prob, threshold) + cv2.recoverPose(E, kps1, kps2, K, mask=mask)
         on the device (reference vo_pipeline.py:139-162) -> dict(ok, T34, mask, E, iters, best_iter, best_model, n_inliers, n_good)."""

@@ -904,7 +904,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         b = get_frame(c, next_key);
         if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
     }
-    if (n_new > 0) {   // stage the candidate feed early so the copy overlaps the tracking
+    if (n_new > 0 && !tracked) {   // stage the candidate feed early so the copy overlaps the tracking
         VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
         VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
     }
@@ -928,6 +928,10 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     L.refit_on_pose_stream = split;
     if (pipelined && !p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
     VO_TRY(launch_pnp(c, L));
+    if (n_new > 0 && tracked) {   // (tracking done ahead: the PnP launch is what the GPU is waiting for - the feed goes behind it)
+        VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
+    }
     if (prof) cudaEventRecord(p->ev[4], c->stream);
     const int ncand_before = p->n_cand_upper;
     const bool early_used = p->early_valid;   // the promotion below only finishes an early classification

@@ -110,6 +110,8 @@ class _Runtime:
         self.ahead = None         # frame_ahead: what estimatePose assumed about the coming triangulate_landmark call
         self.tracks_ahead = 0     # tracking steps the device has taken beyond the last associate call (0 or 1)
         self.need_adopt = False   # an adopted step ahead the C side has not been told about yet
+        self.cnt = _cabi.Counters()   # filled in place by the frame_ahead pose call
+        self.keep_alive = []      # landmark rows queued for the device, kept until it has read them
 
     # frames arrive as host uint8 arrays; the same object is passed to several stages and then
     # becomes the "old" frame of the next iteration (main.py:293), so upload + pyramid happen once
@@ -627,19 +629,35 @@ class PoseEstimator():
     def _estimate_frame_ahead(self, rt, associations, img_idx):
         """config frame_ahead: PnP, then - before the pose is waited for - the promotion step, the append of this
         frame's candidate feed and landmark batches and the tracking step into the frame handed over early
-        (vo_process_frame_pipelined on the tracking step associate made).  triangulate_landmark only confirms."""
+        (vo_process_frame_pipelined on the tracking step associate made).  triangulate_landmark only confirms.
+        This is the host's critical path between two frames: no conversions that are not needed."""
         alpha = float(_alpha_threshold())
         feed = _candidate_feed[0] if _candidate_feed else None
         batches = _landmark_feed[0] if _landmark_feed else None
-        for bP, bX, target in (batches or ()):
-            if len(bP):
-                rt.ctx.append_landmarks(bP, bX, target, queue=True)
-        T, cnt = rt.ctx.process_frame(None, rt.pair[2], rt.pair[3], self.K, alpha, feed if feed is not None and len(feed) else None,
-                                      klt=rt.klt, pnp=self._params(), pipelined=True)
-        ok, n_inl = bool(cnt['pnp_ok']), cnt['n_inliers']
+        keep = rt.keep_alive            # rows the device reads after this call returns
+        if batches:
+            for bP, bX, target in batches:
+                if len(bP):
+                    if not (isinstance(bP, np.ndarray) and bP.dtype == np.float32 and bP.flags.c_contiguous):
+                        bP = np.ascontiguousarray(bP, np.float32).reshape(-1, 2)
+                    if not (isinstance(bX, np.ndarray) and bX.dtype == np.float64 and bX.flags.c_contiguous):
+                        bX = np.ascontiguousarray(bX, np.float64).reshape(-1, 3)
+                    keep.append((bP, bX))
+                    rt.ctx.queue_landmarks_raw(bP, bX, int(target))
+        del keep[:-8]
+        fd = None
+        if feed is not None and len(feed):
+            fd = feed if (isinstance(feed, np.ndarray) and feed.dtype == np.float64 and feed.flags.c_contiguous) \
+                else np.ascontiguousarray(feed, np.float64).reshape(-1, 2)
+        Kc = self.K if (isinstance(self.K, np.ndarray) and self.K.dtype == np.float64 and self.K.flags.c_contiguous) \
+            else np.ascontiguousarray(self.K, np.float64)
+        T = np.empty((4, 4), np.float64)
+        cnt = rt.cnt
+        rt.ctx.process_frame_tracked(rt.pair[2], rt.pair[3], Kc, alpha, fd, rt.klt, self._params(), T, cnt)
+        ok, n_inl = bool(cnt.pnp_ok), cnt.n_inliers
         self.last = {'ok': ok, 'n_inliers': n_inl}
         rt.need_adopt = False
-        rt.tracks_ahead = 1 if (cnt['reserved_'] & 1) else 0
+        rt.tracks_ahead = cnt.reserved_ & 1
         if not ok or n_inl < 4:
             rt.tracks_ahead = 0
             if _candidate_feed:
@@ -651,9 +669,8 @@ class PoseEstimator():
             return self._rebootstrap(associations, img_idx)
         rt.state_version += 1
         associations._rebind(rt.state_version)
-        rt.ahead = {'T': T.tobytes(), 'alpha': alpha, 'K': np.asarray(self.K, np.float64).tobytes(), 'pair': rt.pair,
-                    'state': associations, 'n_inl': n_inl, 'feed': feed, 'batches': batches, 'ext_version': rt.ext_version,
-                    'pre': rt.last_prefetch if rt.tracks_ahead else None}
+        rt.ahead = {'T': T, 'alpha': alpha, 'K': Kc, 'pair': rt.pair, 'state': associations, 'n_inl': n_inl, 'feed': feed,
+                    'batches': batches, 'ext_version': rt.ext_version, 'pre': rt.last_prefetch if rt.tracks_ahead else None}
         return T
 
     def _rebootstrap(self, associations, img_idx):
@@ -745,17 +762,18 @@ class LandmarkTriangulator():
         """config frame_ahead: estimatePose has enqueued this whole stage already; check that it is being asked for
         what it assumed (main.py:280-284 always does) and hand the state objects on."""
         ah, rt.ahead = rt.ahead, None
-        new_pose = np.ascontiguousarray(new_pose, np.float64)
         if isinstance(extended_state, DeviceExtendedState):
             ext_ok = extended_state._current()
         else:
             ext_ok = rt.ext_version == 0 and len(np.asarray(extended_state['C'])) == 0
         feed = _candidate_feed.pop(0) if _candidate_feed else None
         batches = _landmark_feed.pop(0) if _landmark_feed else None
+        same_pose = new_pose is ah['T'] or (isinstance(new_pose, np.ndarray) and new_pose.shape == (4, 4) and np.array_equal(new_pose, ah['T']))
+        same_K = self.K is ah['K'] or np.array_equal(np.asarray(self.K, np.float64), ah['K'])
         if not (ext_ok and ah['ext_version'] == rt.ext_version and state is ah['state'] and state._current()
                 and ah['pair'] is rt.pair and rt.pair[0] is old_frame and rt.pair[1] is new_frame
-                and float(_alpha_threshold()) == ah['alpha'] and new_pose.tobytes() == ah['T']
-                and np.asarray(self.K, np.float64).tobytes() == ah['K'] and feed is ah['feed'] and batches is ah['batches']):
+                and float(_alpha_threshold()) == ah['alpha'] and same_pose and same_K
+                and feed is ah['feed'] and batches is ah['batches']):
             raise RuntimeError("frame_ahead: triangulate_landmark was not called with the frames, state and pose of the "
                                "estimatePose call before it (set frame_ahead: False for arbitrary call sequences)")
         rt.state_version += 1
