@@ -1,5 +1,6 @@
 // Internal context of libvo_b200.so (not part of the ABI).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -36,6 +37,8 @@ struct LevelDesc {
 struct PyramidDesc {
     LevelDesc lv[kMaxLevels];
     int nlevels;
+    // host side only: TMA descriptors of the u8 planes of levels 0..3 (FrameSlot::tmap_img), or NULL
+    const CUtensorMap* tmaps;
 };
 
 struct FrameSlot {
@@ -48,6 +51,9 @@ struct FrameSlot {
     short2* deriv_pool = nullptr;
     size_t raw_bytes = 0, img_bytes = 0, deriv_bytes = 0;
     PyramidDesc pyr{};
+    // one TMA descriptor per pyramid level over the padded u8 plane (box: the KLT kernel's 64 B x 32 row window tile)
+    alignas(64) CUtensorMap tmap_img[4];
+    bool tmap_valid = false;
     // frame ingest (vo_prefetch_frame): the slot is being filled on the ingest stream; `ready` is
     // recorded there behind the last pyramid level and the first reader on the main stream waits on it
     cudaEvent_t ready = nullptr;

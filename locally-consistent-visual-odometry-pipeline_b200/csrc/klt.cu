@@ -16,6 +16,7 @@
 // tile holding its neighbourhood (see Tile below), from global memory when it leaves the tile.  The
 // per-step sums are exact: products fit int32 per lane and the cross-lane sum is two REDUX.SUM
 // instructions (16-bit split), so results do not depend on the lane mapping or summation order.
+#include <stdlib.h>
 #include "ctx.cuh"
 
 namespace vo {
@@ -149,9 +150,39 @@ __device__ __forceinline__ void sample_run_s(const unsigned* __restrict__ row, i
     for (int x = 0; x < kRun; x++) v[x] >>= 9;
 }
 
+// ---- TMA staging of the window tile (A/B switch VO_KLT_TMA=1) ---------------------------------------------------------
+// The (WIN+11)-row window tile is a regular 2-D box of the padded level: one elected lane issues a single
+// cp.async.bulk.tensor.2d (64 B x 32 rows) into the warp's 128 B aligned tile and the warp waits on its own mbarrier,
+// instead of twelve __ldg + st.shared requests per lane.
+struct KltTmaps { CUtensorMap m[4]; };
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%1], %0;" ::"r"(count), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %0;" ::"r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned phase)
+{
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tWAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n\t"
+        "@P1 bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(phase) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, unsigned long long* bar, int x, int y)
+{
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(smem_u32(dst)),
+                 "l"(reinterpret_cast<unsigned long long>(map)), "r"(smem_u32(bar)), "r"(x), "r"(y)
+                 : "memory");
+}
+
 template <int WIN>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
-klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const float2* __restrict__ ptsA,
+klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const __grid_constant__ KltTmaps maps, const int top,
+                 const float2* __restrict__ ptsA,
                  const int32_t* __restrict__ nA_dev, const int nA_upper, const float2* __restrict__ ptsB,
                  const int32_t* __restrict__ nB_dev, const int nB_upper, const int b_off,
                  float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
@@ -163,11 +194,28 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
     constexpr int NRUNS = WIN * RPR;           // 63
     constexpr int NR = (NRUNS + 31) / 32;      // runs per lane
     using TL = Tile<WIN>;
-    __shared__ unsigned s_tile[kWarpsPerBlock][TL::kSmemWords];
+    static_assert((TL::kSmemWords * 4) % 128 == 0, "per-warp tiles must keep the 128 B alignment TMA needs");
+    __shared__ __align__(128) unsigned s_tile[kWarpsPerBlock][TL::kSmemWords];
+    __shared__ __align__(8) unsigned long long s_bar[kWarpsPerBlock];
     pdl_prologue();
     if (gate && !*gate) return;   // enqueued ahead of a pose that did not come: leave every buffer as it is
     const int lane = threadIdx.x & 31;
     unsigned* const tile = s_tile[threadIdx.x >> 5];
+    unsigned long long* const bar = &s_bar[threadIdx.x >> 5];
+    const bool tma = use_tile == 2;
+    // TMA wants the box origin on a 16 B boundary (an unaligned one is an illegal instruction) and writes dense rows: the
+    // box is 64 B wide to cover every alignment, rows 16 words apart - rows two apart share their banks
+    constexpr int kWordsT = 16, kOx0T = 13, kOxMaxT = 4 * (kWordsT - 3) + 3 - (WIN - kRun);   // 41
+    const int jpitch = tma ? kWordsT : TL::kPitch;
+    const int oxmax = tma ? kOxMaxT : TL::kOxMax;
+    unsigned phase = 0;
+    if (tma) {
+        if (lane == 0) {
+            mbar_init(bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        __syncwarp();
+    }
     int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
     // two track lists share one launch: landmarks (A) then candidates (B, written at b_off)
     float2 pt;
@@ -296,10 +344,22 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
         for (int r = 0; r < NR; r++) joff[r] = rrow[r] * jstride + rcol[r];
         // stage the neighbourhood of the starting position (padded coordinates, x origin word aligned)
         const int X0 = __float2int_rd(qx) + kPad, Y0 = __float2int_rd(qy) + kPad;
-        const int tx0 = (X0 - TL::kOx0 + 3) & ~3, ty0 = Y0 - TL::kOy0;
-        const bool tile_ok = use_tile && max_iters > 0 && X0 >= 0 && X0 < jstride && tx0 >= 0 && tx0 + 4 * TL::kWords <= jstride &&
-                             ty0 >= 0 && ty0 + TL::kRows <= LJ.h + 2 * kPad;
-        if (tile_ok) {
+        const int tx0 = tma ? ((X0 - kOx0T) & ~15) : ((X0 - TL::kOx0 + 3) & ~3), ty0 = Y0 - TL::kOy0;
+        const bool tile_ok = use_tile && max_iters > 0 && X0 >= 0 && X0 < jstride && tx0 >= 0 &&
+                             tx0 + 4 * (tma ? kWordsT : TL::kWords) <= jstride && ty0 >= 0 && ty0 + TL::kRows <= LJ.h + 2 * kPad;
+        if (tile_ok && tma) {
+            // every lane's generic-proxy accesses to the tile (the set-up staging above, the previous level's samples)
+            // are ordered before the async-proxy write that is about to land in the same bytes
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+                mbar_expect_tx(bar, TL::kRows * kWordsT * 4);
+                tma_load_2d(tile, &maps.m[level], bar, tx0, ty0);
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1;
+            __syncwarp();
+        } else if (tile_ok) {
             const unsigned* src = reinterpret_cast<const unsigned*>(LJ.img + (size_t)ty0 * jstride + tx0);
             const int wstride = jstride >> 2;
             __syncwarp();   // the previous level's readers are done
@@ -322,11 +382,11 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const int top, const 
             const int wtop = pack_w(w.w00, w.w01), wbot = pack_w(w.w10, w.w11);
             int b1 = 0, b2 = 0;
             const int ox = jx + kPad - tx0, oy = jy + kPad - ty0;
-            if (tile_ok && (unsigned)ox <= (unsigned)TL::kOxMax && (unsigned)oy <= (unsigned)TL::kOyMax) {
+            if (tile_ok && (unsigned)ox <= (unsigned)oxmax && (unsigned)oy <= (unsigned)TL::kOyMax) {
 #pragma unroll
                 for (int r = 0; r < NR; r++) {
                     int v[kRun];
-                    sample_run_s(tile + (oy + rrow[r]) * TL::kPitch, TL::kPitch, ox + rcol[r], wtop, wbot, v);
+                    sample_run_s(tile + (oy + rrow[r]) * jpitch, jpitch, ox + rcol[r], wtop, wbot, v);
 #pragma unroll
                     for (int x = 0; x < kRun; x++) {
                         const int diff = v[x] - Iw[r][x];
@@ -461,11 +521,15 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
     int max_iters = prm.max_iters < 0 ? 0 : (prm.max_iters > 100 ? 100 : prm.max_iters);
     const double eps = prm.epsilon < 0. ? 0. : (prm.epsilon > 10. ? 10. : prm.epsilon);
     const double eps2 = eps * eps;
-    static const bool no_tile = getenv("VO_KLT_NO_TILE") != nullptr;   // A/B switch (same results either way)
+    static const bool no_tile = getenv("VO_KLT_NO_TILE") != nullptr;   // A/B switches (same results either way)
+    const char* e_tma = getenv("VO_KLT_TMA");                         // read per launch (tests toggle it)
+    const bool want_tma = e_tma && e_tma[0] == '1' && next.tmaps != nullptr && top <= 3;
+    KltTmaps maps;
+    if (want_tma) memcpy(&maps, next.tmaps, sizeof(maps)); else memset(&maps, 0, sizeof(maps));
     const int blocks = (n_upper + nB_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
     klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
-        prev, next, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
-        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : 1, gate);
+        prev, next, maps, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
+        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : (want_tma ? 2 : 1), gate);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;

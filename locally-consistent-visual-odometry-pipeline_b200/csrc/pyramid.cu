@@ -72,6 +72,47 @@ build_level_kernel(const uint8_t* __restrict__ src, int sstride, LevelDesc dst)
 
 }  // namespace
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (the library links against cudart only)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn()
+{
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+// TMA descriptors of the padded u8 planes: 2-D tensors (row stride x rows) of bytes, box 64 B x 32 rows = the tile
+// the KLT kernel stages per warp and level around a track's starting position (klt.cu)
+static void encode_level_maps(FrameSlot& s)
+{
+    s.tmap_valid = false;
+    s.pyr.tmaps = nullptr;
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return;
+    for (int l = 0; l < 4; l++) {
+        if (l >= s.pyr.nlevels) { memset(&s.tmap_img[l], 0, sizeof(CUtensorMap)); continue; }
+        const LevelDesc& d = s.pyr.lv[l];
+        const cuuint64_t gdim[2] = { (cuuint64_t)d.stride, (cuuint64_t)(d.h + 2 * kPad) };
+        const cuuint64_t gstride[1] = { (cuuint64_t)d.stride };
+        const cuuint32_t box[2] = { 64, 32 };
+        const cuuint32_t estr[2] = { 1, 1 };
+        if (fn(&s.tmap_img[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, d.img, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+            return;
+    }
+    s.tmap_valid = true;
+    s.pyr.tmaps = s.tmap_img;
+}
+
 int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap, cudaStream_t stream)
 {
     if (!stream) stream = c->stream;
@@ -108,6 +149,8 @@ int build_pyramid(Ctx* c, FrameSlot& s, int max_level_cap, cudaStream_t stream)
         d.deriv = s.deriv_pool + off[l];
         d.w = ws[l]; d.h = hs[l]; d.stride = st[l];
     }
+    if (!same || !s.tmap_valid) encode_level_maps(s);   // (geometry or buffers changed)
+    s.pyr.tmaps = s.tmap_valid ? s.tmap_img : nullptr;
     for (int l = 0; l < nl; l++) {
         const LevelDesc& d = s.pyr.lv[l];
         dim3 grid((d.w + 2 * kPad + TX - 1) / TX, (d.h + 2 * kPad + TY - 1) / TY), block(TX, TY);

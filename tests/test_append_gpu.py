@@ -202,12 +202,12 @@ def _oracle_fb(oracle, prev, nxt, pts, thr):
 def test_fb_check_unit_level_vs_two_oracle_calls(pkg, ctx, oracle, thr):
     import synth
     prev, nxt, pts = synth.klt_pair(240, 320, 21, 600, shift=(-7.5, 5.2))   # ~100 tracks fail the way back
-    ctx.upload_frame(prev, 7001)
-    ctx.upload_frame(nxt, 7002)
+    ctx.upload_frame(prev, 7301)     # (keys identify frames: 7001 / 7002 belong to test_pipeline_gpu)
+    ctx.upload_frame(nxt, 7302)
     prm = pkg.klt_defaults()
-    out0, st0, _ = ctx.calc_optical_flow_pyr_lk(7001, 7002, pts, prm)
+    out0, st0, _ = ctx.calc_optical_flow_pyr_lk(7301, 7302, pts, prm)
     prm.fb_check, prm.fb_thresh = 1, thr
-    out1, st1, _ = ctx.calc_optical_flow_pyr_lk(7001, 7002, pts, prm)
+    out1, st1, _ = ctx.calc_optical_flow_pyr_lk(7301, 7302, pts, prm)
     o_out, o_st, o_keep, o_d = _oracle_fb(oracle, prev, nxt, pts, thr)
     assert np.array_equal(out0, out1)                       # the check only clears status flags
     assert (st0 == o_st).mean() >= 0.995

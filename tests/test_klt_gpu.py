@@ -97,3 +97,27 @@ def test_klt_saturation_linearity(ctx):
     st = st.reshape(32, n)
     assert np.array_equal(out, np.broadcast_to(out[0], out.shape))
     assert np.array_equal(st, np.broadcast_to(st[0], st.shape))
+
+
+def test_klt_tma_staging_is_bit_identical(pkg, monkeypatch):
+    """VO_KLT_TMA=1: the window tile staged by one cp.async.bulk.tensor.2d per warp and level (64 B x 32 rows, origin on a
+    16 B boundary, mbarrier wait) instead of the __ldg loop.  Same bytes in shared memory, so the same results - positions,
+    status, error and iteration counts, bit for bit - on every golden shape, with points outside the frame and across slot
+    reuse with another geometry."""
+    c = pkg.Context(device=0, max_w=2048, max_h=1024)
+    try:
+        key = 40
+        for name in ("kitti", "small", "malaga", "tiny", "parking", "kitti"):
+            h, w, seed, n = KLT_CASES[name]
+            prev, nxt, pts = synth.klt_pair(h, w, seed, n)
+            c.upload_frame(prev, key)
+            c.upload_frame(nxt, key + 1)
+            res = []
+            for on in ("0", "1"):
+                monkeypatch.setenv("VO_KLT_TMA", on)
+                res.append(c.calc_optical_flow_pyr_lk(key, key + 1, pts, want_iters=True))
+            for a, b in zip(*res):
+                assert np.array_equal(a, b), name
+            key += 2
+    finally:
+        c.close()
