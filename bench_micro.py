@@ -150,7 +150,7 @@ def main():
         med, best = timed(torch, stream, run, args.reps)
         pairs = float(info[0]) * n
         flops = pairs * 35 + info[0] * 2000.0
-        print(json.dumps({"kernel": "pnp_chunk_kernel (P3P + scoring) + select + LM refit", "regime": "stress config 4", "n": n,
+        print(json.dumps({"kernel": "pnp_ransac_kernel (P3P + scoring + select + mask + prune) + pnp_refit_kernel", "regime": "stress config 4", "n": n,
                           "hypotheses_scored": int(info[0]), "inliers": int(info[2]), "lm_iters": int(info[3]), "ms": med, "ms_min": best,
                           "pairs_per_s": pairs / (med * 1e-3), "achieved_tflops": flops / (med * 1e-3) / 1e12,
                           "fp32_peak_tflops": fp32_peak, "frac_of_fp32_peak": flops / (med * 1e-3) / 1e12 / fp32_peak,
