@@ -710,6 +710,27 @@ def pin_rank_to_cores(local_rank, world):
     return cores
 
 
+_OUT_FD = None
+
+
+def claim_stdout():
+    """stdout carries exactly ONE JSON line: whatever libraries write to fd 1 meanwhile (NCCL's version banner) goes to stderr."""
+    global _OUT_FD
+    if _OUT_FD is None:
+        sys.stdout.flush()
+        _OUT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _OUT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_OUT_FD, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -722,6 +743,7 @@ def main():
                     help="upload + pyramid of a frame inside its own step (no frame ingest one step ahead)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    claim_stdout()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -752,7 +774,6 @@ def main():
         n_streams = max(args.gpus, 1)
         thr = max(cores // n_streams, 1)
         if stress:
-            steps = min(args.steps, 20)
             steps = min(args.steps, 8)
             fps, note = run_stress_port(steps, cores)    # (the RANSAC loop is single-threaded, in OpenCV too)
             sample = "%d runs over the stress correspondences; %s" % (steps, note)
@@ -785,7 +806,7 @@ def main():
                      "dtype": "u8/f32/f64 (OpenCV)", "klt_tracks_per_s": tracks * fps,
                      "cpu_baseline": {"value": fps, "unit": "frames/s", "cores": 1 if stress else (cores if n_streams > 1 else thr), "kind": "port", "sample": sample},
                      "e2e": {"value": fps, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-        print(json.dumps(line))
+        emit(line)
         return
 
     import torch
@@ -822,7 +843,7 @@ def main():
                          "e2e": {"value": e2e_job_fps, "unit": "frames/s", "h2d_bytes_per_step": r["e2e"]["h2d"], "d2h_bytes_per_step": r["e2e"]["d2h"],
                                  "windows": r["e2e"]["windows"]},
                          "gpu_launches": int(r["launches"]), "clocks": r["clocks"],
-                         "roofline": {"bound": "tensor", "kernel": "pnp_chunk_kernel (P3P + scoring)", "achieved": ach, "peak": fp64_peak,
+                         "roofline": {"bound": "tensor", "kernel": "pnp_ransac_kernel (P3P + scoring)", "achieved": ach, "peak": fp64_peak,
                                       "unit": "TFLOP/s", "frac": ach / fp64_peak, "traffic": None,
                                       "peak_source": "FP64 CUDA-core pipe: 148 SMs x 64 DFMA lanes x 2 x %.0f MHz (no tensor cores on this path; "
                                                      "'tensor' is the contract's name for the compute roof)" % sm_mhz,
@@ -833,7 +854,7 @@ def main():
                 cf, note = run_stress_port(n, cores)
                 line["cpu_baseline"] = {"value": cf, "unit": "frames/s", "cores": 1, "kind": "port",
                                         "sample": "%d runs over the same correspondences; %s" % (n, note)}
-            print(json.dumps(line))
+            emit(line)
         if world > 1:
             torch.distributed.destroy_process_group()
         return
@@ -904,7 +925,7 @@ def main():
                                           % (n, PREROLL, min(args.warmup, 5), cores),
                                 "raw_cv2_calls": raw_cv2_baseline(cfg, sq, raw, cores)}
         line["parity"] = parity_block(cfg, sq, r["trace"][:n_par], port_trace)
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         torch.distributed.destroy_process_group()
 

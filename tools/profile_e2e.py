@@ -14,12 +14,13 @@ import bench  # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 300
 pkg = importlib.import_module(bench.PKG)
-_, sq = bench.build_sequence(seed=11)
+cfg = bench.CONFIGS['kitti']
+sq = bench.build_stream(cfg, 11, bench.PREROLL + 20 + steps * bench.E2E_WINDOWS)
 pr = cProfile.Profile()
 PF = "--no-prefetch" not in sys.argv
-r0 = bench.run_e2e(pkg, sq, steps, 20, 0, 1, PF)       # warm (also un-profiled reference number)
+r0 = bench.run_e2e(pkg, cfg, sq, steps, 20, 0, 1, PF)       # warm (also un-profiled reference number)
 pr.enable()
-r = bench.run_e2e(pkg, sq, steps, 20, 0, 1, PF)
+r = bench.run_e2e(pkg, cfg, sq, steps, 20, 0, 1, PF)
 pr.disable()
 print("e2e fps un-profiled %.1f, profiled %.1f" % (r0["fps"], r["fps"]))
 st = pstats.Stats(pr)
