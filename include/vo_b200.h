@@ -361,6 +361,22 @@ int vo_get_stage_times(vo_ctx* ctx, double ms[6], int* frames);
 int vo_solve_pnp_ransac(vo_ctx* ctx, const double* X, const float* P, int n, const double K[9],
                         const vo_pnp_params* params, const int32_t* minimal_sets, double T44[16], double Th12[12],
                         double rvec[3], double tvec[3], uint8_t* inlier_mask, int32_t info[4], int* ok);
+/* ---- vo_solve_pnp_ransac for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that
+ * forbid cudaMalloc.  Same arguments, kernels and results as vo_solve_pnp_ransac, but the call allocates
+ * nothing (no cudaMalloc / cudaFree / allocating library routine): every device buffer of the run - staged
+ * points, float32 pack, minimal sets, hypotheses, counts, inlier mask, inlier pack, cv::RNG draw table - is a
+ * slice of one file-scope `static __device__` array of < 1 MiB that every GPU loading the library holds until
+ * exit.  Limits: n <= VO_NOALLOC_MAX_POINTS and params->max_iters <= VO_NOALLOC_MAX_ITERS, beyond them
+ * VO_ERR_CAPACITY (vo_last_error names the limit).  The array is shared by ALL calls on a device (all
+ * contexts) and keeps the last call's contents; the call clears what must start at zero itself, but calls
+ * that overlap on the GPU (two contexts / host threads at once) race - serialise them.  Synchronises. */
+#define VO_NOALLOC_MAX_POINTS 4096
+#define VO_NOALLOC_MAX_ITERS 1024
+int vo_solve_pnp_ransac_noalloc(vo_ctx* ctx, const double* X, const float* P, int n, const double K[9],
+                                const vo_pnp_params* params, const int32_t* minimal_sets, double T44[16],
+                                double Th12[12], double rvec[3], double tvec[3], uint8_t* inlier_mask,
+                                int32_t info[4], int* ok);
 /* ---- unit-level entry point mirroring cv2.triangulatePoints (vo_pipeline.py:666, :172).
  * M1: 3x4 (per_point_m1=0) or n x 12; X4: n x 4 homogeneous, unit norm.  Synchronises. */
 int vo_triangulate_points(vo_ctx* ctx, const double* M1, const double* M2, int per_point_m1, const double* p1,

@@ -11,7 +11,9 @@ directory on sys.path ahead of the reference's src/ to get the drop-in `vo_pipel
 """
 from . import _build  # noqa: F401
 from ._cabi import (Context, Counters, GfttParams, KltParams, PnpParams, PinnedArray, VoError, gftt_defaults,  # noqa: F401
-                    klt_defaults, pnp_defaults, load, lib_path)
+                    klt_defaults, pnp_defaults, load, lib_path, NOALLOC_MAX_POINTS, NOALLOC_MAX_ITERS)
+
+VO_ERR_CAPACITY = -5   # include/vo_b200.h
 
 __all__ = ["Context", "KltParams", "PnpParams", "PinnedArray", "VoError", "load", "lib_path", "build"]
 

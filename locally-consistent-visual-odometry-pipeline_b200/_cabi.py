@@ -124,6 +124,8 @@ SIGNATURES = {
     "vo_get_stage_times": (c_int, [c_void_p, c_void_p, _PI]),
     "vo_solve_pnp_ransac": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _PI]),
+    "vo_solve_pnp_ransac_noalloc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, _PP, c_void_p, c_void_p,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _PI]),
     "vo_gftt_params_default": (None, [ctypes.POINTER(GfttParams)]),
     "vo_good_features_to_track": (c_int, [c_void_p, c_i64, c_void_p, c_void_p, c_int, ctypes.POINTER(GfttParams),
                                           c_void_p, c_int, _PI, c_void_p, c_void_p]),
@@ -136,6 +138,10 @@ _lib = None
 
 def lib_path():
     return _build.LIB
+
+
+NOALLOC_MAX_POINTS = 4096   # include/vo_b200.h: VO_NOALLOC_MAX_POINTS / VO_NOALLOC_MAX_ITERS
+NOALLOC_MAX_ITERS = 1024
 
 
 def load(build_if_missing=True):
@@ -576,7 +582,9 @@ class Context:
         return {k: float(v) / max(n.value, 1) for k, v in zip(names, ms)}, n.value
 
     # ---- unit-level: cv2.solvePnPRansac / cv2.triangulatePoints ------------------------------------
-    def solve_pnp_ransac(self, X, P, K, params=None, sets=None):
+    def solve_pnp_ransac(self, X, P, K, params=None, sets=None, noalloc=False):
+        """noalloc=True: vo_solve_pnp_ransac_noalloc - same results out of the library's static device scratch
+        (at most NOALLOC_MAX_POINTS correspondences and NOALLOC_MAX_ITERS iterations; no allocation in the call)."""
         X = np.ascontiguousarray(X, np.float64).reshape(-1, 3)
         P = np.ascontiguousarray(P, np.float32).reshape(-1, 2)
         K = np.ascontiguousarray(K, np.float64)
@@ -589,9 +597,9 @@ class Context:
                 raise ValueError("minimal-set table must be max_iters x 4")
         T = np.zeros((4, 4)); Th = np.zeros(12); rvec = np.zeros(3); tvec = np.zeros(3)
         mask = np.zeros(n, np.uint8); info = np.zeros(4, np.int32); ok = c_int()
-        self._check(self.lib.vo_solve_pnp_ransac(self.h, _ptr(X), _ptr(P), n, _ptr(K), ctypes.byref(params), _ptr(sets),
-                                                 _ptr(T), _ptr(Th), _ptr(rvec), _ptr(tvec), _ptr(mask), _ptr(info),
-                                                 ctypes.byref(ok)))
+        fn = self.lib.vo_solve_pnp_ransac_noalloc if noalloc else self.lib.vo_solve_pnp_ransac
+        self._check(fn(self.h, _ptr(X), _ptr(P), n, _ptr(K), ctypes.byref(params), _ptr(sets),
+                       _ptr(T), _ptr(Th), _ptr(rvec), _ptr(tvec), _ptr(mask), _ptr(info), ctypes.byref(ok)))
         return dict(ok=bool(ok.value), T=T, R=T[:3, :3].copy(), t=T[:3, 3].copy(), Rh=Th[:9].reshape(3, 3),
                     th=Th[9:], rvec=rvec, tvec=tvec, mask=mask, iters=int(info[0]), best_iter=int(info[1]),
                     n_inliers=int(info[2]), lm_iters=int(info[3]))

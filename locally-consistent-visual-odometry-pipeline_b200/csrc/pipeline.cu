@@ -1197,3 +1197,161 @@ int vo_triangulate_points(vo_ctx* c, const double* M1, const double* M2, int per
 }
 
 }  // extern "C"
+
+// ---- vo_solve_pnp_ransac without a single allocation -------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and
+// same results as vo_solve_pnp_ransac; every device buffer the run needs - the staged points, the float32 pack,
+// minimal sets, hypotheses, counts, inlier mask, inlier pack, the cv::RNG draw table - lives in ONE file-scope
+// device array of kNoAllocScratchBytes, which every GPU that loads the library holds until exit.
+//   limits: n <= VO_NOALLOC_MAX_POINTS correspondences, params->max_iters <= VO_NOALLOC_MAX_ITERS.
+//   All calls (of all contexts on a device) share the array and it keeps the last call's contents: the regions a
+//   run reads before writing are cleared per call; calls that overlap on the GPU race - serialise them.
+constexpr int kNoAllocMaxPoints = VO_NOALLOC_MAX_POINTS;
+constexpr int kNoAllocMaxIters = VO_NOALLOC_MAX_ITERS;
+constexpr int kNoAllocRngLen = 32768;   // >= kNoAllocMaxIters * 16 + 1024 draws (ensure_rng_table's rule)
+static_assert(kNoAllocRngLen >= kNoAllocMaxIters * 16 + 1024, "draw table too short for the iteration limit");
+
+constexpr size_t al(size_t v) { return (v + 255) & ~(size_t)255; }
+struct NoAllocLayout {   // byte offsets into the scratch array, each a multiple of 256
+    static constexpr size_t kSetRows = kNoAllocMaxIters > kPnpChunk0 ? kNoAllocMaxIters : kPnpChunk0;
+    static constexpr size_t X = 0;                                                         // n x 3 f64
+    static constexpr size_t P = X + al(sizeof(double) * 3 * kNoAllocMaxPoints);            // n x 2 f32
+    static constexpr size_t q4 = P + al(sizeof(float) * 2 * kNoAllocMaxPoints);            // n x 4 f32
+    static constexpr size_t qv = q4 + al(sizeof(float) * 4 * kNoAllocMaxPoints);           // n f32
+    static constexpr size_t q4i = qv + al(sizeof(float) * kNoAllocMaxPoints);
+    static constexpr size_t qvi = q4i + al(sizeof(float) * 4 * kNoAllocMaxPoints);
+    static constexpr size_t sets = qvi + al(sizeof(float) * kNoAllocMaxPoints);            // rows x 4 i32
+    static constexpr size_t sets_in = sets + al(sizeof(int32_t) * kMinimal * kSetRows);    // caller's table, staged
+    static constexpr size_t rng = sets_in + al(sizeof(int32_t) * kMinimal * kNoAllocMaxIters);
+    // --- cleared per call from here on ---
+    static constexpr size_t hyp = rng + al(sizeof(uint32_t) * kNoAllocRngLen);             // H x 12 f64
+    static constexpr size_t counts = hyp + al(sizeof(double) * 12 * kNoAllocMaxIters);     // H i32
+    static constexpr size_t mask = counts + al(sizeof(int32_t) * kNoAllocMaxIters);        // n u8
+    static constexpr size_t end = mask + al(kNoAllocMaxPoints);
+};
+constexpr size_t kNoAllocScratchBytes = NoAllocLayout::end;
+static_assert(kNoAllocScratchBytes <= (1u << 20), "the no-alloc scratch is meant to stay modest (<= 1 MiB)");
+
+// In host code this name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+__global__ void noalloc_rng_fill_kernel(uint32_t* tab, int len)
+{
+    // cv::RNG(2^64-1): raw 32-bit outputs in draw order (as ensure_rng_table draws them on the host)
+    uint64_t s = 0xFFFFFFFFFFFFFFFFULL;
+    for (int i = 0; i < len; i++) {
+        s = (uint64_t)(uint32_t)s * 4164903690ULL + (uint32_t)(s >> 32);
+        tab[i] = (uint32_t)s;
+    }
+}
+
+constexpr int kNoAllocMaxDevices = 64;
+static unsigned char* g_noalloc_ptr[kNoAllocMaxDevices] = {};   // per device: address of ITS copy of the array
+
+// once per device, with that device current: the array's device address, and the draw table inside it
+static int noalloc_setup(Ctx* c, unsigned char** out)
+{
+    const int dev = c->device;
+    if (dev < 0 || dev >= kNoAllocMaxDevices) return set_error(c, VO_ERR_INVALID, "device %d outside the no-alloc table", dev);
+    if (!g_noalloc_ptr[dev]) {
+        VO_CUDA(c, cudaSetDevice(dev));
+        unsigned char* ptr = nullptr;
+        VO_CUDA(c, cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+        if (!ptr) return set_error(c, VO_ERR_CUDA, "cudaGetSymbolAddress returned no address for the no-alloc scratch");
+        noalloc_rng_fill_kernel<<<1, 1, 0, c->stream>>>(reinterpret_cast<uint32_t*>(ptr + NoAllocLayout::rng), kNoAllocRngLen);
+        VO_CUDA(c, cudaGetLastError());
+        VO_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->launches++;
+        g_noalloc_ptr[dev] = ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return VO_OK;
+}
+
+// The launchers take their buffers from the Pipeline: for the duration of one call they are handed views into the
+// scratch array (capacity = the stated maximum, so no ensure() in there can reach cudaMalloc), then the real ones back.
+struct NoAllocViews {
+    Pipeline* p;
+    DevBuf<double> stage_d, hyp; DevBuf<float> stage_f, q4, qv, q4i, qvi; DevBuf<int32_t> stage_i, sets, counts;
+    DevBuf<uint8_t> mask; DevBuf<uint32_t> rng_tab; int rng_tab_len;
+    template <typename T> static void view(DevBuf<T>& b, unsigned char* base, size_t off, size_t cap)
+    {
+        b.p = reinterpret_cast<T*>(base + off); b.cap = cap;
+    }
+    NoAllocViews(Pipeline* pp, unsigned char* s) : p(pp), stage_d(pp->stage_d), hyp(pp->hyp), stage_f(pp->stage_f), q4(pp->q4),
+        qv(pp->qv), q4i(pp->q4i), qvi(pp->qvi), stage_i(pp->stage_i), sets(pp->sets), counts(pp->counts), mask(pp->mask),
+        rng_tab(pp->rng_tab), rng_tab_len(pp->rng_tab_len)
+    {
+        typedef NoAllocLayout Lay;
+        view(p->stage_d, s, Lay::X, (size_t)3 * kNoAllocMaxPoints); view(p->stage_f, s, Lay::P, (size_t)2 * kNoAllocMaxPoints);
+        view(p->q4, s, Lay::q4, (size_t)4 * kNoAllocMaxPoints); view(p->qv, s, Lay::qv, kNoAllocMaxPoints);
+        view(p->q4i, s, Lay::q4i, (size_t)4 * kNoAllocMaxPoints); view(p->qvi, s, Lay::qvi, kNoAllocMaxPoints);
+        view(p->sets, s, Lay::sets, Lay::kSetRows * kMinimal); view(p->stage_i, s, Lay::sets_in, (size_t)kNoAllocMaxIters * kMinimal);
+        view(p->rng_tab, s, Lay::rng, kNoAllocRngLen); p->rng_tab_len = kNoAllocRngLen;
+        view(p->hyp, s, Lay::hyp, (size_t)12 * kNoAllocMaxIters); view(p->counts, s, Lay::counts, kNoAllocMaxIters);
+        view(p->mask, s, Lay::mask, kNoAllocMaxPoints);
+    }
+    ~NoAllocViews()
+    {
+        p->stage_d = stage_d; p->hyp = hyp; p->stage_f = stage_f; p->q4 = q4; p->qv = qv; p->q4i = q4i; p->qvi = qvi;
+        p->stage_i = stage_i; p->sets = sets; p->counts = counts; p->mask = mask; p->rng_tab = rng_tab; p->rng_tab_len = rng_tab_len;
+    }
+};
+
+extern "C" {
+
+int vo_solve_pnp_ransac_noalloc(vo_ctx* c, const double* X, const float* P, int n, const double K[9],
+                                const vo_pnp_params* params, const int32_t* minimal_sets, double T44[16], double Th12[12],
+                                double rvec[3], double tvec[3], uint8_t* inlier_mask, int32_t info[4], int* ok)
+{
+    VO_NEED(c);
+    if (n < 0 || !K || (n > 0 && (!X || !P))) return VO_ERR_INVALID;
+    Pipeline* p = c->pipe;
+    PnpLaunch L{};
+    if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
+    if (n > kNoAllocMaxPoints)
+        return set_error(c, VO_ERR_CAPACITY, "vo_solve_pnp_ransac_noalloc: %d correspondences, the static scratch holds at most %d "
+                         "(use vo_solve_pnp_ransac)", n, kNoAllocMaxPoints);
+    if (L.prm.max_iters > kNoAllocMaxIters)
+        return set_error(c, VO_ERR_CAPACITY, "vo_solve_pnp_ransac_noalloc: max_iters %d, the static scratch holds at most %d "
+                         "hypotheses (use vo_solve_pnp_ransac)", L.prm.max_iters, kNoAllocMaxIters);
+    unsigned char* scratch = nullptr;
+    VO_TRY(noalloc_setup(c, &scratch));
+    VO_TRY(join_side_stream(c));
+    NoAllocViews views(p, scratch);   // (restored on every way out)
+    // what a run reads before it writes must not be the last call's: hypotheses, counts, mask
+    VO_CUDA(c, cudaMemsetAsync(scratch + NoAllocLayout::hyp, 0, NoAllocLayout::end - NoAllocLayout::hyp, c->stream));
+    if (n > 0) {
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p, X, sizeof(double) * 3 * n, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_f.p, P, sizeof(float) * 2 * n, cudaMemcpyDefault, c->stream));
+    }
+    const size_t m = n > 0 ? n : 1;
+    pack_points_kernel<<<(int)((m + 255) / 256), 256, 0, c->stream>>>(p->d_sc, p->stage_d.p, (const float2*)p->stage_f.p, n, 0,
+                                                                      (float4*)p->q4.p, p->qv.p, p->sets.p,
+                                                                      RngTab{ p->rng_tab.p, p->rng_tab_len });
+    c->launches++;
+    if (minimal_sets) {
+        const size_t H = L.prm.max_iters > 0 ? L.prm.max_iters : 1;
+        VO_CUDA(c, cudaMemcpyAsync(p->stage_i.p, minimal_sets, sizeof(int32_t) * kMinimal * H, cudaMemcpyDefault, c->stream));
+        L.d_sets_in = p->stage_i.p;
+    }
+    L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = nullptr; L.n_upper = n; L.compact = false;
+    memcpy(L.K, K, sizeof(L.K));
+    p->packed_valid = false;
+    VO_TRY(launch_pnp(c, L));
+    if (inlier_mask && n > 0) VO_CUDA(c, cudaMemcpyAsync(inlier_mask, p->mask.p, n, cudaMemcpyDefault, c->stream));
+    VO_CUDA(c, cudaMemcpyAsync(p->h_sc, p->d_sc, sizeof(DevScalars), cudaMemcpyDeviceToHost, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));
+    VO_TRY(check_rng(c));
+    const DevScalars* s = p->h_sc;
+    if (ok) *ok = s->ok;
+    if (T44) memcpy(T44, s->T, sizeof(double) * 16);
+    if (Th12) memcpy(Th12, s->Th, sizeof(double) * 12);
+    if (rvec) { if (s->ok) rotation_to_rvec(s->T, rvec); else rvec[0] = rvec[1] = rvec[2] = 0.; }
+    if (tvec) { tvec[0] = s->T[3]; tvec[1] = s->T[7]; tvec[2] = s->T[11]; }
+    if (info) { info[0] = s->iters_run; info[1] = s->best_hyp; info[2] = s->n_inliers; info[3] = s->lm_iters; }
+    return VO_OK;
+}
+
+}  // extern "C"
