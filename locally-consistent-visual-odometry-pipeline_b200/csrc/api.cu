@@ -114,6 +114,9 @@ int vo_create(vo_ctx** out, int device, int max_w, int max_h, int track_capacity
     if (cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream3, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream4, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream5, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_compact, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_trk, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_ransac, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_pose_side, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_snap, cudaEventDisableTiming) != cudaSuccess ||
@@ -146,6 +149,7 @@ int vo_destroy(vo_ctx* c)
     if (c->stream2) cudaStreamSynchronize(c->stream2);
     if (c->stream3) cudaStreamSynchronize(c->stream3);
     if (c->stream4) cudaStreamSynchronize(c->stream4);
+    if (c->stream5) cudaStreamSynchronize(c->stream5);
     map_free(c);
     pipeline_free(c);
     detector_free(c);
@@ -157,6 +161,9 @@ int vo_destroy(vo_ctx* c)
     cudaFreeHost(c->pinned_stage2);
     if (c->stream3) cudaStreamDestroy(c->stream3);
     if (c->stream4) cudaStreamDestroy(c->stream4);
+    if (c->stream5) cudaStreamDestroy(c->stream5);
+    if (c->ev_compact) cudaEventDestroy(c->ev_compact);
+    if (c->ev_trk) cudaEventDestroy(c->ev_trk);
     if (c->ev_ransac) cudaEventDestroy(c->ev_ransac);
     if (c->ev_pose_side) cudaEventDestroy(c->ev_pose_side);
     if (c->ev_snap) cudaEventDestroy(c->ev_snap);

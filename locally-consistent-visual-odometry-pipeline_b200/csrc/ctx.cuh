@@ -113,6 +113,10 @@ struct Ctx {
     cudaEvent_t ev_ransac = nullptr, ev_pose_side = nullptr;
     cudaEvent_t ev_snap = nullptr, ev_pose_done = nullptr;   // counters snapshot taken (main) / pose-side work of the frame done
     bool pose_inflight = false;   // work of the last pipelined frame may still be running on stream4
+    // tracking stream: the NEXT frame's landmark KLT, started beside the current frame's RANSAC kernel over the rows
+    // the tracking step left (before the pruning) plus the rows the frame is about to append - see Pipeline::src_*
+    cudaStream_t stream5 = nullptr;
+    cudaEvent_t ev_compact = nullptr, ev_trk = nullptr;   // behind the last landmark compaction (main) / the KLT on stream5
     cudaEvent_t ev_ingest_fork = nullptr;
     uint64_t ingest_seq = 0;
     int64_t last_ingest_key = 0; bool last_ingest_valid = false;   // newest frame on the ingest stream, not used yet
@@ -211,6 +215,8 @@ int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
         // stream-ordered w.r.t. earlier kernels still reading the old buffer
         cudaStreamSynchronize(c->stream);
         if (c->stream4) cudaStreamSynchronize(c->stream4);
+        if (c->stream5) cudaStreamSynchronize(c->stream5);
+        if (c->stream2) cudaStreamSynchronize(c->stream2);
         cudaFree(b.p);
     }
     b.p = np_;
@@ -221,7 +227,8 @@ int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
 // ---- device-resident Markov state (reference: BestVision.state / .extended_state,
 // /root/reference/src/vo_pipeline.py:36-37) and PnP / promotion scratch ------------------------
 constexpr int kMinimal = 4;          // P3P on 3 points + 1 disambiguation point
-constexpr int kLandBufs = 4;         // landmark buffers in rotation
+constexpr int kLandBufs = 5;         // landmark buffers in rotation (state before the last two tracking steps + compaction and
+                                     // pruning outputs of the current frame and of the step enqueued ahead)
 constexpr int kPnpChunks = 3;        // hypotheses are evaluated in <=3 chunks (adaptive stop between)
 
 // small block of scalars living in device memory; mirrored to pinned host memory on demand
@@ -261,6 +268,8 @@ struct DevScalars {
     int32_t prom_base;     // row of P/X where the promoted rows of the frame start (split promotion)
     // counters as of the pose (vo_process_frame_pipelined reads the block back while the main stream goes on)
     int32_t snap_n_land, snap_n_cand, snap_cf_alias, snap_n_appended;
+    int32_t n_cand_early;  // |C| as the last early classification left it (before the frame tail appends the new candidates)
+    int32_t gate_ok;       // `ok` of the last pipelined frame as its frame tail saw it: what kernels enqueued ahead are gated on
     double T[16];          // refined pose, row-major 4x4 world->camera
     double Th[12];         // winning unrefined hypothesis [R|t]
     double cost;           // final sum of squared reprojection errors over the inliers
@@ -295,6 +304,9 @@ struct Pipeline {
     DevBuf<float> klt_in, klt_out, klt_err;
     DevBuf<uint8_t> klt_status;
     DevBuf<int32_t> klt_iters;
+    // second set: a candidates' KLT that runs ahead of the current frame's pose writes here (the sets are swapped), so
+    // the current frame's results survive until its promotion step is settled (no pose: it is redone from them)
+    DevBuf<float> klt_out2, klt_err2; DevBuf<uint8_t> klt_status2; DevBuf<int32_t> klt_iters2; bool klt_swapped = false;
     DevBuf<float> lost;     // positions of lost landmark tracks (debug output of a1)
     int64_t cand_tracked_prev = -1, cand_tracked_next = -1;  // frames of the cached candidate KLT
     bool cand_tracked_valid = false;
@@ -334,11 +346,31 @@ struct Pipeline {
     // the promoted rows wait in prom_rows / prom_ti for the pose (promote_finish_kernel)
     bool early_valid = false; double early_alpha = 0.; int early_ncand_upper = 0;
     DevBuf<double> prom_rows; DevBuf<int32_t> prom_ti;
+    // ---- tracking ahead of the pruning (pipelined frames) -------------------------------------------------------
+    // A track depends on nothing but its own start position and the two frames, so the next frame's landmark KLT
+    // need not wait for the RANSAC kernel to prune the landmarks: it runs over a SUPERSET of the rows the frame will
+    // hold - list 0: the rows the last compaction kept (buffer b1_buf, sc->n_tracked rows), list 1: the rows the early
+    // classification parked for promotion (prom_P, sc->n_promoted rows), lists 2..: the queued batches (every offered
+    // row) - and every landmark row carries the index of its track in that superset (Lsrc, written by the pruning
+    // and by the frame-tail kernel); the next compaction looks status and position up through it.  Same results.
+    DevBuf<float> lk_out[2], lk_err[2]; DevBuf<uint8_t> lk_status[2]; DevBuf<int32_t> lk_iters[2]; int lk_flip = 0;
+    DevBuf<int32_t> Lsrc[kLandBufs];   // per landmark buffer: row -> superset track index
+    DevBuf<float> prom_P;              // float2 positions of the parked rows (list 1)
+    int b1_buf = -1, b1_upper = 0;     // buffer the last compaction wrote, and the bound it was launched with
+    bool src_valid = false;            // Lsrc[cur] describes the live landmarks under the plan below
+    int src_prom_base = 0, src_prom_upper = 0, src_n_segs = 0, src_total = 0;
+    int src_seg_base[4] = {}, src_seg_n[4] = {}; const float* src_seg_P[4] = {};
+    DevBuf<double> feed_d[2]; int feed_flip = 0;   // the frame's new candidates (pipelined frames: also list 1 of the candidates' KLT)
+    cudaEvent_t ev_feed = nullptr;     // behind the feed's H2D copy (main stream)
     // speculative promotion (vo_pnp_ransac_promote): host-side values to restore on rollback
     bool spec_pending = false;
     // host-side values before the last tracking step (vo_track_rollback)
     // vo_process_frame_pipelined: the tracking step (ahead_prev -> ahead_next) is already enqueued
     bool ahead_valid = false; int64_t ahead_prev = 0, ahead_next = 0;
+    // ... and so is its PnP (RANSAC kernel + refit, gated like the tracking step): the next call only has to ask for
+    // the same camera matrix and parameters; pa_*: what to put back if it asks for something else
+    bool pnp_ahead = false; double pa_K[9] = {}; vo_pnp_params pa_prm = {}; int pa_cur = 0, pa_prev = -1, pa_prev2 = -1;
+    double keep_T[16] = {}; int keep_ok = 0;   // the last frame's pose as the host got it (restored on the device by an undo)
     bool rb_valid = false; int rb_cur = 0, rb_prev = -1, rb_prev_n_upper = 0, rb_n_land_upper = 0, rb_prev2 = -1, rb_prev2_n_upper = 0;
     double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
     cudaEvent_t ev_land = nullptr;   // behind the landmark KLT launch (candidates' KLT ordered after it, see track_both)
@@ -368,6 +400,21 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
                 const int32_t* d_nA, int nA_upper, const float* d_ptsB, const int32_t* d_nB, int nB_upper,
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
                 const vo_klt_params& prm, cudaStream_t st = nullptr, const int32_t* gate = nullptr);
+// up to kKltSegs track lists in one launch: list k = pts[k][0 .. min(*n_dev[k], n_upper[k])), results at element
+// offset out_off[k] (+ *off_dev[k]) of out/status/err/iters (n_dev[k] == nullptr: exactly n_upper[k] rows)
+constexpr int kKltSegs = 6;
+struct KltSegs {
+    int n;
+    const float2* pts[kKltSegs];
+    const int32_t* n_dev[kKltSegs];
+    int n_upper[kKltSegs];
+    int out_off[kKltSegs];
+    const int32_t* off_dev[kKltSegs];   // optional: added to out_off on the device (a list appended behind a live count)
+    uint8_t f64[kKltSegs];              // the list holds double2 rows (converted to float32 like the candidate append does)
+};
+int launch_klt_segs(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const KltSegs& segs, float* d_out,
+                    uint8_t* d_status, float* d_err, int32_t* d_iters, const vo_klt_params& prm,
+                    cudaStream_t st = nullptr, const int32_t* gate = nullptr);
 // make `stream` wait for the work in flight on the side stream (no-op if there is none)
 int join_side_stream(Ctx* c);
 // make `stream` wait for the pose-side work of the last pipelined frame (LM refit, X of the promoted rows)
@@ -397,6 +444,9 @@ struct PnpLaunch {
     bool compact;                       // prune landmark buffers to the inliers (estimatePose)
     bool readback_after_first = false;  // (unused since the RANSAC is one launch)
     bool refit_on_pose_stream = false;  // LM refit on Ctx::stream4: the landmark side of the frame goes on without it
+    const int32_t* gate = nullptr;      // device flag: the RANSAC kernel does nothing when it is 0 (a run enqueued ahead of a
+                                        // pose that may not come); the refit then finds ok == 0 and writes "no pose"
+    bool small_grid = false;            // kernels of the next frame run beside the RANSAC kernel: leave them most of the SMs
 };
 int launch_pnp(Ctx* c, const PnpLaunch& L);
 // raw cv::RNG output table on the device, large enough for H iterations (grows, never shrinks)
@@ -404,7 +454,7 @@ int ensure_rng_table(Ctx* c, int H);
 // tri.cu
 // after KLT: keep status==1, pack q4/qv.  gate (device flag, may be NULL): the kernel does nothing when it is 0
 // - for work enqueued ahead of a pose that may not come (vo_process_frame_pipelined)
-int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate = nullptr);
+int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate = nullptr, bool from_superset = false);
 // Tnew == nullptr: take the pose the last PnP left on the device (fused per-frame call)
 // split (pipelined frames, early classification done): the promoted rows' positions are appended on the main
 // stream at once, their 3-D points (DLT with the refined pose) and the pose-table row `pose_idx` (-1: none)

@@ -182,9 +182,7 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
 template <int WIN>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
 klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const __grid_constant__ KltTmaps maps, const int top,
-                 const float2* __restrict__ ptsA,
-                 const int32_t* __restrict__ nA_dev, const int nA_upper, const float2* __restrict__ ptsB,
-                 const int32_t* __restrict__ nB_dev, const int nB_upper, const int b_off,
+                 const KltSegs segs,
                  float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
                  int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
                  const double min_eig_thr, const int use_tile, const int32_t* __restrict__ gate)
@@ -217,18 +215,22 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const __grid_constant
         __syncwarp();
     }
     int track = blockIdx.x * kWarpsPerBlock + (threadIdx.x >> 5);
-    // two track lists share one launch: landmarks (A) then candidates (B, written at b_off)
+    // several track lists share one launch (landmarks + candidates; or the lists a tracking step ahead of the
+    // pruning covers): list k holds up to n_upper[k] rows (the live count on the device), results at out_off[k]
     float2 pt;
-    if (track < nA_upper) {
-        const int n = nA_dev ? min(*nA_dev, nA_upper) : nA_upper;
+    {
+        int k = 0;
+        while (k < segs.n - 1 && track >= segs.n_upper[k]) { track -= segs.n_upper[k]; k++; }
+        const int32_t* nd = segs.n_dev[k];
+        const int n = nd ? min(*nd, segs.n_upper[k]) : segs.n_upper[k];
         if (track >= n) return;
-        pt = ptsA[track];
-    } else {
-        track -= nA_upper;
-        const int n = nB_dev ? min(*nB_dev, nB_upper) : nB_upper;
-        if (track >= n) return;
-        pt = ptsB[track];
-        track += b_off;
+        if (segs.f64[k]) {
+            const double2 d = reinterpret_cast<const double2*>(segs.pts[k])[track];
+            pt = make_float2((float)d.x, (float)d.y);
+        } else {
+            pt = segs.pts[k][track];
+        }
+        track += segs.out_off[k] + (segs.off_dev[k] ? *segs.off_dev[k] : 0);
     }
 
     const float half = (WIN - 1) * 0.5f;
@@ -504,11 +506,24 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
                 int b_off, float* d_out, uint8_t* d_status, float* d_err, int32_t* d_iters,
                 const vo_klt_params& prm, cudaStream_t st, const int32_t* gate)
 {
-    VO_NVTX("vo:klt_track");
-    if (!st) st = c->stream;
     if (n_upper < 0) n_upper = 0;
     if (nB_upper < 0) nB_upper = 0;
-    if (n_upper + nB_upper <= 0) return VO_OK;
+    KltSegs segs{};
+    segs.n = 2;
+    segs.pts[0] = (const float2*)d_pts; segs.n_dev[0] = d_n; segs.n_upper[0] = n_upper; segs.out_off[0] = 0;
+    segs.pts[1] = (const float2*)d_ptsB; segs.n_dev[1] = d_nB; segs.n_upper[1] = nB_upper; segs.out_off[1] = b_off;
+    return launch_klt_segs(c, prev, next, segs, d_out, d_status, d_err, d_iters, prm, st, gate);
+}
+
+int launch_klt_segs(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const KltSegs& segs, float* d_out,
+                    uint8_t* d_status, float* d_err, int32_t* d_iters, const vo_klt_params& prm, cudaStream_t st,
+                    const int32_t* gate)
+{
+    VO_NVTX("vo:klt_track");
+    if (!st) st = c->stream;
+    int total = 0;
+    for (int k = 0; k < segs.n; k++) total += segs.n_upper[k];
+    if (total <= 0) return VO_OK;
     if (prm.win != 21) return set_error(c, VO_ERR_INVALID, "KLT window %d not built (only 21)", prm.win);
     if (prev.nlevels != next.nlevels || prev.lv[0].w != next.lv[0].w || prev.lv[0].h != next.lv[0].h)
         return set_error(c, VO_ERR_INVALID, "KLT frames differ in size");
@@ -526,9 +541,9 @@ int launch_klt2(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, const 
     const bool want_tma = e_tma && e_tma[0] == '1' && next.tmaps != nullptr && top <= 3;
     KltTmaps maps;
     if (want_tma) memcpy(&maps, next.tmaps, sizeof(maps)); else memset(&maps, 0, sizeof(maps));
-    const int blocks = (n_upper + nB_upper + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const int blocks = (total + kWarpsPerBlock - 1) / kWarpsPerBlock;
     klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
-        prev, next, maps, top, (const float2*)d_pts, d_n, n_upper, (const float2*)d_ptsB, d_nB, nB_upper, b_off,
+        prev, next, maps, top, segs,
         (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : (want_tma ? 2 : 1), gate);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());

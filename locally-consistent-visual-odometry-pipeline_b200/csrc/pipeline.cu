@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdlib.h>
 #include <time.h>
+#include <utility>
 #include "ctx.cuh"
 #include "pnp_sets.cuh"
 
@@ -44,7 +45,12 @@ void pipeline_free(Ctx* c)
     cudaFree(p->poses.p); cudaFree(p->klt_in.p); cudaFree(p->klt_out.p); cudaFree(p->klt_err.p);
     cudaFree(p->klt_status.p); cudaFree(p->klt_iters.p); cudaFree(p->lost.p); cudaFree(p->q4.p); cudaFree(p->qv.p);
     cudaFree(p->sets.p); cudaFree(p->hyp.p); cudaFree(p->counts.p); cudaFree(p->mask.p); cudaFree(p->promote.p);
-    cudaFree(p->q4i.p); cudaFree(p->qvi.p);
+    cudaFree(p->q4i.p); cudaFree(p->qvi.p); cudaFree(p->prom_rows.p); cudaFree(p->prom_ti.p); cudaFree(p->prom_P.p);
+    for (int k = 0; k < 2; k++) { cudaFree(p->lk_out[k].p); cudaFree(p->lk_err[k].p); cudaFree(p->lk_status[k].p); cudaFree(p->lk_iters[k].p); }
+    for (int k = 0; k < kLandBufs; k++) cudaFree(p->Lsrc[k].p);
+    cudaFree(p->klt_out2.p); cudaFree(p->klt_err2.p); cudaFree(p->klt_status2.p); cudaFree(p->klt_iters2.p);
+    cudaFree(p->feed_d[0].p); cudaFree(p->feed_d[1].p);
+    if (p->ev_feed) cudaEventDestroy(p->ev_feed);
     cudaFree(p->stage_d.p); cudaFree(p->stage_f.p); cudaFree(p->stage_i.p);
     cudaFree(p->rng_tab.p); cudaFree(p->blk_counts.p); cudaFree(p->cand_flag.p);
     for (int k = 0; k < 2; k++) { cudaFree(p->d_add[k].p); if (p->h_add[k]) cudaFreeHost(p->h_add[k]); }
@@ -97,8 +103,13 @@ struct DeferredAdd { const double* pts; int n; const double* T44; };
 // landmark launch - the head of the chain the pose depends on - is enqueued FIRST; the candidates
 // (usually most of the tracks, and with them the slowest stragglers) follow on the side stream, behind
 // the optional deferred append, and are joined by the promotion step.
+// superset: the landmark launch goes to the tracking stream and covers the rows of the last compaction (before the
+// pruning), the rows parked for promotion and every row of the queued batches (Pipeline::src_*) - it starts as soon
+// as that compaction and the early classification are done, beside the RANSAC kernel, and needs no gate: it writes
+// nothing but its own result buffers (lk_*), which the gated compaction reads through Lsrc.
 static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& prm, bool with_candidates,
-                      const DeferredAdd* add = nullptr, double early_alpha = -1., const int32_t* gate = nullptr)
+                      const DeferredAdd* add = nullptr, double early_alpha = -1., const int32_t* gate = nullptr,
+                      bool superset = false, const double* d_feed = nullptr, int n_feed = 0)
 {
     Pipeline* p = c->pipe;
     const int nA = p->n_land_upper;
@@ -107,16 +118,46 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
     const size_t tot = (size_t)nA + nB > 0 ? (size_t)nA + nB : 1;
     VO_TRY(early_undo(c));          // (a classification nobody finished: its tracking is being replaced)
     VO_TRY(join_side_stream(c));
+    // superset: the candidates' KLT does not wait for the frame tail either - list 0: the rows the last early
+    // classification kept (sc->n_cand_early of them), list 1: the frame's new candidates straight from the staging
+    // buffer (the tail appends them behind list 0, so their tracks sit where the classification will look)
+    const bool cand_ahead = superset && nB > 0 && n_add == 0 && (n_feed == 0 || d_feed != nullptr);
+    p->klt_swapped = false;
+    if (cand_ahead) {   // (ungated: into the other set of result buffers)
+        std::swap(p->klt_out, p->klt_out2); std::swap(p->klt_err, p->klt_err2);
+        std::swap(p->klt_status, p->klt_status2); std::swap(p->klt_iters, p->klt_iters2);
+        p->klt_swapped = true;
+    }
     VO_TRY(ensure(c, p->klt_out, tot * 2)); VO_TRY(ensure(c, p->klt_err, tot));
     VO_TRY(ensure(c, p->klt_status, tot)); VO_TRY(ensure(c, p->klt_iters, tot));
     if (nB > 0) VO_CUDA(c, cudaEventRecord(c->ev_fork, c->stream));   // the side stream forks BEFORE the landmark launch
+    if (superset) {
+        const int f = p->lk_flip ^= 1;
+        const size_t stot = p->src_total > 0 ? p->src_total : 1;
+        VO_TRY(ensure(c, p->lk_out[f], stot * 2)); VO_TRY(ensure(c, p->lk_err[f], stot));
+        VO_TRY(ensure(c, p->lk_status[f], stot)); VO_TRY(ensure(c, p->lk_iters[f], stot));
+        KltSegs sg{};
+        sg.n = 2 + p->src_n_segs;
+        sg.pts[0] = (const float2*)p->P[p->b1_buf].p; sg.n_dev[0] = &p->d_sc->n_tracked; sg.n_upper[0] = p->b1_upper; sg.out_off[0] = 0;
+        sg.pts[1] = (const float2*)p->prom_P.p; sg.n_dev[1] = &p->d_sc->n_promoted; sg.n_upper[1] = p->src_prom_upper; sg.out_off[1] = p->src_prom_base;
+        for (int k = 0; k < p->src_n_segs; k++) {
+            sg.pts[2 + k] = (const float2*)p->src_seg_P[k]; sg.n_dev[2 + k] = nullptr; sg.n_upper[2 + k] = p->src_seg_n[k];
+            sg.out_off[2 + k] = p->src_seg_base[k];
+        }
+        VO_CUDA(c, cudaStreamWaitEvent(c->stream5, c->ev_compact, 0));   // list 0 and its count
+        VO_CUDA(c, cudaStreamWaitEvent(c->stream5, c->ev_join, 0));      // list 1 and its count (early classification, side stream)
+        if (b->ready) VO_CUDA(c, cudaStreamWaitEvent(c->stream5, b->ready, 0));   // the frame, if it came over the ingest stream
+        VO_TRY(launch_klt_segs(c, a->pyr, b->pyr, sg, p->lk_out[f].p, p->lk_status[f].p, p->lk_err[f].p, p->lk_iters[f].p, prm,
+                               c->stream5, nullptr));
+        VO_CUDA(c, cudaEventRecord(c->ev_trk, c->stream5));
+    } else
     VO_TRY(launch_klt2(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, nullptr, nullptr, 0, 0, p->klt_out.p,
                        p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, nullptr, gate));
     if (prm.fb_check)
         VO_TRY(klt_fb_check(c, a->pyr, b->pyr, p->P[p->cur].p, &p->d_sc->n_land, nA, p->klt_out.p, p->klt_status.p, prm, c->stream, 0, gate));
     p->klt_b_off = nA;
     if (nB > 0) {
-        VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
+        if (!cand_ahead) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));
         if (n_add > 0) {
             const size_t need = (size_t)n_add * 2 + 16;
             if (need > p->h_add_cap) {
@@ -148,6 +189,18 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
             VO_CUDA(c, cudaStreamWaitEvent(c->stream2, p->ev_land, 0));
         }
         if (p->profiling) cudaEventRecord(p->ev_side[0], c->stream2);
+        if (cand_ahead) {
+            KltSegs sg{};
+            sg.n = 2;
+            sg.pts[0] = (const float2*)p->C[p->ccur].p; sg.n_dev[0] = &p->d_sc->n_cand_early; sg.n_upper[0] = nB - n_feed; sg.out_off[0] = nA;
+            sg.pts[1] = (const float2*)d_feed; sg.n_dev[1] = nullptr; sg.n_upper[1] = n_feed; sg.out_off[1] = nA;
+            sg.off_dev[1] = &p->d_sc->n_cand_early; sg.f64[1] = 1;
+            if (n_feed > 0) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, p->ev_feed, 0));
+            if (b->ready) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, b->ready, 0));
+            VO_TRY(launch_klt_segs(c, a->pyr, b->pyr, sg, p->klt_out.p, p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm,
+                                   c->stream2, nullptr));
+            VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_fork, 0));   // the classification needs the tail's append
+        } else
         VO_TRY(launch_klt2(c, a->pyr, b->pyr, nullptr, nullptr, 0, p->C[p->ccur].p, &p->d_sc->n_cand, nB, nA, p->klt_out.p,
                            p->klt_status.p, p->klt_err.p, p->klt_iters.p, prm, c->stream2, gate));
         if (prm.fb_check)
@@ -156,8 +209,14 @@ static int track_both(Ctx* c, FrameSlot* a, FrameSlot* b, const vo_klt_params& p
         if (p->profiling) cudaEventRecord(p->ev_side[1], c->stream2);
         // the pose-independent half of the promotion step follows the candidates' KLT on the side stream
         if (early_alpha >= 0.) {
-            // (a pose read-back still in flight on the pose stream copies the scalar block: let it go first)
-            if (c->pose_inflight && p->ev_pose) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, p->ev_pose, 0));
+            // The pose stream may still owe the previous pipelined frame its scalar read-back and the DLT of the rows it
+            // parked for promotion (prom_rows / prom_ti / n_promoted), all of which this classification overwrites: wait
+            // for the END of that work (ev_pose_done), not just for the read-back.  Usually long over - but when a
+            // tracking launch larger than the GPU (landmarks + an appended map batch + candidates > 148 x 16 warps)
+            // fills every SM, the pose stream's small kernels wait for a free slot and come AFTER the candidates' KLT.
+            if (c->pose_inflight) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_pose_done, 0));
+            // (the tracking stream's launch reads the parked rows and their count, which this classification rewrites)
+            if (superset) VO_CUDA(c, cudaStreamWaitEvent(c->stream2, c->ev_trk, 0));
             VO_TRY(launch_promote_early(c, early_alpha, nB, nA, gate));
         }
         VO_CUDA(c, cudaEventRecord(c->ev_join, c->stream2));
@@ -266,6 +325,8 @@ int vo_set_state(vo_ctx* c, const float* P, const double* X, int n)
     Pipeline* p = c->pipe;
     VO_TRY(drop_ahead(c));
     VO_TRY(join_pose_stream(c));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream5));   // (a landmark KLT that ran ahead reads the rotation's buffers)
+    p->b1_buf = -1; p->src_valid = false;
     const size_t m = n > 0 ? n : 1;
     VO_TRY(ensure(c, p->P[p->cur], m * 2)); VO_TRY(ensure(c, p->X[p->cur], m * 3));
     if (n > 0) {
@@ -289,11 +350,14 @@ int vo_get_state(vo_ctx* c, float* P, double* X, int cap, int* n)
     Pipeline* p = c->pipe;
     VO_TRY(drop_ahead(c));
     VO_TRY(read_scalars(c));   // (joins the pose stream: X of rows promoted by a pipelined frame)
-    const int m = p->h_sc->n_land;
+    // (a tracking step the caller has taken over, with its PnP already on the device: the state between the two is the
+    // rows the tracking step kept - the buffer the pruning read, not the one it wrote)
+    const int buf = p->pnp_ahead ? p->pa_cur : p->cur;
+    const int m = p->pnp_ahead ? p->h_sc->n_tracked : p->h_sc->n_land;
     if (n) *n = m;
     if (m > cap) return (P || X) ? set_error(c, VO_ERR_CAPACITY, "state has %d rows, buffer %d", m, cap) : VO_OK;
-    if (m > 0 && P) VO_CUDA(c, cudaMemcpyAsync(P, p->P[p->cur].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
-    if (m > 0 && X) VO_CUDA(c, cudaMemcpyAsync(X, p->X[p->cur].p, sizeof(double) * 3 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && P) VO_CUDA(c, cudaMemcpyAsync(P, p->P[buf].p, sizeof(float) * 2 * m, cudaMemcpyDefault, c->stream));
+    if (m > 0 && X) VO_CUDA(c, cudaMemcpyAsync(X, p->X[buf].p, sizeof(double) * 3 * m, cudaMemcpyDefault, c->stream));
     VO_CUDA(c, cudaStreamSynchronize(c->stream));
     return VO_OK;
 }
@@ -440,7 +504,8 @@ static int fill_counters(vo_ctx* c, vo_counters* out, bool sync)
     if (!out) return VO_ERR_INVALID;
     if (sync) VO_TRY(read_scalars(c));
     const DevScalars* s = c->pipe->h_sc;
-    out->n_landmarks = s->n_land; out->n_candidates = s->n_cand; out->n_tracked = s->n_tracked; out->n_lost = s->n_lost;
+    out->n_landmarks = c->pipe->pnp_ahead ? s->n_tracked : s->n_land;   // (a PnP enqueued ahead has not happened yet for the caller)
+    out->n_candidates = s->n_cand; out->n_tracked = s->n_tracked; out->n_lost = s->n_lost;
     out->n_inliers = s->n_inliers; out->pnp_ok = s->ok; out->ransac_iters = s->iters_run; out->best_hypothesis = s->best_hyp;
     out->lm_iters = s->lm_iters; out->n_promoted = s->n_promoted; out->n_candidates_lost = s->n_cand_lost;
     out->cf_alias = s->cf_alias; out->klt_iters = s->klt_iters; out->klt_iters_candidates = s->klt_iters_cand;
@@ -503,6 +568,30 @@ int vo_klt_track_landmarks_add(vo_ctx* c, int64_t prev_key, int64_t next_key, co
     return track_landmarks_impl(c, prev_key, next_key, params, n_new > 0 ? &add : nullptr, n_kept);
 }
 
+// A PnP that vo_process_frame_pipelined enqueued ahead (PnpLaunch::gate) is not the one the caller wants after all:
+// the landmarks are again the rows its tracking step kept (the pruning wrote into another buffer of the rotation),
+// and the device-side pose is the last frame's again.  Rare path: waits for the pose stream.
+__global__ void pnp_unahead_kernel(DevScalars* sc, int ok)
+{
+    sc->n_land = sc->n_tracked; sc->ok = ok; sc->n_inliers = 0;
+}
+
+static int pnp_ahead_undo(vo_ctx* c)
+{
+    Pipeline* p = c->pipe;
+    if (!p->pnp_ahead) return VO_OK;
+    p->pnp_ahead = false;
+    VO_CUDA(c, cudaStreamSynchronize(c->stream4));   // its refit
+    pnp_unahead_kernel<<<1, 1, 0, c->stream>>>(p->d_sc, p->keep_ok);
+    c->launches++;
+    VO_CUDA(c, cudaGetLastError());
+    VO_CUDA(c, cudaMemcpyAsync(p->d_sc->T, p->keep_T, sizeof(p->keep_T), cudaMemcpyHostToDevice, c->stream));
+    VO_CUDA(c, cudaStreamSynchronize(c->stream));    // (keep_T is pageable)
+    p->cur = p->pa_cur; p->prev = p->pa_prev; p->prev2 = p->pa_prev2;
+    p->src_valid = false;
+    return VO_OK;
+}
+
 __global__ void track_rollback_kernel(DevScalars* sc)
 {
     sc->n_land = sc->prev_n_land; sc->prev_n_land = sc->prev2_n_land; sc->n_tracked = 0; sc->n_lost = 0;
@@ -531,6 +620,7 @@ int vo_track_rollback(vo_ctx* c)
     VO_NEED(c);
     Pipeline* p = c->pipe;
     if (!p->rb_valid || !p->packed_valid) return set_error(c, VO_ERR_STATE, "no tracking step to undo");
+    VO_TRY(pnp_ahead_undo(c));
     VO_TRY(early_undo(c));
     VO_TRY(join_side_stream(c));
     track_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
@@ -540,6 +630,7 @@ int vo_track_rollback(vo_ctx* c)
     p->cur = p->rb_cur; p->prev = p->rb_prev; p->prev_n_upper = p->rb_prev_n_upper; p->prev2 = -1; p->prev2_n_upper = 0;
     p->n_land_upper = p->rb_n_land_upper;
     p->rb_valid = false; p->packed_valid = false; p->cand_tracked_valid = false;
+    p->b1_buf = -1; p->src_valid = false;
     return VO_OK;
 }
 
@@ -549,6 +640,7 @@ int vo_pnp_ransac(vo_ctx* c, const double K[9], const vo_pnp_params* params, dou
     VO_NEED(c);
     if (!K) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
+    VO_TRY(pnp_ahead_undo(c));
     PnpLaunch L{};
     if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
     if (!p->packed_valid) {   // no tracking step preceded (state set directly): pack P/X now
@@ -615,6 +707,7 @@ int vo_pnp_ransac_promote(vo_ctx* c, const double K[9], const vo_pnp_params* par
     Pipeline* p = c->pipe;
     if (!p->cand_tracked_valid || !p->packed_valid)
         return set_error(c, VO_ERR_STATE, "speculative promotion needs vo_klt_track_landmarks on this frame pair first");
+    VO_TRY(pnp_ahead_undo(c));
     PnpLaunch L{};
     if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
     L.q4 = p->q4.p; L.qv = p->qv.p; L.d_n = &p->d_sc->n_tracked; L.n_upper = p->n_land_upper;
@@ -904,12 +997,27 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         b = get_frame(c, next_key);
         if (!a || !b) return set_error(c, VO_ERR_NOFRAME, "frame %lld not resident", (long long)(!a ? prev_key : next_key));
     }
+    // the frame's new candidates: two staging buffers in turn (the candidates' KLT of the NEXT frame, which a pipelined
+    // call may enqueue ahead, reads the rows straight from here - and may still be running when the next feed arrives)
+    double* feed_ptr = nullptr;
+    if (n_new > 0) {
+        DevBuf<double>& fbuf = p->feed_d[p->feed_flip ^= 1];
+        VO_TRY(ensure(c, fbuf, (size_t)n_new * 2));
+        feed_ptr = fbuf.p;
+        if (!p->ev_feed) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_feed, cudaEventDisableTiming));
+    }
     if (n_new > 0 && !tracked) {   // stage the candidate feed early so the copy overlaps the tracking
-        VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
-        VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(feed_ptr, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaEventRecord(p->ev_feed, c->stream));
     }
     const bool prof = p->profiling;
     if (prof) cudaEventRecord(p->ev[1], c->stream);
+    // Tracking ahead of the pruning (track_both, superset): the next frame's KLT launches run beside this frame's
+    // RANSAC kernel and refit instead of behind them.  Same results.  OFF by default (VO_TRACK_AHEAD=1 turns it on):
+    // measured on the B200 it shortens the main stream's chain (device-resident leg +4 %) but delays the pose the host
+    // is waiting for and costs about ten more driver calls per frame (class-surface leg -9 %).
+    static const int ahead_mode = getenv("VO_TRACK_AHEAD") ? atoi(getenv("VO_TRACK_AHEAD")) : 0;
+    const bool want_superset = pipelined && ahead_mode != 0;
     if (!tracked) VO_TRY(track_both(c, a, b, kp, true, nullptr, alpha_deg));
     if (prof) cudaEventRecord(p->ev[2], c->stream);
     if (!tracked) VO_TRY(launch_landmark_compact(c, p->n_land_upper));
@@ -926,11 +1034,20 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
     // triangulates the promoted rows - needed again only by the next frame's compaction, which waits for it.
     const bool split = pipelined && p->early_valid && alpha_deg == p->early_alpha;
     L.refit_on_pose_stream = split;
+    L.small_grid = split && want_superset;
     if (pipelined && !p->ev_pose) VO_CUDA(c, cudaEventCreateWithFlags(&p->ev_pose, cudaEventDisableTiming));
-    VO_TRY(launch_pnp(c, L));
+    // this frame's PnP may be on the device already (enqueued by the previous call behind the tracking step): it stands if
+    // it was launched for the same camera matrix and parameters and this call splits the frame the same way
+    bool pnp_done = false;
+    if (p->pnp_ahead) {
+        pnp_done = tracked && split && memcmp(p->pa_K, L.K, sizeof(L.K)) == 0 && memcmp(&p->pa_prm, &L.prm, sizeof(L.prm)) == 0;
+        if (pnp_done) p->pnp_ahead = false;
+        else VO_TRY(pnp_ahead_undo(c));
+    }
+    if (!pnp_done) VO_TRY(launch_pnp(c, L));
     if (n_new > 0 && tracked) {   // (tracking done ahead: the PnP launch is what the GPU is waiting for - the feed goes behind it)
-        VO_TRY(ensure(c, p->stage_d, (size_t)n_new * 2 + 16));
-        VO_CUDA(c, cudaMemcpyAsync(p->stage_d.p + 16, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaMemcpyAsync(feed_ptr, new_candidates, sizeof(double) * 2 * n_new, cudaMemcpyDefault, c->stream));
+        VO_CUDA(c, cudaEventRecord(p->ev_feed, c->stream));
     }
     if (prof) cudaEventRecord(p->ev[4], c->stream);
     const int ncand_before = p->n_cand_upper;
@@ -956,14 +1073,14 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
             slots[k] = p->land_slot_used;
             dsegs[k] = Pipeline::LandSeg{ dP, dX, segs[k].n, segs[k].target };
         }
-        VO_TRY(launch_frame_tail(c, K, alpha_deg, p->klt_b_off, n_new > 0 ? p->stage_d.p + 16 : nullptr, n_new, dsegs, n_segs));
+        VO_TRY(launch_frame_tail(c, K, alpha_deg, p->klt_b_off, feed_ptr, n_new, dsegs, n_segs));
         for (int k = 0; k < n_segs; k++) if (slots[k] >= 0) VO_CUDA(c, cudaEventRecord(p->ev_land_slot[slots[k]], c->stream));
         VO_TRY(close_step(c));
     } else {
         if (n_new > 0) VO_TRY(ensure(c, p->poses, (size_t)(p->n_poses + 1) * 16, true));   // (before a kernel gets the pointer)
         VO_TRY(launch_promote(c, K, nullptr, alpha_deg, p->n_cand_upper, true, p->klt_b_off, false, -1));
         VO_TRY(close_step(c));
-        if (n_new > 0) VO_TRY(launch_cand_add(c, p->stage_d.p + 16, n_new, nullptr));
+        if (n_new > 0) VO_TRY(launch_cand_add(c, feed_ptr, n_new, nullptr));
         for (int k = 0; k < n_segs; k++) VO_TRY(append_landmarks_now(c, segs[k].P, segs[k].X, segs[k].n, segs[k].target));
     }
     if (prof) cudaEventRecord(p->ev[5], c->stream);
@@ -983,14 +1100,28 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
                 // every kernel of the step ahead looks at this frame's `ok` first and leaves all buffers alone
                 // when no pose came: the failure path below then finds this frame's tracking results, candidate
                 // buffers and scalars exactly as they were
-                const int32_t* gate = &p->d_sc->ok;
-                VO_TRY(track_both(c, a2, b2, kp, true, nullptr, alpha_deg, gate));
+                const int32_t* gate = split ? &p->d_sc->gate_ok : &p->d_sc->ok;
+                const bool superset = split && p->src_valid && p->b1_buf >= 0 && !kp.fb_check && want_superset;
+                VO_TRY(track_both(c, a2, b2, kp, true, nullptr, alpha_deg, gate, superset, feed_ptr, n_new));
                 p->cand_tracked_prev = next_key; p->cand_tracked_next = nk; p->cand_tracked_valid = true;
                 p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
     p->rb_prev2 = p->prev2; p->rb_prev2_n_upper = p->prev2_n_upper;
-                VO_TRY(launch_landmark_compact(c, p->n_land_upper, gate));
+                VO_TRY(launch_landmark_compact(c, p->n_land_upper, gate, superset));
                 p->rb_valid = true; p->packed_valid = true;
                 p->ahead_valid = true; p->ahead_prev = next_key; p->ahead_next = nk;
+                // ... and its PnP: the RANSAC kernel needs nothing the next call brings (new candidates and landmark
+                // batches come in behind it), so the GPU goes from one frame to the next without waiting for the host
+                // (VO_PNP_AHEAD=0: A/B switch, same results)
+                static const int pnp_ahead_mode = getenv("VO_PNP_AHEAD") ? atoi(getenv("VO_PNP_AHEAD")) : 1;
+                if (split && pnp_ahead_mode != 0) {
+                    PnpLaunch L2 = L;
+                    L2.q4 = p->q4.p; L2.qv = p->qv.p;   // (the compaction above may have grown them)
+                    L2.n_upper = p->n_land_upper; L2.gate = gate; L2.refit_on_pose_stream = true; L2.small_grid = superset;
+                    p->pa_cur = p->cur; p->pa_prev = p->prev; p->pa_prev2 = p->prev2;
+                    memcpy(p->pa_K, L2.K, sizeof(p->pa_K)); p->pa_prm = L2.prm;
+                    VO_TRY(launch_pnp(c, L2));
+                    p->pnp_ahead = true;
+                }
             }
         }
         VO_TRY(flush_frame_hint(c, true));
@@ -1020,7 +1151,16 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
                 if (p->n_cand_upper < p->early_ncand_upper) p->n_cand_upper = p->early_ncand_upper;
             }
             p->klt_b_off = b_off_k; p->mask_src_valid = mask_valid_k; p->mask_src_off = mask_off_k;
+            if (p->klt_swapped) {   // this frame's candidate tracks are in the other set
+                VO_CUDA(c, cudaStreamSynchronize(c->stream2));
+                std::swap(p->klt_out, p->klt_out2); std::swap(p->klt_err, p->klt_err2);
+                std::swap(p->klt_status, p->klt_status2); std::swap(p->klt_iters, p->klt_iters2);
+                p->klt_swapped = false;
+            }
+            p->b1_buf = -1; p->src_valid = false;
             p->rb_valid = false; p->packed_valid = false; p->cand_tracked_valid = false; p->ahead_valid = false;
+            if (p->pnp_ahead) VO_CUDA(c, cudaStreamSynchronize(c->stream4));
+            p->pnp_ahead = false;   // (gated: it did nothing; its refit found ok == 0 and wrote "no pose", as this frame's did)
         }
     } else {
         VO_TRY(read_scalars(c));
@@ -1047,6 +1187,7 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
         if (cudaEventElapsedTime(&ms, p->ev_side[0], p->ev_side[1]) == cudaSuccess) p->stage_ms[5] += ms;
         p->stage_frames++;
     }
+    if (pipelined) { memcpy(p->keep_T, p->h_sc->T, sizeof(p->keep_T)); p->keep_ok = p->h_sc->ok; }
     if (T44) memcpy(T44, p->h_sc->T, sizeof(double) * 16);
     if (counters) {
         fill_counters_from(p->h_sc, counters);
@@ -1133,6 +1274,7 @@ int vo_solve_pnp_ransac(vo_ctx* c, const double* X, const float* P, int n, const
     VO_NEED(c);
     if (n < 0 || !K || (n > 0 && (!X || !P))) return VO_ERR_INVALID;
     Pipeline* p = c->pipe;
+    VO_TRY(drop_ahead(c));   // (a step enqueued ahead keeps its point count in the scalar block this run uses)
     PnpLaunch L{};
     if (params) L.prm = *params; else vo_pnp_params_default(&L.prm);
     const size_t m = n > 0 ? n : 1;
@@ -1316,6 +1458,7 @@ int vo_solve_pnp_ransac_noalloc(vo_ctx* c, const double* X, const float* P, int 
     if (L.prm.max_iters > kNoAllocMaxIters)
         return set_error(c, VO_ERR_CAPACITY, "vo_solve_pnp_ransac_noalloc: max_iters %d, the static scratch holds at most %d "
                          "hypotheses (use vo_solve_pnp_ransac)", L.prm.max_iters, kNoAllocMaxIters);
+    VO_TRY(drop_ahead(c));   // (a step enqueued ahead keeps its point count in the scalar block this run uses)
     unsigned char* scratch = nullptr;
     VO_TRY(noalloc_setup(c, &scratch));
     VO_TRY(join_side_stream(c));

@@ -368,6 +368,7 @@ __device__ void ransac_select(DevScalars* sc, int32_t* sets, const int32_t* coun
 struct FinalizeBufs {
     const float* P_in; const double* X_in; float* P_out; double* X_out;   // landmark rotation
     float4* q4i; float* qvi;                                              // the inliers, packed for the refit
+    int32_t* src_out;   // per kept row: its row before the pruning (= its track when the next KLT ran ahead, Pipeline::Lsrc)
 };
 
 __device__ __forceinline__ void so3_exp(const double* w, double* R)
@@ -636,6 +637,7 @@ __device__ void pnp_mask_prune(DevScalars* sc, const double* hyp, const float4* 
             const int o = ok_ + __popc(bk & below);
             reinterpret_cast<float2*>(fb.P_out)[o] = make_float2(q.w, v);   // (u, v) as the tracking step left them
             fb.X_out[3 * (size_t)o] = x0; fb.X_out[3 * (size_t)o + 1] = x1; fb.X_out[3 * (size_t)o + 2] = x2;
+            if (fb.src_out) fb.src_out[o] = i;
         }
         if (inl) {
             const int o = oi_ + __popc(bi & below);
@@ -669,15 +671,20 @@ __device__ __forceinline__ void st_release(int* p, int v)
 // sequential bookkeeping of the reference loop (first strictly-better model wins, the budget shrinks) over
 // the round's counts and opens the next round (epoch flag the others spin on) or ends the run: then it writes
 // the inlier mask, prunes the landmarks and packs the inliers for the refit kernel.
-//   round 0: one hypothesis per CTA (the adaptive stop usually ends the run inside it);
+//   round 0: the first kPnpChunk0 hypotheses, spread over the CTAs (the adaptive stop usually ends the run inside it);
+//            one per CTA, or - PnpLaunch::small_grid - 4 per CTA on kPnpGridSmall CTAs: their P3Ps run side by side
+//            on 4 warps and ONE pass over the points scores all 4 (16.5 us against 14.2 us for the round), and three
+//            quarters of the SMs stay free for the next frame's KLT, which runs beside this kernel;
 //   later rounds: B = ceil(remaining budget / CTAs), at most kBatch - a run with a pinned budget of 4096 is two rounds.
 constexpr int kBatch = 32;       // hypotheses per CTA per round (P3P quads side by side: 128 threads)
 constexpr int kScoreTile = 4;    // hypotheses scored per pass over the points
 constexpr int kQueue = 512;      // per warp: (hypothesis, point) pairs waiting for the exact float64 test
+constexpr int kPnpGridSmall = 32;   // CTAs of a run launched beside the next frame's KLT (4 hypotheses each in round 0)
 
 __global__ void __launch_bounds__(kHypThreads)
 pnp_ransac_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, const float* __restrict__ qv,
-                  double* hyp, int32_t* counts, uint8_t* mask, PnpArgs a, RngTab rt, FinalizeBufs fb, int H, int epoch0)
+                  double* hyp, int32_t* counts, uint8_t* mask, PnpArgs a, RngTab rt, FinalizeBufs fb, int H, int epoch0,
+                  const int32_t* __restrict__ gate)
 {
     __shared__ double sRt[kBatch][12];
     __shared__ int sValid[kBatch];
@@ -687,6 +694,7 @@ pnp_ransac_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, 
     __shared__ unsigned sQ[kHypThreads / 32][kQueue];
     __shared__ int sQn[kHypThreads / 32];
     pdl_prologue();
+    if (gate && !*gate) return;   // enqueued ahead of a pose that did not come: every CTA leaves, nothing is touched
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int G = gridDim.x;
     const unsigned long long t_in = gtime();
@@ -697,9 +705,10 @@ pnp_ransac_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, 
     for (int round = 0;; round++) {
         const int budget = round == 0 ? niters0 : sc->niters;
         const int remaining = budget - h0;
-        int B = round == 0 ? 1 : (remaining + G - 1) / G;
+        // (round 0 covers the kPnpChunk0 sets drawn ahead by the compaction, however few CTAs share them)
+        int B = round == 0 ? (min(remaining, kPnpChunk0) + G - 1) / G : (remaining + G - 1) / G;
         B = max(1, min(B, kBatch));
-        const int h1 = min(budget, h0 + G * B);
+        const int h1 = round == 0 ? min(min(budget, kPnpChunk0), h0 + G * B) : min(budget, h0 + G * B);
         const int hb = h0 + (int)blockIdx.x * B;         // this CTA's hypotheses: [hb, hb + nb)
         const int nb = max(0, min(B, h1 - hb));
         // ---- P3P: one quad of lanes per warp at a time (the solver's Newton loops and early exits are data
@@ -898,13 +907,23 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         VO_TRY(ensure(c, p->P[nxt], npts * 2));
         VO_TRY(ensure(c, p->X[nxt], npts * 3));
         fb.P_out = p->P[nxt].p; fb.X_out = p->X[nxt].p;
+        VO_TRY(ensure(c, p->Lsrc[nxt], npts + (size_t)p->n_cand_upper + 8192));   // (room for the rows the frame tail appends)
+        fb.src_out = p->Lsrc[nxt].p;
     }
+    p->src_valid = false;
     // one persistent launch: every CTA must be resident (they meet at a flag between rounds)
-    int grid = H < kPnpChunk0 ? (H > 0 ? H : 1) : kPnpChunk0;
+    // one CTA per hypothesis of round 0 is the shortest way to the pose; when the next frame's KLT runs beside this
+    // kernel (L.small_grid) and the run has an adaptive stop (it almost always ends in round 0), a quarter of the CTAs
+    // does the same round 2 us slower and leaves the other SMs alone.  VO_PNP_GRID: A/B switch (same results)
+    static const int grid_env = getenv("VO_PNP_GRID") ? atoi(getenv("VO_PNP_GRID")) : 0;
+    int grid = (L.small_grid && a.confidence < 1.) ? kPnpGridSmall : kPnpChunk0;
+    if (grid_env > 0) grid = grid_env;
+    if (grid > kPnpChunk0) grid = kPnpChunk0;
+    if (grid > H) grid = H > 0 ? H : 1;
     if (grid > c->sm_count) grid = c->sm_count;
     const int epoch0 = (int)((unsigned)(++p->pnp_run) << 12);
     VO_CUDA(c, launch_pdl(pnp_ransac_kernel, dim3(grid), dim3(kHypThreads), c->stream, p->d_sc, sets, (const float4*)L.q4, L.qv,
-                          p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, H, epoch0));
+                          p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, H, epoch0, L.gate));
     c->launches++;
     // the refit: on the caller's stream, or on the pose stream when the landmark side goes on without it
     cudaStream_t rs = c->stream;

@@ -52,7 +52,8 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
                         const uint8_t* __restrict__ status, const int32_t* __restrict__ iters,
                         const double* __restrict__ X_in, float2* __restrict__ P_out, double* __restrict__ X_out,
                         float4* __restrict__ q4, float* __restrict__ qv, float2* __restrict__ lost,
-                        int32_t* __restrict__ sets, RngTab rt, const int32_t* __restrict__ gate)
+                        int32_t* __restrict__ sets, RngTab rt, const int32_t* __restrict__ gate,
+                        const int32_t* __restrict__ src)
 {
     constexpr int NW = kScanThreads / 32 - 1;   // data warps
     __shared__ int sKeepW[32], sLostW[32], sIterW[32];
@@ -69,8 +70,9 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
         for (int i0 = lo; i0 < hi; i0 += 32) {
             const int i = i0 + lane;
             const bool in = i < hi;
-            const bool keep = in && status[i] != 0;
-            if (in && iters) it += iters[i];
+            const int t = in ? (src ? src[i] : i) : 0;   // the row's track (tracking ahead of the pruning: a superset)
+            const bool keep = in && status[t] != 0;
+            if (in && iters) it += iters[t];
             const unsigned bk = __ballot_sync(0xffffffffu, keep);
             const unsigned bi = __ballot_sync(0xffffffffu, in);
             ck += __popc(bk); cl += __popc(bi & ~bk);
@@ -97,20 +99,21 @@ landmark_compact_kernel(DevScalars* sc, int n_upper, const float2* __restrict__ 
     for (int i0 = lo; i0 < hi; i0 += 32) {
         const int i = i0 + lane;
         const bool in = i < hi;
-        const bool keep = in && status[i] != 0;
+        const int t = in ? (src ? src[i] : i) : 0;
+        const bool keep = in && status[t] != 0;
         const unsigned bk = __ballot_sync(0xffffffffu, keep);
         const unsigned bi = __ballot_sync(0xffffffffu, in);
         const unsigned below = (1u << lane) - 1;
         if (keep) {
             const int o = ok_ + __popc(bk & below);
-            const float2 p = klt_out[i];
+            const float2 p = klt_out[t];
             const double x = X_in[3 * (size_t)i], y = X_in[3 * (size_t)i + 1], z = X_in[3 * (size_t)i + 2];
             P_out[o] = p;
             X_out[3 * (size_t)o] = x; X_out[3 * (size_t)o + 1] = y; X_out[3 * (size_t)o + 2] = z;
             q4[o] = make_float4((float)x, (float)y, (float)z, p.x);   // cv2 converts X to float32
             qv[o] = p.y;
         } else if (in) {
-            lost[ol_ + __popc(bi & ~bk & below)] = klt_out[i];
+            lost[ol_ + __popc(bi & ~bk & below)] = klt_out[t];
         }
         ok_ += __popc(bk); ol_ += __popc(bi & ~bk);
     }
@@ -219,7 +222,7 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
                   float2* __restrict__ C_out, double2* __restrict__ F_out, int32_t* __restrict__ Ti_out,
                   const double* __restrict__ poses, float2* __restrict__ P, double* __restrict__ X, int land_cap,
                   int early, double* __restrict__ prom_rows, int32_t* __restrict__ prom_ti,
-                  const int32_t* __restrict__ gate)
+                  const int32_t* __restrict__ gate, float2* __restrict__ prom_P)
 {
     __shared__ int sWarpStay[kCandThreads / 32], sWarpProm[kCandThreads / 32];
     __shared__ int sBaseStay, sBaseProm, sLast;
@@ -256,6 +259,7 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
             prom_rows[4 * (size_t)op] = r.f.x; prom_rows[4 * (size_t)op + 1] = r.f.y;
             prom_rows[4 * (size_t)op + 2] = (double)r.c.x; prom_rows[4 * (size_t)op + 3] = (double)r.c.y;
             prom_ti[op] = Ti_in[i];
+            if (prom_P) prom_P[op] = r.c;
         }
         else if (n_land + op < land_cap) {
             double M1[12], Xh[4];
@@ -288,6 +292,7 @@ cand_apply_kernel(DevScalars* sc, PromoteArgs a, const float2* __restrict__ klt_
             sc->spec_n_cand = sc->n_cand; sc->spec_cf_alias = sc->cf_alias;
             sc->spec_cand_was_empty = sc->cand_was_empty;
             sc->n_cand = st;
+            if (early) sc->n_cand_early = st;
             sc->n_promoted = pr;
             sc->n_cand_lost = n_lost;
             if (!early) sc->n_land = min(n_land + pr, land_cap);
@@ -440,6 +445,7 @@ struct TailArgs {
     const double* prom_rows; float2* P; double* X; int land_cap;
     const double2* feed; int n_new; float2* C; double2* F; int32_t* Ti; int pose_idx; int cand_cap;
     int n_segs; const float2* segP[4]; const double* segX[4]; int segN[4]; int segTarget[4];
+    int32_t* src; int src_prom_base; int src_seg_base[4];   // superset track index of every appended row (Pipeline::Lsrc)
 };
 
 __global__ void __launch_bounds__(1024) frame_tail_kernel(DevScalars* sc, TailArgs a)
@@ -453,8 +459,10 @@ __global__ void __launch_bounds__(1024) frame_tail_kernel(DevScalars* sc, TailAr
     __syncthreads();   // every thread has read the scalars thread 0 is about to rewrite
     // promoted rows: positions now, 3-D points when the refined pose is there (pose stream)
     int n_land = min(n_land0 + n_prom, a.land_cap);
-    for (int i = tid; i < n_prom && n_land0 + i < a.land_cap; i += blockDim.x)
+    for (int i = tid; i < n_prom && n_land0 + i < a.land_cap; i += blockDim.x) {
         a.P[n_land0 + i] = make_float2((float)a.prom_rows[4 * (size_t)i + 2], (float)a.prom_rows[4 * (size_t)i + 3]);
+        if (a.src) a.src[n_land0 + i] = a.src_prom_base + i;
+    }
     // new candidates (no pose this frame: none)
     const bool add = ok && a.n_new > 0;
     if (add)
@@ -473,6 +481,7 @@ __global__ void __launch_bounds__(1024) frame_tail_kernel(DevScalars* sc, TailAr
             a.P[n_land + i] = a.segP[k][i];
             const size_t o = 3 * (size_t)(n_land + i), s = 3 * (size_t)i;
             a.X[o] = a.segX[k][s]; a.X[o + 1] = a.segX[k][s + 1]; a.X[o + 2] = a.segX[k][s + 2];
+            if (a.src) a.src[n_land + i] = a.src_seg_base[k] + i;
         }
         n_land += n_add;
         n_app = n_add;
@@ -482,6 +491,7 @@ __global__ void __launch_bounds__(1024) frame_tail_kernel(DevScalars* sc, TailAr
         sc->prom_base = n_land0; sc->spec_n_land = n_land0;
         sc->klt_iters_cand = iters2; sc->klt_iters_cand2 = 0;
         sc->n_land = n_land; sc->n_appended = n_app;
+        sc->gate_ok = ok ? 1 : 0;
         if (add) { sc->cf_alias = was_empty0 ? 1 : 0; sc->n_cand = min(n_cand0 + a.n_new, a.cand_cap); sc->cand_was_empty = 0; }
     }
 }
@@ -503,7 +513,7 @@ __global__ void triangulate_kernel(const double* __restrict__ M1, const double* 
 
 }  // namespace
 
-int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
+int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate, bool from_superset)
 {
     VO_NVTX("vo:landmark_compact");
     Pipeline* p = c->pipe;
@@ -516,15 +526,26 @@ int launch_landmark_compact(Ctx* c, int n_upper, const int32_t* gate)
     VO_TRY(ensure(c, p->qv, n));
     VO_TRY(ensure(c, p->lost, n * 2));
     VO_TRY(ensure_rng_table(c, p->hyp_capacity));
+    // the tracks: this frame's own KLT launch, or (from_superset) the launch that ran ahead of the pruning on the
+    // tracking stream - rows find their track through Lsrc
+    const int f = p->lk_flip;
+    const float* out = from_superset ? p->lk_out[f].p : p->klt_out.p;
+    const uint8_t* st = from_superset ? p->lk_status[f].p : p->klt_status.p;
+    const int32_t* it = from_superset ? p->lk_iters[f].p : p->klt_iters.p;
+    const int32_t* src = from_superset ? p->Lsrc[p->cur].p : nullptr;
+    if (from_superset) VO_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_trk, 0));
     VO_CUDA(c, launch_pdl(landmark_compact_kernel, dim3(1), dim3(kScanThreads), c->stream,
-        p->d_sc, n_upper, (const float2*)p->klt_out.p, (const uint8_t*)p->klt_status.p, (const int32_t*)p->klt_iters.p,
+        p->d_sc, n_upper, (const float2*)out, st, it,
         (const double*)p->X[p->cur].p, (float2*)p->P[nxt].p, p->X[nxt].p, (float4*)p->q4.p, p->qv.p, (float2*)p->lost.p,
-        p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }, gate));
+        p->sets.p, RngTab{ p->rng_tab.p, p->rng_tab_len }, gate, src));
     c->launches++;
+    VO_CUDA(c, cudaEventRecord(c->ev_compact, c->stream));
     p->prev2 = p->prev == nxt ? -1 : p->prev; p->prev2_n_upper = p->prev_n_upper;
     p->prev = p->cur;
     p->prev_n_upper = n_upper;
     p->cur = nxt;
+    p->b1_buf = nxt; p->b1_upper = n_upper;
+    p->src_valid = false;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
 }
@@ -563,6 +584,7 @@ int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, c
     VO_TRY(ensure(c, p->Ti[p->ccur ^ 1], nc));
     VO_TRY(ensure(c, p->prom_rows, nc * 4));
     VO_TRY(ensure(c, p->prom_ti, nc));
+    VO_TRY(ensure(c, p->prom_P, nc * 2));
     const int nb = (ncand_upper + kCandThreads - 1) / kCandThreads;
     VO_TRY(ensure(c, p->cand_flag, nc));
     VO_TRY(ensure(c, p->blk_counts, (size_t)nb * 2));
@@ -574,7 +596,7 @@ int launch_promote_early(Ctx* c, double alpha_deg, int ncand_upper, int b_off, c
         (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
         (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
         p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)nullptr, (double*)nullptr, 0, 1, p->prom_rows.p,
-        p->prom_ti.p, gate));
+        p->prom_ti.p, gate, (float2*)p->prom_P.p));
     c->launches += 2;
     VO_CUDA(c, cudaGetLastError());
     p->ccur ^= 1;
@@ -670,7 +692,7 @@ int launch_promote(Ctx* c, const double K[9], const double* Tnew, double alpha_d
         (const double2*)p->F[p->ccur].p, (const int32_t*)p->Ti[p->ccur].p, (const uint8_t*)p->cand_flag.p,
         (const int32_t*)p->blk_counts.p, (float2*)p->C[p->ccur ^ 1].p, (double2*)p->F[p->ccur ^ 1].p,
         p->Ti[p->ccur ^ 1].p, (const double*)p->poses.p, (float2*)p->P[p->cur].p, p->X[p->cur].p, land_cap, 0,
-        (double*)nullptr, (int32_t*)nullptr, (const int32_t*)nullptr));
+        (double*)nullptr, (int32_t*)nullptr, (const int32_t*)nullptr, (float2*)nullptr));
     c->launches++;
     c->launches++;
     p->ccur ^= 1;
@@ -720,6 +742,7 @@ int launch_land_append(Ctx* c, const float* d_P, const double* d_X, int n_rows, 
                           target, (float2*)p->P[p->cur].p, p->X[p->cur].p, cap, gate));
     c->launches++;
     p->n_land_upper = upper;
+    p->src_valid = false;   // (rows without a track index)
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
 }
@@ -762,7 +785,21 @@ int launch_frame_tail(Ctx* c, const double K[9], double alpha_deg, int b_off, co
     a.pose_idx = p->n_poses; a.cand_cap = (int)(p->C[p->ccur].cap / 2);
     a.n_segs = n_segs;
     for (int k = 0; k < n_segs; k++) { a.segP[k] = (const float2*)segs[k].P; a.segX[k] = segs[k].X; a.segN[k] = segs[k].n; a.segTarget[k] = segs[k].target; }
+    // where each appended row's track sits, should the next frame's KLT run ahead of this frame's pruning (Pipeline::src_*):
+    // [0, b1_upper) the rows of the last compaction, then the parked rows, then every offered row of every batch
+    if (p->b1_buf >= 0 && p->Lsrc[p->cur].p) {
+        VO_TRY(ensure(c, p->Lsrc[p->cur], (size_t)upper + 1, true));
+        a.src = p->Lsrc[p->cur].p;
+        p->src_prom_base = p->b1_upper; p->src_prom_upper = p->early_ncand_upper;
+        int base = p->src_prom_base + p->src_prom_upper;
+        p->src_n_segs = n_segs;
+        for (int k = 0; k < n_segs; k++) { p->src_seg_base[k] = base; p->src_seg_n[k] = segs[k].n; p->src_seg_P[k] = segs[k].P; base += segs[k].n; }
+        p->src_total = base;
+        a.src_prom_base = p->src_prom_base;
+        for (int k = 0; k < n_segs; k++) a.src_seg_base[k] = p->src_seg_base[k];
+    }
     VO_CUDA(c, launch_pdl(frame_tail_kernel, dim3(1), dim3(1024), c->stream, p->d_sc, a));
+    p->src_valid = a.src != nullptr;
     VO_CUDA(c, cudaEventRecord(c->ev_snap, c->stream));
     // pose stream, behind the refit: scalar block back to the host, then the 3-D points and the pose-table row
     VO_CUDA(c, cudaStreamWaitEvent(c->stream4, c->ev_snap, 0));
