@@ -1125,6 +1125,23 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
             }
         }
         VO_TRY(flush_frame_hint(c, true));
+        {
+            static const bool trace = getenv("VO_TRACE") != nullptr;
+            if (trace) {   // host time blocked on the pose, and how often it was there already (tools/profile_e2e.py)
+                timespec t0, t1;
+                clock_gettime(CLOCK_MONOTONIC, &t0);
+                const bool ready = cudaEventQuery(p->ev_pose) == cudaSuccess;
+                cudaEventSynchronize(p->ev_pose);
+                clock_gettime(CLOCK_MONOTONIC, &t1);
+                p->trace_wait_us += (t1.tv_sec - t0.tv_sec) * 1e6 + (t1.tv_nsec - t0.tv_nsec) * 1e-3;
+                p->trace_ready += ready; p->trace_n++;
+                if (p->trace_n % 300 == 0) {
+                    fprintf(stderr, "[vo trace] pipelined frames: pose wait %.1f us/frame, pose already there %d/%d\n",
+                            p->trace_wait_us / p->trace_n, p->trace_ready, p->trace_n);
+                    p->trace_wait_us = 0.; p->trace_ready = 0; p->trace_n = 0;
+                }
+            }
+        }
         VO_CUDA(c, cudaEventSynchronize(p->ev_pose));
         DevScalars* s = p->h_sc;   // as of the PnP: before the append of the promoted rows and of the new candidates
         if (split) {   // (read back while the main stream went on: the counters come from the snapshot taken at the pose)
