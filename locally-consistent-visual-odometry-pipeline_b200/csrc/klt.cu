@@ -179,8 +179,8 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
                  : "memory");
 }
 
-template <int WIN>
-__global__ void __launch_bounds__(kWarpsPerBlock * 32, 4)
+template <int WIN, int MINB>
+__global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB)
 klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const __grid_constant__ KltTmaps maps, const int top,
                  const KltSegs segs,
                  float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
@@ -542,9 +542,14 @@ int launch_klt_segs(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, co
     KltTmaps maps;
     if (want_tma) memcpy(&maps, next.tmaps, sizeof(maps)); else memset(&maps, 0, sizeof(maps));
     const int blocks = (total + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    klt_track_kernel<21><<<blocks, kWarpsPerBlock * 32, 0, st>>>(
-        prev, next, maps, top, segs,
-        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, no_tile ? 0 : (want_tma ? 2 : 1), gate);
+    // CTAs per SM the register allocation aims at: 4 (128 registers), 5 (96, no spill) or 6 (80, 40 B of spill);
+    // VO_KLT_MINB: A/B switch (same results)
+    static const int minb = getenv("VO_KLT_MINB") ? atoi(getenv("VO_KLT_MINB")) : 4;
+    const int tile_mode = no_tile ? 0 : (want_tma ? 2 : 1);
+#define VO_KLT_LAUNCH(MB) klt_track_kernel<21, MB><<<blocks, kWarpsPerBlock * 32, 0, st>>>( \
+        prev, next, maps, top, segs, (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, tile_mode, gate)
+    if (minb == 5) VO_KLT_LAUNCH(5); else if (minb == 6) VO_KLT_LAUNCH(6); else VO_KLT_LAUNCH(4);
+#undef VO_KLT_LAUNCH
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
     return VO_OK;
