@@ -54,3 +54,39 @@ def test_pipelined_equals_synchronous_when_tracking_oversubscribes_the_gpu(pkg):
                 assert a[1:4] == b[1:4] and a[5] == b[5], (rep, k, a[1:], b[1:])
     finally:
         ctx.close()
+
+
+def _main():
+    """python tests/test_oversubscribed_gpu.py : the comparison in a process of its own (the A/B switches of the
+    library are read once per process from the environment)."""
+    sys.path.insert(0, ROOT)
+    bench = importlib.import_module("bench")
+    pkg = importlib.import_module(bench.PKG)
+    cfg = dict(bench.CONFIGS["kitti"], burst_every=4, burst_n=4000)
+    n = 28
+    sq = bench.build_stream(cfg, 23, n, workers=min(os.cpu_count() or 1, 16))
+    ctx = pkg.Context(device=0, max_w=2048, max_h=1024)
+    ref = _run(ctx, pkg, bench, cfg, sq, n, False)
+    for rep in range(2):
+        got = _run(ctx, pkg, bench, cfg, sq, n, True)
+        bad = [k for k, (a, b) in enumerate(zip(got, ref)) if not np.array_equal(a[0], b[0]) or a[1:4] != b[1:4]]
+        if bad:
+            print("DIFFERENT at steps", bad[:8])
+            return 1
+    ctx.close()
+    print("identical: %d steps x 2 repetitions" % n)
+    return 0
+
+
+@pytest.mark.parametrize("env", [{"VO_TRACK_AHEAD": "1"}, {"VO_TRACK_AHEAD": "1", "VO_PNP_AHEAD": "0"}, {"VO_PNP_AHEAD": "0"}])
+def test_scheduling_switches_are_bit_identical(env):
+    """VO_TRACK_AHEAD=1 (next frame's KLT ahead of the pruning, beside the RANSAC kernel - off by default) and
+    VO_PNP_AHEAD=0 (next frame's PnP not enqueued ahead - on by default) change the schedule, never a result."""
+    import subprocess
+    r = subprocess.run([sys.executable, os.path.abspath(__file__)], env=dict(os.environ, **env), capture_output=True,
+                       text=True, timeout=900)
+    assert r.returncode == 0 and "identical" in r.stdout, (r.stdout[-2000:], r.stderr[-2000:])
+
+
+if __name__ == "__main__":
+    sys.exit(_main())
