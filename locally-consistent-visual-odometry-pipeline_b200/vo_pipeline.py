@@ -497,7 +497,11 @@ class KeypointsToLandmarksAssociator():
                 rt.prev_token += 1
                 if not dict.__contains__(state, 'P'):
                     state._prev = rt.prev_token
-                rt.issue_hint(deferred=True)   # goes out under the coming PnP
+                # The next frame's ingest.  A step that was enqueued one frame ahead (frame_ahead) leaves the GPU busy
+                # until the coming pose call, which tracks INTO that frame right behind this frame's tail: the ingest
+                # (H2D + pyramid, ~35 us) must be on its way now, not halfway through that call - KLT(k+2) would wait for
+                # it (15 us of idle GPU per frame).  Otherwise it goes out under the coming PnP.
+                rt.issue_hint(deferred=not st.get('ahead'))
                 rt.state_version += 1
                 return (DeviceState(rt, rt.state_version), _LazyLost(rt, rt.state_version))
             rt.ctx.track_rollback()
