@@ -703,3 +703,52 @@ def test_early_classification_paths(pkg, scene_mod):
         assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
     finally:
         a.close(); b.close()
+
+
+def test_pipelined_frames_with_changing_pnp_arguments(pkg, scene_mod):
+    """The next frame's PnP is enqueued ahead with the CURRENT call's camera matrix and parameters.  A next call
+    that asks for other ones (iteration budget, threshold, a slightly different K) gets its own run: the run
+    enqueued ahead is taken back (its pruning wrote into another buffer), poses and states stay those of the
+    synchronous path with the same schedule; state reads in between see the rows the tracking step kept."""
+    sq = get_sequence(scene_mod, "kitti_half")
+    a = pkg.Context(device=0, max_w=2048, max_h=1024)
+    b = pkg.Context(device=0, max_w=2048, max_h=1024)
+    n = 13
+
+    def args(k):
+        p = pkg.pnp_defaults()
+        K = sq.K.copy()
+        if k % 4 == 2:
+            p.max_iters = 300
+        if k % 4 == 3:
+            p.reproj_thresh = 1.5
+        if k % 6 == 5:
+            K[0, 2] += 0.25
+        return K, p
+
+    try:
+        for c in (a, b):
+            c.upload_frame(sq.frames[0], 1)
+            c.set_state(sq.P0, sq.X0)
+            c.set_candidates(np.zeros((0, 2)), np.zeros((0, 2)), np.zeros((0, 16)))
+        for k in range(1, n):
+            K, p = args(k)
+            Ta, ca = a.process_frame(sq.frames[k], k, k + 1, K, 1.0, sq.feeds[k], pnp=p)
+            if k + 1 < len(sq.frames):
+                b.prefetch_frame(sq.frames[k + 1], k + 2)
+            Tb, cb = b.process_frame(sq.frames[k], k, k + 1, K, 1.0, sq.feeds[k], pnp=p, pipelined=True)
+            assert ca["pnp_ok"] == 1 and cb["pnp_ok"] == 1 and np.array_equal(Ta, Tb), k
+            assert (ca["n_inliers"], ca["ransac_iters"]) == (cb["n_inliers"], cb["ransac_iters"]), k
+            if k == 7:   # a state read while the step ahead (tracking + PnP) is in flight: it is taken back, then redone
+                Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+                assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+        K, p = args(n)
+        Ta, ca = a.process_frame(sq.frames[n], n, n + 1, K, 1.0, sq.feeds[n], pnp=p)
+        Tb, cb = b.process_frame(sq.frames[n], n, n + 1, K, 1.0, sq.feeds[n], pnp=p)
+        assert np.array_equal(Ta, Tb)
+        Pa, Xa = a.get_state(); Pb, Xb = b.get_state()
+        assert np.array_equal(Pa, Pb) and np.array_equal(Xa, Xb)
+        for u, v in zip(a.get_candidates(), b.get_candidates()):
+            assert np.array_equal(u, v)
+    finally:
+        a.close(); b.close()
