@@ -229,7 +229,6 @@ int ensure(Ctx* c, DevBuf<T>& b, size_t n, bool keep = false)
 constexpr int kMinimal = 4;          // P3P on 3 points + 1 disambiguation point
 constexpr int kLandBufs = 5;         // landmark buffers in rotation (state before the last two tracking steps + compaction and
                                      // pruning outputs of the current frame and of the step enqueued ahead)
-constexpr int kPnpChunks = 3;        // hypotheses are evaluated in <=3 chunks (adaptive stop between)
 
 // small block of scalars living in device memory; mirrored to pinned host memory on demand
 struct DevScalars {
@@ -280,7 +279,7 @@ struct DevScalars {
 
 struct Pipeline {
     int track_capacity = 0, hyp_capacity = 0;
-    // landmarks, three buffers in rotation (cur = index of the live ones): the post-KLT compaction
+    // landmarks, kLandBufs buffers in rotation (cur = index of the live ones): the post-KLT compaction
     // writes cur+1, the inlier pruning cur+2, so the state a frame started from (prev) stays intact
     // until the next frame's compaction - main.py:248 reads it after estimatePose
     int cur = 0;
@@ -290,7 +289,7 @@ struct Pipeline {
     int n_land_upper = 0;   // host-known upper bound of n_land
     int prev_n_upper = 0;   // same for the rows of the `prev` buffer
     // the state before the tracking step before that: with a tracking step enqueued one frame ahead (inside the pose
-    // call) this is the buffer main.py:248 reads - the fourth buffer of the rotation keeps it intact
+    // call) this is the buffer main.py:248 reads - the rotation is long enough to keep it intact
     int prev2 = -1, prev2_n_upper = 0;
     // candidates, ping-pong
     int ccur = 0;
@@ -375,10 +374,6 @@ struct Pipeline {
     double trace_wait_us = 0.; int trace_ready = 0, trace_n = 0;   // VO_TRACE=1 diagnostics
     cudaEvent_t ev_land = nullptr;   // behind the landmark KLT launch (candidates' KLT ordered after it, see track_both)
     cudaEvent_t ev_pose = nullptr;   // behind the scalar read-back between PnP and a speculative promotion
-    // read-back right behind the FIRST RANSAC chunk (the run usually ends there; the second chunk kernel then only
-    // drains): pinned copies of the scalar block taken there and behind the last chunk
-    cudaEvent_t ev_pose_first = nullptr; DevScalars* h_sc_first = nullptr; DevScalars* h_sc_late = nullptr;
-    bool first_rb_enqueued = false;
     int64_t spec_prev_key = -1, spec_next_key = -1;
     DevScalars* d_sc = nullptr;
     DevScalars* h_sc = nullptr;  // pinned mirror
@@ -442,7 +437,6 @@ struct PnpLaunch {
     double K[9];
     vo_pnp_params prm;
     bool compact;                       // prune landmark buffers to the inliers (estimatePose)
-    bool readback_after_first = false;  // (unused since the RANSAC is one launch)
     bool refit_on_pose_stream = false;  // LM refit on Ctx::stream4: the landmark side of the frame goes on without it
     const int32_t* gate = nullptr;      // device flag: the RANSAC kernel does nothing when it is 0 (a run enqueued ahead of a
                                         // pose that may not come); the refit then finds ok == 0 and writes "no pose"

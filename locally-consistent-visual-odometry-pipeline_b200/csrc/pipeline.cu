@@ -61,8 +61,6 @@ void pipeline_free(Ctx* c)
     for (int k = 0; k < 2; k++) if (p->ev_side[k]) cudaEventDestroy(p->ev_side[k]);
     if (p->ev_pose) cudaEventDestroy(p->ev_pose);
     if (p->ev_land) cudaEventDestroy(p->ev_land);
-    if (p->ev_pose_first) cudaEventDestroy(p->ev_pose_first);
-    cudaFreeHost(p->h_sc_first); cudaFreeHost(p->h_sc_late);
     cudaFreeHost(p->h_snapP); cudaFreeHost(p->h_snapX); cudaFreeHost(p->h_snap_sc);
     delete p;
     c->pipe = nullptr;
@@ -626,7 +624,7 @@ int vo_track_rollback(vo_ctx* c)
     track_rollback_kernel<<<1, 1, 0, c->stream>>>(p->d_sc);
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
-    // (the fourth buffer of the rotation: the state before the tracking step before this one is still there)
+    // (the rotation keeps the state before the tracking step before this one, too)
     p->cur = p->rb_cur; p->prev = p->rb_prev; p->prev_n_upper = p->rb_prev_n_upper; p->prev2 = -1; p->prev2_n_upper = 0;
     p->n_land_upper = p->rb_n_land_upper;
     p->rb_valid = false; p->packed_valid = false; p->cand_tracked_valid = false;

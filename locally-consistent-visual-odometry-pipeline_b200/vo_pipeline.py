@@ -522,7 +522,7 @@ class KeypointsToLandmarksAssociator():
             state['P'] = np.asarray(state['P']).astype(np.float32)   # reference side effect (vo:214)
         elif not dict.__contains__(state, 'P'):
             # the caller may still read this (now previous) state after the device has moved on:
-            # the third landmark buffer keeps it until the next tracking step
+            # the landmark rotation keeps it until the next tracking step
             state._prev = rt.prev_token
         rt.ctx.klt_track_landmarks(k_old, k_new, rt.klt, add=add, early_alpha=_early_alpha())
         rt.issue_hint(deferred=True)   # next frame's ingest: enqueued by the pose call, under the GPU's PnP
