@@ -430,6 +430,17 @@ void pipeline_free(Ctx* c);
 
 // pnp.cu: RANSAC over the packed points (q4,qv; n on device at sc->n_tracked or given),
 // then mask + LM refit + (optionally) compaction of the landmark buffers by the inlier mask.
+// The landmark compaction of a tracking step done by the RANSAC kernel itself (its first phase, all CTAs; see
+// pnp_ransac_kernel): saves the compaction kernel and the kernel boundary behind it on the frame's chain.
+constexpr int kFuseMaxRows = 8192;      // 256 scan chunks x 32 rows
+struct FusedCompact {
+    int on, n_upper;
+    const float2* klt_out; const uint8_t* status; const int32_t* iters;   // the tracking step's results (row = track)
+    const double* X_in;                                                    // 3-D points of the rows that were tracked
+    float2* P_out; double* X_out; float2* lost;                            // kept rows (new position, 3-D point), lost positions
+    float4* q4; float* qv;                                                 // the float32 PnP pack of the kept rows
+};
+
 struct PnpLaunch {
     const float* q4; const float* qv;   // packed float32 points
     const int32_t* d_n; int n_upper;    // point count (device) and its host upper bound
@@ -440,6 +451,7 @@ struct PnpLaunch {
     bool refit_on_pose_stream = false;  // LM refit on Ctx::stream4: the landmark side of the frame goes on without it
     const int32_t* gate = nullptr;      // device flag: the RANSAC kernel does nothing when it is 0 (a run enqueued ahead of a
                                         // pose that may not come); the refit then finds ok == 0 and writes "no pose"
+    bool fuse_compact = false;          // the RANSAC kernel compacts the pending tracking step first (process_frame_impl)
     bool small_grid = false;            // kernels of the next frame run beside the RANSAC kernel: leave them most of the SMs
 };
 int launch_pnp(Ctx* c, const PnpLaunch& L);

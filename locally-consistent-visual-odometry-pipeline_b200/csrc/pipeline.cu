@@ -1104,18 +1104,29 @@ static int process_frame_impl(vo_ctx* c, const uint8_t* img, int w, int h, int p
                 p->cand_tracked_prev = next_key; p->cand_tracked_next = nk; p->cand_tracked_valid = true;
                 p->rb_cur = p->cur; p->rb_prev = p->prev; p->rb_prev_n_upper = p->prev_n_upper; p->rb_n_land_upper = p->n_land_upper;
     p->rb_prev2 = p->prev2; p->rb_prev2_n_upper = p->prev2_n_upper;
-                VO_TRY(launch_landmark_compact(c, p->n_land_upper, gate, superset));
+                // Its compaction and its PnP: the RANSAC kernel needs nothing the next call brings (new candidates and
+                // landmark batches come in behind it), so the GPU goes from one frame to the next without waiting for
+                // the host (VO_PNP_AHEAD=0: A/B switch, same results) - and then the kernel does the compaction itself,
+                // as its first phase (VO_FUSE_COMPACT=0: A/B switch, same results), unless the tracks came from the
+                // superset launch or there are more rows than its scan handles.
+                static const int pnp_ahead_mode = getenv("VO_PNP_AHEAD") ? atoi(getenv("VO_PNP_AHEAD")) : 1;
+                static const int fuse_mode = getenv("VO_FUSE_COMPACT") ? atoi(getenv("VO_FUSE_COMPACT")) : 1;
+                const bool pnp_ahead = split && pnp_ahead_mode != 0;
+                const bool fuse = pnp_ahead && fuse_mode != 0 && !superset && !kp.fb_check && p->n_land_upper <= kFuseMaxRows &&
+                                  p->n_land_upper > 0;
+                if (!fuse) VO_TRY(launch_landmark_compact(c, p->n_land_upper, gate, superset));
                 p->rb_valid = true; p->packed_valid = true;
                 p->ahead_valid = true; p->ahead_prev = next_key; p->ahead_next = nk;
-                // ... and its PnP: the RANSAC kernel needs nothing the next call brings (new candidates and landmark
-                // batches come in behind it), so the GPU goes from one frame to the next without waiting for the host
-                // (VO_PNP_AHEAD=0: A/B switch, same results)
-                static const int pnp_ahead_mode = getenv("VO_PNP_AHEAD") ? atoi(getenv("VO_PNP_AHEAD")) : 1;
-                if (split && pnp_ahead_mode != 0) {
+                if (pnp_ahead) {
                     PnpLaunch L2 = L;
                     L2.q4 = p->q4.p; L2.qv = p->qv.p;   // (the compaction above may have grown them)
                     L2.n_upper = p->n_land_upper; L2.gate = gate; L2.refit_on_pose_stream = true; L2.small_grid = superset;
-                    p->pa_cur = p->cur; p->pa_prev = p->prev; p->pa_prev2 = p->prev2;
+                    L2.fuse_compact = fuse;
+                    if (fuse) {   // (what an undo of the PnP alone goes back to: the compacted buffer the kernel is about to write)
+                        p->pa_cur = (p->cur + 1) % kLandBufs; p->pa_prev = p->cur; p->pa_prev2 = p->prev == p->pa_cur ? -1 : p->prev;
+                    } else {
+                        p->pa_cur = p->cur; p->pa_prev = p->prev; p->pa_prev2 = p->prev2;
+                    }
                     memcpy(p->pa_K, L2.K, sizeof(p->pa_K)); p->pa_prm = L2.prm;
                     VO_TRY(launch_pnp(c, L2));
                     p->pnp_ahead = true;

@@ -684,7 +684,7 @@ constexpr int kPnpGridSmall = 32;   // CTAs of a run launched beside the next fr
 __global__ void __launch_bounds__(kHypThreads)
 pnp_ransac_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, const float* __restrict__ qv,
                   double* hyp, int32_t* counts, uint8_t* mask, PnpArgs a, RngTab rt, FinalizeBufs fb, int H, int epoch0,
-                  const int32_t* __restrict__ gate)
+                  const int32_t* __restrict__ gate, FusedCompact fc)
 {
     __shared__ double sRt[kBatch][12];
     __shared__ int sValid[kBatch];
@@ -699,7 +699,92 @@ pnp_ransac_kernel(DevScalars* sc, int32_t* sets, const float4* __restrict__ q4, 
     const int G = gridDim.x;
     const unsigned long long t_in = gtime();
     unsigned long long t_p3p = t_in, t_scored = t_in;
-    const int n = min(sc->n_tracked, a.n_upper);
+    int n_fused = -1;
+    if (fc.on) {
+        // ---- phase 0: the landmark compaction of the tracking step (what landmark_compact_kernel does with one CTA).
+        // Every CTA scans ALL status bytes (a few KB out of L2), so each knows the kept count and the offset of every
+        // 32-row-or-less chunk without talking to the others; the chunks are dealt round-robin to the CTAs, which write
+        // their rows (order preserved); CTA 0 draws the first minimal sets meanwhile; a grid barrier (the ticket / epoch
+        // pair of the rounds) ends the phase, and its last arriver publishes the counts - no CTA may have overwritten
+        // sc->n_land before every CTA has read it.
+        __shared__ unsigned sMask[kHypThreads];
+        __shared__ int sOff[kHypThreads], sWarpTot[kHypThreads / 32], sWarpIt[kHypThreads / 32];
+        const int n_in = min(sc->n_land, fc.n_upper);
+        const int CH = (n_in + kHypThreads - 1) / kHypThreads;   // rows per chunk (<= 32: the host checked n_upper)
+        RngPreload pre;
+        if (blockIdx.x == 0 && warp == 0) pnp_preload_draws(rt, pre);
+        unsigned m = 0;
+        int it = 0;
+        {
+            // (fixed trip count, predicated: all loads of the chunk are in flight together - one L2 latency, not CH)
+            const int r0 = tid * CH;
+            uint8_t stv[32];
+            int itv[32];
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                const int r = r0 + j;
+                const bool in = j < CH && r < n_in;
+                stv[j] = in ? fc.status[r] : (uint8_t)0;
+                itv[j] = (in && fc.iters) ? fc.iters[r] : 0;
+            }
+#pragma unroll
+            for (int j = 0; j < 32; j++) {
+                if (stv[j] != 0) m |= 1u << j;
+                it += itv[j];
+            }
+        }
+        const int cnt = __popc(m);
+        int inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        it = __reduce_add_sync(0xffffffffu, it);
+        if (lane == 31) sWarpTot[warp] = inc;
+        if (lane == 0) sWarpIt[warp] = it;
+        __syncthreads();
+        int base = 0, n_keep = 0, its = 0;
+#pragma unroll
+        for (int w = 0; w < kHypThreads / 32; w++) { if (w < warp) base += sWarpTot[w]; n_keep += sWarpTot[w]; its += sWarpIt[w]; }
+        sMask[tid] = m; sOff[tid] = base + inc - cnt;
+        __syncthreads();
+        // this CTA's chunks: lane j of warp w writes row j of chunk blockIdx + (w + 8 i) G
+        for (int c = (int)blockIdx.x + warp * G; c < kHypThreads; c += (kHypThreads / 32) * G) {
+            const int r = c * CH + lane;
+            if (lane < CH && r < n_in) {
+                const unsigned mk = sMask[c];
+                const unsigned below = (1u << lane) - 1;
+                const float2 p = fc.klt_out[r];
+                if ((mk >> lane) & 1u) {
+                    const int o = sOff[c] + __popc(mk & below);
+                    const double x = fc.X_in[3 * (size_t)r], y = fc.X_in[3 * (size_t)r + 1], z = fc.X_in[3 * (size_t)r + 2];
+                    fc.P_out[o] = p;
+                    fc.X_out[3 * (size_t)o] = x; fc.X_out[3 * (size_t)o + 1] = y; fc.X_out[3 * (size_t)o + 2] = z;
+                    fc.q4[o] = make_float4((float)x, (float)y, (float)z, p.x);   // cv2 converts X to float32
+                    fc.qv[o] = p.y;
+                } else {
+                    fc.lost[r - (sOff[c] + __popc(mk & below))] = p;   // (rows before r minus kept rows before r)
+                }
+            }
+        }
+        if (blockIdx.x == 0 && warp == 0) pnp_prepare_sets(sc, sets, rt, n_keep, pre);
+        // grid barrier
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();
+            sLast = atomicAdd(&sc->ticket, 1) == G - 1;
+            if (sLast) {
+                sc->klt_iters_cand = 0; sc->prev2_n_land = sc->prev_n_land; sc->prev_n_land = n_in; sc->n_land = n_keep;
+                sc->n_tracked = n_keep; sc->n_lost = n_in - n_keep; sc->klt_iters = its;
+                sc->ticket = 0;
+                __threadfence();
+                st_release(&sc->epoch, epoch0);
+            } else {
+                while (ld_acquire(&sc->epoch) != epoch0) __nanosleep(40);
+            }
+        }
+        __syncthreads();
+        n_fused = n_keep;
+    }
+    const int n = fc.on ? min(n_fused, a.n_upper) : min(sc->n_tracked, a.n_upper);
     const int niters0 = (n < kMinimal || a.max_iters <= 0) ? 0 : (n == kMinimal ? 1 : a.max_iters);
     int h0 = 0;
     for (int round = 0;; round++) {
@@ -899,6 +984,24 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
         VO_TRY(ensure_rng_table(c, H));
         rt.tab = p->rng_tab.p; rt.len = p->rng_tab_len;
     }
+    FusedCompact fc{};
+    const float* q4_arg = L.q4; const float* qv_arg = L.qv;
+    if (L.fuse_compact) {
+        // the tracking step's compaction, done by the RANSAC kernel: buffers and bookkeeping as launch_landmark_compact
+        const size_t nn = npts;
+        const int cnx = (p->cur + 1) % kLandBufs;
+        VO_TRY(ensure(c, p->P[cnx], nn * 2)); VO_TRY(ensure(c, p->X[cnx], nn * 3));
+        VO_TRY(ensure(c, p->q4, nn * 4)); VO_TRY(ensure(c, p->qv, nn)); VO_TRY(ensure(c, p->lost, nn * 2));
+        fc.on = 1; fc.n_upper = L.n_upper;
+        fc.klt_out = (const float2*)p->klt_out.p; fc.status = p->klt_status.p; fc.iters = p->klt_iters.p;
+        fc.X_in = p->X[p->cur].p; fc.P_out = (float2*)p->P[cnx].p; fc.X_out = p->X[cnx].p; fc.lost = (float2*)p->lost.p;
+        fc.q4 = (float4*)p->q4.p; fc.qv = p->qv.p;
+        q4_arg = p->q4.p; qv_arg = p->qv.p;
+        p->prev2 = p->prev == cnx ? -1 : p->prev; p->prev2_n_upper = p->prev_n_upper;
+        p->prev = p->cur; p->prev_n_upper = L.n_upper;
+        p->cur = cnx;
+        p->b1_buf = cnx; p->b1_upper = L.n_upper;
+    }
     FinalizeBufs fb{};
     fb.q4i = (float4*)p->q4i.p; fb.qvi = p->qvi.p;
     if (L.compact) {
@@ -922,8 +1025,8 @@ int launch_pnp(Ctx* c, const PnpLaunch& L)
     if (grid > H) grid = H > 0 ? H : 1;
     if (grid > c->sm_count) grid = c->sm_count;
     const int epoch0 = (int)((unsigned)(++p->pnp_run) << 12);
-    VO_CUDA(c, launch_pdl(pnp_ransac_kernel, dim3(grid), dim3(kHypThreads), c->stream, p->d_sc, sets, (const float4*)L.q4, L.qv,
-                          p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, H, epoch0, L.gate));
+    VO_CUDA(c, launch_pdl(pnp_ransac_kernel, dim3(grid), dim3(kHypThreads), c->stream, p->d_sc, sets, (const float4*)q4_arg, qv_arg,
+                          p->hyp.p, p->counts.p, p->mask.p, a, rt, fb, H, epoch0, L.gate, fc));
     c->launches++;
     // the refit: on the caller's stream, or on the pose stream when the landmark side goes on without it
     cudaStream_t rs = c->stream;
