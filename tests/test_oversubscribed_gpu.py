@@ -78,10 +78,12 @@ def _main():
     return 0
 
 
-@pytest.mark.parametrize("env", [{"VO_TRACK_AHEAD": "1"}, {"VO_TRACK_AHEAD": "1", "VO_PNP_AHEAD": "0"}, {"VO_PNP_AHEAD": "0"}])
+@pytest.mark.parametrize("env", [{"VO_TRACK_AHEAD": "1"}, {"VO_TRACK_AHEAD": "1", "VO_PNP_AHEAD": "0"}, {"VO_PNP_AHEAD": "0"},
+                                 {"VO_FUSE_COMPACT": "0"}])
 def test_scheduling_switches_are_bit_identical(env):
     """VO_TRACK_AHEAD=1 (next frame's KLT ahead of the pruning, beside the RANSAC kernel - off by default) and
-    VO_PNP_AHEAD=0 (next frame's PnP not enqueued ahead - on by default) change the schedule, never a result."""
+    VO_PNP_AHEAD=0 (next frame's PnP not enqueued ahead - on by default), VO_FUSE_COMPACT=0 (compaction as a kernel of its
+    own instead of the RANSAC kernel's first phase) change the schedule, never a result."""
     import subprocess
     r = subprocess.run([sys.executable, os.path.abspath(__file__)], env=dict(os.environ, **env), capture_output=True,
                        text=True, timeout=900)
