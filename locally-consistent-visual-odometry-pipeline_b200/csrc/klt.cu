@@ -546,8 +546,13 @@ int launch_klt_segs(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, co
     // VO_KLT_MINB: A/B switch (same results)
     static const int minb = getenv("VO_KLT_MINB") ? atoi(getenv("VO_KLT_MINB")) : 4;
     const int tile_mode = no_tile ? 0 : (want_tma ? 2 : 1);
-#define VO_KLT_LAUNCH(MB) klt_track_kernel<21, MB><<<blocks, kWarpsPerBlock * 32, 0, st>>>( \
-        prev, next, maps, top, segs, (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, tile_mode, gate)
+    // (programmatic dependent launch: the CTAs are made resident while the kernel in front - the frame tail, one CTA - is
+    // still running, and start the moment it ends; VO_KLT_NO_PDL=1: plain launch, A/B switch)
+    static const bool no_pdl = getenv("VO_KLT_NO_PDL") != nullptr;
+#define VO_KLT_LAUNCH(MB) do { if (no_pdl) klt_track_kernel<21, MB><<<blocks, kWarpsPerBlock * 32, 0, st>>>( \
+        prev, next, maps, top, segs, (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, tile_mode, gate); \
+    else VO_CUDA(c, launch_pdl(klt_track_kernel<21, MB>, dim3(blocks), dim3(kWarpsPerBlock * 32), st, prev, next, maps, top, segs, \
+        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, tile_mode, gate)); } while (0)
     if (minb == 5) VO_KLT_LAUNCH(5); else if (minb == 6) VO_KLT_LAUNCH(6); else VO_KLT_LAUNCH(4);
 #undef VO_KLT_LAUNCH
     c->launches++;
