@@ -179,13 +179,15 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
                  : "memory");
 }
 
-template <int WIN, int MINB>
+// TILE: 0 window gathers from global memory, 1 shared-memory tile filled with __ldg, 2 filled by TMA - a template
+// parameter so that the tile's pitch and bounds are constants in the Gauss-Newton step's address arithmetic
+template <int WIN, int MINB, int TILE>
 __global__ void __launch_bounds__(kWarpsPerBlock * 32, MINB)
 klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const __grid_constant__ KltTmaps maps, const int top,
                  const KltSegs segs,
                  float2* __restrict__ out, uint8_t* __restrict__ status_out, float* __restrict__ err_out,
                  int32_t* __restrict__ iters_out, const int max_iters, const double eps2,
-                 const double min_eig_thr, const int use_tile, const int32_t* __restrict__ gate)
+                 const double min_eig_thr, const int32_t* __restrict__ gate)
 {
     static_assert(WIN % kRun == 0, "window side must be a multiple of the run length");
     constexpr int RPR = WIN / kRun;            // runs per row
@@ -200,12 +202,13 @@ klt_track_kernel(const PyramidDesc I, const PyramidDesc J, const __grid_constant
     const int lane = threadIdx.x & 31;
     unsigned* const tile = s_tile[threadIdx.x >> 5];
     unsigned long long* const bar = &s_bar[threadIdx.x >> 5];
-    const bool tma = use_tile == 2;
+    constexpr int use_tile = TILE;
+    constexpr bool tma = TILE == 2;
     // TMA wants the box origin on a 16 B boundary (an unaligned one is an illegal instruction) and writes dense rows: the
     // box is 64 B wide to cover every alignment, rows 16 words apart - rows two apart share their banks
     constexpr int kWordsT = 16, kOx0T = 13, kOxMaxT = 4 * (kWordsT - 3) + 3 - (WIN - kRun);   // 41
-    const int jpitch = tma ? kWordsT : TL::kPitch;
-    const int oxmax = tma ? kOxMaxT : TL::kOxMax;
+    constexpr int jpitch = tma ? kWordsT : TL::kPitch;
+    constexpr int oxmax = tma ? kOxMaxT : TL::kOxMax;
     unsigned phase = 0;
     if (tma) {
         if (lane == 0) {
@@ -549,11 +552,15 @@ int launch_klt_segs(Ctx* c, const PyramidDesc& prev, const PyramidDesc& next, co
     // (programmatic dependent launch: the CTAs are made resident while the kernel in front - the frame tail, one CTA - is
     // still running, and start the moment it ends; VO_KLT_NO_PDL=1: plain launch, A/B switch)
     static const bool no_pdl = getenv("VO_KLT_NO_PDL") != nullptr;
-#define VO_KLT_LAUNCH(MB) do { if (no_pdl) klt_track_kernel<21, MB><<<blocks, kWarpsPerBlock * 32, 0, st>>>( \
-        prev, next, maps, top, segs, (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, tile_mode, gate); \
-    else VO_CUDA(c, launch_pdl(klt_track_kernel<21, MB>, dim3(blocks), dim3(kWarpsPerBlock * 32), st, prev, next, maps, top, segs, \
-        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, tile_mode, gate)); } while (0)
-    if (minb == 5) VO_KLT_LAUNCH(5); else if (minb == 6) VO_KLT_LAUNCH(6); else VO_KLT_LAUNCH(4);
+#define VO_KLT_LAUNCH(MB, TM) do { if (no_pdl) klt_track_kernel<21, MB, TM><<<blocks, kWarpsPerBlock * 32, 0, st>>>( \
+        prev, next, maps, top, segs, (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, gate); \
+    else VO_CUDA(c, launch_pdl(klt_track_kernel<21, MB, TM>, dim3(blocks), dim3(kWarpsPerBlock * 32), st, prev, next, maps, top, segs, \
+        (float2*)d_out, d_status, d_err, d_iters, max_iters, eps2, prm.min_eig_thr, gate)); } while (0)
+    if (tile_mode == 0) VO_KLT_LAUNCH(4, 0);
+    else if (tile_mode == 2) VO_KLT_LAUNCH(4, 2);
+    else if (minb == 5) VO_KLT_LAUNCH(5, 1);
+    else if (minb == 6) VO_KLT_LAUNCH(6, 1);
+    else VO_KLT_LAUNCH(4, 1);
 #undef VO_KLT_LAUNCH
     c->launches++;
     VO_CUDA(c, cudaGetLastError());
