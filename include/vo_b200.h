@@ -340,8 +340,12 @@ int vo_process_frame(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, i
  * as of the PnP: n_landmarks = n_inliers (the n_promoted rows are appended behind the host's back) and the
  * candidates after the classification but before the append of new_candidates.  If a frame has been handed
  * over with vo_prefetch_frame since the last call, the tracking step (next_key -> that frame) is enqueued
- * right behind the append.  The next call for that frame pair finds it done; any other call takes it
- * back (vo_track_rollback).  With the stage timers on it behaves like vo_process_frame. */
+ * right behind the append - and so is its PnP (compaction, RANSAC kernel, refit), launched with this call's
+ * K and pnp parameters and gated on this frame's pose on the device.  The next call for that frame pair finds
+ * both done (a call with other K / pnp parameters gets its own PnP: the one enqueued ahead is taken back);
+ * any other call takes the step back (vo_track_rollback).  While the step is in flight vo_get_state /
+ * vo_get_counters show the landmarks its tracking step kept, not yet pruned.  With the stage timers on it
+ * behaves like vo_process_frame. */
 int vo_process_frame_pipelined(vo_ctx* ctx, const uint8_t* img, int w, int h, int pitch, int64_t prev_key,
                                int64_t next_key, const double K[9], const vo_klt_params* kparams,
                                const vo_pnp_params* pparams, double alpha_deg, const double* new_candidates, int n_new,
